@@ -1,0 +1,189 @@
+/*
+ * radixmesh_b200 — C ABI of the B200-native radix-tree KV-cache index.
+ *
+ * The reference (zzt93/RadixMesh) has no FFI: its boundary for this path is the Python
+ * class surface RadixCache / RadixMesh / CacheAwareRouter.  Each entry point below names
+ * the reference method(s) it replaces (paths relative to /root/reference/python/src).
+ * INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - every function returns an rm_status (0 = RM_OK); nothing throws across the ABI;
+ *   - pointers are DEVICE pointers unless the parameter name ends in _h (HOST pointer);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  All
+ *     calls on one index must be issued on ONE stream: stream order = operation order =
+ *     last-access stamp order.  Calls enqueue work and return without synchronising unless
+ *     the comment says "synchronises";
+ *   - the caller owns every input / output buffer; the index owns the node pool, the edge
+ *     arenas, the child table and its scratch;
+ *   - node handles are int32 node ids; id 0 is the root.  A node's identity for parity is
+ *     its full key from the root, never its id;
+ *   - one host thread at a time per index (the Python shim holds a mutex per index).
+ */
+#ifndef RADIXMESH_B200_H
+#define RADIXMESH_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rm_index rm_index;
+
+typedef enum {
+  RM_OK = 0,
+  RM_E_INVALID = 1,     /* bad argument */
+  RM_E_CUDA = 2,        /* a CUDA runtime call failed; rm_last_error() has the text */
+  RM_E_NOSPACE = 3,     /* node pool / edge arena / scratch exhausted (the reference cannot produce this) */
+  RM_E_TOO_LARGE = 4,   /* batch larger than rm_config.max_batch */
+  RM_E_MODE = 5         /* operation not allowed in this mode (e.g. insert on a ROUTER index,
+                           radix/radix_mesh.py:194) */
+} rm_status;
+
+/* Tree semantics selector.  BASE = RadixCache (radix/sglang/srt/mem_cache/radix_cache.py:87);
+ * the other three are RadixMesh's modes (radix/core_enum.py:4-7, radix/radix_mesh.py:76-84). */
+typedef enum { RM_MODE_BASE = 0, RM_MODE_PREFILL = 1, RM_MODE_DECODE = 2, RM_MODE_ROUTER = 3 } rm_mode;
+
+typedef struct {
+  int32_t struct_size;   /* sizeof(rm_config), for forward compatibility */
+  int32_t device;        /* CUDA device ordinal that hosts this mesh node's tree */
+  int32_t mode;          /* rm_mode */
+  int32_t self_rank;     /* global node rank of this replica (config/cache_config.py:50-75) */
+  int32_t n_prefill;     /* len(prefill_cache_nodes): ranks [0, P) are prefill */
+  int32_t n_decode;      /* len(decode_cache_nodes):  ranks [P, P+D) are decode */
+  int32_t max_batch;     /* largest B / N any *_batch call will pass (scratch is sized from it) */
+  int32_t max_dups;      /* capacity of the duplicate-node table (RadixMesh.dup_nodes) */
+  int32_t max_key_len;   /* longest key (tokens) any insert / query will pass; bounds edge lengths */
+  int32_t reserved;
+  int64_t max_nodes;     /* node pool capacity, including the root */
+  int64_t max_tokens;    /* edge arena capacity in tokens (keys i32 + values i64 per token) */
+} rm_config;
+
+/* Per-index counters, filled by rm_sizes (synchronises). */
+typedef struct {
+  int64_t evictable;     /* RadixCache.evictable_size()  radix_cache.py:232-233 */
+  int64_t protected_;    /* RadixCache.protected_size()  radix_cache.py:235-237 */
+  int64_t n_nodes;       /* live nodes, root excluded */
+  int64_t arena_used;    /* tokens handed out of the edge arena (monotonic until rm_compact) */
+  int64_t n_dups;        /* live entries in the duplicate-node table */
+  int64_t op_seq;        /* operations applied so far (the logical clock) */
+  int32_t device_error;  /* sticky rm_status raised inside a kernel (RM_E_NOSPACE) */
+  int32_t pad;
+} rm_sizes_t;
+
+const char* rm_last_error(void);
+const char* rm_version(void);
+
+/* RadixCache.__init__ / RadixMesh.__init__ tree part (radix_cache.py:89-115, radix_mesh.py:74-89). */
+int rm_create(const rm_config* cfg, rm_index** out);
+int rm_destroy(rm_index* idx);
+/* RadixCache.reset / RadixMesh.reset (radix_cache.py:118-125, radix_mesh.py:240-245). */
+int rm_reset(rm_index* idx, void* stream);
+
+/*
+ * Batched longest-prefix match: RadixCache.match_prefix + _match_prefix_helper + _split_node
+ * (radix_cache.py:127-162, 252-294, 14-20) and RadixMesh.match_prefix/_match_prefix_helper
+ * (radix_mesh.py:203-218, 247-271).  Equivalent to calling match_prefix on queries 0..B-1 in
+ * order.  Query q is tokens[offsets[q] .. offsets[q+1]).  BASE/PREFILL split a partially
+ * matched edge and return the new upper node; DECODE/ROUTER never split and return the
+ * partially matched child.  Zero-length queries return (0, root) (the mesh shim raises
+ * IndexError before calling, radix_mesh.py:253).
+ *   out_len[q]   matched prefix length (= len(device_indices))
+ *   out_node[q]  last_device_node
+ */
+int rm_match_batch(rm_index* idx, const int32_t* tokens, const int64_t* offsets, int32_t B,
+                   int32_t* out_len, int32_t* out_node, void* stream);
+/* Same, HOST buffers: H2D of tokens/offsets, match, D2H of both outputs; synchronises.  Pinned
+ * host memory makes the copies asynchronous with respect to each other. */
+int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offsets_h, int32_t B,
+                     int32_t* out_len_h, int32_t* out_node_h, void* stream);
+
+/*
+ * torch.cat of the values along the matched path (radix_cache.py:154-157, radix_mesh.py:209-213):
+ * for query q writes out_len[q] int64 KV indices to out_values[out_offsets[q] ...].
+ * `nodes`/`lens` are rm_match_batch's outputs (call before any later mutation of the tree).
+ */
+int rm_gather_values(rm_index* idx, const int32_t* nodes, const int32_t* lens, const int64_t* out_offsets,
+                     int32_t B, int64_t* out_values, void* stream);
+
+/*
+ * Ordered batch of inserts: RadixCache.insert/_insert_helper (radix_cache.py:164-170, 296-327);
+ * in the mesh modes RadixMesh._insert_helper + NodeRankConflictResolver.keep + _swap_node
+ * (radix_mesh.py:273-323, 466-495, policy/conflict_resolve.py:1-6), i.e. what
+ * oplog_received does with N INSERT oplogs in arrival order (radix_mesh.py:411-416).
+ * Record r: key = tokens[offsets[r] .. offsets[r+1]), values[same range] (ignored for ROUTER),
+ * owner rank = ranks[r] (ignored for BASE; NULL = self_rank for every record).
+ * Equivalent to applying records 0..N-1 in order.  out_prefix_len[r] = the reference's return
+ * value (matched prefix length at the time record r is applied).
+ */
+int rm_insert_batch(rm_index* idx, const int32_t* tokens, const int64_t* values, const int64_t* offsets,
+                    const int32_t* ranks, int32_t N, int32_t* out_prefix_len, void* stream);
+int rm_insert_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* values_h, const int64_t* offsets_h,
+                      const int32_t* ranks_h, int32_t N, int32_t* out_prefix_len_h, void* stream);
+
+/*
+ * inc_lock_ref / dec_lock_ref (radix_cache.py:204-230; mesh override radix_mesh.py:168-179) for
+ * B nodes, all with the same sign (dir = +1 or -1), equivalent to the calls in order.
+ * out_delta[i] = the reference's return value for call i.
+ * gens (may be NULL): the generation each handle was taken at (rm_dump's gen array at that time).
+ * A tree id whose object was parked by a locked _swap_node (radix_mesh.py:478-495) after the handle
+ * was taken resolves to the parked node, as the reference's TreeNode object would.
+ */
+int rm_lock_batch(rm_index* idx, const int32_t* nodes, const int32_t* gens, int32_t B, int32_t dir,
+                  int64_t* out_delta, void* stream);
+
+/*
+ * RadixCache.evict(num_tokens) (radix_cache.py:179-202 with _collect_leaves :366-377 and
+ * _delete_leaf :347-352).  Evicted nodes are reported in the reference's eviction order:
+ * out_nodes_h[k] = node id, out_offs_h[k] / out_lens_h[k] = its value run in the value arena
+ * (rm_read_values reads it) so the caller can call token_to_kv_pool_allocator.free exactly as
+ * radix_cache.py:195 does.  *out_n_h = number evicted (<= cap).  Synchronises.
+ */
+int rm_evict(rm_index* idx, int64_t num_tokens, int32_t cap, int32_t* out_nodes_h, int64_t* out_offs_h,
+             int32_t* out_lens_h, int32_t* out_n_h, void* stream);
+
+/* RadixMesh._gc candidate scan (radix_mesh.py:151-156): entries of dup_nodes whose parked node is
+ * not None and has lock_ref == 0.  out_h rows are (tree node id, rank, parked node id).  Synchronises. */
+int rm_gc_candidates(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h, void* stream);
+/* All dup_nodes entries (tree node id, rank, parked node id or -1, parked lock_ref or 0).  Synchronises. */
+int rm_dup_entries(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h, void* stream);
+
+/*
+ * Router pick: RadixMesh.match_prefix in ROUTER mode (radix_mesh.py:219-238) fused with
+ * CacheAwareRouter.cache_aware_route (router/cache_aware_router.py:23-39) and the ConsistentHash
+ * fallback (:42-118; ring built once by rm_route_set_rings).
+ *   out_prefill[q] / out_decode[q]  ranks as RouterMatchResult holds them (-1 = none)
+ *   out_paddr[q] / out_daddr[q]     index into prefill_cache_nodes / decode_cache_nodes after the
+ *                                   fallback (the strings stay on the host)
+ *   out_err[q]   0 ok, 1 = the reference raises AssertionError (radix_mesh.py:233-237),
+ *                2 = the reference raises IndexError (radix_mesh.py:451)
+ * warm = 0 reproduces the warm-up gate (cache_aware_router.py:24-25): no match, hash only.
+ */
+int rm_route_batch(rm_index* idx, const int32_t* tokens, const int64_t* offsets, int32_t B, int32_t warm,
+                   int32_t* out_prefill, int32_t* out_decode, int32_t* out_paddr, int32_t* out_daddr,
+                   uint8_t* out_err, void* stream);
+/* Hash rings for the fallback: sorted u32 points and the address index that owns each point
+ * (ConsistentHash.add_node, cache_aware_router.py:58-73).  HOST pointers; copied. */
+int rm_route_set_rings(rm_index* idx, const uint32_t* p_points_h, const int32_t* p_owner_h, int32_t n_p,
+                       const uint32_t* d_points_h, const int32_t* d_owner_h, int32_t n_d);
+
+/* evictable_size / protected_size / node count (radix_cache.py:232-237).  Synchronises. */
+int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream);
+
+/*
+ * Parity / TreeNode-proxy support.  rm_dump copies the per-node arrays of ids [0, n) to HOST
+ * (any pointer may be NULL): parent (-1 = free id; the root also has -1), edge offset, edge length,
+ * lock_ref, last-access stamp (op sequence number), owner rank, full-key length, child count,
+ * generation (< 0 = parked by a locked swap), parked-chain link.
+ * *out_n_h = high-water node id + 1.  Synchronises.
+ */
+int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, int32_t* edge_len_h,
+            int32_t* lock_ref_h, uint64_t* stamp_h, int32_t* rank_h, int32_t* depth_h, int32_t* nchild_h,
+            int32_t* gen_h, int32_t* parked_h, int32_t* out_n_h, void* stream);
+/* Read `n` tokens / values of the edge arenas starting at token offset `off` into HOST buffers. */
+int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RADIXMESH_B200_H */

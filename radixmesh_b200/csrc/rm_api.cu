@@ -1,0 +1,375 @@
+// C ABI (include/radixmesh_b200.h): index lifetime, argument checks, host-buffer variants.
+#include <stdarg.h>
+#include <string.h>
+
+#include "rm_internal.h"
+#include "rm_sort.cuh"
+
+#ifdef RM_EMU
+thread_local rm_emu_dim3 threadIdx, blockIdx, blockDim, gridDim;
+#endif
+
+static thread_local char g_err[512] = "";
+
+void rm_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static int rm_bits(u64 v) {   // bits needed to hold values 0..v
+  int b = 1;
+  while (b < 63 && (v >> b) != 0) ++b;
+  return b;
+}
+
+template <class T>
+static cudaError_t rm_dalloc(T** p, size_t n) {
+  return cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * (n ? n : 1));
+}
+
+extern "C" {
+
+const char* rm_last_error(void) { return g_err; }
+const char* rm_version(void) {
+#ifdef RM_EMU
+  return "radixmesh_b200 0.1 (host emulation, tests only)";
+#else
+  return "radixmesh_b200 0.1 (sm_100a)";
+#endif
+}
+
+int rm_destroy(rm_index* idx) {
+  if (!idx) return RM_OK;
+  cudaSetDevice(idx->cfg.device);
+  RmTree& t = idx->t;
+  RmScratch& sc = idx->sc;
+  void* ptrs[] = {t.table, t.parent, t.edge_off, t.edge_len, t.lock_ref, t.stamp, t.rank, t.depth_end, t.nchild,
+                  t.gen, t.parked, t.tok, t.val, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
+                  sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.hist, sc.ev_key[0], sc.ev_key[1],
+                  sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.lock_first, sc.lock_cnt, sc.lock_flag,
+                  sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b,
+                  idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  delete idx;
+  return RM_OK;
+}
+
+int rm_create(const rm_config* cfg, rm_index** out) {
+  if (!cfg || !out || cfg->struct_size != (int32_t)sizeof(rm_config)) {
+    rm_set_error("rm_create: bad config (struct_size %d, expected %d)", cfg ? cfg->struct_size : -1, (int)sizeof(rm_config));
+    return RM_E_INVALID;
+  }
+  if (cfg->max_nodes < 2 || cfg->max_nodes > (1ll << 30) || cfg->max_tokens < 1 || cfg->max_batch < 1 ||
+      cfg->max_key_len < 1 || cfg->mode < RM_MODE_BASE || cfg->mode > RM_MODE_ROUTER) {
+    rm_set_error("rm_create: max_nodes/max_tokens/max_batch/max_key_len/mode out of range");
+    return RM_E_INVALID;
+  }
+  RM_CUDA(cudaSetDevice(cfg->device));
+  rm_index* idx = new rm_index();
+  memset(idx, 0, sizeof(*idx));
+  idx->cfg = *cfg;
+  RmTree& t = idx->t;
+  RmScratch& sc = idx->sc;
+  const size_t N = (size_t)cfg->max_nodes;
+  size_t cap = 1;
+  while (cap < 2 * N) cap <<= 1;   // load factor <= 0.5: one slot per non-root node
+  size_t dcap = 16;
+  while (dcap < 2 * (size_t)(cfg->max_dups > 0 ? cfg->max_dups : 1)) dcap <<= 1;
+  t.table_mask = (unsigned)(cap - 1);
+  t.dup_mask = (unsigned)(dcap - 1);
+  t.max_nodes = (int)N;
+  t.max_tokens = cfg->max_tokens;
+  t.max_key_len = cfg->max_key_len;
+  t.mode = cfg->mode;
+  t.n_prefill = cfg->n_prefill;
+  t.n_decode = cfg->n_decode;
+  t.self_rank = cfg->self_rank;
+  idx->node_bits = rm_bits((u64)N);
+  idx->len_bits = rm_bits((u64)cfg->max_key_len);
+  const size_t B = (size_t)cfg->max_batch;
+  sc.max_batch = cfg->max_batch;
+  sc.hist_words = rm_sort_scratch_words((int)B);
+  const bool with_values = cfg->mode != RM_MODE_ROUTER;
+  cudaError_t e = cudaSuccess;
+#define A(call) \
+  if (e == cudaSuccess) e = (call)
+  A(rm_dalloc(&t.table, cap));
+  A(rm_dalloc(&t.parent, N));
+  A(rm_dalloc(&t.edge_off, N));
+  A(rm_dalloc(&t.edge_len, N));
+  A(rm_dalloc(&t.lock_ref, N));
+  A(rm_dalloc(&t.stamp, N));
+  A(rm_dalloc(&t.rank, N));
+  A(rm_dalloc(&t.depth_end, N));
+  A(rm_dalloc(&t.nchild, N));
+  A(rm_dalloc(&t.gen, N));
+  A(rm_dalloc(&t.parked, N));
+  A(rm_dalloc(&t.tok, (size_t)cfg->max_tokens));
+  A(rm_dalloc(&t.val, with_values ? (size_t)cfg->max_tokens : 1));
+  A(rm_dalloc(&t.free_ids, N));
+  A(rm_dalloc(&t.ctr, 1));
+  A(rm_dalloc(&t.dup_key, dcap));
+  A(rm_dalloc(&t.dup_parked, dcap));
+  A(rm_dalloc(&sc.key[0], B));
+  A(rm_dalloc(&sc.key[1], B));
+  A(rm_dalloc(&sc.val[0], B));
+  A(rm_dalloc(&sc.val[1], B));
+  A(rm_dalloc(&sc.sufmax, B));
+  A(rm_dalloc(&sc.krank, B));
+  A(rm_dalloc(&sc.uniq_pos, B));
+  A(rm_dalloc(&sc.hist, sc.hist_words));
+  A(rm_dalloc(&sc.ev_key[0], N));
+  A(rm_dalloc(&sc.ev_key[1], N));
+  A(rm_dalloc(&sc.ev_val[0], N));
+  A(rm_dalloc(&sc.ev_val[1], N));
+  A(rm_dalloc(&sc.ev_hist, rm_sort_scratch_words((int)N)));
+  A(rm_dalloc(&sc.ev_lens, N));
+  A(rm_dalloc(&sc.lock_first, N));
+  A(rm_dalloc(&sc.lock_cnt, N));
+  A(rm_dalloc(&sc.lock_flag, 1));
+  A(rm_dalloc(&sc.dup_out, 4 * dcap));
+  A(rm_dalloc(&sc.dup_out_n, 1));
+  A(rm_dalloc(&sc.h_offsets, B + 1));
+  A(rm_dalloc(&sc.h_ranks, B));
+  A(rm_dalloc(&sc.h_out_a, B));
+  A(rm_dalloc(&sc.h_out_b, B));
+#undef A
+  if (e != cudaSuccess) {
+    rm_set_error("rm_create: device allocation failed: %s", cudaGetErrorString(e));
+    rm_destroy(idx);
+    return RM_E_NOSPACE;
+  }
+  int rc = rm_launch_reset(idx, 0);
+  if (rc == RM_OK && cudaStreamSynchronize(0) != cudaSuccess) rc = RM_E_CUDA;
+  if (rc != RM_OK) {
+    rm_destroy(idx);
+    return rc;
+  }
+  *out = idx;
+  return RM_OK;
+}
+
+int rm_reset(rm_index* idx, void* stream) {
+  if (!idx) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_reset(idx, (cudaStream_t)stream);
+}
+
+static int rm_check_batch(rm_index* idx, int n, const char* who) {
+  if (!idx || n < 0) {
+    rm_set_error("%s: bad arguments", who);
+    return RM_E_INVALID;
+  }
+  if (n > idx->cfg.max_batch) {
+    rm_set_error("%s: batch of %d exceeds rm_config.max_batch = %d", who, n, idx->cfg.max_batch);
+    return RM_E_TOO_LARGE;
+  }
+  return RM_OK;
+}
+
+int rm_match_batch(rm_index* idx, const int32_t* tokens, const int64_t* offsets, int32_t B, int32_t* out_len,
+                   int32_t* out_node, void* stream) {
+  int rc = rm_check_batch(idx, B, "rm_match_batch");
+  if (rc) return rc;
+  if (idx->cfg.mode == RM_MODE_ROUTER) {
+    rm_set_error("rm_match_batch: a ROUTER index answers through rm_route_batch");
+    return RM_E_MODE;
+  }
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_match(idx, tokens, (const i64*)offsets, B, out_len, out_node, (cudaStream_t)stream);
+}
+
+// grow the device staging buffers of the *_h entry points
+static int rm_stage_reserve(rm_index* idx, i64 n_tokens, bool values) {
+  RmScratch& sc = idx->sc;
+  if (n_tokens > sc.h_tokens_cap) {
+    if (sc.h_tokens) cudaFree(sc.h_tokens);
+    if (sc.h_values) cudaFree(sc.h_values);
+    sc.h_tokens = nullptr;
+    sc.h_values = nullptr;
+    i64 cap = n_tokens + n_tokens / 4 + 1024;
+    if (rm_dalloc(&sc.h_tokens, (size_t)cap) != cudaSuccess) {
+      rm_set_error("staging allocation of %lld tokens failed", (long long)cap);
+      return RM_E_NOSPACE;
+    }
+    sc.h_tokens_cap = cap;
+  }
+  if (values && !sc.h_values) {
+    if (rm_dalloc(&sc.h_values, (size_t)sc.h_tokens_cap) != cudaSuccess) {
+      rm_set_error("staging allocation failed");
+      return RM_E_NOSPACE;
+    }
+  }
+  return RM_OK;
+}
+
+int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offsets_h, int32_t B, int32_t* out_len_h,
+                     int32_t* out_node_h, void* stream) {
+  int rc = rm_check_batch(idx, B, "rm_match_batch_h");
+  if (rc) return rc;
+  if (B == 0) return RM_OK;
+  if (idx->cfg.mode == RM_MODE_ROUTER) return RM_E_MODE;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RmScratch& sc = idx->sc;
+  const i64 nt = offsets_h[B] - offsets_h[0];
+  if (offsets_h[0] != 0) {
+    rm_set_error("rm_match_batch_h: offsets must start at 0");
+    return RM_E_INVALID;
+  }
+  rc = rm_stage_reserve(idx, nt, false);
+  if (rc) return rc;
+  RM_CUDA(cudaMemcpyAsync(sc.h_offsets, offsets_h, sizeof(i64) * ((size_t)B + 1), cudaMemcpyHostToDevice, s));
+  RM_CUDA(cudaMemcpyAsync(sc.h_tokens, tokens_h, sizeof(int) * (size_t)nt, cudaMemcpyHostToDevice, s));
+  rc = rm_launch_match(idx, sc.h_tokens, sc.h_offsets, B, sc.h_out_a, sc.h_out_b, s);
+  if (rc) return rc;
+  RM_CUDA(cudaMemcpyAsync(out_len_h, sc.h_out_a, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaMemcpyAsync(out_node_h, sc.h_out_b, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
+int rm_gather_values(rm_index* idx, const int32_t* nodes, const int32_t* lens, const int64_t* out_offsets, int32_t B,
+                     int64_t* out_values, void* stream) {
+  int rc = rm_check_batch(idx, B, "rm_gather_values");
+  if (rc) return rc;
+  if (idx->cfg.mode == RM_MODE_ROUTER) return RM_E_MODE;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_gather(idx, nodes, lens, (const i64*)out_offsets, B, (i64*)out_values, (cudaStream_t)stream);
+}
+
+int rm_insert_batch(rm_index* idx, const int32_t* tokens, const int64_t* values, const int64_t* offsets,
+                    const int32_t* ranks, int32_t N, int32_t* out_prefix_len, void* stream) {
+  int rc = rm_check_batch(idx, N, "rm_insert_batch");
+  if (rc) return rc;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_insert(idx, tokens, (const i64*)values, (const i64*)offsets, ranks, N, out_prefix_len,
+                          (cudaStream_t)stream);
+}
+
+int rm_insert_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* values_h, const int64_t* offsets_h,
+                      const int32_t* ranks_h, int32_t N, int32_t* out_prefix_len_h, void* stream) {
+  int rc = rm_check_batch(idx, N, "rm_insert_batch_h");
+  if (rc) return rc;
+  if (N == 0) return RM_OK;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RmScratch& sc = idx->sc;
+  if (offsets_h[0] != 0) {
+    rm_set_error("rm_insert_batch_h: offsets must start at 0");
+    return RM_E_INVALID;
+  }
+  const i64 nt = offsets_h[N];
+  const bool with_values = idx->cfg.mode != RM_MODE_ROUTER && values_h != nullptr;
+  rc = rm_stage_reserve(idx, nt, with_values);
+  if (rc) return rc;
+  RM_CUDA(cudaMemcpyAsync(sc.h_offsets, offsets_h, sizeof(i64) * ((size_t)N + 1), cudaMemcpyHostToDevice, s));
+  RM_CUDA(cudaMemcpyAsync(sc.h_tokens, tokens_h, sizeof(int) * (size_t)nt, cudaMemcpyHostToDevice, s));
+  if (with_values) RM_CUDA(cudaMemcpyAsync(sc.h_values, values_h, sizeof(i64) * (size_t)nt, cudaMemcpyHostToDevice, s));
+  if (ranks_h) RM_CUDA(cudaMemcpyAsync(sc.h_ranks, ranks_h, sizeof(int) * (size_t)N, cudaMemcpyHostToDevice, s));
+  rc = rm_launch_insert(idx, sc.h_tokens, sc.h_values, sc.h_offsets, ranks_h ? sc.h_ranks : nullptr, N, sc.h_out_a, s);
+  if (rc) return rc;
+  if (out_prefix_len_h)
+    RM_CUDA(cudaMemcpyAsync(out_prefix_len_h, sc.h_out_a, sizeof(int) * (size_t)N, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
+int rm_lock_batch(rm_index* idx, const int32_t* nodes, const int32_t* gens, int32_t B, int32_t dir, int64_t* out_delta,
+                  void* stream) {
+  int rc = rm_check_batch(idx, B, "rm_lock_batch");
+  if (rc) return rc;
+  if (dir != 1 && dir != -1) {
+    rm_set_error("rm_lock_batch: dir must be +1 or -1");
+    return RM_E_INVALID;
+  }
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_lock_g(idx, nodes, gens, B, dir, (i64*)out_delta, (cudaStream_t)stream);
+}
+
+int rm_evict(rm_index* idx, int64_t num_tokens, int32_t cap, int32_t* out_nodes_h, int64_t* out_offs_h,
+             int32_t* out_lens_h, int32_t* out_n_h, void* stream) {
+  if (!idx || !out_n_h) return RM_E_INVALID;
+  if (idx->cfg.mode != RM_MODE_BASE) {
+    *out_n_h = 0;   // RadixMesh.evict is a no-op (radix_mesh.py:349-351)
+    return RM_OK;
+  }
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_evict(idx, num_tokens, cap, out_nodes_h, (i64*)out_offs_h, out_lens_h, out_n_h, (cudaStream_t)stream);
+}
+
+int rm_gc_candidates(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h, void* stream) {
+  if (!idx || !out_n_h) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_dups(idx, 1, cap, out_h, out_n_h, (cudaStream_t)stream);
+}
+
+int rm_dup_entries(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h, void* stream) {
+  if (!idx || !out_n_h) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_dups(idx, 0, cap, out_h, out_n_h, (cudaStream_t)stream);
+}
+
+int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream) {
+  if (!idx || !out_h) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RmCounters c;
+  RM_CUDA(cudaMemcpyAsync(&c, idx->t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  out_h->evictable = c.evictable;
+  out_h->protected_ = c.protected_;
+  out_h->n_nodes = c.n_nodes;
+  out_h->arena_used = (int64_t)c.arena_top;
+  out_h->n_dups = c.n_dups;
+  out_h->op_seq = (int64_t)idx->op_seq;
+  out_h->device_error = c.err;
+  out_h->pad = c.node_hwm;
+  return RM_OK;
+}
+
+int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, int32_t* edge_len_h, int32_t* lock_ref_h,
+            uint64_t* stamp_h, int32_t* rank_h, int32_t* depth_h, int32_t* nchild_h, int32_t* gen_h, int32_t* parked_h,
+            int32_t* out_n_h, void* stream) {
+  if (!idx || !out_n_h) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RmCounters c;
+  RM_CUDA(cudaMemcpyAsync(&c, idx->t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  int n = c.node_hwm;
+  *out_n_h = n;
+  if (n > cap) n = cap;
+  RmTree& t = idx->t;
+#define D(dst, src, T) \
+  if (dst) RM_CUDA(cudaMemcpyAsync(dst, src, sizeof(T) * (size_t)n, cudaMemcpyDeviceToHost, s))
+  D(parent_h, t.parent, int);
+  D(edge_off_h, t.edge_off, i64);
+  D(edge_len_h, t.edge_len, int);
+  D(lock_ref_h, t.lock_ref, int);
+  D(stamp_h, t.stamp, u64);
+  D(rank_h, t.rank, int);
+  D(depth_h, t.depth_end, int);
+  D(nchild_h, t.nchild, int);
+  D(gen_h, t.gen, int);
+  D(parked_h, t.parked, int);
+#undef D
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
+int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream) {
+  if (!idx || off < 0 || n < 0 || off + n > idx->t.max_tokens) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (tokens_h) RM_CUDA(cudaMemcpyAsync(tokens_h, idx->t.tok + off, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  if (values_h && idx->cfg.mode != RM_MODE_ROUTER)
+    RM_CUDA(cudaMemcpyAsync(values_h, idx->t.val + off, sizeof(i64) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,216 @@
+// Shared device-side types and helpers of the radix-tree index (sm_100a).
+//
+// HBM layout (DESIGN.md "Data layout"):
+//   child table  open-addressed, 32-byte slots (= one DRAM sector) keyed (parent id, first token);
+//                a slot carries everything one hop of a walk needs: child id, edge length, edge
+//                offset, owner rank.  Replaces TreeNode.children (radix_cache.py:39).
+//   node pool    structure of arrays indexed by node id (TreeNode fields, radix_cache.py:35-53).
+//   edge arenas  tok[i32] and val[i64] in parallel: a node's key and value are the same
+//                [edge_off, edge_off+edge_len) run of both, so _split_node (radix_cache.py:277-294)
+//                is zero-copy.
+#pragma once
+#include <stdint.h>
+#ifdef RM_EMU
+#include "rm_emu.h"
+#define RM_G_DEFAULT 1
+#else
+#include <cuda_runtime.h>
+#define RM_LAUNCH(kernel, grid, block, stream, ...) kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
+#endif
+#include "../../include/radixmesh_b200.h"
+
+typedef unsigned long long u64;
+typedef long long i64;
+
+#define RM_EMPTY_KEY 0xFFFFFFFFFFFFFFFFull
+#define RM_TOMB_KEY 0xFFFFFFFFFFFFFFFEull
+#define RM_NO_REQ 0xFFFFFFFFFFFFFFFFull
+
+struct __align__(32) RmSlot {
+  u64 key;        // (parent id << 32) | first token of the child's edge
+  int child;      // child node id
+  int edge_len;   // tokens on the child's edge
+  i64 edge_off;   // start of the edge in the arenas
+  int rank;       // owner rank of the child's value (mesh modes)
+  int pad;
+};
+
+struct RmCounters {
+  u64 free_head;      // node ids handed out  (ring of free ids)
+  u64 free_tail;      // node ids returned
+  u64 arena_top;      // tokens handed out of the arenas
+  i64 evictable;      // RadixCache.evictable_size_
+  i64 protected_;     // RadixCache.protected_size_
+  i64 n_nodes;        // live non-root nodes
+  int node_hwm;       // high-water node id + 1
+  int err;            // sticky rm_status raised on the device
+  int n_dups;
+  int n_req;          // scratch: split requests of the current match batch
+  int evict_n;        // scratch: nodes evicted by the current rm_evict
+  int pad;
+};
+
+struct RmTree {
+  int max_key_len;   // bound on key / edge length (rm_config.max_key_len)
+  RmSlot* table;
+  unsigned table_mask;
+  int* parent;
+  i64* edge_off;
+  int* edge_len;
+  int* lock_ref;
+  u64* stamp;
+  int* rank;
+  int* depth_end;
+  int* nchild;
+  int* gen;        // generation of the object a tree id stands for (bumped by a locked swap); parked: -(gen)-1
+  int* parked;     // tree node: most recently parked predecessor (or -1); parked node: the one parked before it
+  int* tok;
+  i64* val;
+  int* free_ids;
+  RmCounters* ctr;
+  int max_nodes;
+  i64 max_tokens;
+  int mode, n_prefill, n_decode, self_rank;
+  // duplicate-node table (RadixMesh.dup_nodes): open addressed, key (tree node << 32 | rank+1)
+  u64* dup_key;
+  int* dup_parked;
+  unsigned dup_mask;
+};
+
+__device__ __forceinline__ unsigned rm_hash(u64 k, unsigned mask) {
+  k ^= k >> 32;
+  k *= 0x9E3779B97F4A7C15ull;
+  k ^= k >> 29;
+  k *= 0xBF58476D1CE4E5B9ull;
+  k ^= k >> 32;
+  return (unsigned)k & mask;
+}
+
+__device__ __forceinline__ u64 rm_key(int parent, int token) { return ((u64)(unsigned)parent << 32) | (unsigned)token; }
+
+// Lane bookkeeping for a cooperating group of G lanes (G = 32: one warp per unit of work;
+// smaller G: several independent walks per warp to keep more dependent-load chains in flight).
+template <int G>
+struct RmGroup {
+  int lane;
+  unsigned mask;
+  __device__ __forceinline__ RmGroup() {
+#ifdef RM_EMU
+    lane = 0;
+    mask = 1u;
+#else
+    lane = threadIdx.x & (G - 1);
+    unsigned base = (threadIdx.x & 31) & ~(G - 1);
+    mask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << base);
+#endif
+  }
+  __device__ __forceinline__ unsigned ballot(int pred) const {
+#ifdef RM_EMU
+    return pred ? 1u : 0u;
+#else
+    unsigned b = __ballot_sync(mask, pred);
+    return (G == 32) ? b : ((b & mask) >> ((threadIdx.x & 31) & ~(G - 1)));
+#endif
+  }
+  template <class T>
+  __device__ __forceinline__ T bcast(T v, int src) const {
+#ifdef RM_EMU
+    return v;
+#else
+    return __shfl_sync(mask, v, src, G);
+#endif
+  }
+  template <class T>
+  __device__ __forceinline__ T shfl_up(T v, int d) const {
+#ifdef RM_EMU
+    return v;
+#else
+    return __shfl_up_sync(mask, v, d, G);
+#endif
+  }
+  __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+  static __device__ __forceinline__ unsigned full() { return (G == 32) ? 0xffffffffu : ((1u << G) - 1u); }
+};
+
+// Probe the child table for `key`.  Returns the slot index or -1.  Every lane of the calling
+// group passes the same key, so the loads are broadcasts (one 32-byte sector per probe step).
+// COHERENT = true reads through L2 (ld.cg) for kernels that mutate the table themselves.
+template <bool COHERENT>
+__device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
+  unsigned i = rm_hash(key, t.table_mask);
+  while (true) {
+    const int4* p = reinterpret_cast<const int4*>(t.table + i);
+    int4 a = COHERENT ? __ldcg(p) : __ldg(p);
+    u64 k = ((u64)(unsigned)a.y << 32) | (unsigned)a.x;
+    if (k == key) {
+      int4 b = COHERENT ? __ldcg(p + 1) : __ldg(p + 1);
+      out.key = k;
+      out.child = a.z;
+      out.edge_len = a.w;
+      out.edge_off = (i64)(((u64)(unsigned)b.y << 32) | (unsigned)b.x);
+      out.rank = b.z;
+      return (int)i;
+    }
+    if (k == RM_EMPTY_KEY) return -1;
+    i = (i + 1) & t.table_mask;
+  }
+}
+
+__device__ __forceinline__ void rm_slot_store(RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank) {
+  // payload first, key last (a probe only trusts a slot whose key matches)
+  s->child = child;
+  s->edge_len = edge_len;
+  s->edge_off = edge_off;
+  s->rank = rank;
+  s->pad = 0;
+  __threadfence();
+  *reinterpret_cast<volatile u64*>(&s->key) = key;
+}
+
+// Claim a free (empty or tombstoned) slot for `key` and fill it.  Caller guarantees the key is
+// not present.  One lane calls this.
+__device__ __forceinline__ void rm_table_insert(const RmTree& t, u64 key, int child, int edge_len, i64 edge_off, int rank) {
+  unsigned i = rm_hash(key, t.table_mask);
+  while (true) {
+    u64* kp = &t.table[i].key;
+    u64 cur = *reinterpret_cast<volatile u64*>(kp);
+    if (cur == RM_EMPTY_KEY || cur == RM_TOMB_KEY) {
+      // reserve with a key nobody looks up (parent id 0xFFFFFFFD never exists), then publish
+      u64 reserve = 0xFFFFFFFD00000000ull | (unsigned)child;
+      if (atomicCAS(kp, cur, reserve) == cur) {
+        rm_slot_store(&t.table[i], key, child, edge_len, edge_off, rank);
+        return;
+      }
+      continue;  // lost the race for this slot: look at it again
+    }
+    i = (i + 1) & t.table_mask;
+  }
+}
+
+// Pop `n` node ids from the free ring.  One lane calls this; returns the ring position of the
+// first id (ids are free_ids[(pos + k) % max_nodes]) or sets the sticky error and returns ~0.
+__device__ __forceinline__ u64 rm_alloc_nodes(const RmTree& t, int n) {
+  u64 pos = atomicAdd(&t.ctr->free_head, (u64)n);
+  u64 tail = *reinterpret_cast<volatile u64*>(&t.ctr->free_tail);
+  if (pos + (u64)n > tail) {
+    atomicMax(&t.ctr->err, (int)RM_E_NOSPACE);
+    return ~0ull;
+  }
+  return pos;
+}
+__device__ __forceinline__ int rm_free_id_at(const RmTree& t, u64 pos) { return t.free_ids[pos % (u64)t.max_nodes]; }
+
+__device__ __forceinline__ i64 rm_alloc_arena(const RmTree& t, int n) {
+  u64 off = atomicAdd(&t.ctr->arena_top, (u64)n);
+  if (off + (u64)n > (u64)t.max_tokens) {
+    atomicMax(&t.ctr->err, (int)RM_E_NOSPACE);
+    return -1;
+  }
+  return (i64)off;
+}
+
+// 64-bit signed add (CUDA only has the unsigned overload; two's complement makes them the same)
+__device__ __forceinline__ void rm_add_i64(i64* p, i64 v) { atomicAdd(reinterpret_cast<u64*>(p), (u64)v); }
+
+// Host-side launchers implemented in the .cu files (rm_api.cu calls them).
+struct RmScratch;

@@ -1,0 +1,314 @@
+// K4 ordered batched insert apply (sm_100a).
+//
+// Replaces RadixCache._insert_helper (radix_cache.py:296-327) and, in the mesh modes,
+// RadixMesh._insert_helper + NodeRankConflictResolver.keep + _swap_node (radix_mesh.py:273-323,
+// 466-495; policy/conflict_resolve.py:1-6): what oplog_received does with a run of INSERT oplogs.
+//
+// Order equivalence.  Two inserts can only interact if their keys start with the same token (they
+// then share a root child); everything else about the tree they touch is disjoint.  The batch is
+// therefore stably sorted by first token, and one warp per distinct first token applies its records
+// one after another in arrival order, while different first tokens proceed in parallel.  Inside a
+// warp the lanes cooperate on the edge compares and on copying the new leaf's key/value run into
+// the arenas; node ids and arena space come from device-wide bump allocators (one atomic per record).
+#include "rm_internal.h"
+#include "rm_sort.cuh"
+
+#ifndef RM_EMU
+#define RM_INS_TPB 128
+#define RM_INS_G 32
+#else
+#define RM_INS_TPB 64
+#define RM_INS_G 1
+#endif
+
+// group key = first token (u32) of each record; empty records get the "none" marker
+__global__ void rm_insert_keys_kernel(const int* __restrict__ tok, const i64* __restrict__ off, int N,
+                                      u64* __restrict__ key, unsigned* __restrict__ val) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  i64 o = off[r];
+  int len = (int)(off[r + 1] - o);
+  key[r] = len > 0 ? (u64)(unsigned)tok[o] : (1ull << 32);
+  val[r] = (unsigned)r;
+}
+
+// Record a duplicate-node entry: dup_nodes[(full_key(node), rank)] = parked (radix_mesh.py:310, 476, 493).
+// The tree node id stands for its full key (stable under splits: the lower half keeps the id).
+__device__ __forceinline__ void rm_dup_put(const RmTree& t, int node, int rank, int parked) {
+  u64 key = ((u64)(unsigned)node << 32) | (unsigned)(rank + 1);
+  unsigned i = rm_hash(key, t.dup_mask);
+  for (unsigned probes = 0; probes <= t.dup_mask; ++probes) {
+    u64 cur = *reinterpret_cast<volatile u64*>(&t.dup_key[i]);
+    if (cur == key) {
+      t.dup_parked[i] = parked;  // dict assignment overwrites
+      return;
+    }
+    if (cur == RM_EMPTY_KEY) {
+      u64 old = atomicCAS(&t.dup_key[i], RM_EMPTY_KEY, key);
+      if (old == RM_EMPTY_KEY || old == key) {
+        t.dup_parked[i] = parked;
+        if (old == RM_EMPTY_KEY) atomicAdd(&t.ctr->n_dups, 1);
+        return;
+      }
+    }
+    i = (i + 1) & t.dup_mask;
+  }
+  atomicMax(&t.ctr->err, (int)RM_E_NOSPACE);
+}
+
+// MESH: 0 = RadixCache semantics, 1 = prefill/decode replica (values compared), 2 = router replica
+// (owner ranks compared, no value arena traffic).
+template <int G, int MESH>
+__global__ void __launch_bounds__(RM_INS_TPB)
+rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__ rval, const i64* __restrict__ roff,
+                 const int* __restrict__ rrank, int N, const u64* __restrict__ skey, const unsigned* __restrict__ sval,
+                 u64 seq_base, int* __restrict__ out_prefix) {
+  RmGroup<G> g;
+  const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (i >= N) return;
+  const u64 gk = skey[i];
+  if (i > 0 && skey[i - 1] == gk) return;  // one group per distinct first token
+  if (gk == (1ull << 32)) {
+    // empty keys: insert returns 0 and only stamps the root (radix_cache.py:297-299)
+    for (int j = i + g.lane; j < N; j += G) out_prefix[sval[j]] = 0;
+    return;
+  }
+  for (int j = i; j < N && skey[j] == gk; ++j) {
+    const int r = (int)sval[j];
+    const i64 o = roff[r];
+    const int n = (int)(roff[r + 1] - o);
+    const int* __restrict__ key = rtok + o;
+    const i64* __restrict__ val = (MESH == 2) ? nullptr : (rval + o);
+    const int owner = (MESH == 0) ? -1 : (rrank ? rrank[r] : t.self_rank);
+    // Stamp encoding.  The reference stamps with a monotonic clock, so inside ONE operation a node
+    // visited earlier is older.  All nodes an operation stamps lie on one root path (where the
+    // tree shape already forces child-before-parent eviction) except the lower half of a node it
+    // split: that half is stamped on the way down, before the new upper node and the new leaf
+    // exist, and ends up as a SIBLING of the new leaf.  Stamps are therefore 2*op+1, and 2*op for
+    // that lower half, which keeps "older than the leaf of the same operation" (radix_cache.py:306-324).
+    const u64 seq = ((seq_base + (u64)r) << 1) | 1ull;
+    if (n > t.max_key_len) {
+      if (g.lane == 0) {
+        atomicMax(&t.ctr->err, (int)RM_E_INVALID);
+        out_prefix[r] = 0;
+      }
+      continue;
+    }
+    int node = 0, pos = 0, total = 0;
+    while (pos < n) {
+      RmSlot s;
+      const int sidx = rm_find<true>(t, rm_key(node, key[pos]), s);
+      if (sidx < 0) break;
+      int c = s.child;
+      const int elen = s.edge_len;
+      const i64 eoff = s.edge_off;
+      const int lim = min(elen, n - pos);
+      // longest common prefix of the edge and the rest of the key (radix_cache.py:14-20)
+      int m = lim;
+      for (int base = 1; base < lim; base += G) {
+        int x = base + g.lane;
+        bool ne = x < lim && __ldcg(t.tok + eoff + x) != key[pos + x];
+        unsigned mb = g.ballot(ne);
+        if (mb) {
+          m = base + __ffs(mb) - 1;
+          break;
+        }
+      }
+      // mesh: does the incoming value agree with the stored one over the matched part?
+      bool lost = false, swap = false;
+      if (MESH == 1) {
+        bool diff = false;
+        for (int base = 0; base < m; base += G) {
+          int x = base + g.lane;
+          bool ne = x < m && __ldcg(t.val + eoff + x) != val[pos + x];
+          if (g.ballot(ne)) {
+            diff = true;
+            break;
+          }
+        }
+        if (diff) {
+          if (s.rank <= owner) lost = true;   // keep(now, new): the lower rank wins
+          else swap = true;
+        }
+      } else if (MESH == 2) {
+        if (s.rank != owner) {
+          if (s.rank <= owner) lost = true;
+          else swap = true;
+        }
+      }
+      total += m;
+      if (g.lane == 0) t.stamp[c] = seq;
+      int target = c;
+      if (m < elen) {
+        // _split_node (radix_cache.py:277-294): new upper node [0, m), c keeps [m, elen)
+        u64 apos = 0;
+        if (g.lane == 0) apos = rm_alloc_nodes(t, 1);
+        apos = g.bcast(apos, 0);
+        if (apos == ~0ull) break;
+        const int u = rm_free_id_at(t, apos);
+        if (g.lane == 0) {
+          const int par = t.parent[c];
+          t.parent[u] = par;
+          t.edge_off[u] = eoff;
+          t.edge_len[u] = m;
+          t.depth_end[u] = t.depth_end[c] - elen + m;
+          t.lock_ref[u] = t.lock_ref[c];
+          t.rank[u] = s.rank;
+          t.nchild[u] = 1;
+          t.gen[u] = 0;
+          t.parked[u] = -1;
+          t.stamp[u] = seq;
+          atomicMax(&t.ctr->node_hwm, u + 1);
+          t.table[sidx].child = u;
+          t.table[sidx].edge_len = m;
+          rm_table_insert(t, rm_key(u, __ldcg(t.tok + eoff + m)), c, elen - m, eoff + m, s.rank);
+          t.parent[c] = u;
+          t.edge_off[c] = eoff + m;
+          t.edge_len[c] = elen - m;
+          t.stamp[c] = seq - 1;   // lower half: stamped before the split, see above
+          rm_add_i64(&t.ctr->n_nodes, (i64)1);
+          __threadfence();
+        }
+        g.sync();
+        target = u;
+      }
+      if (MESH != 0 && swap) {
+        // _swap_node (radix_mesh.py:466-495): the incoming (lower-rank) value takes the node
+        const int old_rank = s.rank;
+        if (MESH == 2) {
+          if (g.lane == 0) {
+            t.rank[target] = owner;
+            t.table[sidx].rank = owner;
+          }
+        } else {
+          const int lk = __ldcg(t.lock_ref + target);
+          if (lk == 0) {
+            for (int x = g.lane; x < m; x += G) t.val[eoff + x] = val[pos + x];
+            if (g.lane == 0) {
+              t.rank[target] = owner;
+              t.table[sidx].rank = owner;
+              rm_dup_put(t, target, old_rank, -1);
+            }
+          } else {
+            // locked: the tree node keeps its id with the new value in a fresh arena run and
+            // lock_ref 0; the old value, rank and lock move to a parked node that dup_nodes owns.
+            // gen[target] is bumped so that handles taken before the swap resolve to the parked
+            // node (DESIGN.md "locked swap").
+            u64 apos = 0;
+            i64 noff = 0;
+            if (g.lane == 0) {
+              apos = rm_alloc_nodes(t, 1);
+              noff = rm_alloc_arena(t, m);
+            }
+            apos = g.bcast(apos, 0);
+            noff = g.bcast(noff, 0);
+            if (apos == ~0ull || noff < 0) break;
+            const int d = rm_free_id_at(t, apos);
+            for (int x = g.lane; x < m; x += G) {
+              t.tok[noff + x] = __ldcg(t.tok + eoff + x);
+              t.val[noff + x] = val[pos + x];
+            }
+            if (g.lane == 0) {
+              t.parent[d] = t.parent[target];
+              t.edge_off[d] = eoff;
+              t.edge_len[d] = m;
+              t.depth_end[d] = t.depth_end[target];
+              t.lock_ref[d] = lk;
+              t.rank[d] = old_rank;
+              t.nchild[d] = 0;
+              t.gen[d] = -(t.gen[target] + 1);   // parked marker: -(generation it was known under) - 1
+              t.stamp[d] = t.stamp[target];
+              atomicMax(&t.ctr->node_hwm, d + 1);
+              t.edge_off[target] = noff;
+              t.lock_ref[target] = 0;
+              t.rank[target] = owner;
+              t.gen[target] = t.gen[target] + 1;
+              t.stamp[target] = seq;
+              t.table[sidx].edge_off = noff;
+              t.table[sidx].rank = owner;
+              t.parked[d] = t.parked[target];
+              t.parked[target] = d;
+              // like the reference, neither size counter moves (radix_mesh.py:478-495)
+              rm_dup_put(t, target, old_rank, d);
+            }
+          }
+        }
+        g.sync();
+      }
+      if (MESH != 0 && lost && g.lane == 0) rm_dup_put(t, target, owner, -1);
+      pos += m;
+      node = target;
+      if (m < elen) break;  // the key diverged (or ended) inside this edge
+    }
+    if (pos < n && node >= 0) {
+      // append the remainder as a new leaf (radix_cache.py:319-326)
+      const int rem = n - pos;
+      u64 apos = 0;
+      i64 noff = 0;
+      if (g.lane == 0) {
+        apos = rm_alloc_nodes(t, 1);
+        noff = rm_alloc_arena(t, rem);
+      }
+      apos = g.bcast(apos, 0);
+      noff = g.bcast(noff, 0);
+      if (apos != ~0ull && noff >= 0) {
+        const int leaf = rm_free_id_at(t, apos);
+        for (int x = g.lane; x < rem; x += G) {
+          t.tok[noff + x] = key[pos + x];
+          if (MESH != 2) t.val[noff + x] = val[pos + x];
+        }
+        if (g.lane == 0) {
+          t.parent[leaf] = node;
+          t.edge_off[leaf] = noff;
+          t.edge_len[leaf] = rem;
+          t.depth_end[leaf] = n;
+          t.lock_ref[leaf] = 0;
+          t.rank[leaf] = owner;
+          t.nchild[leaf] = 0;
+          t.gen[leaf] = 0;
+          t.parked[leaf] = -1;
+          t.stamp[leaf] = seq;
+          atomicMax(&t.ctr->node_hwm, leaf + 1);
+          atomicAdd(&t.nchild[node], 1);
+          rm_table_insert(t, rm_key(node, key[pos]), leaf, rem, noff, owner);
+          // evictable_size_ += len(value): 1 for a router value (radix_mesh.py:62-63, 321)
+          rm_add_i64(&t.ctr->evictable, (i64)(MESH == 2 ? 1 : rem));
+          rm_add_i64(&t.ctr->n_nodes, (i64)1);
+          __threadfence();
+        }
+      }
+      g.sync();
+    }
+    if (g.lane == 0) out_prefix[r] = total;
+  }
+}
+
+int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const i64* offsets, const int* ranks, int N,
+                     int* out_prefix_len, cudaStream_t s) {
+  if (N <= 0) return RM_OK;
+  RmScratch& sc = idx->sc;
+  const u64 seq_base = idx->op_seq + 1;
+  idx->op_seq += (u64)N;
+  RM_LAUNCH(rm_insert_keys_kernel, (N + 255) / 256, 256, s, tokens, offsets, N, sc.key[0], sc.val[0]);
+  RM_CUDA(cudaGetLastError());
+  const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], N, 33, sc.hist, s);
+  RM_CUDA(cudaGetLastError());
+  const long long threads = (long long)N * RM_INS_G;
+  const int grid = (int)((threads + RM_INS_TPB - 1) / RM_INS_TPB);
+  switch (idx->cfg.mode) {
+    case RM_MODE_BASE: {
+      auto k = rm_insert_kernel<RM_INS_G, 0>;
+      RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base, out_prefix_len);
+    } break;
+    case RM_MODE_ROUTER: {
+      auto k = rm_insert_kernel<RM_INS_G, 2>;
+      RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base, out_prefix_len);
+    } break;
+    default: {
+      auto k = rm_insert_kernel<RM_INS_G, 1>;
+      RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base, out_prefix_len);
+    } break;
+  }
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}

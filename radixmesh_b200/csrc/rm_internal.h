@@ -1,0 +1,79 @@
+// Host-side state of one index and the launchers each .cu file exports to rm_api.cu.
+#pragma once
+#include <stdio.h>
+#include <stdlib.h>
+#include "rm_common.cuh"
+
+struct RmScratch {
+  int max_batch;
+  u64* key[2];        // sort ping-pong: split requests of a match batch / group keys of an insert batch
+  unsigned* val[2];
+  u64* sufmax;        // per sorted split request: max op seq of requests at or beyond it on the same edge
+  int* krank;         // per sorted split request: rank of its split point among the edge's distinct points
+  int* uniq_pos;      // per edge group: sorted positions of the distinct split points
+  unsigned* hist;     // radix-sort histogram table
+  size_t hist_words;
+  // eviction (sized by max_nodes)
+  u64* ev_key[2];
+  unsigned* ev_val[2];
+  unsigned* ev_hist;
+  int* ev_lens;       // value-run lengths of the evicted nodes, in eviction order
+  // lock batches (sized by max_nodes)
+  int* lock_first;
+  int* lock_cnt;
+  int* lock_flag;
+  // duplicate-node table scan output: rows of (tree node, rank, parked node, parked lock_ref)
+  int* dup_out;
+  int* dup_out_n;
+  // staging for the *_h entry points
+  int* h_tokens;      // device copies of host inputs
+  i64* h_values;
+  i64* h_offsets;
+  int* h_ranks;
+  int* h_out_a;
+  int* h_out_b;
+  i64 h_tokens_cap;
+};
+
+struct rm_index {
+  rm_config cfg;
+  RmTree t;           // device pointers, passed by value to kernels
+  RmScratch sc;
+  u64 op_seq;         // logical clock: operations applied so far
+  int node_bits;      // bits of a node id
+  int len_bits;       // bits of an edge length / split point
+  unsigned* ring_p;   // consistent-hash rings (device)
+  int* ring_p_owner;
+  int ring_p_n;
+  unsigned* ring_d;
+  int* ring_d_owner;
+  int ring_d_n;
+};
+
+void rm_set_error(const char* fmt, ...);
+#define RM_CUDA(call)                                                                         \
+  do {                                                                                        \
+    cudaError_t _e = (call);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      rm_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return RM_E_CUDA;                                                                       \
+    }                                                                                         \
+  } while (0)
+
+// rm_match.cu
+int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B, int* out_len, int* out_node,
+                    cudaStream_t s);
+int rm_launch_gather(rm_index* idx, const int* nodes, const int* lens, const i64* out_offsets, int B, i64* out_values,
+                     cudaStream_t s);
+int rm_launch_route(rm_index* idx, const int* tokens, const i64* offsets, int B, int warm, int* out_prefill,
+                    int* out_decode, int* out_paddr, int* out_daddr, unsigned char* out_err, cudaStream_t s);
+// rm_insert.cu
+int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const i64* offsets, const int* ranks, int N,
+                     int* out_prefix_len, cudaStream_t s);
+// rm_maint.cu
+int rm_launch_reset(rm_index* idx, cudaStream_t s);
+int rm_launch_lock(rm_index* idx, const int* nodes, int B, int dir, i64* out_delta, cudaStream_t s);
+int rm_launch_lock_g(rm_index* idx, const int* nodes, const int* gens, int B, int dir, i64* out_delta, cudaStream_t s);
+int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
+                    int* out_n_h, cudaStream_t s);
+int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int* out_n_h, cudaStream_t s);

@@ -1,0 +1,393 @@
+// Reset, K5 lock refs, K6 LRU eviction, K7 GC-duplicate candidate scan (sm_100a).
+//
+//   reset   RadixCache.reset                     radix_cache.py:118-125
+//   K5      inc_lock_ref / dec_lock_ref          radix_cache.py:204-230, radix_mesh.py:168-179
+//   K6      evict + _collect_leaves + _delete_leaf   radix_cache.py:179-202, 366-377, 347-352
+//   K7      RadixMesh._gc candidate scan         radix_mesh.py:151-156
+#include "rm_internal.h"
+#include "rm_sort.cuh"
+
+#ifdef RM_EMU
+#define RM_MT_TPB 64
+#else
+#define RM_MT_TPB 256
+#endif
+#define RM_INT_MAX 0x7fffffff
+
+// ------------------------------------------------------------------ reset
+__global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
+  const i64 n = t.max_nodes;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 x = (i64)blockIdx.x * blockDim.x + threadIdx.x; x < n; x += stride) {
+    t.free_ids[x] = (int)(x + 1);       // ring position x hands out id x+1 (id 0 is the root)
+    t.parent[x] = -1;
+    t.edge_len[x] = 0;
+    t.edge_off[x] = 0;
+    t.lock_ref[x] = (x == 0) ? 1 : 0;   // root.lock_ref = 1 (radix_cache.py:122)
+    t.stamp[x] = 0;
+    t.rank[x] = (t.mode == RM_MODE_BASE) ? -1 : 0;   // mesh roots belong to the master rank (radix_mesh.py:243-245)
+    t.depth_end[x] = 0;
+    t.nchild[x] = 0;
+    t.gen[x] = 0;
+    t.parked[x] = -1;
+    lock_first[x] = RM_INT_MAX;
+    lock_cnt[x] = 0;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    RmCounters c;
+    c.free_head = 0;
+    c.free_tail = (u64)(t.max_nodes - 1);
+    c.arena_top = 0;
+    c.evictable = 0;
+    c.protected_ = 0;
+    c.n_nodes = 0;
+    c.node_hwm = 1;
+    c.err = 0;
+    c.n_dups = 0;
+    c.n_req = 0;
+    c.evict_n = 0;
+    c.pad = 0;
+    *t.ctr = c;
+  }
+}
+
+struct RmLockScratch {
+  int* first;   // per node: lowest op index of the batch that touches it
+  int* cnt;     // per node: ops of the batch that touch it
+  int* flag;    // batch needs the exact sequential path
+};
+static inline RmLockScratch rm_lock_scratch(rm_index* idx) {
+  RmLockScratch ls = {idx->sc.lock_first, idx->sc.lock_cnt, idx->sc.lock_flag};
+  return ls;
+}
+
+int rm_launch_reset(rm_index* idx, cudaStream_t s) {
+  RmTree& t = idx->t;
+  RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
+  RM_CUDA(cudaMemsetAsync(t.dup_key, 0xFF, sizeof(u64) * ((size_t)t.dup_mask + 1), s));
+  RmLockScratch ls = rm_lock_scratch(idx);
+  RM_CUDA(cudaMemsetAsync(ls.flag, 0, sizeof(int), s));
+  int grid = (int)min((i64)1184, ((i64)t.max_nodes + RM_MT_TPB - 1) / RM_MT_TPB);
+  RM_LAUNCH(rm_reset_kernel, grid, RM_MT_TPB, s, t, ls.first, ls.cnt);
+  RM_CUDA(cudaGetLastError());
+  idx->op_seq = 1;   // reset itself is operation 1 of the logical clock
+  return RM_OK;
+}
+
+// ------------------------------------------------------------------ K5 lock refs
+// A handle (node id, generation) taken before a locked swap stands for the parked object.
+__device__ __forceinline__ int rm_resolve(const RmTree& t, int node, const int* gens, int i) {
+  if (gens == nullptr || node <= 0) return node;
+  int want = gens[i];
+  if (want < 0 || t.gen[node] == want) return node;
+  int d = t.parked[node];
+  while (d >= 0) {
+    if (t.gen[d] == -(want + 1)) return d;
+    d = t.parked[d];
+  }
+  return node;
+}
+
+__global__ void rm_lock_mark_kernel(RmTree t, const int* nodes, const int* gens, int B, RmLockScratch ls) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  int x = rm_resolve(t, nodes[i], gens, i);
+  while (x > 0) {
+    atomicAdd(&ls.cnt[x], 1);
+    atomicMin(&ls.first[x], i);
+    x = t.parent[x];
+  }
+}
+
+// len(node.value): edge length, except router values whose len() is 1 (radix_mesh.py:62-63)
+__device__ __forceinline__ i64 rm_value_len(const RmTree& t, int x) {
+  return t.mode == RM_MODE_ROUTER ? 1 : (i64)t.edge_len[x];
+}
+
+__global__ void rm_lock_delta_kernel(RmTree t, const int* nodes, const int* gens, int B, int dir, RmLockScratch ls,
+                                     i64* out_delta) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  int x = rm_resolve(t, nodes[i], gens, i);
+  i64 delta = 0;
+  while (x > 0) {
+    const int r0 = t.lock_ref[x];
+    if (dir > 0) {
+      if (r0 == 0 && ls.first[x] == i) delta -= rm_value_len(t, x);
+    } else {
+      if (r0 == 1 && ls.first[x] == i) delta += rm_value_len(t, x);
+      if (r0 >= 2 && ls.cnt[x] >= r0) atomicExch(ls.flag, 1);   // a later op of the batch hits 1 -> 0
+    }
+    x = t.parent[x];
+  }
+  out_delta[i] = delta;
+}
+
+__global__ void rm_lock_apply_kernel(RmTree t, const int* nodes, const int* gens, int B, int dir, RmLockScratch ls,
+                                     const i64* out_delta) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  if (*ls.flag) return;
+  int x = rm_resolve(t, nodes[i], gens, i);
+  while (x > 0) {
+    const int par = t.parent[x];
+    if (ls.first[x] == i) {
+      const int r0 = t.lock_ref[x], c = ls.cnt[x];
+      int r1 = dir > 0 ? r0 + c : r0 - c;
+      if (dir < 0 && t.mode != RM_MODE_BASE && r1 < 0) r1 = 0;   // radix_mesh.py:175-177
+      t.lock_ref[x] = r1;
+    }
+    x = par;
+  }
+  const i64 d = out_delta[i];
+  if (d != 0) {
+    rm_add_i64(&t.ctr->evictable, d);
+    rm_add_i64(&t.ctr->protected_, -d);
+  }
+}
+
+__global__ void rm_lock_clear_kernel(RmTree t, const int* nodes, const int* gens, int B, RmLockScratch ls) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  int x = rm_resolve(t, nodes[i], gens, i);
+  while (x > 0) {
+    ls.cnt[x] = 0;
+    ls.first[x] = RM_INT_MAX;
+    x = t.parent[x];
+  }
+}
+
+// Exact fallback: the batch in order, one thread (only when several decrements of one batch
+// take the same node from >= 2 down to 0).
+__global__ void rm_lock_seq_kernel(RmTree t, const int* nodes, const int* gens, int B, int dir, RmLockScratch ls,
+                                   i64* out_delta) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  if (*ls.flag == 0) return;
+  *ls.flag = 0;
+  i64 ev = 0;
+  for (int i = 0; i < B; ++i) {
+    int x = rm_resolve(t, nodes[i], gens, i);
+    i64 delta = 0;
+    while (x > 0) {
+      int r = t.lock_ref[x];
+      if (dir > 0) {
+        if (r == 0) delta -= rm_value_len(t, x);
+        t.lock_ref[x] = r + 1;
+      } else {
+        if (r == 1) delta += rm_value_len(t, x);
+        if (t.mode == RM_MODE_BASE || r > 0) t.lock_ref[x] = r - 1;
+      }
+      x = t.parent[x];
+    }
+    out_delta[i] = delta;
+    ev += delta;
+  }
+  rm_add_i64(&t.ctr->evictable, ev);
+  rm_add_i64(&t.ctr->protected_, -ev);
+}
+
+int rm_launch_lock_g(rm_index* idx, const int* nodes, const int* gens, int B, int dir, i64* out_delta, cudaStream_t s) {
+  if (B <= 0) return RM_OK;
+  RmLockScratch ls = rm_lock_scratch(idx);
+  const int grid = (B + RM_MT_TPB - 1) / RM_MT_TPB;
+  RM_LAUNCH(rm_lock_mark_kernel, grid, RM_MT_TPB, s, idx->t, nodes, gens, B, ls);
+  RM_LAUNCH(rm_lock_delta_kernel, grid, RM_MT_TPB, s, idx->t, nodes, gens, B, dir, ls, out_delta);
+  RM_LAUNCH(rm_lock_apply_kernel, grid, RM_MT_TPB, s, idx->t, nodes, gens, B, dir, ls, out_delta);
+  RM_LAUNCH(rm_lock_clear_kernel, grid, RM_MT_TPB, s, idx->t, nodes, gens, B, ls);
+  RM_LAUNCH(rm_lock_seq_kernel, 1, 1, s, idx->t, nodes, gens, B, dir, ls, out_delta);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
+int rm_launch_lock(rm_index* idx, const int* nodes, int B, int dir, i64* out_delta, cudaStream_t s) {
+  return rm_launch_lock_g(idx, nodes, nullptr, B, dir, out_delta, s);
+}
+
+// ------------------------------------------------------------------ K6 eviction
+// Closed form of the heap loop: with one stamp per operation a parent's stamp is
+// never older than a child's, so leaves leave the heap in ascending (stamp, deeper first) order and
+// the evicted set is the shortest prefix of that order whose value lengths sum to >= num_tokens.
+__global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, u64* key, unsigned* val) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n) return;
+  u64 k = RM_NO_REQ;
+  if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0) {
+    u64 dmask = (1ull << depth_bits) - 1ull;
+    k = (t.stamp[x] << depth_bits) | (dmask - (u64)(unsigned)t.depth_end[x]);
+  }
+  key[x] = k;
+  val[x] = (unsigned)x;
+}
+
+// One block: walk the sorted candidates in chunks, prefix-sum their value lengths, stop at the first
+// position where the running total reaches num_tokens.  Writes the count to ctr->evict_n.
+__global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int n,
+                                    i64 num_tokens, int cap) {
+#ifdef RM_EMU
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  i64 run = 0;
+  int k = 0;
+  while (k < n && k < cap && run < num_tokens && skey[k] != RM_NO_REQ) {
+    run += t.edge_len[sval[k]];
+    ++k;
+  }
+  t.ctr->evict_n = k;
+#else
+  __shared__ i64 warp_tot[32];
+  __shared__ i64 carry_s;
+  __shared__ int cut_s;
+  if (threadIdx.x == 0) {
+    carry_s = 0;
+    cut_s = RM_INT_MAX;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int lim = min(n, cap);
+  for (int base = 0; base < lim; base += 1024) {
+    const i64 carry = carry_s;
+    const int j = base + threadIdx.x;
+    const bool ok = j < lim && skey[j] != RM_NO_REQ;
+    const i64 v = ok ? (i64)t.edge_len[sval[j]] : 0;
+    i64 inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      i64 o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) warp_tot[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+      i64 w = warp_tot[lane], winc = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        i64 o = __shfl_up_sync(0xffffffffu, winc, d);
+        if (lane >= d) winc += o;
+      }
+      warp_tot[lane] = winc - w;
+    }
+    __syncthreads();
+    const i64 incl = carry + warp_tot[wid] + inc;   // running total including candidate j
+    // the list ends at the first non-candidate; the cut falls after the first candidate whose
+    // running total reaches num_tokens
+    int mycut = RM_INT_MAX;
+    if (!ok) mycut = j;
+    else if (incl >= num_tokens) mycut = j + 1;
+    if (mycut != RM_INT_MAX) atomicMin(&cut_s, mycut);
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = incl;
+    const int cut = cut_s;
+    __syncthreads();
+    if (cut != RM_INT_MAX) break;
+  }
+  if (threadIdx.x == 0) t.ctr->evict_n = min(cut_s, lim);
+#endif
+}
+
+__global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sval, int* out_nodes, i64* out_offs,
+                                      int* out_lens) {
+  const int n = t.ctr->evict_n;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int x = (int)sval[k];
+  const int par = t.parent[x];
+  const i64 off = t.edge_off[x];
+  const int len = t.edge_len[x];
+  out_nodes[k] = x;
+  out_offs[k] = off;
+  out_lens[k] = len;
+  RmSlot s;
+  int sidx = rm_find<true>(t, rm_key(par, t.tok[off]), s);
+  if (sidx >= 0) *reinterpret_cast<volatile u64*>(&t.table[sidx].key) = RM_TOMB_KEY;
+  atomicSub(&t.nchild[par], 1);
+  t.parent[x] = -1;
+  t.edge_len[x] = 0;
+  // _delete_leaf: evictable_size_ -= len(node.key) (radix_cache.py:352)
+  rm_add_i64(&t.ctr->evictable, -(i64)len);
+  rm_add_i64(&t.ctr->n_nodes, (i64)-1);
+  u64 pos = atomicAdd(&t.ctr->free_tail, 1ull);
+  t.free_ids[pos % (u64)t.max_nodes] = x;
+}
+
+static int rm_bits_for(u64 v) {
+  int b = 1;
+  while ((v >> b) != 0 && b < 63) ++b;
+  return b;
+}
+
+int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
+                    int* out_n_h, cudaStream_t s) {
+  RmTree& t = idx->t;
+  RmScratch& sc = idx->sc;
+  idx->op_seq += 1;   // evict is one operation of the logical clock (it stamps nothing)
+  RmCounters c;
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  const int n = c.node_hwm;
+  *out_n_h = 0;
+  if (n <= 1 || num_tokens <= 0 || cap <= 0) return RM_OK;
+  const int depth_bits = idx->len_bits;
+  const int bits = rm_bits_for(idx->op_seq * 2 + 1) + depth_bits + 1;
+  RM_LAUNCH(rm_evict_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, sc.ev_key[0], sc.ev_val[0]);
+  const int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, bits, sc.ev_hist, s);
+#ifdef RM_EMU
+  RM_LAUNCH(rm_evict_cut_kernel, 1, 1, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, cap);
+#else
+  RM_LAUNCH(rm_evict_cut_kernel, 1, 1024, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, cap);
+#endif
+  // outputs are staged in the other ping-pong buffer (large enough: n entries of 8/4 bytes)
+  int* d_nodes = reinterpret_cast<int*>(sc.ev_val[w ^ 1]);
+  i64* d_offs = reinterpret_cast<i64*>(sc.ev_key[w ^ 1]);
+  int* d_lens = sc.ev_lens;
+  const int lim = min(n, cap);
+  RM_LAUNCH(rm_evict_apply_kernel, (lim + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, sc.ev_val[w], d_nodes, d_offs, d_lens);
+  RM_CUDA(cudaGetLastError());
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  const int k = c.evict_n;
+  if (k > 0) {
+    RM_CUDA(cudaMemcpyAsync(out_nodes_h, d_nodes, sizeof(int) * k, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(out_offs_h, d_offs, sizeof(i64) * k, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(out_lens_h, d_lens, sizeof(int) * k, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaStreamSynchronize(s));
+  }
+  *out_n_h = k;
+  return RM_OK;
+}
+
+// ------------------------------------------------------------------ K7 duplicate-node table scan
+__global__ void rm_dup_scan_kernel(RmTree t, int only_candidates, int cap, int* out, int* out_n) {
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > t.dup_mask) return;
+  u64 k = t.dup_key[i];
+  if (k == RM_EMPTY_KEY) return;
+  int parked = t.dup_parked[i];
+  int lk = parked >= 0 ? t.lock_ref[parked] : 0;
+  if (only_candidates && !(parked >= 0 && lk == 0)) return;   // radix_mesh.py:152-156
+  int slot = atomicAdd(out_n, 1);
+  if (slot >= cap) return;
+  out[slot * 4 + 0] = (int)(k >> 32);
+  out[slot * 4 + 1] = (int)(unsigned)(k & 0xffffffffu) - 1;
+  out[slot * 4 + 2] = parked;
+  out[slot * 4 + 3] = lk;
+}
+
+int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int* out_n_h, cudaStream_t s) {
+  RmTree& t = idx->t;
+  RmScratch& sc = idx->sc;
+  *out_n_h = 0;
+  if (cap <= 0) return RM_OK;
+  int dcap = (int)min((i64)cap, (i64)t.dup_mask + 1);
+  RM_CUDA(cudaMemsetAsync(sc.dup_out_n, 0, sizeof(int), s));
+  RM_LAUNCH(rm_dup_scan_kernel, (int)((t.dup_mask + RM_MT_TPB) / RM_MT_TPB), RM_MT_TPB, s, t, only_candidates, dcap, sc.dup_out, sc.dup_out_n);
+  RM_CUDA(cudaGetLastError());
+  int n = 0;
+  RM_CUDA(cudaMemcpyAsync(&n, sc.dup_out_n, sizeof(int), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  if (n > dcap) n = dcap;
+  if (n > 0) {
+    RM_CUDA(cudaMemcpyAsync(out_h, sc.dup_out, sizeof(int) * 4 * n, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaStreamSynchronize(s));
+  }
+  *out_n_h = n;
+  return RM_OK;
+}

@@ -1,0 +1,408 @@
+// K1 batched longest-prefix match, K3 deferred split apply, K2 value gather (sm_100a).
+//
+// Replaces RadixCache._match_prefix_helper / _key_match_page_size1 / _split_node
+// (radix_cache.py:252-294, 14-20) and RadixMesh._match_prefix_helper (radix_mesh.py:247-271).
+//
+// K1 is read-only on the tree structure: one group of G lanes walks one query.  Each hop is ONE
+// dependent 32-byte load (the child-table slot, which carries child id, edge length, edge offset and
+// owner rank); the probe for the NEXT hop is issued before the current edge's tokens are compared,
+// so edge compares sit off the critical path and the chain per query is `hops` slot latencies.
+// Partial edge matches in the splitting modes are recorded as (node, split point) requests; K3 sorts
+// them, creates each distinct upper node once and derives every segment's last-access stamp in closed
+// form so that the result equals the reference processing the batch query by query.
+#include "rm_internal.h"
+#include "rm_sort.cuh"
+
+#ifndef RM_EMU
+#define RM_MATCH_TPB 256
+#else
+#define RM_MATCH_TPB 64
+#endif
+
+struct RmRouteOut {
+  int* prefill;
+  int* decode;
+  unsigned char* err;
+};
+
+template <int G, bool SPLIT, bool ROUTER>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base, int len_bits,
+                int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
+                unsigned* __restrict__ req_val, RmRouteOut ro) {
+  RmGroup<G> g;
+  const int q = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (q >= B) return;
+  const i64 o0 = qoff[q];
+  const int L = (int)(qoff[q + 1] - o0);
+  const int* __restrict__ key = qtok + o0;
+  const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;   // stamp encoding: see rm_insert.cu
+
+  int node = 0, pos = 0;
+  u64 req = RM_NO_REQ;
+  // router pick state (radix_mesh.py:219-238), O(1) per hop
+  int cnt = 0, deepest = -1, last_prefill = -1;
+  bool bad_below = false;
+
+  // slot of the hop being examined, as two 16-byte halves
+  int4 sa, sb;
+  u64 want = 0;
+  unsigned si = 0;
+  bool have = L > 0;
+  if (have) {
+    want = rm_key(0, __ldg(key));
+    si = rm_hash(want, t.table_mask);
+    const int4* p = reinterpret_cast<const int4*>(t.table + si);
+    sa = __ldg(p);
+    sb = __ldg(p + 1);
+  }
+  while (have) {
+    // resolve the probe: linear probing past foreign keys (rare at load factor <= 0.5)
+    u64 k = ((u64)(unsigned)sa.y << 32) | (unsigned)sa.x;
+    while (k != want && k != RM_EMPTY_KEY) {
+      si = (si + 1) & t.table_mask;
+      const int4* p = reinterpret_cast<const int4*>(t.table + si);
+      sa = __ldg(p);
+      sb = __ldg(p + 1);
+      k = ((u64)(unsigned)sa.y << 32) | (unsigned)sa.x;
+    }
+    if (k != want) break;  // no child starts with this token
+    const int c = sa.z, elen = sa.w, crank = sb.z;
+    const i64 eoff = (i64)(((u64)(unsigned)sb.y << 32) | (unsigned)sb.x);
+    const int n = min(elen, L - pos);
+    // issue the next hop's probe now (speculative: only used if this edge matches in full)
+    const int npos = pos + elen;
+    const bool have_next = npos < L;
+    int4 na = sa, nb = sb;
+    u64 nwant = 0;
+    unsigned ni = 0;
+    if (have_next) {
+      nwant = rm_key(c, __ldg(key + npos));
+      ni = rm_hash(nwant, t.table_mask);
+      const int4* p = reinterpret_cast<const int4*>(t.table + ni);
+      na = __ldg(p);
+      nb = __ldg(p + 1);
+    }
+    // compare edge tokens 1..n-1 (token 0 is equal by construction of the table key)
+    int m = n;
+    {
+      const int* __restrict__ e = t.tok + eoff;
+      const int* __restrict__ kq = key + pos;
+      for (int base = 1; base < n; base += 4 * G) {
+        int i0 = base + g.lane, i1 = i0 + G, i2 = i1 + G, i3 = i2 + G;
+        int a0 = 0, b0 = 0, a1 = 0, b1 = 0, a2 = 0, b2 = 0, a3 = 0, b3 = 0;
+        if (i0 < n) { a0 = __ldg(e + i0); b0 = __ldg(kq + i0); }
+        if (i1 < n) { a1 = __ldg(e + i1); b1 = __ldg(kq + i1); }
+        if (i2 < n) { a2 = __ldg(e + i2); b2 = __ldg(kq + i2); }
+        if (i3 < n) { a3 = __ldg(e + i3); b3 = __ldg(kq + i3); }
+        unsigned m0 = g.ballot(a0 != b0), m1 = g.ballot(a1 != b1), m2 = g.ballot(a2 != b2), m3 = g.ballot(a3 != b3);
+        if (m0 | m1 | m2 | m3) {
+          int first = m0 ? (__ffs(m0) - 1) : m1 ? (G + __ffs(m1) - 1) : m2 ? (2 * G + __ffs(m2) - 1) : (3 * G + __ffs(m3) - 1);
+          m = base + first;
+          break;
+        }
+      }
+    }
+    const bool partial = m < elen;
+    if (SPLIT && partial) {
+      // the reference would split child c at m and return the new upper node (radix_cache.py:262-266)
+      pos += m;
+      req = ((u64)(unsigned)c << len_bits) | (u64)(unsigned)m;
+      break;
+    }
+    // child c is reached: stamp it (radix_cache.py:260 / radix_mesh.py:257); the max over the batch is
+    // the stamp the last query in order leaves behind
+    if (g.lane == 0) atomicMax(&t.stamp[c], seq);
+    if (ROUTER) {
+      ++cnt;
+      deepest = crank;
+      if (crank < t.n_prefill) {
+        last_prefill = crank;
+        bad_below = false;
+      } else if (crank >= t.n_prefill + t.n_decode) {
+        bad_below = true;
+      }
+    }
+    pos += m;
+    node = c;
+    if (partial || !have_next) break;
+    sa = na;
+    sb = nb;
+    want = nwant;
+    si = ni;
+  }
+  if (g.lane == 0) {
+    out_len[q] = pos;
+    out_node[q] = node;   // K3 overwrites this for queries that asked for a split
+    if (SPLIT) {
+      req_key[q] = req;
+      req_val[q] = (unsigned)q;
+    }
+    if (ROUTER) {
+      int pf = -1, dc = -1, er = 0;
+      if (cnt == 1) {
+        pf = deepest;
+      } else if (cnt > 1) {
+        if (deepest < t.n_prefill) {
+          pf = deepest;
+        } else if (bad_below || last_prefill < 0) {
+          er = 1;  // the reference asserts (radix_mesh.py:233-237)
+        } else {
+          pf = last_prefill;
+          dc = deepest;
+        }
+      }
+      ro.prefill[q] = pf;
+      ro.decode[q] = dc;
+      ro.err[q] = (unsigned char)er;
+    }
+  }
+}
+
+// K3: one group per edge that received split requests.  `skey` is sorted by (node, split point) and,
+// inside equal keys, by query index (the sort is stable), `sval` holds the query index.
+template <int G>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int B, int len_bits,
+                      u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
+                      int* __restrict__ uniq_pos) {
+  RmGroup<G> g;
+  const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (i >= B) return;
+  const u64 ki = skey[i];
+  if (ki == RM_NO_REQ) return;
+  const int c = (int)(ki >> len_bits);
+  if (i > 0) {
+    u64 kp = skey[i - 1];
+    if (kp != RM_NO_REQ && (int)(kp >> len_bits) == c) return;  // not the first request of its edge
+  }
+  const u64 pmask = (1ull << len_bits) - 1ull;
+  // pass 1 (forward): extent of the group, distinct split points, rank of each request's point
+  int e = i, U = 0;
+  for (int base = i;; base += G) {
+    int j = base + g.lane;
+    u64 kj = (j < B) ? skey[j] : RM_NO_REQ;
+    bool valid = kj != RM_NO_REQ && (int)(kj >> len_bits) == c;
+    unsigned vb = g.ballot(valid);
+    int nvalid = (vb == g.full()) ? G : (__ffs(~vb) - 1);
+    bool mine = g.lane < nvalid;
+    bool head = mine && (j == i || kj != skey[j - 1]);
+    unsigned hb = g.ballot(head);
+    if (mine) {
+      unsigned upto = (g.lane == 31) ? 0xffffffffu : ((2u << g.lane) - 1u);
+      int kk = U + __popc(hb & upto) - 1;
+      krank[j] = kk;
+      if (head) uniq_pos[i + kk] = j;
+    }
+    U += __popc(hb);
+    e = base + nvalid;
+    if (nvalid < G) break;
+  }
+  g.sync();
+  // pass 2 (backward): sufmax[j] = max op seq over requests j' >= j of this edge
+  {
+    u64 carry = 0;
+    for (int hi = e; hi > i; hi -= G) {
+      int j = hi - 1 - g.lane;
+      u64 v = (j >= i) ? (((seq_base + (u64)sval[j]) << 1) | 1ull) : 0ull;
+#pragma unroll
+      for (int d = 1; d < G; d <<= 1) {
+        u64 o = g.shfl_up(v, d);
+        if (g.lane >= d) v = (o > v) ? o : v;
+      }
+      v = (carry > v) ? carry : v;
+      if (j >= i) sufmax[j] = v;
+      carry = g.bcast(v, G - 1);
+    }
+  }
+  g.sync();
+  u64 apos = 0;
+  if (g.lane == 0) apos = rm_alloc_nodes(t, U);
+  apos = g.bcast(apos, 0);
+  if (apos == ~0ull) return;
+  const int par = t.parent[c];
+  const i64 off = t.edge_off[c];
+  const int len = t.edge_len[c];
+  const int dend = t.depth_end[c];
+  const int lk = t.lock_ref[c];
+  const int rk = t.rank[c];
+  const u64 st_c = t.stamp[c];
+  g.sync();
+  // pass 3: one upper node per distinct split point, chained parent -> u_0 -> ... -> u_{U-1} -> c
+  for (int kk = g.lane; kk < U; kk += G) {
+    const int j = uniq_pos[i + kk];
+    const int p = (int)(skey[j] & pmask);
+    const int jprev = kk > 0 ? uniq_pos[i + kk - 1] : -1;
+    const int a = kk > 0 ? (int)(skey[jprev] & pmask) : 0;
+    const int u = rm_free_id_at(t, apos + (u64)kk);
+    const int uprev = kk > 0 ? rm_free_id_at(t, apos + (u64)kk - 1) : par;
+    // stamp of segment [a, p): queries that went on past p, the query that created boundary a
+    // (it stamped the whole remainder of the edge before splitting it), and full-edge passers
+    u64 st = st_c;
+    if (sufmax[j] > st) st = sufmax[j];
+    if (kk > 0) {
+      u64 smin_prev = ((seq_base + (u64)sval[jprev]) << 1) | 1ull;
+      if (smin_prev > st) st = smin_prev;
+    }
+    t.parent[u] = uprev;
+    t.edge_off[u] = off + a;
+    t.edge_len[u] = p - a;
+    t.depth_end[u] = dend - len + p;
+    t.lock_ref[u] = lk;       // radix_cache.py:283
+    t.rank[u] = rk;
+    t.nchild[u] = 1;
+    t.gen[u] = 0;
+    t.parked[u] = -1;
+    t.stamp[u] = st;
+    atomicMax(&t.ctr->node_hwm, u + 1);
+    if (kk == 0) {
+      RmSlot s;
+      int sidx = rm_find<true>(t, rm_key(par, t.tok[off]), s);
+      if (sidx < 0) {
+        atomicMax(&t.ctr->err, (int)RM_E_INVALID);
+      } else {
+        t.table[sidx].child = u;
+        t.table[sidx].edge_len = p;
+      }
+    } else {
+      rm_table_insert(t, rm_key(uprev, t.tok[off + a]), u, p - a, off + a, rk);
+    }
+    if (kk == U - 1) {
+      rm_table_insert(t, rm_key(u, t.tok[off + p]), c, len - p, off + p, rk);
+      t.parent[c] = u;
+      t.edge_off[c] = off + p;
+      t.edge_len[c] = len - p;
+      u64 smin = ((seq_base + (u64)sval[j]) << 1) | 1ull;
+      t.stamp[c] = smin > st_c ? smin : st_c;
+    }
+  }
+  if (g.lane == 0) rm_add_i64(&t.ctr->n_nodes, (i64)U);
+  // pass 4: every request's last node is the upper node that ends at its split point
+  for (int j = i + g.lane; j < e; j += G) out_node[sval[j]] = rm_free_id_at(t, apos + (u64)krank[j]);
+}
+
+// K2: values along the matched path, written back to front by walking parent links from the last
+// node; depth_end gives each node's place in the output without a prefix sum.
+template <int G>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_gather_kernel(RmTree t, const int* __restrict__ nodes, const int* __restrict__ lens, const i64* __restrict__ out_off,
+                 int B, i64* __restrict__ out) {
+  RmGroup<G> g;
+  const int q = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (q >= B) return;
+  const int mlen = lens[q];
+  int node = nodes[q];
+  i64* __restrict__ dst = out + out_off[q];
+  while (node > 0) {
+    const int dend = t.depth_end[node];
+    const int elen = t.edge_len[node];
+    const i64 eoff = t.edge_off[node];
+    const int start = dend - elen;
+    const int cnt = min(elen, mlen - start);   // the last node may be matched only in part (no-split modes)
+    for (int x = g.lane; x < cnt; x += G) dst[start + x] = t.val[eoff + x];
+    node = t.parent[node];
+  }
+}
+
+static int rm_match_group() {
+#ifdef RM_EMU
+  return 1;
+#else
+  static int g = -1;
+  if (g < 0) {
+    const char* e = getenv("RM_MATCH_G");
+    g = e ? atoi(e) : 8;
+    if (g != 4 && g != 8 && g != 16 && g != 32) g = 8;
+  }
+  return g;
+#endif
+}
+
+template <bool SPLIT, bool ROUTER>
+static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offsets, int B, u64 seq_base, int* out_len,
+                              int* out_node, RmRouteOut ro, cudaStream_t s) {
+  const int G = rm_match_group();
+  const long long threads = (long long)B * G;
+  const int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
+#ifdef RM_EMU
+  auto k = rm_match_kernel<1, SPLIT, ROUTER>;
+  RM_LAUNCH(k, grid, RM_MATCH_TPB, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+            idx->sc.key[0], idx->sc.val[0], ro);
+#else
+#define RM_CASE(GG)                                                                                              \
+  case GG: {                                                                                                     \
+    auto k = rm_match_kernel<GG, SPLIT, ROUTER>;                                                                 \
+    RM_LAUNCH(k, grid, RM_MATCH_TPB, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node, \
+              idx->sc.key[0], idx->sc.val[0], ro);                                                               \
+  } break;
+  switch (G) {
+    RM_CASE(4)
+    RM_CASE(8)
+    RM_CASE(16)
+    RM_CASE(32)
+  }
+#undef RM_CASE
+#endif
+}
+
+#ifdef RM_EMU
+#define RM_WIDE_G 1
+#else
+#define RM_WIDE_G 32
+#endif
+
+int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B, int* out_len, int* out_node,
+                    cudaStream_t s) {
+  if (B <= 0) return RM_OK;
+  const u64 seq_base = idx->op_seq + 1;
+  idx->op_seq += (u64)B;
+  RmRouteOut ro = {nullptr, nullptr, nullptr};
+  const bool split = idx->cfg.mode == RM_MODE_BASE || idx->cfg.mode == RM_MODE_PREFILL;
+  if (!split) {
+    rm_match_dispatch<false, false>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+  }
+  rm_match_dispatch<true, false>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
+  RM_CUDA(cudaGetLastError());
+  // group the split requests by (node, split point); +1 bit keeps the "no request" marker last
+  RmScratch& sc = idx->sc;
+  const int bits = idx->node_bits + idx->len_bits + 1;
+  const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], B, bits, sc.hist, s);
+  RM_CUDA(cudaGetLastError());
+  const long long threads = (long long)B * RM_WIDE_G;
+  const int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
+  auto k3 = rm_split_apply_kernel<RM_WIDE_G>;
+  RM_LAUNCH(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
+            sc.krank, sc.uniq_pos);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
+int rm_launch_gather(rm_index* idx, const int* nodes, const int* lens, const i64* out_offsets, int B, i64* out_values,
+                     cudaStream_t s) {
+  if (B <= 0) return RM_OK;
+  const int G = RM_WIDE_G == 1 ? 1 : 8;
+  const long long threads = (long long)B * G;
+  const int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
+#ifdef RM_EMU
+  auto k = rm_gather_kernel<1>;
+#else
+  auto k = rm_gather_kernel<8>;
+#endif
+  RM_LAUNCH(k, grid, RM_MATCH_TPB, s, idx->t, nodes, lens, out_offsets, B, out_values);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
+// ROUTER-mode walk (never splits) that also evaluates the rank pick; used by rm_route.cu.
+int rm_launch_router_match(rm_index* idx, const int* tokens, const i64* offsets, int B, int* out_len, int* out_node,
+                           int* out_prefill, int* out_decode, unsigned char* out_err, cudaStream_t s) {
+  if (B <= 0) return RM_OK;
+  const u64 seq_base = idx->op_seq + 1;
+  idx->op_seq += (u64)B;
+  RmRouteOut ro = {out_prefill, out_decode, out_err};
+  rm_match_dispatch<false, true>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}

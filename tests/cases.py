@@ -1,0 +1,147 @@
+"""Op-sequence scenarios shared by the host-emulation tests (CPU) and the GPU parity tests: each one
+drives a DeviceIndex through the C ABI and the CPU oracle side by side and requires identical results."""
+import random
+
+import numpy as np
+
+from oracle.radix_port import PortRadixCache
+from tests.parity import assert_same_tree, device_canonical, pack
+
+def run_sequence(make_index, seed, n_steps=30, vocab=3, maxlen=8, batch=6):
+    rnd = random.Random(seed)
+    ix = make_index(mode=0, max_nodes=4096, max_tokens=1 << 16, max_batch=64, max_key_len=64)
+    orc = PortRadixCache(1)
+    held_dev, held_orc = [], []
+    vc = 0
+    for step in range(n_steps):
+        kind = rnd.choice(["ins", "ins", "match", "match", "lock", "unlock", "evict"])
+        if kind == "ins":
+            keys = [[rnd.randrange(vocab) for _ in range(rnd.randrange(0, maxlen))] for _ in range(rnd.randrange(1, batch))]
+            vals = []
+            for k in keys:
+                vals.append(list(range(vc, vc + len(k))))
+                vc += len(k)
+            tk, offs = pack(keys)
+            vv, _ = pack(vals, np.int64)
+            got = ix.insert_host(tk, vv, offs)
+            exp = [orc.insert(list(k), np.asarray(v, dtype=np.int64)) for k, v in zip(keys, vals)]
+            assert got.tolist() == exp
+        elif kind == "match":
+            keys = [[rnd.randrange(vocab) for _ in range(rnd.randrange(1, maxlen))] for _ in range(rnd.randrange(1, batch))]
+            tk, offs = pack(keys)
+            ol = np.zeros(len(keys), np.int32)
+            on = np.zeros(len(keys), np.int32)
+            ix.match_host(tk, offs, ol, on)
+            exp = [orc.match_prefix(list(k)) for k in keys]
+            assert ol.tolist() == [len(m.indices) for m in exp]
+            # gather values
+            oo = np.zeros(len(keys) + 1, np.int64)
+            oo[1:] = np.cumsum(ol)
+            outv = np.zeros(int(oo[-1]) + 1, np.int64)
+            ix.gather(on, ol, oo, len(keys), outv)
+            for i, m in enumerate(exp):
+                assert outv[oo[i]:oo[i + 1]].tolist() == m.indices.tolist()
+            dev = device_canonical(ix)
+            inv = {v: k for k, v in dev["_ids"].items()}
+            inv[0] = ()
+            for i, m in enumerate(exp):
+                assert inv[int(on[i])] == tuple(orc.full_key(m.last_node)), f"last node of query {i}"
+                held_dev.append(int(on[i]))
+                held_orc.append(m.last_node)
+        elif kind == "lock" and held_dev:
+            sel = [rnd.randrange(len(held_dev)) for _ in range(rnd.randrange(1, 4))]
+            nodes = np.asarray([held_dev[i] for i in sel], np.int32)
+            out = np.zeros(len(sel), np.int64)
+            ix.lock(nodes, None, len(sel), +1, out)
+            exp = [orc.inc_lock_ref(held_orc[i]) for i in sel]
+            assert out.tolist() == exp
+            for i in sel:
+                held_dev.append(held_dev[i])
+                held_orc.append(held_orc[i])
+        elif kind == "unlock" and held_dev:
+            sel = [i for i in {rnd.randrange(len(held_dev)) for _ in range(3)}
+                   if held_orc[i].lock_ref > 0 and held_orc[i] is not orc.root]
+            # keep the oracle's lock_refs non-negative: at most lock_ref decrements per node path
+            ok = []
+            budget = {}
+            for i in sel:
+                n = held_orc[i]
+                path = []
+                while n is not orc.root:
+                    path.append(n)
+                    n = n.parent
+                if all(budget.get(id(p), p.lock_ref) > 0 for p in path):
+                    for p in path:
+                        budget[id(p)] = budget.get(id(p), p.lock_ref) - 1
+                    ok.append(i)
+            if ok:
+                nodes = np.asarray([held_dev[i] for i in ok], np.int32)
+                out = np.zeros(len(ok), np.int64)
+                ix.lock(nodes, None, len(ok), -1, out)
+                exp = [orc.dec_lock_ref(held_orc[i]) for i in ok]
+                assert out.tolist() == exp
+        elif kind == "evict":
+            n = rnd.randrange(0, 12)
+            before = len(orc.freed)
+            orc.evict(n)
+            nodes, offs, lens = ix.evict(n)
+            got = [ix.read_arena(int(o), int(l))[1].tolist() for o, l in zip(offs, lens)]
+            assert got == orc.freed[before:]
+            # evicted handles are dead on both sides
+            dead = set(int(x) for x in nodes)
+            keep = [i for i in range(len(held_dev)) if held_dev[i] not in dead]
+            held_dev = [held_dev[i] for i in keep]
+            held_orc = [held_orc[i] for i in keep]
+        ix.check_device_error()
+        assert_same_tree(device_canonical(ix), orc.canonical())
+    ix.close()
+
+
+
+def run_split_evict(make_index, seed):
+    """Many queries of one batch split the same long edges; the stamps K3 derives in closed form must
+    reproduce the reference's query-by-query stamps, which the full eviction order exposes."""
+    rnd = random.Random(seed)
+    ix = make_index(mode=0, max_nodes=4096, max_tokens=1 << 16, max_batch=128, max_key_len=64)
+    orc = PortRadixCache(1)
+    docs = [[rnd.randrange(2) for _ in range(rnd.randrange(10, 40))] for _ in range(rnd.randrange(1, 4))]
+    vc = 0
+    for rounds in range(rnd.randrange(1, 4)):
+        keys = [list(d) for d in docs if rnd.random() < 0.8] or [list(docs[0])]
+        vals = []
+        for k in keys:
+            vals.append(list(range(vc, vc + len(k))))
+            vc += len(k)
+        tk, offs = pack(keys)
+        vv, _ = pack(vals, np.int64)
+        got = ix.insert_host(tk, vv, offs)
+        assert got.tolist() == [orc.insert(list(k), np.asarray(v, dtype=np.int64)) for k, v in zip(keys, vals)]
+        qs = []
+        for _ in range(rnd.randrange(5, 100)):
+            d = rnd.choice(docs)
+            cut = rnd.randrange(1, len(d) + 1)
+            qs.append(d[:cut] + [rnd.randrange(2, 4) for _ in range(rnd.randrange(0, 3))])
+        tk, offs = pack(qs)
+        ol = np.zeros(len(qs), np.int32)
+        on = np.zeros(len(qs), np.int32)
+        ix.match_host(tk, offs, ol, on)
+        exp = [orc.match_prefix(list(k)) for k in qs]
+        assert ol.tolist() == [len(m.indices) for m in exp]
+        dev = device_canonical(ix)
+        inv = {v: k for k, v in dev["_ids"].items()}
+        inv[0] = ()
+        for i, m in enumerate(exp):
+            assert inv[int(on[i])] == tuple(orc.full_key(m.last_node))
+        assert_same_tree(dev, orc.canonical())
+        # extend some docs so later rounds split fresh edges
+        docs = [d + [rnd.randrange(2) for _ in range(rnd.randrange(0, 12))] for d in docs]
+    while orc.canonical()["nodes"]:
+        n = rnd.randrange(1, 9)
+        before = len(orc.freed)
+        orc.evict(n)
+        _, offs, lens = ix.evict(n)
+        got = [ix.read_arena(int(o), int(l))[1].tolist() for o, l in zip(offs, lens)]
+        assert got == orc.freed[before:]
+        assert_same_tree(device_canonical(ix), orc.canonical())
+    ix.check_device_error()
+    ix.close()

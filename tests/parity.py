@@ -1,0 +1,91 @@
+"""Shared parity helpers: canonical views of a device index and of the oracle, workloads."""
+import numpy as np
+
+
+def device_canonical(ix, with_stamps=True, mesh=False):
+    """Canonical dump of a DeviceIndex (same row shape as oracle canonical())."""
+    d = ix.dump()
+    s = ix.sizes()
+    n = d["n"]
+    used = int(s.arena_used)
+    tok, val = ix.read_arena(0, used) if used else (np.zeros(0, np.int32), np.zeros(0, np.int64))
+    full = {0: ()}
+    alive = [x for x in range(1, n) if d["parent"][x] >= 0 and d["gen"][x] >= 0]
+
+    def fk(x):
+        if x in full:
+            return full[x]
+        chain = []
+        y = x
+        while y not in full:
+            chain.append(y)
+            y = int(d["parent"][y])
+        base = full[y]
+        for z in reversed(chain):
+            o, l = int(d["edge_off"][z]), int(d["edge_len"][z])
+            base = base + tuple(int(t) for t in tok[o:o + l])
+            full[z] = base
+        return full[x]
+
+    rows = []
+    for x in alive:
+        o, l = int(d["edge_off"][x]), int(d["edge_len"][x])
+        v = tuple(int(t) for t in val[o:o + l]) if val is not None else ()
+        row = (fk(x), l, v, int(d["rank"][x]), int(d["lock_ref"][x]))
+        if not mesh:
+            row = row + (int(d["stamp"][x]) >> 1,)   # 2*op (+1): compare the operation only
+        rows.append(row)
+    rows.sort()
+    out = {"nodes": rows, "evictable": int(s.evictable), "protected": int(s.protected_)}
+    out["_ids"] = {fk(x): x for x in alive}
+    out["_dump"] = d
+    return out
+
+
+def rank_stamps(rows):
+    """Replace the stamp column (last) by its dense rank: only the order matters (eviction)."""
+    if rows and rows[0][-1] >= (1 << 20):          # oracle stamps: (op << 20) + k
+        rows = [r[:-1] + (r[-1] >> 20,) for r in rows]
+    stamps = sorted({r[-1] for r in rows})
+    pos = {s: i for i, s in enumerate(stamps)}
+    return [r[:-1] + (pos[r[-1]],) for r in rows]
+
+
+def assert_same_tree(dev, orc, stamps=True):
+    a, b = dev["nodes"], orc["nodes"]
+    if stamps:
+        a, b = rank_stamps(a), rank_stamps(b)
+    else:
+        a, b = [r[:5] for r in a], [r[:5] for r in b]
+    assert len(a) == len(b), f"node count {len(a)} != {len(b)}"
+    for x, y in zip(a, b):
+        assert x == y, f"node differs:\n dev {x}\n orc {y}"
+    assert dev["evictable"] == orc["evictable"], (dev["evictable"], orc["evictable"])
+    assert dev["protected"] == orc["protected"], (dev["protected"], orc["protected"])
+
+
+def pack(keys, dtype=np.int32):
+    """list of lists -> (flat, offsets[int64])"""
+    offs = np.zeros(len(keys) + 1, dtype=np.int64)
+    for i, k in enumerate(keys):
+        offs[i + 1] = offs[i] + len(k)
+    flat = np.zeros(int(offs[-1]), dtype=dtype)
+    for i, k in enumerate(keys):
+        flat[offs[i]:offs[i + 1]] = k
+    return flat, offs
+
+
+def zipf_prefix(seed, n_docs, n_seq, L, s=1.1, vocab=32000, docs=None):
+    """SURVEY.md 8d generator: sequences = docs[d][:cut] ++ fresh random tail, d ~ Zipf(s)."""
+    rng = np.random.default_rng(seed)
+    if docs is None:
+        docs = np.random.default_rng(seed ^ 0x5EED).integers(0, vocab, (n_docs, L), dtype=np.int32)
+    w = 1.0 / np.arange(1, n_docs + 1) ** s
+    w /= w.sum()
+    d = rng.choice(n_docs, size=n_seq, p=w)
+    cut = rng.integers(L // 8, L + 1, size=n_seq)
+    out = rng.integers(0, vocab, (n_seq, L), dtype=np.int32)
+    cols = np.arange(L)[None, :]
+    mask = cols < cut[:, None]
+    out[mask] = docs[d][mask]
+    return out, docs
