@@ -183,6 +183,17 @@ int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, 
 /* Read `n` tokens / values of the edge arenas starting at token offset `off` into HOST buffers. */
 int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream);
 
+/*
+ * Measurement aids (no counterpart in the reference, which has no instrumentation).
+ * rm_launch_count: kernels this library has launched in this process.
+ * rm_profile(idx, 1): record a CUDA-event pair around the walk kernel (K1) of every following
+ * rm_match_batch; rm_profile_read returns the summed device time of those kernels and their count,
+ * and clears the record (at most 256 batches are kept).  Synchronises.
+ */
+unsigned long long rm_launch_count(void);
+int rm_profile(rm_index* idx, int enable);
+int rm_profile_read(rm_index* idx, double* walk_ms_h, int* n_h);
+
 #ifdef __cplusplus
 }
 #endif

@@ -135,6 +135,7 @@ class PortRadixCache:
         self.clock = clock or LogicalClock()
         self.free_hook = free_hook          # allocator.free stand-in (radix_cache.py:195)
         self.freed: List[list] = []
+        self.hops = 0
         self.reset()
 
     # -- helpers -----------------------------------------------------------
@@ -262,6 +263,7 @@ class PortRadixCache:
         while len(key) > 0 and ck in node.children:
             child = node.children[ck]
             child.stamp = self.clock.now()
+            self.hops += 1          # instrumentation only (roofline bytes per lookup)
             p = self._lcp(child.key, key)
             if p < len(child.key):
                 upper = self._split(child, p)

@@ -59,6 +59,9 @@ _PROTOS = {
     "rm_sizes": (C.c_int, [_P, C.POINTER(RmSizes), _P]),
     "rm_dump": (C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "rm_read_arena": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
+    "rm_launch_count": (C.c_uint64, []),
+    "rm_profile": (C.c_int, [_P, C.c_int]),
+    "rm_profile_read": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
 }
 EXPORTS = tuple(_PROTOS)
 
@@ -256,6 +259,14 @@ class DeviceIndex:
                                          ptr(a["nchild"]), ptr(a["gen"]), ptr(a["parked"]), C.addressof(out_n), self._s()))
         a["n"] = n
         return a
+
+    def profile(self, enable: bool) -> None:
+        self._check(self.lib.rm_profile(self._h, 1 if enable else 0))
+
+    def profile_read(self):
+        ms, n = C.c_double(0.0), C.c_int(0)
+        self._check(self.lib.rm_profile_read(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def read_arena(self, off: int, n: int, values: bool = True):
         tok = np.zeros(n, np.int32)

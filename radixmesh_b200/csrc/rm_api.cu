@@ -9,6 +9,9 @@
 thread_local rm_emu_dim3 threadIdx, blockIdx, blockDim, gridDim;
 #endif
 
+#ifndef RM_EMU
+unsigned long long g_rm_launches = 0;
+#endif
 static thread_local char g_err[512] = "";
 
 void rm_set_error(const char* fmt, ...) {
@@ -38,6 +41,48 @@ const char* rm_version(void) {
 #else
   return "radixmesh_b200 0.1 (sm_100a)";
 #endif
+}
+
+unsigned long long rm_launch_count(void) {
+#ifdef RM_EMU
+  return 0;
+#else
+  return g_rm_launches;
+#endif
+}
+
+int rm_profile(rm_index* idx, int enable) {
+  if (!idx) return RM_E_INVALID;
+#ifndef RM_EMU
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  if (enable && !idx->prof_ev[0]) {
+    for (int i = 0; i < RM_PROF_EVENTS; ++i) RM_CUDA(cudaEventCreate(&idx->prof_ev[i]));
+  }
+  idx->prof_on = enable ? 1 : 0;
+  idx->prof_n = 0;
+#endif
+  return RM_OK;
+}
+
+int rm_profile_read(rm_index* idx, double* walk_ms_h, int* n_h) {
+  if (!idx || !walk_ms_h || !n_h) return RM_E_INVALID;
+  *walk_ms_h = 0.0;
+  *n_h = 0;
+#ifndef RM_EMU
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  const int n = idx->prof_n < RM_PROF_EVENTS / 2 ? idx->prof_n : RM_PROF_EVENTS / 2;
+  double tot = 0.0;
+  for (int i = 0; i < n; ++i) {
+    RM_CUDA(cudaEventSynchronize(idx->prof_ev[2 * i + 1]));
+    float ms = 0.f;
+    RM_CUDA(cudaEventElapsedTime(&ms, idx->prof_ev[2 * i], idx->prof_ev[2 * i + 1]));
+    tot += ms;
+  }
+  *walk_ms_h = tot;
+  *n_h = n;
+  idx->prof_n = 0;
+#endif
+  return RM_OK;
 }
 
 int rm_destroy(rm_index* idx) {

@@ -15,7 +15,12 @@
 #define RM_G_DEFAULT 1
 #else
 #include <cuda_runtime.h>
-#define RM_LAUNCH(kernel, grid, block, stream, ...) kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
+extern unsigned long long g_rm_launches;   // kernels launched by this library (rm_launch_count)
+#define RM_LAUNCH(kernel, grid, block, stream, ...) \
+  do {                                               \
+    ++g_rm_launches;                                 \
+    kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__); \
+  } while (0)
 #endif
 #include "../../include/radixmesh_b200.h"
 

@@ -363,7 +363,17 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
     RM_CUDA(cudaGetLastError());
     return RM_OK;
   }
+#ifndef RM_EMU
+  const bool prof = idx->prof_on && idx->prof_n < RM_PROF_EVENTS / 2;
+  if (prof) cudaEventRecord(idx->prof_ev[2 * idx->prof_n], s);
+#endif
   rm_match_dispatch<true, false>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
+#ifndef RM_EMU
+  if (prof) {
+    cudaEventRecord(idx->prof_ev[2 * idx->prof_n + 1], s);
+    ++idx->prof_n;
+  }
+#endif
   RM_CUDA(cudaGetLastError());
   // group the split requests by (node, split point); +1 bit keeps the "no request" marker last
   RmScratch& sc = idx->sc;

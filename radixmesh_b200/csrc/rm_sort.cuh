@@ -141,9 +141,9 @@ static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, in
     unsigned* vi = cur ? v1 : v0;
     u64* ko = cur ? k0 : k1;
     unsigned* vo = cur ? v0 : v1;
-    rm_sort_hist_kernel<<<nb, RM_SORT_TPB, 0, s>>>(ki, n, p * 8, hist, nb);
-    rm_scan_u32_kernel<<<1, 1024, 0, s>>>(hist, 256 * nb);
-    rm_sort_scatter_kernel<<<nb, RM_SORT_TPB, 0, s>>>(ki, vi, ko, vo, n, p * 8, hist, nb);
+    RM_LAUNCH(rm_sort_hist_kernel, nb, RM_SORT_TPB, s, ki, n, p * 8, hist, nb);
+    RM_LAUNCH(rm_scan_u32_kernel, 1, 1024, s, hist, 256 * nb);
+    RM_LAUNCH(rm_sort_scatter_kernel, nb, RM_SORT_TPB, s, ki, vi, ko, vo, n, p * 8, hist, nb);
     cur ^= 1;
   }
   return cur;

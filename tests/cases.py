@@ -37,8 +37,9 @@ def run_sequence(make_index, seed, n_steps=30, vocab=3, maxlen=8, batch=6):
             # gather values
             oo = np.zeros(len(keys) + 1, np.int64)
             oo[1:] = np.cumsum(ol)
-            outv = np.zeros(int(oo[-1]) + 1, np.int64)
-            ix.gather(on, ol, oo, len(keys), outv)
+            d_out = ix.be.empty(int(oo[-1]) + 1, np.int64)
+            ix.gather(ix.be.to_device(on), ix.be.to_device(ol), ix.be.to_device(oo), len(keys), d_out)
+            outv = ix.be.to_host(d_out)
             for i, m in enumerate(exp):
                 assert outv[oo[i]:oo[i + 1]].tolist() == m.indices.tolist()
             dev = device_canonical(ix)
@@ -51,8 +52,9 @@ def run_sequence(make_index, seed, n_steps=30, vocab=3, maxlen=8, batch=6):
         elif kind == "lock" and held_dev:
             sel = [rnd.randrange(len(held_dev)) for _ in range(rnd.randrange(1, 4))]
             nodes = np.asarray([held_dev[i] for i in sel], np.int32)
-            out = np.zeros(len(sel), np.int64)
-            ix.lock(nodes, None, len(sel), +1, out)
+            d_out = ix.be.empty(len(sel), np.int64)
+            ix.lock(ix.be.to_device(nodes), None, len(sel), +1, d_out)
+            out = ix.be.to_host(d_out)
             exp = [orc.inc_lock_ref(held_orc[i]) for i in sel]
             assert out.tolist() == exp
             for i in sel:
@@ -76,8 +78,9 @@ def run_sequence(make_index, seed, n_steps=30, vocab=3, maxlen=8, batch=6):
                     ok.append(i)
             if ok:
                 nodes = np.asarray([held_dev[i] for i in ok], np.int32)
-                out = np.zeros(len(ok), np.int64)
-                ix.lock(nodes, None, len(ok), -1, out)
+                d_out = ix.be.empty(len(ok), np.int64)
+                ix.lock(ix.be.to_device(nodes), None, len(ok), -1, d_out)
+                out = ix.be.to_host(d_out)
                 exp = [orc.dec_lock_ref(held_orc[i]) for i in ok]
                 assert out.tolist() == exp
         elif kind == "evict":

@@ -1,0 +1,97 @@
+"""GPU parity tests proper: the CUDA library through its C ABI against the CPU oracle (RadixCache semantics)."""
+import numpy as np
+import pytest
+
+from tests import cases
+from tests.parity import assert_same_tree, device_canonical, pack, zipf_prefix
+
+pytestmark = pytest.mark.gpu
+
+
+def make_index(**kw):
+    from radixmesh_b200 import capi
+    return capi.DeviceIndex(**kw)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_gpu_random_sequences(seed):
+    cases.run_sequence(make_index, seed)
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_gpu_longer_keys(seed):
+    cases.run_sequence(make_index, 1000 + seed, n_steps=25, vocab=4, maxlen=40, batch=12)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_gpu_batched_match_splits_then_evict_order(seed):
+    cases.run_split_evict(make_index, seed)
+
+
+@pytest.mark.parametrize("group", [4, 8, 16, 32])
+def test_gpu_zipf_match_all_group_widths(group, monkeypatch):
+    """Zipf shared-prefix workload at reduced size, device-pointer entry points, every
+    lanes-per-query variant of the match kernel: lengths, last nodes, values and final tree."""
+    import subprocess
+    import sys
+    # the group width is read once per process: run the check in a child with RM_MATCH_G set
+    code = ("import sys; sys.path.insert(0, '.'); from tests.test_gpu_base import zipf_check; "
+            "zipf_check(seed=5, n_docs=64, L=96, n_ins=600, n_q=3000)")
+    import os
+    env = dict(os.environ, RM_MATCH_G=str(group))
+    subprocess.run([sys.executable, "-c", code], check=True, env=env,
+                   cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def zipf_check(seed, n_docs, L, n_ins, n_q, batch=4096):
+    import torch
+    from oracle.radix_port import PortRadixCache
+    ix = make_index(mode=0, max_nodes=1 << 21, max_tokens=1 << 26, max_batch=1 << 16, max_key_len=max(L, 1024))
+    orc = PortRadixCache(1)
+    ins, docs = zipf_prefix(seed, n_docs, n_ins, L)
+    qs, _ = zipf_prefix(seed + 1, n_docs, n_q, L, docs=docs)
+    dev = torch.device("cuda")
+    vc = 0
+    for b0 in range(0, n_ins, batch):
+        chunk = ins[b0:b0 + batch]
+        n = len(chunk)
+        tok = torch.from_numpy(chunk.reshape(-1)).to(dev)
+        val = torch.arange(vc, vc + n * L, dtype=torch.int64, device=dev)
+        offs = torch.arange(0, (n + 1) * L, L, dtype=torch.int64, device=dev)
+        out = torch.empty(n, dtype=torch.int32, device=dev)
+        ix.insert(tok, val, offs, None, n, out)
+        exp = [orc.insert(row.tolist(), np.arange(vc + i * L, vc + (i + 1) * L, dtype=np.int64)) for i, row in enumerate(chunk)]
+        assert out.cpu().tolist() == exp
+        vc += n * L
+    ix.check_device_error()
+    assert_same_tree(device_canonical(ix), orc.canonical())
+    for b0 in range(0, n_q, batch):
+        chunk = qs[b0:b0 + batch]
+        n = len(chunk)
+        tok = torch.from_numpy(chunk.reshape(-1)).to(dev)
+        offs = torch.arange(0, (n + 1) * L, L, dtype=torch.int64, device=dev)
+        ol = torch.empty(n, dtype=torch.int32, device=dev)
+        on = torch.empty(n, dtype=torch.int32, device=dev)
+        ix.match(tok, offs, n, ol, on)
+        exp = [orc.match_prefix(row.tolist()) for row in chunk]
+        assert ol.cpu().tolist() == [len(m.indices) for m in exp]
+        oo = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+        oo[1:] = torch.cumsum(ol.to(torch.int64), 0)
+        vals = torch.empty(int(oo[-1].item()) + 1, dtype=torch.int64, device=dev)
+        ix.gather(on, ol, oo, n, vals)
+        hv, ho = vals.cpu().numpy(), oo.cpu().numpy()
+        d = device_canonical(ix)
+        inv = {v: k for k, v in d["_ids"].items()}
+        inv[0] = ()
+        onh = on.cpu().tolist()
+        for i, m in enumerate(exp):
+            assert hv[ho[i]:ho[i + 1]].tolist() == m.indices.tolist()
+            assert inv[onh[i]] == tuple(orc.full_key(m.last_node))
+    ix.check_device_error()
+    assert_same_tree(device_canonical(ix), orc.canonical())
+    ix.close()
+
+
+def test_gpu_zipf_c2_reduced():
+    """configs[1] shape (Zipf, 4096 docs, L=256) at a size the oracle finishes in seconds."""
+    zipf_check(seed=0, n_docs=4096, L=256, n_ins=6000, n_q=8192)
