@@ -99,6 +99,24 @@ int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offs
                      int32_t* out_len_h, int32_t* out_node_h, void* stream);
 
 /*
+ * rm_match_batch for callers that must not allocate device memory.  No counterpart in the reference
+ * (a Python dict tree has no device scratch).  Same arguments and results as rm_match_batch, but the
+ * scratch of the match pipeline (split-request arrays, sort buffers, histograms) lives in a fixed
+ * 192 KiB array inside the library image instead of memory sized by rm_config.max_batch, so an index
+ * created with max_batch = 1 can still serve batches here.  For engines that gave all of HBM to their
+ * KV pool (a later cudaMalloc can fail), for request-path threads that cannot take cudaMalloc's
+ * device-wide synchronisation, and for code running while a stream is captured.
+ *   - at most 4096 queries per call, else RM_E_TOO_LARGE;
+ *   - makes no cudaMalloc / cudaFree / allocating call;
+ *   - the first call on each device looks the array's address up (cudaGetSymbolAddress): make it
+ *     before any stream capture starts;
+ *   - every GPU that loads the library holds the 192 KiB until exit; all calls on a device share
+ *     it, so calls that overlap on the GPU race: keep them on one stream or order them.
+ */
+int rm_match_batch_static(rm_index* idx, const int32_t* tokens, const int64_t* offsets, int32_t B,
+                          int32_t* out_len, int32_t* out_node, void* stream);
+
+/*
  * torch.cat of the values along the matched path (radix_cache.py:154-157, radix_mesh.py:209-213):
  * for query q writes out_len[q] int64 KV indices to out_values[out_offsets[q] ...].
  * `nodes`/`lens` are rm_match_batch's outputs (call before any later mutation of the tree).

@@ -47,6 +47,7 @@ _PROTOS = {
     "rm_reset": (C.c_int, [_P, _P]),
     "rm_match_batch": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P]),
     "rm_match_batch_h": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P]),
+    "rm_match_batch_static": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P]),
     "rm_gather_values": (C.c_int, [_P, _P, _P, _P, C.c_int32, _P, _P]),
     "rm_insert_batch": (C.c_int, [_P, _P, _P, _P, _P, C.c_int32, _P, _P]),
     "rm_insert_batch_h": (C.c_int, [_P, _P, _P, _P, _P, C.c_int32, _P, _P]),
@@ -174,6 +175,11 @@ class DeviceIndex:
     def match(self, tokens, offsets, B, out_len, out_node) -> None:
         with self._mutex:
             self._check(self.lib.rm_match_batch(self._h, ptr(tokens), ptr(offsets), B, ptr(out_len), ptr(out_node), self._s()))
+
+    def match_static(self, tokens, offsets, B, out_len, out_node) -> None:
+        """rm_match_batch_static: same as match(), scratch in the library's fixed device array (<= 4096 queries)."""
+        with self._mutex:
+            self._check(self.lib.rm_match_batch_static(self._h, ptr(tokens), ptr(offsets), B, ptr(out_len), ptr(out_node), self._s()))
 
     def match_host(self, tokens_h: np.ndarray, offsets_h: np.ndarray, out_len_h: np.ndarray, out_node_h: np.ndarray) -> None:
         B = len(offsets_h) - 1
