@@ -227,7 +227,7 @@ def main():
     assert W >= 3 or os.environ.get("RM_BENCH_ALLOW_SHORT_WARMUP"), "timing rules: at least 3 warm-up steps"
 
     n_batches = 2 * (K + W)
-    max_nodes = int(wl["tree_nodes"] * 1.3) + n_batches * B + (1 << 16)
+    max_nodes = int(wl["tree_nodes"] * 1.3) + n_batches * (B // 2) + (1 << 16)   # ~15 % of first-sight queries add a node
     ix = capi.DeviceIndex(mode=capi.MODE_BASE, device=local, max_nodes=max_nodes,
                           max_tokens=int(wl["tree_nodes"] * L * 0.9) + (1 << 22), max_batch=B, max_key_len=max(L, 1024))
     docs = gen_docs(wl)
@@ -320,7 +320,7 @@ def main():
                 "vs_baseline": None, "dtype": "int32", "data": "synthetic",
                 "config": {"workload": wl["name"], "tree_nodes_start": nodes_start, "tree_nodes_end": nodes_end,
                            "inserts_to_build": n_ins, "build_s": round(build_s, 2), "batch": B, "query_len": L,
-                           "mode": "RadixCache (splitting match)", "lanes_per_query": int(os.environ.get("RM_MATCH_G", "8")),
+                           "mode": "RadixCache (splitting match)", "lanes_per_query": int(os.environ.get("RM_MATCH_G", "1")),
                            "l2": f"every step reads a fresh {B * L * 4 >> 20} MiB query batch ({(K + W) * B * L * 4 >> 20} MiB "
                                  "of distinct batches > 126 MB L2); the tree stays warm as in steady-state serving",
                            "parallelism": f"replica x{world}, query batches sharded, no collective"},

@@ -107,7 +107,7 @@ int rm_create(const rm_config* cfg, rm_index** out) {
     rm_set_error("rm_create: bad config (struct_size %d, expected %d)", cfg ? cfg->struct_size : -1, (int)sizeof(rm_config));
     return RM_E_INVALID;
   }
-  if (cfg->max_nodes < 2 || cfg->max_nodes > (1ll << 30) || cfg->max_tokens < 1 || cfg->max_batch < 1 ||
+  if (cfg->max_nodes < 2 || cfg->max_nodes > (1ll << 29) || cfg->max_tokens < 1 || cfg->max_batch < 1 ||
       cfg->max_key_len < 1 || cfg->mode < RM_MODE_BASE || cfg->mode > RM_MODE_ROUTER) {
     rm_set_error("rm_create: max_nodes/max_tokens/max_batch/max_key_len/mode out of range");
     return RM_E_INVALID;
@@ -124,6 +124,11 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   size_t dcap = 16;
   while (dcap < 2 * (size_t)(cfg->max_dups > 0 ? cfg->max_dups : 1)) dcap <<= 1;
   t.table_mask = (unsigned)(cap - 1);
+  {
+    int lg = 0;
+    while ((1ull << lg) < cap) ++lg;
+    t.table_shift = (unsigned)(32 - lg);
+  }
   t.dup_mask = (unsigned)(dcap - 1);
   t.max_nodes = (int)N;
   t.max_tokens = cfg->max_tokens;

@@ -59,6 +59,7 @@ struct RmTree {
   int max_key_len;   // bound on key / edge length (rm_config.max_key_len)
   RmSlot* table;
   unsigned table_mask;
+  unsigned table_shift;   // 32 - log2(capacity)
   int* parent;
   i64* edge_off;
   int* edge_len;
@@ -82,14 +83,13 @@ struct RmTree {
   unsigned dup_mask;
 };
 
-__device__ __forceinline__ unsigned rm_hash(u64 k, unsigned mask) {
-  k ^= k >> 32;
-  k *= 0x9E3779B97F4A7C15ull;
-  k ^= k >> 29;
-  k *= 0xBF58476D1CE4E5B9ull;
-  k ^= k >> 32;
-  return (unsigned)k & mask;
+// Table hash of (parent id, first token): Fibonacci-style multiplicative hash, top bits.  It sits on
+// the dependent chain of every hop of the walk, so it is two independent IMADs, an add and a shift
+// (`shift` = 32 - log2(table capacity)).
+__device__ __forceinline__ unsigned rm_hash2(unsigned parent, unsigned token, unsigned shift) {
+  return (parent * 0x9E3779B1u + token * 0x85EBCA77u) >> shift;
 }
+__device__ __forceinline__ unsigned rm_hash(u64 k, unsigned shift) { return rm_hash2((unsigned)(k >> 32), (unsigned)k, shift); }
 
 __device__ __forceinline__ u64 rm_key(int parent, int token) { return ((u64)(unsigned)parent << 32) | (unsigned)token; }
 
@@ -113,6 +113,7 @@ struct RmGroup {
 #ifdef RM_EMU
     return pred ? 1u : 0u;
 #else
+    if (G == 1) return pred ? 1u : 0u;   // one lane per unit of work: no cross-lane traffic at all
     unsigned b = __ballot_sync(mask, pred);
     return (G == 32) ? b : ((b & mask) >> ((threadIdx.x & 31) & ~(G - 1)));
 #endif
@@ -122,6 +123,7 @@ struct RmGroup {
 #ifdef RM_EMU
     return v;
 #else
+    if (G == 1) return v;
     return __shfl_sync(mask, v, src, G);
 #endif
   }
@@ -130,19 +132,61 @@ struct RmGroup {
 #ifdef RM_EMU
     return v;
 #else
+    if (G == 1) return v;
     return __shfl_up_sync(mask, v, d, G);
 #endif
   }
-  __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+  __device__ __forceinline__ void sync() const {
+    if (G > 1) __syncwarp(mask);
+  }
   static __device__ __forceinline__ unsigned full() { return (G == 32) ? 0xffffffffu : ((1u << G) - 1u); }
 };
+
+// ---- cache-policy loads (sm_100a).  The tree must stay L2 resident while every batch streams tens
+// of MB of query tokens through the same L2, so table slots are read with L2::evict_last (one
+// 256-bit LDG.E.ELL2 per slot) and query tokens with an evict-first policy.
+struct RmSlotRegs {
+  int4 a, b;   // a = {token, parent, child, edge_len}; b = {edge_off lo, edge_off hi, rank, pad}
+};
+__device__ __forceinline__ RmSlotRegs rm_ld_slot(const RmSlot* p) {
+  RmSlotRegs r;
+#ifdef RM_EMU
+  const int4* q = reinterpret_cast<const int4*>(p);
+  r.a = q[0];
+  r.b = q[1];
+#else
+  asm volatile("ld.global.nc.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.a.x), "=r"(r.a.y), "=r"(r.a.z), "=r"(r.a.w), "=r"(r.b.x), "=r"(r.b.y), "=r"(r.b.z), "=r"(r.b.w)
+               : "l"(p));
+#endif
+  return r;
+}
+__device__ __forceinline__ u64 rm_policy_evict_first() {
+#ifdef RM_EMU
+  return 0;
+#else
+  u64 pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+#endif
+}
+// query token: cached in L1 (a lane re-reads its own 32-byte sector for several hops), first out of L2
+__device__ __forceinline__ int rm_ld_query(const int* p, u64 pol) {
+#ifdef RM_EMU
+  return *p;
+#else
+  int v;
+  asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+  return v;
+#endif
+}
 
 // Probe the child table for `key`.  Returns the slot index or -1.  Every lane of the calling
 // group passes the same key, so the loads are broadcasts (one 32-byte sector per probe step).
 // COHERENT = true reads through L2 (ld.cg) for kernels that mutate the table themselves.
 template <bool COHERENT>
 __device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
-  unsigned i = rm_hash(key, t.table_mask);
+  unsigned i = rm_hash(key, t.table_shift);
   while (true) {
     const int4* p = reinterpret_cast<const int4*>(t.table + i);
     int4 a = COHERENT ? __ldcg(p) : __ldg(p);
@@ -175,7 +219,7 @@ __device__ __forceinline__ void rm_slot_store(RmSlot* s, u64 key, int child, int
 // Claim a free (empty or tombstoned) slot for `key` and fill it.  Caller guarantees the key is
 // not present.  One lane calls this.
 __device__ __forceinline__ void rm_table_insert(const RmTree& t, u64 key, int child, int edge_len, i64 edge_off, int rank) {
-  unsigned i = rm_hash(key, t.table_mask);
+  unsigned i = rm_hash(key, t.table_shift);
   while (true) {
     u64* kp = &t.table[i].key;
     u64 cur = *reinterpret_cast<volatile u64*>(kp);

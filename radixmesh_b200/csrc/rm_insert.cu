@@ -36,7 +36,7 @@ __global__ void rm_insert_keys_kernel(const int* __restrict__ tok, const i64* __
 // The tree node id stands for its full key (stable under splits: the lower half keeps the id).
 __device__ __forceinline__ void rm_dup_put(const RmTree& t, int node, int rank, int parked) {
   u64 key = ((u64)(unsigned)node << 32) | (unsigned)(rank + 1);
-  unsigned i = rm_hash(key, t.dup_mask);
+  unsigned i = (rm_hash2((unsigned)(key >> 32), (unsigned)key, 0) >> 7) & t.dup_mask;
   for (unsigned probes = 0; probes <= t.dup_mask; ++probes) {
     u64 cur = *reinterpret_cast<volatile u64*>(&t.dup_key[i]);
     if (cur == key) {

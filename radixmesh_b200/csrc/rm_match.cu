@@ -51,7 +51,7 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
   bool have = L > 0;
   if (have) {
     want = rm_key(0, __ldg(key));
-    si = rm_hash(want, t.table_mask);
+    si = rm_hash(want, t.table_shift);
     const int4* p = reinterpret_cast<const int4*>(t.table + si);
     sa = __ldg(p);
     sb = __ldg(p + 1);
@@ -78,7 +78,7 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
     unsigned ni = 0;
     if (have_next) {
       nwant = rm_key(c, __ldg(key + npos));
-      ni = rm_hash(nwant, t.table_mask);
+      ni = rm_hash(nwant, t.table_shift);
       const int4* p = reinterpret_cast<const int4*>(t.table + ni);
       na = __ldg(p);
       nb = __ldg(p + 1);
@@ -156,6 +156,193 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
       ro.decode[q] = dc;
       ro.err[q] = (unsigned char)er;
     }
+  }
+}
+
+// K1, lane-per-query form (the default).  ncu on the group form showed the walk is latency bound
+// (long-scoreboard stalls at three points of every hop: the slot, the query token that forms the next
+// key, the edge tokens) and that lanes idle while a neighbour compares a long edge (9.9 of 32 lanes
+// active per instruction; 89 % of the edges a Zipf workload walks are one token long).
+// Here every lane owns one query and the hop loop is software pipelined so that an iteration waits
+// ONCE: the slot of hop i+1 and the edge tokens of hop i are requested together in iteration i and
+// consumed together at the top of iteration i+1.  Hop i is only committed (stamped, position advanced)
+// after its edge has been verified; the probe for hop i+1 is speculative until then.  Long edges are
+// verified RM_CH tokens per iteration while the lane's other state stands still, so lanes on many
+// one-token edges and lanes on one long edge advance side by side.
+#define RM_CH 4
+template <bool SPLIT, bool ROUTER>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
+                    int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
+                    unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
+  const int q = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
+  if (q >= B) return;
+  const i64 o0 = qoff[q];
+  const int L = (int)(qoff[q + 1] - o0);
+  const int* __restrict__ key = qtok + o0;
+  const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
+  const RmSlot* __restrict__ table = t.table;
+  const unsigned tmask = t.table_mask, tshift = t.table_shift;
+  u64* __restrict__ stamp = t.stamp;
+  const u64 qpol = rm_policy_evict_first();
+
+  int node = 0, pos = 0;               // committed: `node` is matched in full through `pos`
+  u64 req = RM_NO_REQ;
+  int cnt = 0, deepest = -1, last_prefill = -1;
+  bool bad_below = false;
+
+  // probe in flight: the slot looked up with (want_par, want_tok)
+  RmSlotRegs S;
+  unsigned want_par = 0, want_tok = 0, si = 0;
+  // the two query tokens after want_tok (kept ahead of the walk so that after a one-token edge the
+  // next key needs no load on the dependent chain)
+  int g1 = 0, g2 = 0;
+  // pending multi-token edge: found by its first token, remaining tokens not verified yet
+  bool pend = false;
+  int pc = 0, pelen = 0, pn = 0, pdone = 0, prank = 0;
+  const int* __restrict__ pe = nullptr;
+  int ca[RM_CH], cb[RM_CH];            // chunk of edge / query tokens requested last iteration
+
+  bool have_probe = L > 0;
+  if (have_probe) {
+    want_tok = (unsigned)rm_ld_query(key, qpol);
+    si = rm_hash2(0u, want_tok, tshift);
+    S = rm_ld_slot(table + si);
+    if (1 < L) g1 = rm_ld_query(key + 1, qpol);
+    if (2 < L) g2 = rm_ld_query(key + 2, qpol);
+  }
+  while (true) {
+    if (pend) {
+      // ---- verify the chunk requested in the previous iteration
+      const int lim = min(pn - pdone, RM_CH);
+      int m = lim;
+#pragma unroll
+      for (int x = RM_CH - 1; x >= 0; --x)
+        if (x < lim && ca[x] != cb[x]) m = x;
+      pdone += m;
+      if (m == lim && pdone < pn) {
+        // long edge: request the next chunk, nothing else moves
+        const int* __restrict__ ee = pe + pdone;
+        const int* __restrict__ kk = key + pos + pdone;
+        const int l2 = pn - pdone;
+#pragma unroll
+        for (int x = 0; x < RM_CH; ++x) {
+          if (x < l2) {
+            ca[x] = __ldg(ee + x);
+            cb[x] = rm_ld_query(kk + x, qpol);
+          }
+        }
+        continue;
+      }
+      // ---- the edge is decided: pdone of its pelen tokens match
+      pend = false;
+      const bool partial = pdone < pelen;
+      if (SPLIT && partial) {
+        // the reference splits pc here and returns the new upper node (radix_cache.py:262-266); K3 does it
+        pos += pdone;
+        req = ((u64)(unsigned)pc << len_bits) | (u64)(unsigned)pdone;
+        break;
+      }
+      if (!(flags & 1)) atomicMax(stamp + pc, seq);      // radix_cache.py:260 / radix_mesh.py:257
+      if (ROUTER) {
+        ++cnt;
+        deepest = prank;
+        if (prank < t.n_prefill) {
+          last_prefill = prank;
+          bad_below = false;
+        } else if (prank >= t.n_prefill + t.n_decode) {
+          bad_below = true;
+        }
+      }
+      pos += pdone;
+      node = pc;
+      if (partial) break;
+    }
+    if (!have_probe) break;             // the query ended exactly at a node boundary
+    // ---- resolve the probe in flight (one step of linear probing per iteration)
+    if ((unsigned)S.a.x != want_tok || (unsigned)S.a.y != want_par) {
+      if ((S.a.x & S.a.y) == -1) break;  // empty slot: no child starts with this token
+      si = (si + 1) & tmask;
+      S = rm_ld_slot(table + si);
+      continue;
+    }
+    const int c = S.a.z, elen = S.a.w;
+    const int nxt = pos + elen;
+    if (elen == 1) {
+      // ---- one-token edge (89 % of the hops of a Zipf workload): matched by the key itself; commit now
+      if (!(flags & 1)) atomicMax(stamp + c, seq);
+      if (ROUTER) {
+        const int r = S.b.z;
+        ++cnt;
+        deepest = r;
+        if (r < t.n_prefill) {
+          last_prefill = r;
+          bad_below = false;
+        } else if (r >= t.n_prefill + t.n_decode) {
+          bad_below = true;
+        }
+      }
+      node = c;
+      pos = nxt;
+      have_probe = nxt < L;
+      want_tok = (unsigned)g1;
+      g1 = g2;
+    } else {
+      // ---- multi-token edge: verify it next iteration, keep walking speculatively
+      pc = c;
+      pelen = elen;
+      pn = min(elen, L - pos);
+      pdone = 1;                        // token 0 is equal by construction of the table key
+      pend = true;
+      if (ROUTER) prank = S.b.z;
+      pe = t.tok + (i64)(((u64)(unsigned)S.b.y << 32) | (unsigned)S.b.x);
+      have_probe = nxt < L;
+      if (have_probe) {
+        want_tok = (unsigned)rm_ld_query(key + nxt, qpol);
+        g1 = (nxt + 1 < L) ? rm_ld_query(key + nxt + 1, qpol) : 0;
+      }
+      const int* __restrict__ ee = pe + 1;
+      const int* __restrict__ kk = key + pos + 1;
+      const int l2 = pn - 1;
+#pragma unroll
+      for (int x = 0; x < RM_CH; ++x) {
+        if (x < l2) {
+          ca[x] = __ldg(ee + x);
+          cb[x] = rm_ld_query(kk + x, qpol);
+        }
+      }
+    }
+    if (have_probe) {
+      // request the next hop's slot (speculative while an edge is pending) and top up the look-ahead
+      g2 = (nxt + 2 < L) ? rm_ld_query(key + nxt + 2, qpol) : 0;
+      want_par = (unsigned)c;
+      si = rm_hash2((unsigned)c, want_tok, tshift);
+      S = rm_ld_slot(table + si);
+    }
+  }
+  out_len[q] = pos;
+  out_node[q] = node;
+  if (SPLIT) {
+    req_key[q] = req;
+    req_val[q] = (unsigned)q;
+  }
+  if (ROUTER) {
+    int pf = -1, dc = -1, er = 0;
+    if (cnt == 1) {
+      pf = deepest;
+    } else if (cnt > 1) {
+      if (deepest < t.n_prefill) {
+        pf = deepest;
+      } else if (bad_below || last_prefill < 0) {
+        er = 1;
+      } else {
+        pf = last_prefill;
+        dc = deepest;
+      }
+    }
+    ro.prefill[q] = pf;
+    ro.decode[q] = dc;
+    ro.err[q] = (unsigned char)er;
   }
 }
 
@@ -311,8 +498,8 @@ static int rm_match_group() {
   static int g = -1;
   if (g < 0) {
     const char* e = getenv("RM_MATCH_G");
-    g = e ? atoi(e) : 8;
-    if (g != 4 && g != 8 && g != 16 && g != 32) g = 8;
+    g = e ? atoi(e) : 1;
+    if (g != 1 && g != 2 && g != 4 && g != 8 && g != 16 && g != 32) g = 1;
   }
   return g;
 #endif
@@ -323,19 +510,42 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
                               int* out_node, RmRouteOut ro, cudaStream_t s) {
   const int G = rm_match_group();
   const long long threads = (long long)B * G;
-  const int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
+#ifndef RM_EMU
+  // a grid of B*G threads must still cover all 148 SMs several times: narrow groups get small blocks
+  const int tpb = threads >= 148LL * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (threads >= 148LL * 8 * 128 ? 128 : 64);
+#else
+  const int tpb = RM_MATCH_TPB;
+#endif
+  const int grid = (int)((threads + tpb - 1) / tpb);
 #ifdef RM_EMU
+  // the emulation build runs the lane-per-query kernel (the default on the GPU) unless RM_EMU_GROUP is set
+  static const bool emu_group = getenv("RM_EMU_GROUP") != nullptr;
+  if (!emu_group) {
+    auto kq = rm_match_lpq_kernel<SPLIT, ROUTER>;
+    RM_LAUNCH(kq, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+              idx->sc.key[0], idx->sc.val[0], ro, 0);
+    return;
+  }
   auto k = rm_match_kernel<1, SPLIT, ROUTER>;
-  RM_LAUNCH(k, grid, RM_MATCH_TPB, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+  RM_LAUNCH(k, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
             idx->sc.key[0], idx->sc.val[0], ro);
 #else
 #define RM_CASE(GG)                                                                                              \
   case GG: {                                                                                                     \
     auto k = rm_match_kernel<GG, SPLIT, ROUTER>;                                                                 \
-    RM_LAUNCH(k, grid, RM_MATCH_TPB, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node, \
+    RM_LAUNCH(k, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,          \
               idx->sc.key[0], idx->sc.val[0], ro);                                                               \
   } break;
   switch (G) {
+    case 1: {
+      auto k = rm_match_lpq_kernel<SPLIT, ROUTER>;
+      // RM_EXP_FLAGS: measurement experiments only (bit 0 = skip the stamp atomics; results then differ
+      // from the reference in eviction order, never use it outside a profiling run)
+      static const int exp_flags = getenv("RM_EXP_FLAGS") ? atoi(getenv("RM_EXP_FLAGS")) : 0;
+      RM_LAUNCH(k, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+                idx->sc.key[0], idx->sc.val[0], ro, exp_flags);
+    } break;
+    RM_CASE(2)
     RM_CASE(4)
     RM_CASE(8)
     RM_CASE(16)

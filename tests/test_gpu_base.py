@@ -28,7 +28,7 @@ def test_gpu_batched_match_splits_then_evict_order(seed):
     cases.run_split_evict(make_index, seed)
 
 
-@pytest.mark.parametrize("group", [4, 8, 16, 32])
+@pytest.mark.parametrize("group", [1, 2, 4, 8, 16, 32])
 def test_gpu_zipf_match_all_group_widths(group, monkeypatch):
     """Zipf shared-prefix workload at reduced size, device-pointer entry points, every
     lanes-per-query variant of the match kernel: lengths, last nodes, values and final tree."""
