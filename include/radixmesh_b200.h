@@ -102,7 +102,7 @@ int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offs
  * rm_match_batch for callers that must not allocate device memory.  No counterpart in the reference
  * (a Python dict tree has no device scratch).  Same arguments and results as rm_match_batch, but the
  * scratch of the match pipeline (split-request arrays, sort buffers, histograms) lives in a fixed
- * 192 KiB array inside the library image instead of memory sized by rm_config.max_batch, so an index
+ * 256 KiB array inside the library image instead of memory sized by rm_config.max_batch, so an index
  * created with max_batch = 1 can still serve batches here.  For engines that gave all of HBM to their
  * KV pool (a later cudaMalloc can fail), for request-path threads that cannot take cudaMalloc's
  * device-wide synchronisation, and for code running while a stream is captured.
@@ -110,7 +110,7 @@ int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offs
  *   - makes no cudaMalloc / cudaFree / allocating call;
  *   - the first call on each device looks the array's address up (cudaGetSymbolAddress): make it
  *     before any stream capture starts;
- *   - every GPU that loads the library holds the 192 KiB until exit; all calls on a device share
+ *   - every GPU that loads the library holds the 256 KiB until exit; all calls on a device share
  *     it, so calls that overlap on the GPU race: keep them on one stream or order them.
  */
 int rm_match_batch_static(rm_index* idx, const int32_t* tokens, const int64_t* offsets, int32_t B,

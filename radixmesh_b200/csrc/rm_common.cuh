@@ -206,13 +206,13 @@ __device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
 }
 
 __device__ __forceinline__ void rm_slot_store(RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank) {
-  // payload first, key last (a probe only trusts a slot whose key matches)
+  // payload first, key last.  No fence: inside one kernel only the warp that inserts a key looks it
+  // up again (program order + __syncwarp cover that); every other reader runs in a later kernel.
   s->child = child;
   s->edge_len = edge_len;
   s->edge_off = edge_off;
   s->rank = rank;
   s->pad = 0;
-  __threadfence();
   *reinterpret_cast<volatile u64*>(&s->key) = key;
 }
 

@@ -11,6 +11,7 @@ struct RmScratch {
   u64* sufmax;        // per sorted split request: max op seq of requests at or beyond it on the same edge
   int* krank;         // per sorted split request: rank of its split point among the edge's distinct points
   int* uniq_pos;      // per edge group: sorted positions of the distinct split points
+  unsigned* uniq_min; // per distinct split point: lowest query index that asked for it
   unsigned* hist;     // radix-sort histogram table
   size_t hist_words;
   // eviction (sized by max_nodes)

@@ -134,9 +134,10 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
   if (g.lane == 0) {
     out_len[q] = pos;
     out_node[q] = node;   // K3 overwrites this for queries that asked for a split
-    if (SPLIT) {
-      req_key[q] = req;
-      req_val[q] = (unsigned)q;
+    if (SPLIT && req != RM_NO_REQ) {
+      const int slot = atomicAdd(&t.ctr->n_req, 1);   // compact list of split requests
+      req_key[slot] = req;
+      req_val[slot] = (unsigned)q;
     }
     if (ROUTER) {
       int pf = -1, dc = -1, er = 0;
@@ -322,9 +323,10 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
   }
   out_len[q] = pos;
   out_node[q] = node;
-  if (SPLIT) {
-    req_key[q] = req;
-    req_val[q] = (unsigned)q;
+  if (SPLIT && req != RM_NO_REQ) {
+    const int slot = atomicAdd(&t.ctr->n_req, 1);     // compact list of split requests
+    req_key[slot] = req;
+    req_val[slot] = (unsigned)q;
   }
   if (ROUTER) {
     int pf = -1, dc = -1, er = 0;
@@ -350,11 +352,12 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
 // inside equal keys, by query index (the sort is stable), `sval` holds the query index.
 template <int G>
 __global__ void __launch_bounds__(RM_MATCH_TPB)
-rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int B, int len_bits,
+rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int Bmax, int len_bits,
                       u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
-                      int* __restrict__ uniq_pos) {
+                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min) {
   RmGroup<G> g;
   const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  const int B = min(t.ctr->n_req, Bmax);   // requests were appended compactly by K1, in no particular order
   if (i >= B) return;
   const u64 ki = skey[i];
   if (ki == RM_NO_REQ) return;
@@ -379,8 +382,14 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
       unsigned upto = (g.lane == 31) ? 0xffffffffu : ((2u << g.lane) - 1u);
       int kk = U + __popc(hb & upto) - 1;
       krank[j] = kk;
-      if (head) uniq_pos[i + kk] = j;
+      if (head) {
+        uniq_pos[i + kk] = j;
+        uniq_min[i + kk] = sval[j];
+      }
     }
+    g.sync();
+    // the query that created a boundary is the lowest-numbered one that asked for it
+    if (mine && !head) atomicMin(&uniq_min[i + krank[j]], sval[j]);
     U += __popc(hb);
     e = base + nvalid;
     if (nvalid < G) break;
@@ -428,7 +437,7 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
     u64 st = st_c;
     if (sufmax[j] > st) st = sufmax[j];
     if (kk > 0) {
-      u64 smin_prev = ((seq_base + (u64)sval[jprev]) << 1) | 1ull;
+      u64 smin_prev = ((seq_base + (u64)uniq_min[i + kk - 1]) << 1) | 1ull;
       if (smin_prev > st) st = smin_prev;
     }
     t.parent[u] = uprev;
@@ -459,7 +468,7 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
       t.parent[c] = u;
       t.edge_off[c] = off + p;
       t.edge_len[c] = len - p;
-      u64 smin = ((seq_base + (u64)sval[j]) << 1) | 1ull;
+      u64 smin = ((seq_base + (u64)uniq_min[i + kk]) << 1) | 1ull;
       t.stamp[c] = smin > st_c ? smin : st_c;
     }
   }
@@ -577,6 +586,7 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   const bool prof = idx->prof_on && idx->prof_n < RM_PROF_EVENTS / 2;
   if (prof) cudaEventRecord(idx->prof_ev[2 * idx->prof_n], s);
 #endif
+  RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_req, 0, sizeof(int), s));
   rm_match_dispatch<true, false>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
 #ifndef RM_EMU
   if (prof) {
@@ -585,16 +595,16 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   }
 #endif
   RM_CUDA(cudaGetLastError());
-  // group the split requests by (node, split point); +1 bit keeps the "no request" marker last
+  // group the split requests by (node, split point); their number stays on the device
   RmScratch& sc = idx->sc;
-  const int bits = idx->node_bits + idx->len_bits + 1;
-  const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], B, bits, sc.hist, s);
+  const int bits = idx->node_bits + idx->len_bits;
+  const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], B, bits, sc.hist, s, &idx->t.ctr->n_req);
   RM_CUDA(cudaGetLastError());
   const long long threads = (long long)B * RM_WIDE_G;
   const int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
   auto k3 = rm_split_apply_kernel<RM_WIDE_G>;
   RM_LAUNCH(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
-            sc.krank, sc.uniq_pos);
+            sc.krank, sc.uniq_pos, sc.uniq_min);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }

@@ -27,7 +27,7 @@
 #include "rm_sort.cuh"
 
 #define RM_STATIC_MAX_BATCH 4096
-#define RM_STATIC_SCRATCH_BYTES (192 * 1024)
+#define RM_STATIC_SCRATCH_BYTES (256 * 1024)
 #define RM_STATIC_MAX_DEVICES 64
 
 static __device__ __align__(256) unsigned char g_rm_static_scratch[RM_STATIC_SCRATCH_BYTES];
@@ -93,6 +93,7 @@ extern "C" int rm_match_batch_static(rm_index* idx, const int32_t* tokens, const
   view.sufmax = rm_carve<u64>(cur, RM_STATIC_MAX_BATCH);
   view.krank = rm_carve<int>(cur, RM_STATIC_MAX_BATCH);
   view.uniq_pos = rm_carve<int>(cur, RM_STATIC_MAX_BATCH);
+  view.uniq_min = rm_carve<unsigned>(cur, RM_STATIC_MAX_BATCH);
   view.hist_words = rm_sort_scratch_words(RM_STATIC_MAX_BATCH);
   view.hist = rm_carve<unsigned>(cur, view.hist_words);
   if ((size_t)(cur - base) > (size_t)RM_STATIC_SCRATCH_BYTES) {

@@ -10,85 +10,114 @@
 #include "rm_common.cuh"
 
 #define RM_SORT_TPB 256
-#define RM_SORT_TILE 4096          // items per block: 8 warps x 16 rounds x 32 lanes
 #define RM_SORT_WARPS (RM_SORT_TPB / 32)
-#define RM_SORT_PER_WARP (RM_SORT_TILE / RM_SORT_WARPS)
+#define RM_SORT_MIN_TILE 256       // 8 warps x 1 round x 32 lanes
+#define RM_SORT_MAX_TILE 4096      // 8 warps x 16 rounds x 32 lanes
 
-static inline int rm_sort_nblocks(int n) { return (n + RM_SORT_TILE - 1) / RM_SORT_TILE; }
-// u32 words of histogram scratch rm_sort_pairs needs for up to n items
-static inline size_t rm_sort_scratch_words(int n) { return (size_t)256 * (size_t)(rm_sort_nblocks(n) + 1) + 8; }
+// Items per block: small inputs get small tiles so that the grid still covers the 148 SMs (a 64K-item
+// sort with 4096-item tiles ran on 16 blocks and was latency bound); large inputs get 4096-item tiles.
+static inline int rm_sort_tile(int n) {
+  int t = (n + 295) / 296;                       // aim at >= 2 blocks per SM
+  t = (t + RM_SORT_MIN_TILE - 1) / RM_SORT_MIN_TILE * RM_SORT_MIN_TILE;
+  if (t < RM_SORT_MIN_TILE) t = RM_SORT_MIN_TILE;
+  if (t > RM_SORT_MAX_TILE) t = RM_SORT_MAX_TILE;
+  return t;
+}
+static inline int rm_sort_nblocks(int n) { int t = rm_sort_tile(n); return (n + t - 1) / t; }
+// u32 words of histogram scratch rm_sort_pairs needs for up to n items (worst case: smallest tiles)
+static inline size_t rm_sort_scratch_words(int n) {
+  size_t nb_small = ((size_t)n + RM_SORT_MIN_TILE - 1) / RM_SORT_MIN_TILE;
+  size_t nb = nb_small < 296 ? nb_small : 296;
+  size_t nb_big = ((size_t)n + RM_SORT_MAX_TILE - 1) / RM_SORT_MAX_TILE;
+  if (nb_big > nb) nb = nb_big;
+  return (size_t)256 * (nb + 2) + 8;
+}
 
 #ifndef RM_EMU
 
-static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_hist_kernel(const u64* __restrict__ keys, int n, int shift,
-                                                                  unsigned* __restrict__ ghist, int nblocks) {
+static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_hist_kernel(const u64* __restrict__ keys, int n_max,
+                                                                  const int* __restrict__ n_dev, int shift,
+                                                                  unsigned* __restrict__ ghist, int nblocks, int tile) {
   __shared__ unsigned h[256];
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
   h[threadIdx.x] = 0;
   __syncthreads();
-  int base = blockIdx.x * RM_SORT_TILE;
-  int end = min(base + RM_SORT_TILE, n);
+  int base = blockIdx.x * tile;
+  int end = min(base + tile, n);
   for (int i = base + threadIdx.x; i < end; i += RM_SORT_TPB) atomicAdd(&h[(unsigned)(keys[i] >> shift) & 255u], 1u);
   __syncthreads();
   ghist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// Exclusive scan of `len` u32 values in place, one block of 1024 threads, 8 values per thread per chunk.
-static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __restrict__ data, int len) {
-  __shared__ unsigned warp_tot[32];
-  __shared__ unsigned carry_s;
-  if (threadIdx.x == 0) carry_s = 0;
-  __syncthreads();
+// Exclusive scan, in place, of the digit-major histogram table data[256][nb] (row d = counts of digit d
+// per tile).  One block: a warp per row sums it, one warp scans the 256 row totals, then every warp
+// rescans its rows from their base.  Two coalesced sweeps over the table, three block barriers.
+static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __restrict__ data, int nb) {
+  __shared__ unsigned tot[256];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  for (int chunk = 0; chunk < len; chunk += 1024 * 8) {
-    int i0 = chunk + threadIdx.x * 8;
+  for (int d = wid; d < 256; d += 32) {
+    const unsigned* row = data + (size_t)d * nb;
+    unsigned s = 0;
+    for (int j = lane; j < nb; j += 32) s += row[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) tot[d] = s;
+  }
+  __syncthreads();
+  if (wid == 0) {
+    // lane l owns digits 8l .. 8l+7
     unsigned v[8], sum = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      v[k] = (i0 + k < len) ? data[i0 + k] : 0u;
+      v[k] = tot[lane * 8 + k];
       sum += v[k];
     }
     unsigned inc = sum;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      unsigned o = __shfl_up_sync(0xffffffffu, inc, d);
-      if (lane >= d) inc += o;
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += x;
     }
-    if (lane == 31) warp_tot[wid] = inc;
-    __syncthreads();
-    if (wid == 0) {
-      unsigned w = warp_tot[lane], winc = w;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        unsigned o = __shfl_up_sync(0xffffffffu, winc, d);
-        if (lane >= d) winc += o;
-      }
-      warp_tot[lane] = winc - w;  // exclusive offset of each warp
-    }
-    __syncthreads();
-    unsigned carry = carry_s;
-    unsigned excl = carry + warp_tot[wid] + (inc - sum);
+    unsigned run = inc - sum;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      if (i0 + k < len) data[i0 + k] = excl;
-      excl += v[k];
+      tot[lane * 8 + k] = run;
+      run += v[k];
     }
-    __syncthreads();
-    if (threadIdx.x == 1023) carry_s = excl;  // last thread ends at the chunk total
-    __syncthreads();
+  }
+  __syncthreads();
+  for (int d = wid; d < 256; d += 32) {
+    unsigned* row = data + (size_t)d * nb;
+    unsigned run = tot[d];
+    for (int j0 = 0; j0 < nb; j0 += 32) {
+      const int j = j0 + lane;
+      const unsigned v = j < nb ? row[j] : 0u;
+      unsigned inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += x;
+      }
+      if (j < nb) row[j] = run + inc - v;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
   }
 }
 
 static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_scatter_kernel(const u64* __restrict__ kin, const unsigned* __restrict__ vin,
-                                                                     u64* __restrict__ kout, unsigned* __restrict__ vout, int n,
-                                                                     int shift, const unsigned* __restrict__ gscan, int nblocks) {
+                                                                     u64* __restrict__ kout, unsigned* __restrict__ vout, int n_max,
+                                                                     const int* __restrict__ n_dev, int shift,
+                                                                     const unsigned* __restrict__ gscan, int nblocks, int tile) {
   __shared__ unsigned wcnt[RM_SORT_WARPS][256];
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  const int per_warp = tile / RM_SORT_WARPS;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < RM_SORT_WARPS * 256; i += RM_SORT_TPB) (&wcnt[0][0])[i] = 0;
   __syncthreads();
-  const int wbase = blockIdx.x * RM_SORT_TILE + wid * RM_SORT_PER_WARP;
+  const int wbase = blockIdx.x * tile + wid * per_warp;
   const unsigned lt = (1u << lane) - 1u;
   // phase 1: digit counts of this warp's contiguous run
-  for (int r = 0; r < RM_SORT_PER_WARP; r += 32) {
+  for (int r = 0; r < per_warp; r += 32) {
     int i = wbase + r + lane;
     unsigned d = (i < n) ? ((unsigned)(kin[i] >> shift) & 255u) : 0xFFFFu;
     unsigned m = __match_any_sync(0xffffffffu, d);
@@ -110,7 +139,7 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_scatter_kernel(con
   __syncthreads();
   // phase 3: same walk, now scattering; equal digits keep their order (lane order inside a
   // round, rounds in order, warps in order, blocks in order) => the sort is stable
-  for (int r = 0; r < RM_SORT_PER_WARP; r += 32) {
+  for (int r = 0; r < per_warp; r += 32) {
     int i = wbase + r + lane;
     bool ok = i < n;
     u64 k = ok ? kin[i] : 0;
@@ -129,21 +158,23 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_scatter_kernel(con
 }
 
 // Sorts n pairs by the low `bits` bits of the key.  Returns 0 if the result is in (k0, v0), 1 if in
-// (k1, v1).  hist must hold rm_sort_scratch_words(n) u32.
+// (k1, v1).  hist must hold rm_sort_scratch_words(n) u32.  If n_dev is not NULL the item count is read on
+// the device (min(*n_dev, n)) and n only bounds the grid, so no host synchronisation is needed.
 static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n, int bits, unsigned* hist,
-                                cudaStream_t s) {
+                                cudaStream_t s, const int* n_dev = nullptr) {
   if (n <= 1 || bits <= 0) return 0;
   int passes = (bits + 7) / 8;
-  int nb = rm_sort_nblocks(n);
+  int tile = rm_sort_tile(n);
+  int nb = (n + tile - 1) / tile;
   int cur = 0;
   for (int p = 0; p < passes; ++p) {
     u64* ki = cur ? k1 : k0;
     unsigned* vi = cur ? v1 : v0;
     u64* ko = cur ? k0 : k1;
     unsigned* vo = cur ? v0 : v1;
-    RM_LAUNCH(rm_sort_hist_kernel, nb, RM_SORT_TPB, s, ki, n, p * 8, hist, nb);
-    RM_LAUNCH(rm_scan_u32_kernel, 1, 1024, s, hist, 256 * nb);
-    RM_LAUNCH(rm_sort_scatter_kernel, nb, RM_SORT_TPB, s, ki, vi, ko, vo, n, p * 8, hist, nb);
+    RM_LAUNCH(rm_sort_hist_kernel, nb, RM_SORT_TPB, s, ki, n, n_dev, p * 8, hist, nb, tile);
+    RM_LAUNCH(rm_scan_u32_kernel, 1, 1024, s, hist, nb);
+    RM_LAUNCH(rm_sort_scatter_kernel, nb, RM_SORT_TPB, s, ki, vi, ko, vo, n, n_dev, p * 8, hist, nb, tile);
     cur ^= 1;
   }
   return cur;
@@ -152,8 +183,18 @@ static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, in
 #else  // RM_EMU: the emulation build sorts on the host (the sort kernels need real block-level parallelism)
 
 #include <vector>
-static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n, int bits, unsigned*, cudaStream_t) {
-  if (n <= 1 || bits <= 0) return 0;
+static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n, int bits, unsigned*, cudaStream_t,
+                                const int* n_dev = nullptr) {
+  if (n_dev && *n_dev < n) n = *n_dev;
+  if (bits <= 0) return 0;
+  if (n <= 1) {
+    int passes1 = (bits + 7) / 8;
+    if (passes1 % 2 == 1 && n == 1) {
+      k1[0] = k0[0];
+      v1[0] = v0[0];
+    }
+    return passes1 % 2;
+  }
   int eff = ((bits + 7) / 8) * 8;
   u64 mask = eff >= 64 ? ~0ull : ((1ull << eff) - 1ull);
   std::vector<int> ord(n);
