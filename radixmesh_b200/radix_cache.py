@@ -1,0 +1,324 @@
+"""Drop-in for the reference's `RadixCache` (radix/sglang/srt/mem_cache/radix_cache.py:87-436) on the
+device index.  Same constructor, same method names, same argument meaning and return values; the
+tree itself lives in HBM behind the C ABI (`capi.DeviceIndex`).  `*_batch` methods are additions.
+
+Single-key calls are thin wrappers over the batch entry points (a batch of one); the throughput
+path is `match_prefix_batch` / `insert_batch` with tensors.
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import Any, List, Optional
+
+import numpy as np
+
+from . import capi
+
+
+class TreeNode:
+    """Handle to a node of the device tree (reference: radix_cache.py:35-64).  Attributes are read from
+    the device on access.  `id` is the node's pool id; like the reference's creation counter it is not
+    comparable across replicas — identity for parity is the full key."""
+
+    __slots__ = ("_cache", "id", "_gen")
+
+    def __init__(self, cache: "RadixCache", node_id: int, gen: int = -1):
+        self._cache = cache
+        self.id = int(node_id)
+        self._gen = int(gen)
+
+    def _resolved(self) -> int:
+        return self._cache._resolve(self.id, self._gen)
+
+    @property
+    def key(self) -> List[int]:
+        return self._cache._node_tokens(self._resolved())
+
+    @property
+    def value(self):
+        return self._cache._node_value(self._resolved())
+
+    @property
+    def lock_ref(self) -> int:
+        return int(self._cache._dump()["lock_ref"][self._resolved()])
+
+    @property
+    def last_access_time(self) -> int:
+        return int(self._cache._dump()["stamp"][self._resolved()])
+
+    @property
+    def parent(self) -> Optional["TreeNode"]:
+        x = self._resolved()
+        if x == 0:
+            return None
+        return self._cache._handle(int(self._cache._dump()["parent"][x]))
+
+    @property
+    def children(self) -> dict:
+        d = self._cache._dump()
+        x = self._resolved()
+        out = {}
+        for c in np.nonzero((d["parent"][:d["n"]] == x) & (d["gen"][:d["n"]] >= 0))[0]:
+            if c != 0:
+                out[self._cache._node_tokens(int(c))[0]] = self._cache._handle(int(c))
+        return out
+
+    hit_count = 0          # never incremented in the reference either
+    loading = False
+    host_value = None
+
+    @property
+    def evicted(self) -> bool:
+        return False
+
+    @property
+    def backuped(self) -> bool:
+        return False
+
+    def __eq__(self, other) -> bool:
+        return isinstance(other, TreeNode) and other._cache is self._cache and other._resolved() == self._resolved()
+
+    def __hash__(self) -> int:
+        return hash((id(self._cache), self.id, self._gen))
+
+    def __lt__(self, other: "TreeNode") -> bool:
+        return self.last_access_time < other.last_access_time
+
+    def __repr__(self) -> str:
+        return f"TreeNode(id={self.id})"
+
+
+@dataclasses.dataclass
+class MatchResult:
+    """radix_cache.py:67-84."""
+    device_indices: Any
+    last_device_node: Any
+    last_host_node: Any
+    host_hit_length: int = 0
+
+
+class RadixCache:
+    MODE = capi.MODE_BASE
+
+    def __init__(self, req_to_token_pool, token_to_kv_pool_allocator, page_size: int, disable: bool = False,
+                 enable_kv_cache_events: bool = False, *, max_nodes: int = 1 << 20, max_tokens: int = 1 << 26,
+                 max_batch: int = 1 << 16, max_key_len: int = 1 << 15, max_dups: int = 1 << 12, device: int = 0,
+                 _index_kwargs: Optional[dict] = None, _backend=None, _library=None):
+        if page_size != 1:
+            raise NotImplementedError("radixmesh_b200: page_size > 1 is a 'next' row (SURVEY.md 8f-4); RadixMesh uses 1")
+        self.req_to_token_pool = req_to_token_pool
+        self.token_to_kv_pool_allocator = token_to_kv_pool_allocator
+        self.page_size = page_size
+        self.disable = disable
+        self.enable_kv_cache_events = enable_kv_cache_events   # events are not produced (reference: NameError if on)
+        self.kv_event_queue = []
+        kw = dict(mode=self.MODE, max_nodes=max_nodes, max_tokens=max_tokens, max_batch=max_batch,
+                  max_key_len=max_key_len, max_dups=max_dups, device=device, backend=_backend, library=_library)
+        kw.update(_index_kwargs or {})
+        self._ix = capi.DeviceIndex(**kw)
+        self._be = self._ix.be
+        self.device = getattr(self._be, "device", "cpu")
+        self._dump_cache = None
+        self.root_node = TreeNode(self, 0, 0)
+
+    # ------------------------------------------------------------------ helpers
+    def _invalidate(self) -> None:
+        self._dump_cache = None
+
+    def _dump(self) -> dict:
+        self._flush()          # staged remote inserts (RadixMesh) must be visible to every read
+        if self._dump_cache is None:
+            self._dump_cache = self._ix.dump()
+        return self._dump_cache
+
+    def _flush(self) -> None:       # RadixMesh stages remote inserts; the base class has nothing pending
+        return None
+
+    def _handle(self, node_id: int) -> TreeNode:
+        if node_id == 0:
+            return self.root_node
+        return TreeNode(self, node_id, int(self._dump()["gen"][node_id]))
+
+    def _resolve(self, node_id: int, gen: int) -> int:
+        if gen < 0 or node_id == 0:
+            return node_id
+        d = self._dump()
+        if int(d["gen"][node_id]) == gen:
+            return node_id
+        x = int(d["parked"][node_id])
+        while x >= 0:
+            if int(d["gen"][x]) == -(gen + 1):
+                return x
+            x = int(d["parked"][x])
+        return node_id
+
+    def _node_tokens(self, x: int) -> List[int]:
+        if x == 0:
+            return []
+        d = self._dump()
+        tok, _ = self._ix.read_arena(int(d["edge_off"][x]), int(d["edge_len"][x]), values=False)
+        return tok.tolist()
+
+    def _node_value(self, x: int):
+        import torch
+        if x == 0:
+            return []
+        d = self._dump()
+        _, val = self._ix.read_arena(int(d["edge_off"][x]), int(d["edge_len"][x]))
+        return torch.from_numpy(val)
+
+    def _tensor(self, a):
+        import torch
+        return a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+
+    # ------------------------------------------------------------------ public API (radix_cache.py:117-248)
+    def reset(self) -> None:
+        self._ix.reset()
+        self._invalidate()
+
+    def match_prefix(self, key: List[int], **kwargs) -> MatchResult:
+        import torch
+        if self.disable or len(key) == 0:
+            return MatchResult(torch.empty((0,), dtype=torch.int64), self.root_node, self.root_node)
+        lens, nodes, vals, offs = self._match_keys([key])
+        node = self._handle(int(nodes[0]))
+        return MatchResult(self._tensor(vals[:int(lens[0])]), node, node)
+
+    def _match_keys(self, keys):
+        """Host lists -> (lens, nodes, values, value offsets) as host arrays."""
+        self._flush()
+        flat = np.fromiter((t for k in keys for t in k), dtype=np.int32, count=sum(len(k) for k in keys))
+        offs = np.zeros(len(keys) + 1, dtype=np.int64)
+        np.cumsum([len(k) for k in keys], out=offs[1:])
+        lens = np.zeros(len(keys), np.int32)
+        nodes = np.zeros(len(keys), np.int32)
+        self._ix.match_host(flat, offs, lens, nodes)
+        self._invalidate()
+        voffs = np.zeros(len(keys) + 1, dtype=np.int64)
+        np.cumsum(lens, out=voffs[1:])
+        be = self._be
+        d_out = be.empty(int(voffs[-1]) + 1, np.int64)
+        self._ix.gather(be.to_device(nodes), be.to_device(lens), be.to_device(voffs), len(keys), d_out)
+        return lens, nodes, d_out[:int(voffs[-1])], voffs
+
+    def match_prefix_batch(self, tokens, offsets, out_len=None, out_node=None):
+        """Addition: device tensors in, device tensors out (int32 lengths, int32 last-node ids), equal to
+        match_prefix on each query in order."""
+        self._flush()
+        B = int(offsets.shape[0]) - 1
+        out_len = out_len if out_len is not None else self._be.empty(B, np.int32)
+        out_node = out_node if out_node is not None else self._be.empty(B, np.int32)
+        self._ix.match(tokens, offsets, B, out_len, out_node)
+        self._invalidate()
+        return out_len, out_node
+
+    def gather_values_batch(self, nodes, lens, out_offsets, out_values):
+        """Addition: the torch.cat of match_prefix for a whole batch (ragged, caller-provided offsets)."""
+        self._ix.gather(nodes, lens, out_offsets, int(nodes.shape[0]), out_values)
+        return out_values
+
+    def insert(self, key: List, value=None) -> int:
+        if self.disable:
+            return 0
+        if value is None:
+            value = [x for x in key]
+        return int(self._insert_records([(list(key), value, -1)])[0])
+
+    def _insert_records(self, recs) -> np.ndarray:
+        flat = np.fromiter((t for k, _, _ in recs for t in k), dtype=np.int32, count=sum(len(k) for k, _, _ in recs))
+        offs = np.zeros(len(recs) + 1, dtype=np.int64)
+        np.cumsum([len(k) for k, _, _ in recs], out=offs[1:])
+        vals = None
+        if self.MODE != capi.MODE_ROUTER:
+            vals = np.zeros(int(offs[-1]), dtype=np.int64)
+            for i, (_, v, _) in enumerate(recs):
+                a = v.cpu().numpy() if hasattr(v, "cpu") else np.asarray(v)
+                vals[offs[i]:offs[i + 1]] = a
+        ranks = np.asarray([r for _, _, r in recs], dtype=np.int32) if self.MODE != capi.MODE_BASE else None
+        out = self._ix.insert_host(flat, vals, offs, ranks)
+        self._invalidate()
+        self._ix.check_device_error()
+        return out
+
+    def insert_batch(self, tokens, values, offsets, ranks=None, out_prefix_len=None):
+        """Addition: ordered batch of inserts on device tensors (rm_insert_batch)."""
+        self._flush()
+        N = int(offsets.shape[0]) - 1
+        out = out_prefix_len if out_prefix_len is not None else self._be.empty(N, np.int32)
+        self._ix.insert(tokens, values, offsets, ranks, N, out)
+        self._invalidate()
+        return out
+
+    def evict(self, num_tokens: int) -> None:
+        if self.disable:
+            return
+        self._flush()
+        nodes, offs, lens = self._ix.evict(int(num_tokens))
+        self._invalidate()
+        for o, n in zip(offs.tolist(), lens.tolist()):
+            _, val = self._ix.read_arena(o, n)
+            if self.token_to_kv_pool_allocator is not None:
+                self.token_to_kv_pool_allocator.free(self._tensor(val))      # radix_cache.py:195
+
+    def _lock(self, node: TreeNode, direction: int) -> int:
+        self._flush()
+        be = self._be
+        d_out = be.empty(1, np.int64)
+        self._ix.lock(be.to_device(np.asarray([node.id], np.int32)), be.to_device(np.asarray([node._gen], np.int32)),
+                      1, direction, d_out)
+        self._invalidate()
+        return int(be.to_host(d_out)[0])
+
+    def inc_lock_ref(self, node: TreeNode) -> int:
+        return 0 if self.disable else self._lock(node, +1)
+
+    def dec_lock_ref(self, node: TreeNode) -> int:
+        return 0 if self.disable else self._lock(node, -1)
+
+    def evictable_size(self) -> int:
+        self._flush()
+        return int(self._ix.sizes().evictable)
+
+    def protected_size(self) -> int:
+        self._flush()
+        return int(self._ix.sizes().protected_)
+
+    def total_size(self) -> int:
+        d = self._dump()
+        live = (d["parent"][:d["n"]] >= 0) & (d["gen"][:d["n"]] >= 0)
+        live[0] = False
+        return int(d["edge_len"][:d["n"]][live].sum())
+
+    def all_values_flatten(self):
+        """All values of the tree; node order is by pool id, not the reference's dict order."""
+        import torch
+        d = self._dump()
+        out = [self._node_value(int(x)) for x in range(1, d["n"]) if d["parent"][x] >= 0 and d["gen"][x] >= 0]
+        return torch.cat(out) if out else torch.empty((0,), dtype=torch.int64)
+
+    def pretty_print(self) -> None:
+        d = self._dump()
+        kids = {}
+        for x in range(1, d["n"]):
+            if d["parent"][x] >= 0 and d["gen"][x] >= 0:
+                kids.setdefault(int(d["parent"][x]), []).append(x)
+        stack = [(0, 0)]
+        while stack:
+            x, ind = stack.pop()
+            print(" " * ind, int(d["edge_len"][x]), self._node_tokens(x)[:10], f"r={int(d['lock_ref'][x])}")
+            for c in kids.get(x, []):
+                stack.append((c, ind + 2))
+        print(f"#tokens: {self.total_size()}")
+
+    def take_events(self):
+        return []
+
+    # parity helper shared with the oracle's canonical()
+    def full_key(self, node: TreeNode) -> List[int]:
+        d = self._dump()
+        x = node._resolved()
+        parts = []
+        while x != 0:
+            parts.append(self._node_tokens(x))
+            x = int(d["parent"][x])
+        return [t for p in reversed(parts) for t in p]

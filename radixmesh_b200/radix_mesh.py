@@ -1,0 +1,205 @@
+"""Drop-in for the reference's `RadixMesh` (radix/radix_mesh.py:72-495) on the device index.
+
+What stays host Python, exactly as in the reference: who forwards what to whom (ring + routers fed by
+rank 0), the oplog objects, the tick counting.  What moves to the GPU: the tree.  Remote INSERT oplogs
+are staged on the host in arrival order and applied as ONE ordered `rm_insert_batch_h` before the next
+operation that reads the tree, which is equivalent to the reference applying them one by one under its
+`_tree_lock` (radix_mesh.py:198-199).
+"""
+from __future__ import annotations
+
+import dataclasses
+import threading
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from . import capi
+from .host import CacheOplog, CacheOplogType, NodeKey, RadixMode, RingPolicy
+from .radix_cache import MatchResult, RadixCache, TreeNode
+
+
+@dataclasses.dataclass
+class RouterMatchResult:              # radix_mesh.py:66-69
+    prefill_node_rank: int = -1
+    decode_node_rank: int = -1
+
+
+class OwnedValue:
+    """What `TreeNode.value` is on a prefill/decode replica (radix_mesh.py:21-44): `.value` tensor + `.node_rank`."""
+
+    def __init__(self, value, node_rank: int):
+        self.value = value
+        self.node_rank = node_rank
+
+    def __len__(self):
+        return len(self.value)
+
+
+class RankValue:
+    """Router replicas keep only the owner rank (radix_mesh.py:47-63)."""
+
+    def __init__(self, node_rank: int):
+        self.node_rank = node_rank
+
+    def __len__(self):
+        return 1
+
+
+_MODES = {RadixMode.PREFILL: capi.MODE_PREFILL, RadixMode.DECODE: capi.MODE_DECODE, RadixMode.ROUTER: capi.MODE_ROUTER}
+
+
+class RadixMesh(RadixCache):
+    def __init__(self, args, communicator=None, routers=None, token_to_kv_pool_allocator=None, **index_kwargs):
+        if args.prefill_node_rank != -1:                       # radix_mesh.py:76-84
+            self._global_node_rank, self.mode = args.prefill_node_rank, RadixMode.PREFILL
+        elif args.decode_node_rank != -1:
+            self._global_node_rank, self.mode = args.decode_node_rank, RadixMode.DECODE
+        else:
+            self._global_node_rank, self.mode = args.router_node_rank, RadixMode.ROUTER
+        self.MODE = _MODES[self.mode]
+        self.args = args
+        self.sync_algo = RingPolicy()
+        self.communicator = communicator
+        self.router_communicators = routers
+        self.logic_op_counter = 0
+        self._pending: List[tuple] = []
+        self._pending_lock = threading.Lock()
+        self.tick_received: Dict[int, int] = {}
+        backend = index_kwargs.pop("_backend", None)
+        library = index_kwargs.pop("_library", None)
+        ikw = dict(self_rank=self._global_node_rank, n_prefill=len(args.prefill_cache_nodes),
+                   n_decode=len(args.decode_cache_nodes))
+        super().__init__(None, token_to_kv_pool_allocator, 1, _index_kwargs=ikw, _backend=backend, _library=library,
+                         **index_kwargs)
+        if self.communicator is not None:
+            self.communicator.register_rcv_callback(self.oplog_received)
+
+    # ------------------------------------------------------------------ reference surface
+    def global_node_rank(self) -> int:
+        return self._global_node_rank
+
+    def prefill_cache_nodes(self, prefill_node_rank=None):
+        if prefill_node_rank is None:
+            return self.args.prefill_cache_nodes
+        return self.args.prefill_cache_nodes[prefill_node_rank]
+
+    def decode_cache_nodes(self, decode_node_rank=None):
+        if decode_node_rank is None:
+            return self.args.decode_cache_nodes
+        return self.args.decode_cache_nodes[self.args.local_node_rank(decode_node_rank)]
+
+    def match_prefix(self, key: List[int], **kwargs):
+        if len(key) == 0:
+            raise IndexError("list index out of range")          # radix_mesh.py:253 has no empty-key guard
+        if self.mode == RadixMode.ROUTER:
+            pf, dc, _, _, err = self._route_keys([key], warm=True)
+            if err[0] == 1:
+                raise AssertionError("[RadixMesh] Prefix match node_rank is invalid")   # radix_mesh.py:233-237
+            return RouterMatchResult(int(pf[0]), int(dc[0]))
+        lens, nodes, vals, _ = self._match_keys([key])
+        node = self._handle(int(nodes[0]))
+        return MatchResult(self._tensor(vals[:int(lens[0])]), node, node)
+
+    def insert(self, key: List, value=None) -> int:
+        assert self.mode in (RadixMode.PREFILL, RadixMode.DECODE), "only support prefill/decode node to insert"
+        return self._insert(list(key), value, self._global_node_rank)
+
+    def _insert(self, key, value, owner_rank: int) -> int:
+        with self._pending_lock:
+            self._pending.append((key, value, owner_rank))
+        ret = self._flush()
+        self.send_insert_event(key, value, owner_rank)
+        return ret
+
+    def _flush(self):
+        """Apply the staged INSERTs, in arrival order, as one ordered device batch."""
+        with self._pending_lock:
+            recs, self._pending = self._pending, []
+        if not recs:
+            return 0
+        out = None
+        step = int(self._ix.cfg.max_batch)
+        for i in range(0, len(recs), step):
+            out = self._insert_records(recs[i:i + step])
+        return int(out[-1])
+
+    def send_insert_event(self, key, value, owner_rank: int) -> None:
+        # radix_mesh.py:325-347: routers never send; rank 0 also feeds the routers
+        if self.mode == RadixMode.ROUTER or self.communicator is None:
+            return
+        vals = value.tolist() if hasattr(value, "tolist") else list(value)
+        self.logic_op_counter += 1
+        oplog = CacheOplog(oplog_type=CacheOplogType.INSERT, node_rank=owner_rank, local_logic_id=self.logic_op_counter,
+                           key=list(key), value=vals, ttl=self.sync_algo.ttl(self.args))
+        self.communicator.send(oplog)
+        if self._global_node_rank == self.sync_algo.master_node_rank() and self.router_communicators:
+            for r in self.router_communicators:
+                r.send(oplog)
+
+    def oplog_received(self, oplog) -> None:
+        # radix_mesh.py:391-423
+        oplog.ttl -= 1
+        t = int(oplog.oplog_type)
+        if t == CacheOplogType.TICK:
+            self.tick_received[oplog.node_rank] = self.tick_received.get(oplog.node_rank, 0) + 1
+            return None
+        if t in (CacheOplogType.GC_QUERY, CacheOplogType.GC_EXEC):
+            return None                       # the GC protocol is a 'next' row
+        if oplog.node_rank == self._global_node_rank or oplog.ttl <= 0:
+            return None
+        if t == CacheOplogType.INSERT:
+            with self._pending_lock:
+                self._pending.append((list(oplog.key), oplog.value, oplog.node_rank))
+            self.send_insert_event(oplog.key, oplog.value, oplog.node_rank)   # re-forward with a fresh ttl
+        elif t == CacheOplogType.RESET:
+            RadixCache.reset(self)
+        elif t != CacheOplogType.DELETE:
+            assert False, "unknown oplog type"
+        return None
+
+    def dec_lock_ref(self, node: TreeNode) -> int:
+        return self._lock(node, -1)           # the device clamps at zero in mesh modes (radix_mesh.py:175-177)
+
+    def inc_lock_ref(self, node: TreeNode) -> int:
+        return self._lock(node, +1)
+
+    def evict(self, node=None) -> None:       # radix_mesh.py:349-351
+        return None
+
+    def _node_value(self, x: int):
+        d = self._dump()
+        rank = int(d["rank"][x])
+        if self.mode == RadixMode.ROUTER:
+            return RankValue(rank)
+        return OwnedValue(super()._node_value(x) if x else None, rank)
+
+    @property
+    def dup_nodes(self) -> dict:
+        """{NodeKey(full key, rank): parked TreeNode or None} (radix_mesh.py:97, 310, 476, 493)."""
+        self._flush()
+        out = {}
+        for node, rank, parked, _lk in self._ix.dup_entries().tolist():
+            k = NodeKey(tuple(self.full_key(TreeNode(self, node, -1))), rank)
+            out[k] = None if parked < 0 else TreeNode(self, parked, -1)
+        return out
+
+    def gc_candidates(self) -> List[NodeKey]:
+        """The scan of RadixMesh._gc (radix_mesh.py:151-156)."""
+        self._flush()
+        return [NodeKey(tuple(self.full_key(TreeNode(self, n, -1))), r)
+                for n, r, _, _ in self._ix.dup_entries(only_candidates=True).tolist()]
+
+    # ------------------------------------------------------------------ router side (used by CacheAwareRouter)
+    def _route_keys(self, keys, warm: bool):
+        self._flush()
+        flat = np.fromiter((t for k in keys for t in k), dtype=np.int32, count=sum(len(k) for k in keys))
+        offs = np.zeros(len(keys) + 1, dtype=np.int64)
+        np.cumsum([len(k) for k in keys], out=offs[1:])
+        be = self._be
+        n = len(keys)
+        outs = [be.empty(n, np.int32) for _ in range(4)]
+        err = be.empty(n, np.uint8)
+        self._ix.route(be.to_device(flat), be.to_device(offs), n, warm, outs[0], outs[1], outs[2], outs[3], err)
+        self._invalidate()
+        return [be.to_host(o) for o in outs] + [be.to_host(err)]

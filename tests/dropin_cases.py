@@ -1,0 +1,176 @@
+"""Golden replays through the drop-in classes (RadixCache / RadixMesh / CacheAwareRouter): the same
+scenarios the reference's own tests run (test/correctness.py) plus recorded op sequences, with the
+results the unmodified reference produced (tests/golden/*.json)."""
+import numpy as np
+import pytest
+import torch
+
+from radixmesh_b200 import CacheAwareRouter, RadixCache, RadixMesh, ServerArgs
+from tests.golden_util import load
+
+P_ADDRS = [f"localhost:{50000 + i}" for i in range(3)]
+D_ADDRS = [f"localhost:{50003 + i}" for i in range(2)]
+R_ADDRS = ["localhost:50010"]
+
+
+class LoopComm:
+    """In-process stand-in for the reference's TcpCommunicator: delivers to the next hop synchronously."""
+
+    def __init__(self):
+        self.peer_cb = None
+        self.cb = None
+
+    def send(self, oplog):
+        if self.peer_cb is not None:
+            import copy
+            self.peer_cb(copy.deepcopy(oplog))
+        return 1
+
+    def register_rcv_callback(self, fn):
+        self.cb = fn
+
+    def is_ordered(self):
+        return True
+
+    def target_address(self):
+        return "loop"
+
+
+class FakeAllocator:
+    def __init__(self):
+        self.device = torch.device("cpu")
+        self.freed = []
+
+    def free(self, t):
+        self.freed.append([int(x) for x in t.tolist()])
+
+
+def build_mesh(kw):
+    """3 prefill + 2 decode in a ring, 1 router fed by rank 0 (policy/sync_algo.py:57-75)."""
+    ring = [LoopComm() for _ in range(5)]
+    to_router, router_in = LoopComm(), LoopComm()
+    nodes = []
+    for rank in range(6):
+        args = ServerArgs(prefill_cache_nodes=P_ADDRS, decode_cache_nodes=D_ADDRS, router_cache_nodes=R_ADDRS)
+        if rank < 3:
+            args.prefill_node_rank = rank
+        elif rank < 5:
+            args.decode_node_rank = rank
+        else:
+            args.router_node_rank = rank
+        small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64, max_dups=512)
+        small.update(kw)
+        if rank < 5:
+            nodes.append(RadixMesh(args, communicator=ring[rank], routers=[to_router] if rank == 0 else None, **small))
+        else:
+            nodes.append(RadixMesh(args, communicator=router_in, **small))
+    for i in range(5):
+        ring[i].peer_cb = ring[(i + 1) % 5].cb
+    to_router.peer_cb = router_in.cb
+    return nodes
+
+
+def canon(mesh):
+    d = mesh._dump()
+    rows = []
+    for x in range(1, d["n"]):
+        if d["parent"][x] >= 0 and d["gen"][x] >= 0:
+            from radixmesh_b200 import TreeNode
+            h = TreeNode(mesh, x, -1)
+            v = mesh._node_value(x)
+            raw = [int(t) for t in v.value.tolist()] if hasattr(v, "value") and v.value is not None else []
+            rows.append([mesh.full_key(h), int(d["edge_len"][x]), raw, int(d["rank"][x]), int(d["lock_ref"][x])])
+    rows.sort()
+    dup = sorted([[list(k.key), k.node_rank, None if n is None else n.lock_ref] for k, n in mesh.dup_nodes.items()])
+    return {"nodes": rows, "evictable": mesh.evictable_size(), "protected": mesh.protected_size(), "dup": dup}
+
+
+def replay_correctness_block(block, kw):
+    nodes = build_mesh(kw)
+    router = CacheAwareRouter(nodes[5], skip_warm_up=True)
+    for r, k, v in block["inserts"]:
+        nodes[r].insert(k, torch.tensor(v))
+    for row in block["expect"]:
+        for r, idx in row["pd"].items():
+            res = nodes[int(r)].match_prefix(row["key"])
+            assert res.device_indices.tolist() == idx            # test/correctness.py:52-55, 86-89, 158-162
+        res = nodes[5].match_prefix(row["key"])
+        assert [res.prefill_node_rank, res.decode_node_rank] == row["router"]   # :56-58, 90-93
+        rr = router.cache_aware_route(row["key"])
+        assert [rr.prefill_addr, rr.decode_addr] == row["route"]                # :66-70, 100-103
+    if "state" in block:
+        for r, st in block["state"].items():
+            assert canon(nodes[int(r)]) == st, f"rank {r}"
+
+
+def replay_mesh_sequence(case, kw):
+    nodes = build_mesh(kw)
+    router = CacheAwareRouter(nodes[5], skip_warm_up=True)
+    held = []
+    for op in case["ops"]:
+        if op["op"] == "ins":
+            assert nodes[op["rank"]].insert(op["key"], torch.tensor(op["val"])) == op["ret"]
+        elif op["op"] == "match":
+            m = nodes[op["rank"]].match_prefix(op["key"])
+            assert m.device_indices.tolist() == op["idx"]
+            assert nodes[op["rank"]].full_key(m.last_device_node) == op["last"]
+            held.append((op["rank"], m.last_device_node))
+        elif op["op"] == "route":
+            if op.get("error") == "AssertionError":
+                with pytest.raises(AssertionError):
+                    nodes[5].match_prefix(op["key"])
+                continue
+            m = nodes[5].match_prefix(op["key"])
+            assert [m.prefill_node_rank, m.decode_node_rank] == op["ranks"]
+            if op.get("error") == "IndexError":
+                with pytest.raises(IndexError):
+                    router.cache_aware_route(op["key"])
+            else:
+                rr = router.cache_aware_route(op["key"])
+                assert [rr.prefill_addr, rr.decode_addr] == op["addrs"]
+        elif op["op"] == "lock":
+            r, n = held[op["h"]]
+            assert nodes[r].inc_lock_ref(n) == op["ret"]
+        elif op["op"] == "unlock":
+            r, n = held[op["h"]]
+            assert nodes[r].dec_lock_ref(n) == op["ret"]
+    for r, st in case["state"].items():
+        assert canon(nodes[int(r)]) == st, f"rank {r}"
+    for r, cands in case["gc_candidates"].items():
+        assert sorted([list(k.key), k.node_rank] for k in nodes[int(r)].gc_candidates()) == cands
+
+
+def replay_base_sequence(case, kw):
+    alloc = FakeAllocator()
+    small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64)
+    small.update(kw)
+    t = RadixCache(None, alloc, 1, **small)
+    held = []
+    for op in case["ops"]:
+        if op["op"] == "ins":
+            assert t.insert(list(op["key"]), torch.tensor(op["val"], dtype=torch.int64)) == op["ret"]
+        elif op["op"] == "match":
+            m = t.match_prefix(list(op["key"]))
+            assert m.device_indices.tolist() == op["idx"]
+            assert t.full_key(m.last_device_node) == op["last"]
+            held.append(m.last_device_node)
+        elif op["op"] == "lock":
+            assert t.inc_lock_ref(held[op["h"]]) == op["ret"]
+            held.append(held[op["h"]])
+        elif op["op"] == "unlock":
+            assert t.dec_lock_ref(held[op["h"]]) == op["ret"]
+        elif op["op"] == "evict":
+            before = len(alloc.freed)
+            t.evict(op["n"])
+            assert alloc.freed[before:] == op["freed"]
+        st = op["state"]
+        assert t.evictable_size() == st["evictable"] and t.protected_size() == st["protected"]
+        d = t._dump()
+        from radixmesh_b200 import TreeNode
+        rows = sorted([t.full_key(TreeNode(t, x, -1)), int(d["edge_len"][x]), t._node_value(x).tolist(), -1,
+                       int(d["lock_ref"][x])] for x in range(1, d["n"]) if d["parent"][x] >= 0)
+        assert rows == [r[:5] for r in st["nodes"]]
+
+
+def golden(name):
+    return load(name)

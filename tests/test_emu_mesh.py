@@ -1,0 +1,41 @@
+"""Mesh kernels (host emulation build) against the CPU oracle: conflict rule, duplicate table, locked
+swap with handle generations, router pick, consistent-hash fallback (MD5 on the device)."""
+import pytest
+
+from tests import cases_mesh
+from tests.emu.emu_backend import make_index
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_emu_mesh_sequences(seed):
+    cases_mesh.run_mesh_sequence(make_index, seed)
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_emu_mesh_binary_vocab(seed):
+    cases_mesh.run_mesh_sequence(make_index, 500 + seed, n_steps=30, vocab=2, maxlen=6)
+
+
+def test_emu_consistent_hash_vectors():
+    """ConsistentHash golden vectors (recorded from the reference) through the MD5 fallback kernel."""
+    import numpy as np
+    from oracle.radix_port import PortConsistentHash
+    from tests.golden_util import load
+    from tests.parity import pack
+    for case in load("consistent_hash"):
+        addrs = case["addrs"]
+        ix = make_index(mode=3, n_prefill=len(addrs), n_decode=len(addrs), max_nodes=64, max_tokens=64, max_batch=64,
+                        max_key_len=512)
+        h = PortConsistentHash(addrs)
+        pts = np.asarray(case["ring"], dtype=np.uint32)
+        own = np.asarray([addrs.index(h.owner[p]) for p in h.ring], dtype=np.int32)
+        ix.set_rings(pts, own, pts, own)
+        keys = [q["key"] for q in case["queries"]]
+        tk, offs = pack(keys)
+        n = len(keys)
+        outs = [np.zeros(n, np.int32) for _ in range(4)]
+        err = np.zeros(n, np.uint8)
+        ix.route(tk, offs, n, False, outs[0], outs[1], outs[2], outs[3], err)
+        assert [addrs[i] for i in outs[2].tolist()] == [q["node"] for q in case["queries"]]
+        assert err.tolist() == [0] * n
+        ix.close()

@@ -1,0 +1,66 @@
+"""GPU parity: mesh kernels (conflict rule, duplicate table, locked swap, router pick, device MD5
+fallback) and the drop-in classes against the oracle / the reference's recorded results."""
+import pytest
+
+from tests import cases_mesh
+from tests import dropin_cases as dc
+
+pytestmark = pytest.mark.gpu
+
+
+def make_index(**kw):
+    from radixmesh_b200 import capi
+    return capi.DeviceIndex(**kw)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_gpu_mesh_sequences(seed):
+    cases_mesh.run_mesh_sequence(make_index, seed)
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_gpu_mesh_binary_vocab(seed):
+    cases_mesh.run_mesh_sequence(make_index, 500 + seed, n_steps=30, vocab=2, maxlen=6)
+
+
+@pytest.mark.parametrize("block", dc.golden("correctness_blocks"), ids=lambda b: b["name"])
+def test_gpu_reference_correctness_blocks(block):
+    dc.replay_correctness_block(block, {})
+
+
+@pytest.mark.parametrize("case", dc.golden("mesh_sequences")[:5], ids=lambda c: f"seed{c['seed']}")
+def test_gpu_golden_mesh_sequences(case):
+    dc.replay_mesh_sequence(case, {})
+
+
+@pytest.mark.parametrize("case", dc.golden("base_sequences")[:6], ids=lambda c: f"seed{c['seed']}")
+def test_gpu_golden_base_sequences(case):
+    dc.replay_base_sequence(case, {})
+
+
+def test_gpu_consistent_hash_vectors():
+    """ConsistentHash golden vectors (recorded from the reference) through the device MD5 fallback."""
+    import numpy as np
+    import torch
+    from radixmesh_b200 import capi
+    from tests.parity import pack
+    for case in dc.golden("consistent_hash"):
+        addrs = case["addrs"]
+        ix = capi.DeviceIndex(mode=capi.MODE_ROUTER, n_prefill=len(addrs), n_decode=len(addrs), max_nodes=64,
+                              max_tokens=64, max_batch=64, max_key_len=512)
+        pts = np.asarray(case["ring"], dtype=np.uint32)
+        from oracle.radix_port import PortConsistentHash
+        h = PortConsistentHash(addrs)
+        own = np.asarray([addrs.index(h.owner[p]) for p in h.ring], dtype=np.int32)
+        ix.set_rings(pts, own, pts, own)
+        keys = [q["key"] for q in case["queries"]]
+        tk, offs = pack(keys)
+        n = len(keys)
+        dev = torch.device("cuda")
+        outs = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(4)]
+        err = torch.empty(n, dtype=torch.uint8, device=dev)
+        ix.route(torch.from_numpy(tk).to(dev), torch.from_numpy(offs).to(dev), n, False, outs[0], outs[1], outs[2], outs[3], err)
+        pa = outs[2].cpu().tolist()
+        assert [addrs[i] for i in pa] == [q["node"] for q in case["queries"]]
+        assert outs[3].cpu().tolist() == pa and err.cpu().tolist() == [0] * n
+        ix.close()
