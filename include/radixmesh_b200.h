@@ -185,6 +185,19 @@ int rm_route_batch(rm_index* idx, const int32_t* tokens, const int64_t* offsets,
 int rm_route_set_rings(rm_index* idx, const uint32_t* p_points_h, const int32_t* p_owner_h, int32_t n_p,
                        const uint32_t* d_points_h, const int32_t* d_owner_h, int32_t n_d);
 
+/*
+ * Mesh routing across the GPUs of one box (north_star item 4; no single counterpart in the reference,
+ * whose router reads owner ranks from its own replicated tree, radix_mesh.py:219-238).  GPU g hosts the
+ * tree of mesh node g holding the keys rank g inserted; after an all-gather of the per-GPU matched
+ * lengths, depths[g*B + q], this picks prefill = lowest prefill rank with the deepest match (> 0),
+ * decode = lowest decode rank with the deepest match if strictly deeper than the prefill match, then
+ * applies the same address lookup / consistent-hash fallback as rm_route_batch.  `idx` supplies
+ * n_prefill / n_decode and the rings.
+ */
+int rm_pick_batch(rm_index* idx, const int32_t* depths, int32_t n_ranks, const int32_t* tokens,
+                  const int64_t* offsets, int32_t B, int32_t* out_prefill, int32_t* out_decode,
+                  int32_t* out_paddr, int32_t* out_daddr, uint8_t* out_err, void* stream);
+
 /* evictable_size / protected_size / node count (radix_cache.py:232-237).  Synchronises. */
 int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream);
 

@@ -1,6 +1,8 @@
 """Build libradixmesh_b200.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).
 
-    python -m radixmesh_b200.build [--force]
+    python radixmesh_b200/build.py [--force] [-v]
+
+Run it as a script (not with -m): importing the package itself requires the library to exist.
 """
 import os
 import subprocess

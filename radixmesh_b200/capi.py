@@ -56,6 +56,7 @@ _PROTOS = {
     "rm_gc_candidates": (C.c_int, [_P, C.c_int32, _P, _P, _P]),
     "rm_dup_entries": (C.c_int, [_P, C.c_int32, _P, _P, _P]),
     "rm_route_batch": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P]),
+    "rm_pick_batch": (C.c_int, [_P, _P, C.c_int32, _P, _P, C.c_int32, _P, _P, _P, _P, _P, _P]),
     "rm_route_set_rings": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, C.c_int32]),
     "rm_sizes": (C.c_int, [_P, C.POINTER(RmSizes), _P]),
     "rm_dump": (C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
@@ -71,7 +72,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     path = path or LIB_PATH
     if not os.path.exists(path):
         raise ImportError(
-            f"radixmesh_b200: {path} is missing. Build it with `python -m radixmesh_b200.build` "
+            f"radixmesh_b200: {path} is missing. Build it with `python radixmesh_b200/build.py` "
             "(nvcc, sm_100a); this package has no CPU fallback.")
     lib = C.CDLL(path)
     for name, (res, args) in _PROTOS.items():
@@ -229,6 +230,11 @@ class DeviceIndex:
         with self._mutex:
             self._check(self.lib.rm_route_batch(self._h, ptr(tokens), ptr(offsets), B, 1 if warm else 0, ptr(out_prefill),
                                                 ptr(out_decode), ptr(out_paddr), ptr(out_daddr), ptr(out_err), self._s()))
+
+    def pick(self, depths, n_ranks, tokens, offsets, B, out_prefill, out_decode, out_paddr, out_daddr, out_err) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_pick_batch(self._h, ptr(depths), n_ranks, ptr(tokens), ptr(offsets), B, ptr(out_prefill),
+                                               ptr(out_decode), ptr(out_paddr), ptr(out_daddr), ptr(out_err), self._s()))
 
     def set_rings(self, p_points: np.ndarray, p_owner: np.ndarray, d_points: np.ndarray, d_owner: np.ndarray) -> None:
         p_points = np.ascontiguousarray(p_points, dtype=np.uint32)

@@ -230,6 +230,50 @@ extern "C" int rm_route_batch(rm_index* idx, const int32_t* tokens, const int64_
                          out_err, (cudaStream_t)stream);
 }
 
+// K9 pick: after the all-gather of per-GPU match depths (GPU g's tree holds the keys rank g inserted),
+// choose the prefill / decode rank the way the reference's router tree would:
+// deepest owner among prefill ranks; a decode rank only if it is strictly deeper; lowest rank on ties.
+__global__ void __launch_bounds__(RM_RT_TPB)
+rm_pick_kernel(const int* __restrict__ depths, int n_ranks, int B, int n_prefill, int n_decode, int* __restrict__ prefill,
+               int* __restrict__ decode, unsigned char* __restrict__ err) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= B) return;
+  int bp = 0, bd = 0, pr = -1, dr = -1;
+  for (int g = 0; g < n_ranks; ++g) {
+    const int d = depths[(size_t)g * B + q];
+    if (g < n_prefill) {
+      if (d > bp) {
+        bp = d;
+        pr = g;
+      }
+    } else if (g < n_prefill + n_decode) {
+      if (d > bd) {
+        bd = d;
+        dr = g;
+      }
+    }
+  }
+  prefill[q] = bp > 0 ? pr : -1;
+  decode[q] = (bd > 0 && bd > bp) ? dr : -1;
+  err[q] = 0;
+}
+
+extern "C" int rm_pick_batch(rm_index* idx, const int32_t* depths, int32_t n_ranks, const int32_t* tokens,
+                             const int64_t* offsets, int32_t B, int32_t* out_prefill, int32_t* out_decode,
+                             int32_t* out_paddr, int32_t* out_daddr, uint8_t* out_err, void* stream) {
+  if (!idx || B < 0 || n_ranks < 1) return RM_E_INVALID;
+  if (B == 0) return RM_OK;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RM_LAUNCH(rm_pick_kernel, (B + RM_RT_TPB - 1) / RM_RT_TPB, RM_RT_TPB, s, depths, n_ranks, B, idx->cfg.n_prefill,
+            idx->cfg.n_decode, out_prefill, out_decode, out_err);
+  RM_LAUNCH(rm_route_finish_kernel, (B + RM_RT_TPB - 1) / RM_RT_TPB, RM_RT_TPB, s, idx->t, tokens, (const i64*)offsets, B, 1,
+            out_prefill, out_decode, out_err, out_paddr, out_daddr, idx->ring_p, idx->ring_p_owner, idx->ring_p_n,
+            idx->ring_d, idx->ring_d_owner, idx->ring_d_n);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
 static int rm_set_ring(unsigned** dpts, int** down, int* dn, const uint32_t* pts_h, const int32_t* own_h, int n) {
   if (*dpts) cudaFree(*dpts);
   if (*down) cudaFree(*down);
