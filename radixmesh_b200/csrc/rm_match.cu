@@ -176,7 +176,12 @@ __global__ void __launch_bounds__(RM_MATCH_TPB)
 rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
                     int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
                     unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
-  const int q = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
+  // flags >> 4 = log2(lanes left idle per query lane), a measurement knob: spreading the same queries
+  // over more warps trades issue slots for latency hiding
+  const int spread = flags >> 4;
+  const unsigned gt = blockIdx.x * (unsigned)blockDim.x + threadIdx.x;
+  if (spread && (gt & ((1u << spread) - 1u))) return;
+  const int q = (int)(gt >> spread);
   if (q >= B) return;
   const i64 o0 = qoff[q];
   const int L = (int)(qoff[q + 1] - o0);
@@ -212,7 +217,13 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
     if (1 < L) g1 = rm_ld_query(key + 1, qpol);
     if (2 < L) g2 = rm_ld_query(key + 2, qpol);
   }
+  // A lone warp showed ~490 ns per hop against an L2 hit of ~215 ns: the time between a slot arriving
+  // and the next probe leaving is on the critical path of every hop.  So each iteration first does the
+  // minimum needed to issue the next probe (key compare, next token, hash, load) and only then the
+  // bookkeeping (stamps, router state, look-ahead), which overlaps with the load's latency.
   while (true) {
+    int st1 = -1, st2 = -1;             // nodes this iteration has to stamp (done last)
+    bool finish = false;
     if (pend) {
       // ---- verify the chunk requested in the previous iteration
       const int lim = min(pn - pdone, RM_CH);
@@ -244,7 +255,7 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
         req = ((u64)(unsigned)pc << len_bits) | (u64)(unsigned)pdone;
         break;
       }
-      if (!(flags & 1)) atomicMax(stamp + pc, seq);      // radix_cache.py:260 / radix_mesh.py:257
+      st1 = pc;                         // radix_cache.py:260 / radix_mesh.py:257
       if (ROUTER) {
         ++cnt;
         deepest = prank;
@@ -257,69 +268,78 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
       }
       pos += pdone;
       node = pc;
-      if (partial) break;
+      finish = partial;
     }
-    if (!have_probe) break;             // the query ended exactly at a node boundary
-    // ---- resolve the probe in flight (one step of linear probing per iteration)
-    if ((unsigned)S.a.x != want_tok || (unsigned)S.a.y != want_par) {
-      if ((S.a.x & S.a.y) == -1) break;  // empty slot: no child starts with this token
-      si = (si + 1) & tmask;
-      S = rm_ld_slot(table + si);
-      continue;
-    }
-    const int c = S.a.z, elen = S.a.w;
-    const int nxt = pos + elen;
-    if (elen == 1) {
-      // ---- one-token edge (89 % of the hops of a Zipf workload): matched by the key itself; commit now
-      if (!(flags & 1)) atomicMax(stamp + c, seq);
-      if (ROUTER) {
-        const int r = S.b.z;
-        ++cnt;
-        deepest = r;
-        if (r < t.n_prefill) {
-          last_prefill = r;
-          bad_below = false;
-        } else if (r >= t.n_prefill + t.n_decode) {
-          bad_below = true;
+    if (!finish) {
+      if (!have_probe) {
+        finish = true;                  // the query ended exactly at a node boundary
+      } else if ((unsigned)S.a.x != want_tok || (unsigned)S.a.y != want_par) {
+        // ---- linear probing: one step per iteration
+        if ((S.a.x & S.a.y) == -1) {
+          finish = true;                // empty slot: no child starts with this token
+        } else {
+          si = (si + 1) & tmask;
+          S = rm_ld_slot(table + si);
         }
-      }
-      node = c;
-      pos = nxt;
-      have_probe = nxt < L;
-      want_tok = (unsigned)g1;
-      g1 = g2;
-    } else {
-      // ---- multi-token edge: verify it next iteration, keep walking speculatively
-      pc = c;
-      pelen = elen;
-      pn = min(elen, L - pos);
-      pdone = 1;                        // token 0 is equal by construction of the table key
-      pend = true;
-      if (ROUTER) prank = S.b.z;
-      pe = t.tok + (i64)(((u64)(unsigned)S.b.y << 32) | (unsigned)S.b.x);
-      have_probe = nxt < L;
-      if (have_probe) {
-        want_tok = (unsigned)rm_ld_query(key + nxt, qpol);
-        g1 = (nxt + 1 < L) ? rm_ld_query(key + nxt + 1, qpol) : 0;
-      }
-      const int* __restrict__ ee = pe + 1;
-      const int* __restrict__ kk = key + pos + 1;
-      const int l2 = pn - 1;
+      } else {
+        // ---- hit: issue the probe of the following hop before anything else
+        const int c = S.a.z, elen = S.a.w;
+        const int eoff_lo = S.b.x, eoff_hi = S.b.y, erank = S.b.z;
+        const int nxt = pos + elen;
+        have_probe = nxt < L;
+        int tk = g1;
+        if (elen != 1 && have_probe) tk = rm_ld_query(key + nxt, qpol);
+        if (have_probe) {
+          want_par = (unsigned)c;
+          want_tok = (unsigned)tk;
+          si = rm_hash2((unsigned)c, want_tok, tshift);
+          S = rm_ld_slot(table + si);
+        }
+        if (elen == 1) {
+          // one-token edge (89 % of the hops of a Zipf workload): matched by the key itself
+          st2 = c;
+          if (ROUTER) {
+            ++cnt;
+            deepest = erank;
+            if (erank < t.n_prefill) {
+              last_prefill = erank;
+              bad_below = false;
+            } else if (erank >= t.n_prefill + t.n_decode) {
+              bad_below = true;
+            }
+          }
+          node = c;
+          pos = nxt;
+          g1 = g2;
+        } else {
+          // multi-token edge: verified next iteration while the walk continues speculatively
+          pc = c;
+          pelen = elen;
+          pn = min(elen, L - pos);
+          pdone = 1;                    // token 0 is equal by construction of the table key
+          pend = true;
+          if (ROUTER) prank = erank;
+          pe = t.tok + (i64)(((u64)(unsigned)eoff_hi << 32) | (unsigned)eoff_lo);
+          g1 = (nxt + 1 < L) ? rm_ld_query(key + nxt + 1, qpol) : 0;
+          const int* __restrict__ ee = pe + 1;
+          const int* __restrict__ kk = key + pos + 1;
+          const int l2 = pn - 1;
 #pragma unroll
-      for (int x = 0; x < RM_CH; ++x) {
-        if (x < l2) {
-          ca[x] = __ldg(ee + x);
-          cb[x] = rm_ld_query(kk + x, qpol);
+          for (int x = 0; x < RM_CH; ++x) {
+            if (x < l2) {
+              ca[x] = __ldg(ee + x);
+              cb[x] = rm_ld_query(kk + x, qpol);
+            }
+          }
         }
+        g2 = (nxt + 2 < L) ? rm_ld_query(key + nxt + 2, qpol) : 0;
       }
     }
-    if (have_probe) {
-      // request the next hop's slot (speculative while an edge is pending) and top up the look-ahead
-      g2 = (nxt + 2 < L) ? rm_ld_query(key + nxt + 2, qpol) : 0;
-      want_par = (unsigned)c;
-      si = rm_hash2((unsigned)c, want_tok, tshift);
-      S = rm_ld_slot(table + si);
+    if (!(flags & 1)) {
+      if (st1 >= 0) atomicMax(stamp + st1, seq);
+      if (st2 >= 0) atomicMax(stamp + st2, seq);
     }
+    if (finish) break;
   }
   out_len[q] = pos;
   out_node[q] = node;
@@ -551,7 +571,8 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
       // RM_EXP_FLAGS: measurement experiments only (bit 0 = skip the stamp atomics; results then differ
       // from the reference in eviction order, never use it outside a profiling run)
       static const int exp_flags = getenv("RM_EXP_FLAGS") ? atoi(getenv("RM_EXP_FLAGS")) : 0;
-      RM_LAUNCH(k, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+      const int grid2 = (int)(((threads << (exp_flags >> 4)) + tpb - 1) / tpb);
+      RM_LAUNCH(k, grid2, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
                 idx->sc.key[0], idx->sc.val[0], ro, exp_flags);
     } break;
     RM_CASE(2)
