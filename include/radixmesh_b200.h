@@ -160,6 +160,14 @@ int rm_lock_batch(rm_index* idx, const int32_t* nodes, const int32_t* gens, int3
 int rm_evict(rm_index* idx, int64_t num_tokens, int32_t cap, int32_t* out_nodes_h, int64_t* out_offs_h,
              int32_t* out_lens_h, int32_t* out_n_h, void* stream);
 
+/*
+ * Maintenance (no counterpart in the reference, whose Python objects are garbage collected): slide all
+ * live key/value runs to the front of fresh edge arenas and rebuild the child table, reclaiming the
+ * space of evicted nodes and dropping tombstones.  Node ids and everything observable stay the same.
+ * Allocates the new arenas, frees the old ones, synchronises.
+ */
+int rm_compact(rm_index* idx, void* stream);
+
 /* RadixMesh._gc candidate scan (radix_mesh.py:151-156): entries of dup_nodes whose parked node is
  * not None and has lock_ref == 0.  out_h rows are (tree node id, rank, parked node id).  Synchronises. */
 int rm_gc_candidates(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h, void* stream);

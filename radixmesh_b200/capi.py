@@ -53,6 +53,7 @@ _PROTOS = {
     "rm_insert_batch_h": (C.c_int, [_P, _P, _P, _P, _P, C.c_int32, _P, _P]),
     "rm_lock_batch": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, _P, _P]),
     "rm_evict": (C.c_int, [_P, C.c_int64, C.c_int32, _P, _P, _P, _P, _P]),
+    "rm_compact": (C.c_int, [_P, _P]),
     "rm_gc_candidates": (C.c_int, [_P, C.c_int32, _P, _P, _P]),
     "rm_dup_entries": (C.c_int, [_P, C.c_int32, _P, _P, _P]),
     "rm_route_batch": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P]),
@@ -216,6 +217,10 @@ class DeviceIndex:
             self._check(self.lib.rm_evict(self._h, int(num_tokens), cap, ptr(nodes), ptr(offs), ptr(lens), C.addressof(n), self._s()))
         k = n.value
         return nodes[:k], offs[:k], lens[:k]
+
+    def compact(self) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_compact(self._h, self._s()))
 
     def dup_entries(self, only_candidates: bool = False) -> np.ndarray:
         cap = int(self.cfg.max_dups) * 2 + 16

@@ -108,7 +108,8 @@ int rm_create(const rm_config* cfg, rm_index** out) {
     return RM_E_INVALID;
   }
   if (cfg->max_nodes < 2 || cfg->max_nodes > (1ll << 29) || cfg->max_tokens < 1 || cfg->max_batch < 1 ||
-      cfg->max_key_len < 1 || cfg->mode < RM_MODE_BASE || cfg->mode > RM_MODE_ROUTER) {
+      cfg->max_key_len < 1 || cfg->max_key_len > RM_MAX_EDGE_LEN || cfg->n_prefill < 0 || cfg->n_decode < 0 ||
+      cfg->n_prefill + cfg->n_decode > 250 || cfg->self_rank > 253 || cfg->mode < RM_MODE_BASE || cfg->mode > RM_MODE_ROUTER) {
     rm_set_error("rm_create: max_nodes/max_tokens/max_batch/max_key_len/mode out of range");
     return RM_E_INVALID;
   }
@@ -379,6 +380,7 @@ int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream) {
   out_h->op_seq = (int64_t)idx->op_seq;
   out_h->device_error = c.err;
   out_h->pad = c.node_hwm;
+  if (getenv("RM_DEBUG_COUNTERS")) fprintf(stderr, "[rm] n_req %d groups %d max_group %d\n", c.n_req, c.dbg_groups, c.dbg_max_group);
   return RM_OK;
 }
 

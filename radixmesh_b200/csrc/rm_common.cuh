@@ -32,13 +32,17 @@ typedef long long i64;
 #define RM_NO_REQ 0xFFFFFFFFFFFFFFFFull
 
 struct __align__(32) RmSlot {
-  u64 key;        // (parent id << 32) | first token of the child's edge
-  int child;      // child node id
-  int edge_len;   // tokens on the child's edge
-  i64 edge_off;   // start of the edge in the arenas
-  int rank;       // owner rank of the child's value (mesh modes)
-  int pad;
+  u64 key;            // (parent id << 32) | first token of the child's edge
+  int child;          // child node id
+  unsigned len_rank;  // edge length (low 24 bits) | (owner rank + 1) << 24
+  i64 edge_off;       // start of the edge in the arenas
+  int tok1, tok2;     // 2nd and 3rd token of the edge, inline: edges of <= 3 tokens (96 % of the hops of a
+                      // Zipf workload once first-sight splits have happened) are verified from the slot alone
 };
+#define RM_MAX_EDGE_LEN 0xFFFFFF
+__device__ __forceinline__ int rm_slot_len(unsigned w) { return (int)(w & 0xFFFFFFu); }
+__device__ __forceinline__ int rm_slot_rank(unsigned w) { return (int)(w >> 24) - 1; }
+__device__ __forceinline__ unsigned rm_slot_pack(int len, int rank) { return ((unsigned)len & 0xFFFFFFu) | ((unsigned)(rank + 1) << 24); }
 
 struct RmCounters {
   u64 free_head;      // node ids handed out  (ring of free ids)
@@ -53,6 +57,9 @@ struct RmCounters {
   int n_req;          // scratch: split requests of the current match batch
   int evict_n;        // scratch: nodes evicted by the current rm_evict
   int pad;
+  int n_big;          // scratch: split-request groups with more than one request (handled a warp each)
+  int dbg_max_group;  // largest split-request group seen (diagnostics)
+  int dbg_groups;     // split-request groups seen (diagnostics)
 };
 
 struct RmTree {
@@ -146,7 +153,7 @@ struct RmGroup {
 // of MB of query tokens through the same L2, so table slots are read with L2::evict_last (one
 // 256-bit LDG.E.ELL2 per slot) and query tokens with an evict-first policy.
 struct RmSlotRegs {
-  int4 a, b;   // a = {token, parent, child, edge_len}; b = {edge_off lo, edge_off hi, rank, pad}
+  int4 a, b;   // a = {token, parent, child, len_rank}; b = {edge_off lo, edge_off hi, tok1, tok2}
 };
 __device__ __forceinline__ RmSlotRegs rm_ld_slot(const RmSlot* p) {
   RmSlotRegs r;
@@ -195,9 +202,10 @@ __device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
       int4 b = COHERENT ? __ldcg(p + 1) : __ldg(p + 1);
       out.key = k;
       out.child = a.z;
-      out.edge_len = a.w;
+      out.len_rank = (unsigned)a.w;
       out.edge_off = (i64)(((u64)(unsigned)b.y << 32) | (unsigned)b.x);
-      out.rank = b.z;
+      out.tok1 = b.z;
+      out.tok2 = b.w;
       return (int)i;
     }
     if (k == RM_EMPTY_KEY) return -1;
@@ -205,16 +213,19 @@ __device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
   }
 }
 
-__device__ __forceinline__ void rm_slot_store(RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank) {
+__device__ __forceinline__ void rm_slot_store(const RmTree& t, RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank) {
   // payload first, key last.  No fence: inside one kernel only the warp that inserts a key looks it
   // up again (program order + __syncwarp cover that); every other reader runs in a later kernel.
   s->child = child;
-  s->edge_len = edge_len;
+  s->len_rank = rm_slot_pack(edge_len, rank);
   s->edge_off = edge_off;
-  s->rank = rank;
-  s->pad = 0;
+  s->tok1 = edge_len > 1 ? __ldcg(t.tok + edge_off + 1) : 0;   // the edge's tokens are in the arena already
+  s->tok2 = edge_len > 2 ? __ldcg(t.tok + edge_off + 2) : 0;
   *reinterpret_cast<volatile u64*>(&s->key) = key;
 }
+// in-place edits of a live slot (its key and edge start do not change, so the inline tokens stay valid)
+__device__ __forceinline__ void rm_slot_set_len(RmSlot* s, int len) { s->len_rank = (s->len_rank & 0xFF000000u) | ((unsigned)len & 0xFFFFFFu); }
+__device__ __forceinline__ void rm_slot_set_rank(RmSlot* s, int rank) { s->len_rank = (s->len_rank & 0xFFFFFFu) | ((unsigned)(rank + 1) << 24); }
 
 // Claim a free (empty or tombstoned) slot for `key` and fill it.  Caller guarantees the key is
 // not present.  One lane calls this.
@@ -227,7 +238,7 @@ __device__ __forceinline__ void rm_table_insert(const RmTree& t, u64 key, int ch
       // reserve with a key nobody looks up (parent id 0xFFFFFFFD never exists), then publish
       u64 reserve = 0xFFFFFFFD00000000ull | (unsigned)child;
       if (atomicCAS(kp, cur, reserve) == cur) {
-        rm_slot_store(&t.table[i], key, child, edge_len, edge_off, rank);
+        rm_slot_store(t, &t.table[i], key, child, edge_len, edge_off, rank);
         return;
       }
       continue;  // lost the race for this slot: look at it again

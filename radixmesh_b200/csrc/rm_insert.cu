@@ -100,7 +100,8 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       const int sidx = rm_find<true>(t, rm_key(node, key[pos]), s);
       if (sidx < 0) break;
       int c = s.child;
-      const int elen = s.edge_len;
+      const int elen = rm_slot_len(s.len_rank);
+      const int srank = rm_slot_rank(s.len_rank);
       const i64 eoff = s.edge_off;
       const int lim = min(elen, n - pos);
       // longest common prefix of the edge and the rest of the key (radix_cache.py:14-20)
@@ -127,12 +128,12 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           }
         }
         if (diff) {
-          if (s.rank <= owner) lost = true;   // keep(now, new): the lower rank wins
+          if (srank <= owner) lost = true;   // keep(now, new): the lower rank wins
           else swap = true;
         }
       } else if (MESH == 2) {
-        if (s.rank != owner) {
-          if (s.rank <= owner) lost = true;
+        if (srank != owner) {
+          if (srank <= owner) lost = true;
           else swap = true;
         }
       }
@@ -153,15 +154,15 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.edge_len[u] = m;
           t.depth_end[u] = t.depth_end[c] - elen + m;
           t.lock_ref[u] = t.lock_ref[c];
-          t.rank[u] = s.rank;
+          t.rank[u] = srank;
           t.nchild[u] = 1;
           t.gen[u] = 0;
           t.parked[u] = -1;
           t.stamp[u] = seq;
           atomicMax(&t.ctr->node_hwm, u + 1);
           t.table[sidx].child = u;
-          t.table[sidx].edge_len = m;
-          rm_table_insert(t, rm_key(u, __ldcg(t.tok + eoff + m)), c, elen - m, eoff + m, s.rank);
+          rm_slot_set_len(&t.table[sidx], m);
+          rm_table_insert(t, rm_key(u, __ldcg(t.tok + eoff + m)), c, elen - m, eoff + m, srank);
           t.parent[c] = u;
           t.edge_off[c] = eoff + m;
           t.edge_len[c] = elen - m;
@@ -174,11 +175,11 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       }
       if (MESH != 0 && swap) {
         // _swap_node (radix_mesh.py:466-495): the incoming (lower-rank) value takes the node
-        const int old_rank = s.rank;
+        const int old_rank = srank;
         if (MESH == 2) {
           if (g.lane == 0) {
             t.rank[target] = owner;
-            t.table[sidx].rank = owner;
+            rm_slot_set_rank(&t.table[sidx], owner);
           }
         } else {
           const int lk = __ldcg(t.lock_ref + target);
@@ -186,7 +187,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
             for (int x = g.lane; x < m; x += G) t.val[eoff + x] = val[pos + x];
             if (g.lane == 0) {
               t.rank[target] = owner;
-              t.table[sidx].rank = owner;
+              rm_slot_set_rank(&t.table[sidx], owner);
               rm_dup_put(t, target, old_rank, -1);
             }
           } else {
@@ -225,7 +226,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
               t.gen[target] = t.gen[target] + 1;
               t.stamp[target] = seq;
               t.table[sidx].edge_off = noff;
-              t.table[sidx].rank = owner;
+              rm_slot_set_rank(&t.table[sidx], owner);
               t.parked[d] = t.parked[target];
               t.parked[target] = d;
               // like the reference, neither size counter moves (radix_mesh.py:478-495)
@@ -257,6 +258,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.tok[noff + x] = key[pos + x];
           if (MESH != 2) t.val[noff + x] = val[pos + x];
         }
+        g.sync();   // the slot's inline tokens are read back from the arena
         if (g.lane == 0) {
           t.parent[leaf] = node;
           t.edge_off[leaf] = noff;

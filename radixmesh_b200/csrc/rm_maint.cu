@@ -47,6 +47,9 @@ __global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
     c.n_req = 0;
     c.evict_n = 0;
     c.pad = 0;
+    c.n_big = 0;
+    c.dbg_max_group = 0;
+    c.dbg_groups = 0;
     *t.ctr = c;
   }
 }
@@ -207,11 +210,23 @@ int rm_launch_lock(rm_index* idx, const int* nodes, int B, int dir, i64* out_del
 // Closed form of the heap loop: with one stamp per operation a parent's stamp is
 // never older than a child's, so leaves leave the heap in ascending (stamp, deeper first) order and
 // the evicted set is the shortest prefix of that order whose value lengths sum to >= num_tokens.
-__global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, u64* key, unsigned* val) {
+// A node can only be evicted after all its descendants, so a locked node pins every ancestor, whatever
+// the ancestors' own lock_ref (inc/dec pairs keep lock_ref monotone along a path, but nothing forces
+// callers to pair them: the heap loop of radix_cache.py:187-202 simply never reaches such a parent).
+__global__ void rm_evict_pin_kernel(RmTree t, int n, int* __restrict__ pinned) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || x == 0) return;
+  if (t.parent[x] < 0 || t.gen[x] < 0 || t.lock_ref[x] <= 0) return;
+  int y = t.parent[x];
+  while (y > 0 && atomicExch(&pinned[y], 1) == 0) y = t.parent[y];
+}
+
+__global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int* __restrict__ pinned, u64* key,
+                                     unsigned* val) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= n) return;
   u64 k = RM_NO_REQ;
-  if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0) {
+  if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0 && pinned[x] == 0) {
     u64 dmask = (1ull << depth_bits) - 1ull;
     k = (t.stamp[x] << depth_bits) | (dmask - (u64)(unsigned)t.depth_end[x]);
   }
@@ -327,7 +342,11 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
   if (n <= 1 || num_tokens <= 0 || cap <= 0) return RM_OK;
   const int depth_bits = idx->len_bits;
   const int bits = rm_bits_for(idx->op_seq * 2 + 1) + depth_bits + 1;
-  RM_LAUNCH(rm_evict_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, sc.ev_key[0], sc.ev_val[0]);
+  int* pinned = sc.ev_lens;   // free until rm_evict_apply_kernel writes the evicted lengths
+  RM_CUDA(cudaMemsetAsync(pinned, 0, sizeof(int) * (size_t)n, s));
+  RM_LAUNCH(rm_evict_pin_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, pinned);
+  RM_LAUNCH(rm_evict_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_key[0],
+            sc.ev_val[0]);
   const int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, bits, sc.ev_hist, s);
 #ifdef RM_EMU
   RM_LAUNCH(rm_evict_cut_kernel, 1, 1, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, cap);
@@ -389,5 +408,146 @@ int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int*
     RM_CUDA(cudaStreamSynchronize(s));
   }
   *out_n_h = n;
+  return RM_OK;
+}
+
+// ------------------------------------------------------------------ arena compaction + table rebuild
+// Eviction frees node ids and tombstones table slots, but the edge arenas are bump allocated: under
+// streaming inserts at steady occupancy (BASELINE configs[2]) the space of evicted runs has to be
+// reclaimed.  rm_compact slides every live run (tree nodes and parked duplicates) to the front of fresh
+// arenas in node-id order, rewrites edge_off, and rebuilds the child table from the node pool (which
+// also drops the tombstones).  A maintenance call: it allocates the new arenas and synchronises.
+__global__ void rm_compact_len_kernel(RmTree t, int n, i64* __restrict__ len_out) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n) return;
+  const bool live = x > 0 && (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
+  len_out[x] = live ? (i64)t.edge_len[x] : 0;
+}
+
+// exclusive scan of n i64 values in place, one block (maintenance path: simplicity over speed)
+__global__ void rm_scan_i64_kernel(i64* __restrict__ data, int n, i64* __restrict__ total) {
+#ifdef RM_EMU
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  i64 run = 0;
+  for (int i = 0; i < n; ++i) {
+    i64 v = data[i];
+    data[i] = run;
+    run += v;
+  }
+  *total = run;
+#else
+  __shared__ i64 warp_tot[32];
+  __shared__ i64 carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int base = 0; base < n; base += 1024) {
+    const i64 carry = carry_s;
+    const int j = base + threadIdx.x;
+    const i64 v = j < n ? data[j] : 0;
+    i64 inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      i64 o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) warp_tot[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+      i64 w = warp_tot[lane], winc = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        i64 o = __shfl_up_sync(0xffffffffu, winc, d);
+        if (lane >= d) winc += o;
+      }
+      warp_tot[lane] = winc - w;
+    }
+    __syncthreads();
+    const i64 incl = carry + warp_tot[wid] + inc;
+    if (j < n) data[j] = incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry_s;
+#endif
+}
+
+template <int G>
+__global__ void rm_compact_copy_kernel(RmTree t, int n, const i64* __restrict__ new_off, int* __restrict__ ntok,
+                                       i64* __restrict__ nval, int with_values) {
+  RmGroup<G> g;
+  const int x = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (x >= n || x == 0) return;
+  const bool live = (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
+  if (!live) return;
+  const i64 src = t.edge_off[x], dst = new_off[x];
+  const int len = t.edge_len[x];
+  for (int k = g.lane; k < len; k += G) {
+    ntok[dst + k] = t.tok[src + k];
+    if (with_values) nval[dst + k] = t.val[src + k];
+  }
+}
+
+// after the arenas were swapped: new offsets into the node pool, then one table slot per tree node
+__global__ void rm_compact_relink_kernel(RmTree t, int n, const i64* __restrict__ new_off) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || x == 0) return;
+  const bool live = (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
+  if (!live) return;
+  const i64 off = new_off[x];
+  t.edge_off[x] = off;
+  if (t.gen[x] >= 0)   // parked duplicates are not reachable from the table
+    rm_table_insert(t, rm_key(t.parent[x], t.tok[off]), x, t.edge_len[x], off, t.rank[x]);
+}
+
+extern "C" int rm_compact(rm_index* idx, void* stream) {
+  if (!idx) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RmTree& t = idx->t;
+  RmCounters c;
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  const int n = c.node_hwm;
+  const bool with_values = idx->cfg.mode != RM_MODE_ROUTER;
+  i64* new_off = reinterpret_cast<i64*>(idx->sc.ev_key[0]);   // scratch sized max_nodes x 8 bytes
+  i64* total_d = reinterpret_cast<i64*>(idx->sc.ev_key[1]);
+  RM_LAUNCH(rm_compact_len_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, new_off);
+#ifdef RM_EMU
+  RM_LAUNCH(rm_scan_i64_kernel, 1, 1, s, new_off, n, total_d);
+#else
+  RM_LAUNCH(rm_scan_i64_kernel, 1, 1024, s, new_off, n, total_d);
+#endif
+  int* ntok = nullptr;
+  i64* nval = nullptr;
+  RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&ntok), sizeof(int) * (size_t)t.max_tokens));
+  if (with_values) RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&nval), sizeof(i64) * (size_t)t.max_tokens));
+#ifdef RM_EMU
+  auto kc = rm_compact_copy_kernel<1>;
+  const long long cthreads = n;
+#else
+  auto kc = rm_compact_copy_kernel<32>;
+  const long long cthreads = (long long)n * 32;
+#endif
+  RM_LAUNCH(kc, (int)((cthreads + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, n, new_off, ntok, nval, with_values ? 1 : 0);
+  RM_CUDA(cudaGetLastError());
+  RM_CUDA(cudaStreamSynchronize(s));
+  // swap the arenas in, drop the old ones
+  cudaFree(t.tok);
+  t.tok = ntok;
+  if (with_values) {
+    cudaFree(t.val);
+    t.val = nval;
+  }
+  RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
+  RM_LAUNCH(rm_compact_relink_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, new_off);
+  i64 total = 0;
+  RM_CUDA(cudaMemcpyAsync(&total, total_d, sizeof(i64), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  const u64 top = (u64)total;
+  RM_CUDA(cudaMemcpyAsync(&t.ctr->arena_top, &top, sizeof(u64), cudaMemcpyHostToDevice, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  RM_CUDA(cudaGetLastError());
   return RM_OK;
 }

@@ -67,7 +67,7 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
       k = ((u64)(unsigned)sa.y << 32) | (unsigned)sa.x;
     }
     if (k != want) break;  // no child starts with this token
-    const int c = sa.z, elen = sa.w, crank = sb.z;
+    const int c = sa.z, elen = rm_slot_len((unsigned)sa.w), crank = rm_slot_rank((unsigned)sa.w);
     const i64 eoff = (i64)(((u64)(unsigned)sb.y << 32) | (unsigned)sb.x);
     const int n = min(elen, L - pos);
     // issue the next hop's probe now (speculative: only used if this edge matches in full)
@@ -160,24 +160,23 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
   }
 }
 
-// K1, lane-per-query form (the default).  ncu on the group form showed the walk is latency bound
-// (long-scoreboard stalls at three points of every hop: the slot, the query token that forms the next
-// key, the edge tokens) and that lanes idle while a neighbour compares a long edge (9.9 of 32 lanes
-// active per instruction; 89 % of the edges a Zipf workload walks are one token long).
-// Here every lane owns one query and the hop loop is software pipelined so that an iteration waits
-// ONCE: the slot of hop i+1 and the edge tokens of hop i are requested together in iteration i and
-// consumed together at the top of iteration i+1.  Hop i is only committed (stamped, position advanced)
-// after its edge has been verified; the probe for hop i+1 is speculative until then.  Long edges are
-// verified RM_CH tokens per iteration while the lane's other state stands still, so lanes on many
-// one-token edges and lanes on one long edge advance side by side.
+// K1, lane-per-query form (the default).  What the measurements said (profiles/README.md):
+//   * the walk is a chain of dependent loads; a lone warp of the group form needs ~490 ns per hop while a
+//     32-byte slot read from L2 costs ~200 ns (tools/chase.cu), the rest being instructions executed
+//     between a slot's arrival and the next probe's issue;
+//   * 89 % of the edges a Zipf workload walks are one token long and 96 % at most three, because every
+//     first-sight match splits at its divergence point.
+// So: one lane per query; the slot carries the edge's 2nd and 3rd token inline, and the lane keeps the
+// next three query tokens in registers, so an edge of <= 3 tokens is verified, committed and followed by
+// the next probe without touching the arena or the query again.  Longer edges are rare: they are
+// verified RM_CH tokens per loop iteration, non-speculatively, while the other lanes keep hopping.
 #define RM_CH 4
 template <bool SPLIT, bool ROUTER>
 __global__ void __launch_bounds__(RM_MATCH_TPB)
 rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
                     int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
                     unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
-  // flags >> 4 = log2(lanes left idle per query lane), a measurement knob: spreading the same queries
-  // over more warps trades issue slots for latency hiding
+  // flags >> 4 = log2(lanes left idle per query lane), a measurement knob (see tools/)
   const int spread = flags >> 4;
   const unsigned gt = blockIdx.x * (unsigned)blockDim.x + threadIdx.x;
   if (spread && (gt & ((1u << spread) - 1u))) return;
@@ -192,22 +191,19 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
   u64* __restrict__ stamp = t.stamp;
   const u64 qpol = rm_policy_evict_first();
 
-  int node = 0, pos = 0;               // committed: `node` is matched in full through `pos`
+  int node = 0, pos = 0;               // `node` is matched in full through `pos`
   u64 req = RM_NO_REQ;
   int cnt = 0, deepest = -1, last_prefill = -1;
   bool bad_below = false;
 
-  // probe in flight: the slot looked up with (want_par, want_tok)
-  RmSlotRegs S;
+  RmSlotRegs S;                        // probe in flight, keyed (want_par, key[pos])
   unsigned want_par = 0, want_tok = 0, si = 0;
-  // the two query tokens after want_tok (kept ahead of the walk so that after a one-token edge the
-  // next key needs no load on the dependent chain)
-  int g1 = 0, g2 = 0;
-  // pending multi-token edge: found by its first token, remaining tokens not verified yet
+  int g1 = 0, g2 = 0, g3 = 0;          // key[pos+1], key[pos+2], key[pos+3] (0 past the end; lengths guard their use)
+  // long edge being verified: found by its first three tokens, the rest not compared yet
   bool pend = false;
   int pc = 0, pelen = 0, pn = 0, pdone = 0, prank = 0;
   const int* __restrict__ pe = nullptr;
-  int ca[RM_CH], cb[RM_CH];            // chunk of edge / query tokens requested last iteration
+  int ca[RM_CH], cb[RM_CH];
 
   bool have_probe = L > 0;
   if (have_probe) {
@@ -216,24 +212,19 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
     S = rm_ld_slot(table + si);
     if (1 < L) g1 = rm_ld_query(key + 1, qpol);
     if (2 < L) g2 = rm_ld_query(key + 2, qpol);
+    if (3 < L) g3 = rm_ld_query(key + 3, qpol);
   }
-  // A lone warp showed ~490 ns per hop against an L2 hit of ~215 ns: the time between a slot arriving
-  // and the next probe leaving is on the critical path of every hop.  So each iteration first does the
-  // minimum needed to issue the next probe (key compare, next token, hash, load) and only then the
-  // bookkeeping (stamps, router state, look-ahead), which overlaps with the load's latency.
   while (true) {
-    int st1 = -1, st2 = -1;             // nodes this iteration has to stamp (done last)
-    bool finish = false;
+    int c, elen, m, erank;              // the edge decided in this iteration: m of its elen tokens match
     if (pend) {
-      // ---- verify the chunk requested in the previous iteration
+      // ---- long edge: verify the chunk requested in the previous iteration
       const int lim = min(pn - pdone, RM_CH);
-      int m = lim;
+      int mm = lim;
 #pragma unroll
       for (int x = RM_CH - 1; x >= 0; --x)
-        if (x < lim && ca[x] != cb[x]) m = x;
-      pdone += m;
-      if (m == lim && pdone < pn) {
-        // long edge: request the next chunk, nothing else moves
+        if (x < lim && ca[x] != cb[x]) mm = x;
+      pdone += mm;
+      if (mm == lim && pdone < pn) {
         const int* __restrict__ ee = pe + pdone;
         const int* __restrict__ kk = key + pos + pdone;
         const int l2 = pn - pdone;
@@ -246,100 +237,123 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
         }
         continue;
       }
-      // ---- the edge is decided: pdone of its pelen tokens match
       pend = false;
-      const bool partial = pdone < pelen;
-      if (SPLIT && partial) {
-        // the reference splits pc here and returns the new upper node (radix_cache.py:262-266); K3 does it
-        pos += pdone;
-        req = ((u64)(unsigned)pc << len_bits) | (u64)(unsigned)pdone;
-        break;
+      c = pc;
+      elen = pelen;
+      m = pdone;
+      erank = prank;
+    } else {
+      if (!have_probe) break;           // the query ended exactly at a node boundary
+      // ---- resolve the probe in flight (one step of linear probing per iteration)
+      if ((unsigned)S.a.x != want_tok || (unsigned)S.a.y != want_par) {
+        if ((S.a.x & S.a.y) == -1) break;   // empty slot: no child starts with this token
+        si = (si + 1) & tmask;
+        S = rm_ld_slot(table + si);
+        continue;
       }
-      st1 = pc;                         // radix_cache.py:260 / radix_mesh.py:257
-      if (ROUTER) {
-        ++cnt;
-        deepest = prank;
-        if (prank < t.n_prefill) {
-          last_prefill = prank;
-          bad_below = false;
-        } else if (prank >= t.n_prefill + t.n_decode) {
-          bad_below = true;
-        }
+      c = S.a.z;
+      elen = rm_slot_len((unsigned)S.a.w);
+      erank = rm_slot_rank((unsigned)S.a.w);
+      const int n = min(elen, L - pos);
+      // tokens 1 and 2 of the edge are in the slot, tokens 1 and 2 after the key token are in g1, g2
+      m = 1;
+      if (n >= 2 && S.b.z == g1) {
+        m = 2;
+        if (n >= 3 && S.b.w == g2) m = 3;
       }
-      pos += pdone;
-      node = pc;
-      finish = partial;
-    }
-    if (!finish) {
-      if (!have_probe) {
-        finish = true;                  // the query ended exactly at a node boundary
-      } else if ((unsigned)S.a.x != want_tok || (unsigned)S.a.y != want_par) {
-        // ---- linear probing: one step per iteration
-        if ((S.a.x & S.a.y) == -1) {
-          finish = true;                // empty slot: no child starts with this token
-        } else {
-          si = (si + 1) & tmask;
-          S = rm_ld_slot(table + si);
-        }
-      } else {
-        // ---- hit: issue the probe of the following hop before anything else
-        const int c = S.a.z, elen = S.a.w;
-        const int eoff_lo = S.b.x, eoff_hi = S.b.y, erank = S.b.z;
+      if (elen <= 3 && m == elen) {
+        // ---- short edge matched in full: issue the next probe first, commit while it is in flight
+        const int tk = (elen == 1) ? g1 : (elen == 2) ? g2 : g3;
         const int nxt = pos + elen;
         have_probe = nxt < L;
-        int tk = g1;
-        if (elen != 1 && have_probe) tk = rm_ld_query(key + nxt, qpol);
         if (have_probe) {
           want_par = (unsigned)c;
           want_tok = (unsigned)tk;
           si = rm_hash2((unsigned)c, want_tok, tshift);
           S = rm_ld_slot(table + si);
         }
-        if (elen == 1) {
-          // one-token edge (89 % of the hops of a Zipf workload): matched by the key itself
-          st2 = c;
-          if (ROUTER) {
-            ++cnt;
-            deepest = erank;
-            if (erank < t.n_prefill) {
-              last_prefill = erank;
-              bad_below = false;
-            } else if (erank >= t.n_prefill + t.n_decode) {
-              bad_below = true;
-            }
-          }
-          node = c;
-          pos = nxt;
-          g1 = g2;
-        } else {
-          // multi-token edge: verified next iteration while the walk continues speculatively
-          pc = c;
-          pelen = elen;
-          pn = min(elen, L - pos);
-          pdone = 1;                    // token 0 is equal by construction of the table key
-          pend = true;
-          if (ROUTER) prank = erank;
-          pe = t.tok + (i64)(((u64)(unsigned)eoff_hi << 32) | (unsigned)eoff_lo);
-          g1 = (nxt + 1 < L) ? rm_ld_query(key + nxt + 1, qpol) : 0;
-          const int* __restrict__ ee = pe + 1;
-          const int* __restrict__ kk = key + pos + 1;
-          const int l2 = pn - 1;
-#pragma unroll
-          for (int x = 0; x < RM_CH; ++x) {
-            if (x < l2) {
-              ca[x] = __ldg(ee + x);
-              cb[x] = rm_ld_query(kk + x, qpol);
-            }
+        if (!(flags & 1)) atomicMax(stamp + c, seq);   // radix_cache.py:260 / radix_mesh.py:257
+        if (ROUTER) {
+          ++cnt;
+          deepest = erank;
+          if (erank < t.n_prefill) {
+            last_prefill = erank;
+            bad_below = false;
+          } else if (erank >= t.n_prefill + t.n_decode) {
+            bad_below = true;
           }
         }
-        g2 = (nxt + 2 < L) ? rm_ld_query(key + nxt + 2, qpol) : 0;
+        node = c;
+        pos = nxt;
+        // slide the three look-ahead tokens by elen
+        if (elen == 1) {
+          g1 = g2;
+          g2 = g3;
+        } else if (elen == 2) {
+          g1 = g3;
+          g2 = (nxt + 2 < L) ? rm_ld_query(key + nxt + 2, qpol) : 0;
+        } else {
+          g1 = (nxt + 1 < L) ? rm_ld_query(key + nxt + 1, qpol) : 0;
+          g2 = (nxt + 2 < L) ? rm_ld_query(key + nxt + 2, qpol) : 0;
+        }
+        g3 = (nxt + 3 < L) ? rm_ld_query(key + nxt + 3, qpol) : 0;
+        continue;
+      }
+      if (m == 3 && n > 3) {
+        // ---- long edge whose first three tokens match: compare the rest chunk by chunk
+        pend = true;
+        pc = c;
+        pelen = elen;
+        pn = n;
+        pdone = 3;
+        prank = erank;
+        pe = t.tok + (i64)(((u64)(unsigned)S.b.y << 32) | (unsigned)S.b.x);
+        const int* __restrict__ ee = pe + 3;
+        const int* __restrict__ kk = key + pos + 3;
+        const int l2 = n - 3;
+#pragma unroll
+        for (int x = 0; x < RM_CH; ++x) {
+          if (x < l2) {
+            ca[x] = __ldg(ee + x);
+            cb[x] = rm_ld_query(kk + x, qpol);
+          }
+        }
+        continue;
+      }
+      // otherwise the edge is decided right here with m < elen (mismatch or query exhausted)
+    }
+    // ---- an edge has been decided with m of its elen tokens matching, and it is not a fully matched short edge
+    const bool partial = m < elen;
+    if (SPLIT && partial) {
+      // the reference splits c here and returns the new upper node (radix_cache.py:262-266); K3 does it
+      pos += m;
+      req = ((u64)(unsigned)c << len_bits) | (u64)(unsigned)m;
+      break;
+    }
+    if (!(flags & 1)) atomicMax(stamp + c, seq);
+    if (ROUTER) {
+      ++cnt;
+      deepest = erank;
+      if (erank < t.n_prefill) {
+        last_prefill = erank;
+        bad_below = false;
+      } else if (erank >= t.n_prefill + t.n_decode) {
+        bad_below = true;
       }
     }
-    if (!(flags & 1)) {
-      if (st1 >= 0) atomicMax(stamp + st1, seq);
-      if (st2 >= 0) atomicMax(stamp + st2, seq);
-    }
-    if (finish) break;
+    pos += m;
+    node = c;
+    if (partial) break;                 // no-split modes: the partially matched child is the last node
+    // a long edge matched in full: only now look up the next hop
+    have_probe = pos < L;
+    if (!have_probe) break;
+    want_par = (unsigned)c;
+    want_tok = (unsigned)rm_ld_query(key + pos, qpol);
+    si = rm_hash2((unsigned)c, want_tok, tshift);
+    S = rm_ld_slot(table + si);
+    g1 = (pos + 1 < L) ? rm_ld_query(key + pos + 1, qpol) : 0;
+    g2 = (pos + 2 < L) ? rm_ld_query(key + pos + 2, qpol) : 0;
+    g3 = (pos + 3 < L) ? rm_ld_query(key + pos + 3, qpol) : 0;
   }
   out_len[q] = pos;
   out_node[q] = node;
@@ -374,19 +388,18 @@ template <int G>
 __global__ void __launch_bounds__(RM_MATCH_TPB)
 rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int Bmax, int len_bits,
                       u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
-                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min) {
+                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min, const int* __restrict__ big_list) {
   RmGroup<G> g;
-  const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
   const int B = min(t.ctr->n_req, Bmax);   // requests were appended compactly by K1, in no particular order
-  if (i >= B) return;
-  const u64 ki = skey[i];
-  if (ki == RM_NO_REQ) return;
-  const int c = (int)(ki >> len_bits);
-  if (i > 0) {
-    u64 kp = skey[i - 1];
-    if (kp != RM_NO_REQ && (int)(kp >> len_bits) == c) return;  // not the first request of its edge
-  }
   const u64 pmask = (1ull << len_bits) - 1ull;
+  // one group of lanes per edge that received SEVERAL requests (rm_split_single_kernel listed them and
+  // handled the single-request edges itself); grid-stride, the counts live on the device
+  const int n_big = t.ctr->n_big;
+  const int gstride = (int)((gridDim.x * (unsigned)blockDim.x) / G);
+  for (int w = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G); w < n_big; w += gstride) {
+  const int i = big_list[w];
+  const u64 ki = skey[i];
+  const int c = (int)(ki >> len_bits);
   // pass 1 (forward): extent of the group, distinct split points, rank of each request's point
   int e = i, U = 0;
   for (int base = i;; base += G) {
@@ -414,6 +427,10 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
     e = base + nvalid;
     if (nvalid < G) break;
   }
+  if (g.lane == 0) {
+    atomicMax(&t.ctr->dbg_max_group, e - i);
+    atomicAdd(&t.ctr->dbg_groups, 1);
+  }
   g.sync();
   // pass 2 (backward): sufmax[j] = max op seq over requests j' >= j of this edge
   {
@@ -435,7 +452,7 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
   u64 apos = 0;
   if (g.lane == 0) apos = rm_alloc_nodes(t, U);
   apos = g.bcast(apos, 0);
-  if (apos == ~0ull) return;
+  if (apos == ~0ull) continue;
   const int par = t.parent[c];
   const i64 off = t.edge_off[c];
   const int len = t.edge_len[c];
@@ -478,7 +495,7 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
         atomicMax(&t.ctr->err, (int)RM_E_INVALID);
       } else {
         t.table[sidx].child = u;
-        t.table[sidx].edge_len = p;
+        rm_slot_set_len(&t.table[sidx], p);
       }
     } else {
       rm_table_insert(t, rm_key(uprev, t.tok[off + a]), u, p - a, off + a, rk);
@@ -495,6 +512,67 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
   if (g.lane == 0) rm_add_i64(&t.ctr->n_nodes, (i64)U);
   // pass 4: every request's last node is the upper node that ends at its split point
   for (int j = i + g.lane; j < e; j += G) out_node[sval[j]] = rm_free_id_at(t, apos + (u64)krank[j]);
+  }
+}
+
+// K3, common case: an edge that received exactly ONE split request this batch (in steady state almost
+// all of them: ~10K single requests per 64K-query batch against a handful of shared ones).  One thread per
+// sorted request, so 32 independent splits share every memory round trip of a warp.  Edges with several
+// requests are only listed here; rm_split_apply_kernel takes them a warp each.
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_split_single_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int Bmax, int len_bits,
+                       u64 seq_base, int* __restrict__ out_node, int* __restrict__ big_list) {
+  const int B = min(t.ctr->n_req, Bmax);
+  const int i = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
+  if (i >= B) return;
+  const u64 ki = skey[i];
+  const int c = (int)(ki >> len_bits);
+  if (i > 0 && (int)(skey[i - 1] >> len_bits) == c) return;            // not the first request of its edge
+  if (i + 1 < B && (int)(skey[i + 1] >> len_bits) == c) {              // shared edge: a warp will do it
+    big_list[atomicAdd(&t.ctr->n_big, 1)] = i;
+    return;
+  }
+  const int p = (int)(ki & ((1ull << len_bits) - 1ull));
+  const unsigned q = sval[i];
+  const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
+  const u64 apos = rm_alloc_nodes(t, 1);
+  if (apos == ~0ull) return;
+  const int u = rm_free_id_at(t, apos);
+  const int par = t.parent[c];
+  const i64 off = t.edge_off[c];
+  const int len = t.edge_len[c];
+  const int dend = t.depth_end[c];
+  const int lk = t.lock_ref[c];
+  const int rk = t.rank[c];
+  const u64 st_c = t.stamp[c];
+  const u64 st = seq > st_c ? seq : st_c;       // the query stamped the whole edge, then split it
+  const int tok0 = t.tok[off], tokp = t.tok[off + p];
+  t.parent[u] = par;
+  t.edge_off[u] = off;
+  t.edge_len[u] = p;
+  t.depth_end[u] = dend - len + p;
+  t.lock_ref[u] = lk;       // radix_cache.py:283
+  t.rank[u] = rk;
+  t.nchild[u] = 1;
+  t.gen[u] = 0;
+  t.parked[u] = -1;
+  t.stamp[u] = st;
+  atomicMax(&t.ctr->node_hwm, u + 1);
+  RmSlot s;
+  const int sidx = rm_find<true>(t, rm_key(par, tok0), s);
+  if (sidx < 0) {
+    atomicMax(&t.ctr->err, (int)RM_E_INVALID);
+  } else {
+    t.table[sidx].child = u;
+    rm_slot_set_len(&t.table[sidx], p);
+  }
+  rm_table_insert(t, rm_key(u, tokp), c, len - p, off + p, rk);
+  t.parent[c] = u;
+  t.edge_off[c] = off + p;
+  t.edge_len[c] = len - p;
+  t.stamp[c] = st;
+  rm_add_i64(&t.ctr->n_nodes, (i64)1);
+  out_node[q] = u;
 }
 
 // K2: values along the matched path, written back to front by walking parent links from the last
@@ -622,10 +700,18 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], B, bits, sc.hist, s, &idx->t.ctr->n_req);
   RM_CUDA(cudaGetLastError());
   const long long threads = (long long)B * RM_WIDE_G;
-  const int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
+  int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
+#ifndef RM_EMU
+  if (grid > 148 * 8) grid = 148 * 8;    // persistent: 8 blocks of 8 warps per SM, grid-stride inside
+#endif
+  RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_big, 0, sizeof(int), s));
+  // edges with one request: a thread each; the others are listed in the spare half of the value ping-pong
+  int* big_list = reinterpret_cast<int*>(sc.val[w ^ 1]);
+  RM_LAUNCH(rm_split_single_kernel, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w],
+            B, idx->len_bits, seq_base, out_node, big_list);
   auto k3 = rm_split_apply_kernel<RM_WIDE_G>;
   RM_LAUNCH(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
-            sc.krank, sc.uniq_pos, sc.uniq_min);
+            sc.krank, sc.uniq_pos, sc.uniq_min, big_list);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }

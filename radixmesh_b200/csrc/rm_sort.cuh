@@ -11,13 +11,13 @@
 
 #define RM_SORT_TPB 256
 #define RM_SORT_WARPS (RM_SORT_TPB / 32)
-#define RM_SORT_MIN_TILE 256       // 8 warps x 1 round x 32 lanes
+#define RM_SORT_MIN_TILE 1024      // 8 warps x 4 rounds x 32 lanes: keeps the histogram table (256 x tiles) small
 #define RM_SORT_MAX_TILE 4096      // 8 warps x 16 rounds x 32 lanes
 
 // Items per block: small inputs get small tiles so that the grid still covers the 148 SMs (a 64K-item
 // sort with 4096-item tiles ran on 16 blocks and was latency bound); large inputs get 4096-item tiles.
 static inline int rm_sort_tile(int n) {
-  int t = (n + 295) / 296;                       // aim at >= 2 blocks per SM
+  int t = (n + 147) / 148;                       // aim at >= 1 block per SM
   t = (t + RM_SORT_MIN_TILE - 1) / RM_SORT_MIN_TILE * RM_SORT_MIN_TILE;
   if (t < RM_SORT_MIN_TILE) t = RM_SORT_MIN_TILE;
   if (t > RM_SORT_MAX_TILE) t = RM_SORT_MAX_TILE;
@@ -27,7 +27,7 @@ static inline int rm_sort_nblocks(int n) { int t = rm_sort_tile(n); return (n + 
 // u32 words of histogram scratch rm_sort_pairs needs for up to n items (worst case: smallest tiles)
 static inline size_t rm_sort_scratch_words(int n) {
   size_t nb_small = ((size_t)n + RM_SORT_MIN_TILE - 1) / RM_SORT_MIN_TILE;
-  size_t nb = nb_small < 296 ? nb_small : 296;
+  size_t nb = nb_small < 148 ? nb_small : 148;
   size_t nb_big = ((size_t)n + RM_SORT_MAX_TILE - 1) / RM_SORT_MAX_TILE;
   if (nb_big > nb) nb = nb_big;
   return (size_t)256 * (nb + 2) + 8;

@@ -95,6 +95,10 @@ def run_sequence(make_index, seed, n_steps=30, vocab=3, maxlen=8, batch=6):
             keep = [i for i in range(len(held_dev)) if held_dev[i] not in dead]
             held_dev = [held_dev[i] for i in keep]
             held_orc = [held_orc[i] for i in keep]
+            if rnd.random() < 0.5:
+                used = ix.sizes().arena_used
+                ix.compact()          # reclaims the evicted runs; nothing observable may change
+                assert ix.sizes().arena_used <= used
         ix.check_device_error()
         assert_same_tree(device_canonical(ix), orc.canonical())
     ix.close()
