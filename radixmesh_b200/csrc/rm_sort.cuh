@@ -50,18 +50,27 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_hist_kernel(const 
 }
 
 // Exclusive scan, in place, of the digit-major histogram table data[256][nb] (row d = counts of digit d
-// per tile).  One block: a warp per row sums it, one warp scans the 256 row totals, then every warp
-// rescans its rows from their base.  Two coalesced sweeps over the table, three block barriers.
+// per tile).  One block of 32 warps; warp w owns rows w, w+32, ..., w+224.  The eight rows of a warp are
+// walked together so that their loads are in flight at the same time (a row-after-row version spent
+// 15 us waiting on one L2 round trip after another).
 static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __restrict__ data, int nb) {
   __shared__ unsigned tot[256];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  for (int d = wid; d < 256; d += 32) {
-    const unsigned* row = data + (size_t)d * nb;
-    unsigned s = 0;
-    for (int j = lane; j < nb; j += 32) s += row[j];
+  {
+    unsigned s[8];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) tot[d] = s;
+    for (int r = 0; r < 8; ++r) s[r] = 0;
+    for (int j = lane; j < nb; j += 32) {
+#pragma unroll
+      for (int r = 0; r < 8; ++r) s[r] += data[(size_t)(wid + 32 * r) * nb + j];
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      unsigned v = s[r];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) tot[wid + 32 * r] = v;
+    }
   }
   __syncthreads();
   if (wid == 0) {
@@ -86,20 +95,24 @@ static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __re
     }
   }
   __syncthreads();
-  for (int d = wid; d < 256; d += 32) {
-    unsigned* row = data + (size_t)d * nb;
-    unsigned run = tot[d];
-    for (int j0 = 0; j0 < nb; j0 += 32) {
-      const int j = j0 + lane;
-      const unsigned v = j < nb ? row[j] : 0u;
-      unsigned inc = v;
+  unsigned run[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) run[r] = tot[wid + 32 * r];
+  for (int j0 = 0; j0 < nb; j0 += 32) {
+    const int j = j0 + lane;
+    unsigned v[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) v[r] = j < nb ? data[(size_t)(wid + 32 * r) * nb + j] : 0u;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      unsigned inc = v[r];
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += x;
       }
-      if (j < nb) row[j] = run + inc - v;
-      run += __shfl_sync(0xffffffffu, inc, 31);
+      if (j < nb) data[(size_t)(wid + 32 * r) * nb + j] = run[r] + inc - v[r];
+      run[r] += __shfl_sync(0xffffffffu, inc, 31);
     }
   }
 }
