@@ -339,11 +339,11 @@ def main():
             traffic = None
             try:
                 with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                    traffic = json.load(f).get("walk_kernel_dram_bytes_per_launch")
+                    traffic = json.load(f).get(args.workload, {}).get("walk_kernel_dram_bytes_per_launch")
             except Exception:
                 pass
             line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                "traffic": traffic, "kernel": "rm_match_kernel (K1 walk)", "peak_source": peak_src,
+                                "traffic": traffic, "kernel": "rm_match_lpq_kernel (K1 walk)", "peak_source": peak_src,
                                 "bytes_per_lookup": bpl, "mean_hops": hops, "kernel_ms": walk_ms_mean,
                                 "kernel_share_of_step": walk_ms_mean / (ms / K),
                                 "lookups_per_s_kernel_only": B / (walk_ms_mean * 1e-3)}
