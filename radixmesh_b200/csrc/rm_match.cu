@@ -215,6 +215,36 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
     if (3 < L) g3 = rm_ld_query(key + 3, qpol);
   }
   while (true) {
+    // ---- fast path first: the probe hit a one-token edge (89 % of the hops) and the query goes on.
+    // Nothing but the key compare, the hash and the address sits between the slot's arrival and the
+    // next probe's issue; stamp, router state and look-ahead refill overlap with the new load.
+    if (!pend && have_probe && (unsigned)S.a.x == want_tok && (unsigned)S.a.y == want_par &&
+        ((unsigned)S.a.w & 0xFFFFFFu) == 1u && pos + 1 < L) {
+      const int c1 = S.a.z;
+      const unsigned w1 = (unsigned)S.a.w;
+      want_par = (unsigned)c1;
+      want_tok = (unsigned)g1;
+      si = rm_hash2((unsigned)c1, want_tok, tshift);
+      S = rm_ld_slot(table + si);
+      if (!(flags & 1)) atomicMax(stamp + c1, seq);   // radix_cache.py:260 / radix_mesh.py:257
+      if (ROUTER) {
+        const int r1 = rm_slot_rank(w1);
+        ++cnt;
+        deepest = r1;
+        if (r1 < t.n_prefill) {
+          last_prefill = r1;
+          bad_below = false;
+        } else if (r1 >= t.n_prefill + t.n_decode) {
+          bad_below = true;
+        }
+      }
+      node = c1;
+      pos += 1;
+      g1 = g2;
+      g2 = g3;
+      g3 = (pos + 3 < L) ? rm_ld_query(key + pos + 3, qpol) : 0;
+      continue;
+    }
     int c, elen, m, erank;              // the edge decided in this iteration: m of its elen tokens match
     if (pend) {
       // ---- long edge: verify the chunk requested in the previous iteration
