@@ -32,6 +32,26 @@ __global__ void rm_insert_keys_kernel(const int* __restrict__ tok, const i64* __
   val[r] = (unsigned)r;
 }
 
+// RadixCache semantics, fast path: group key of a record after the read-only pre-pass.  Two records can only
+// interact if they leave the old tree at the same node through the same token, so the key is a hash of
+// (deepest fully matched node, next token); unrelated records that collide merely share a warp.
+// Records that matched in full need nothing more: insert returns len(key) (radix_cache.py:327).
+__global__ void rm_insert_keys2_kernel(RmTree t, const int* __restrict__ tok, const i64* __restrict__ off, int N,
+                                       const int* __restrict__ xnode, u64* __restrict__ key, unsigned* __restrict__ val,
+                                       int* __restrict__ out_prefix) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  const i64 o = off[r];
+  const int n = (int)(off[r + 1] - o);
+  const int x = xnode[r];
+  const int pos = x > 0 ? t.depth_end[x] : 0;
+  u64 k = 0;                                   // 0 = nothing left to do
+  if (pos < n) k = 1ull + (u64)(rm_hash2((unsigned)x, (unsigned)tok[o + pos], 0) >> 12);   // 20-bit group hash
+  else out_prefix[r] = n;
+  key[r] = k;
+  val[r] = (unsigned)r;
+}
+
 // Record a duplicate-node entry: dup_nodes[(full_key(node), rank)] = parked (radix_mesh.py:310, 476, 493).
 // The tree node id stands for its full key (stable under splits: the lower half keeps the id).
 __device__ __forceinline__ void rm_dup_put(const RmTree& t, int node, int rank, int parked) {
@@ -62,13 +82,17 @@ template <int G, int MESH>
 __global__ void __launch_bounds__(RM_INS_TPB)
 rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__ rval, const i64* __restrict__ roff,
                  const int* __restrict__ rrank, int N, const u64* __restrict__ skey, const unsigned* __restrict__ sval,
-                 u64 seq_base, int* __restrict__ out_prefix) {
+                 u64 seq_base, int* __restrict__ out_prefix, const int* __restrict__ start) {
+  // start != NULL (RadixCache semantics): a read-only pre-pass already walked every record to its deepest
+  // fully matched node start[r] and stamped that path; groups are keyed by (that node, next token) and the
+  // walk resumes there.  start == NULL (mesh modes): groups are keyed by first token, walks start at the root.
   RmGroup<G> g;
   const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
   if (i >= N) return;
   const u64 gk = skey[i];
-  if (i > 0 && skey[i - 1] == gk) return;  // one group per distinct first token
-  if (gk == (1ull << 32)) {
+  if (i > 0 && skey[i - 1] == gk) return;  // one group per distinct key
+  if (start != nullptr && gk == 0) return;  // records the pre-pass finished
+  if (start == nullptr && gk == (1ull << 32)) {
     // empty keys: insert returns 0 and only stamps the root (radix_cache.py:297-299)
     for (int j = i + g.lane; j < N; j += G) out_prefix[sval[j]] = 0;
     return;
@@ -95,6 +119,10 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       continue;
     }
     int node = 0, pos = 0, total = 0;
+    if (start != nullptr) {
+      node = start[r];
+      pos = total = node > 0 ? t.depth_end[node] : 0;
+    }
     while (pos < n) {
       RmSlot s;
       const int sidx = rm_find<true>(t, rm_key(node, key[pos]), s);
@@ -138,7 +166,14 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
         }
       }
       total += m;
-      if (g.lane == 0) t.stamp[c] = seq;
+      // stamp: 2*op+1, or 2*op for the lower half of a node this record splits (see above).  With the
+      // pre-pass other records of the batch may already have stamped c, so the stamp is a max.
+      const u64 c_before = start != nullptr ? t.stamp[c] : 0ull;
+      if (g.lane == 0) {
+        const u64 sv = (m < elen) ? seq - 1 : seq;
+        if (start != nullptr) atomicMax(&t.stamp[c], sv);
+        else t.stamp[c] = sv;
+      }
       int target = c;
       if (m < elen) {
         // _split_node (radix_cache.py:277-294): new upper node [0, m), c keeps [m, elen)
@@ -158,7 +193,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.nchild[u] = 1;
           t.gen[u] = 0;
           t.parked[u] = -1;
-          t.stamp[u] = seq;
+          t.stamp[u] = c_before > seq ? c_before : seq;   // later records that passed c in full pass u as well
           atomicMax(&t.ctr->node_hwm, u + 1);
           t.table[sidx].child = u;
           rm_slot_set_len(&t.table[sidx], m);
@@ -166,7 +201,6 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.parent[c] = u;
           t.edge_off[c] = eoff + m;
           t.edge_len[c] = elen - m;
-          t.stamp[c] = seq - 1;   // lower half: stamped before the split, see above
           rm_add_i64(&t.ctr->n_nodes, (i64)1);
           __threadfence();
         }
@@ -285,31 +319,45 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
   }
 }
 
+int rm_launch_walk_records(rm_index* idx, const int* tokens, const i64* offsets, int N, u64 seq_base, int* out_len,
+                           int* out_node, cudaStream_t s);
+
 int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const i64* offsets, const int* ranks, int N,
                      int* out_prefix_len, cudaStream_t s) {
   if (N <= 0) return RM_OK;
   RmScratch& sc = idx->sc;
   const u64 seq_base = idx->op_seq + 1;
   idx->op_seq += (u64)N;
+  const long long threads = (long long)N * RM_INS_G;
+  const int grid = (int)((threads + RM_INS_TPB - 1) / RM_INS_TPB);
+  if (idx->cfg.mode == RM_MODE_BASE) {
+    // RadixCache semantics: parallel read-only walk of all records, then in-order apply per
+    // (divergence node, next token) group, resumed at the divergence node
+    int* xnode = sc.krank;
+    int* xlen = sc.uniq_pos;
+    int rc = rm_launch_walk_records(idx, tokens, offsets, N, seq_base, xlen, xnode, s);
+    if (rc) return rc;
+    RM_LAUNCH(rm_insert_keys2_kernel, (N + 255) / 256, 256, s, idx->t, tokens, offsets, N, xnode, sc.key[0], sc.val[0],
+              out_prefix_len);
+    const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], N, 21, sc.hist, s);
+    auto k = rm_insert_kernel<RM_INS_G, 0>;
+    RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base,
+              out_prefix_len, xnode);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+  }
   RM_LAUNCH(rm_insert_keys_kernel, (N + 255) / 256, 256, s, tokens, offsets, N, sc.key[0], sc.val[0]);
   RM_CUDA(cudaGetLastError());
   const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], N, 33, sc.hist, s);
   RM_CUDA(cudaGetLastError());
-  const long long threads = (long long)N * RM_INS_G;
-  const int grid = (int)((threads + RM_INS_TPB - 1) / RM_INS_TPB);
-  switch (idx->cfg.mode) {
-    case RM_MODE_BASE: {
-      auto k = rm_insert_kernel<RM_INS_G, 0>;
-      RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base, out_prefix_len);
-    } break;
-    case RM_MODE_ROUTER: {
-      auto k = rm_insert_kernel<RM_INS_G, 2>;
-      RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base, out_prefix_len);
-    } break;
-    default: {
-      auto k = rm_insert_kernel<RM_INS_G, 1>;
-      RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base, out_prefix_len);
-    } break;
+  if (idx->cfg.mode == RM_MODE_ROUTER) {
+    auto k = rm_insert_kernel<RM_INS_G, 2>;
+    RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base,
+              out_prefix_len, (const int*)nullptr);
+  } else {
+    auto k = rm_insert_kernel<RM_INS_G, 1>;
+    RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base,
+              out_prefix_len, (const int*)nullptr);
   }
   RM_CUDA(cudaGetLastError());
   return RM_OK;

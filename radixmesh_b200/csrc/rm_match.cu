@@ -387,7 +387,7 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
   }
   out_len[q] = pos;
   out_node[q] = node;
-  if (SPLIT && req != RM_NO_REQ) {
+  if (SPLIT && req != RM_NO_REQ && !(flags & 4)) {   // flags bit 2: walk only (insert pre-pass)
     const int slot = atomicAdd(&t.ctr->n_req, 1);     // compact list of split requests
     req_key[slot] = req;
     req_val[slot] = (unsigned)q;
@@ -770,6 +770,25 @@ int rm_launch_router_match(rm_index* idx, const int* tokens, const i64* offsets,
   idx->op_seq += (u64)B;
   RmRouteOut ro = {out_prefill, out_decode, out_err};
   rm_match_dispatch<false, true>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
+// Read-only pre-pass of the ordered insert (rm_insert.cu): walk every record of the batch against the
+// tree as it stands, stamp the nodes it matches in full, and report the deepest such node.  Same kernel
+// as the splitting match, with the split requests switched off.
+int rm_launch_walk_records(rm_index* idx, const int* tokens, const i64* offsets, int N, u64 seq_base, int* out_len,
+                           int* out_node, cudaStream_t s) {
+  if (N <= 0) return RM_OK;
+  RmRouteOut ro = {nullptr, nullptr, nullptr};
+#ifdef RM_EMU
+  const int tpb = RM_MATCH_TPB;
+#else
+  const int tpb = N >= 148 * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (N >= 148 * 8 * 128 ? 128 : 64);
+#endif
+  auto k = rm_match_lpq_kernel<true, false>;
+  RM_LAUNCH(k, (N + tpb - 1) / tpb, tpb, s, idx->t, tokens, offsets, N, seq_base, idx->len_bits, out_len, out_node,
+            idx->sc.key[0], idx->sc.val[0], ro, 4);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }
