@@ -152,3 +152,41 @@ def run_split_evict(make_index, seed):
         assert_same_tree(device_canonical(ix), orc.canonical())
     ix.check_device_error()
     ix.close()
+
+
+def run_stream_evict(make_index, seed, n_batches=12, batch=48, L=24, n_docs=12, capacity=1500):
+    """BASELINE configs[2] in miniature: streaming insert batches into a pool kept at <= 90 % occupancy by
+    evicting a batch's worth of tokens whenever it is exceeded (occupancy is a harness
+    notion applied identically to both sides), with arena compaction when the bump arena fills up.
+    Evicted runs (in order) and the final tree must equal the oracle's."""
+    from tests.parity import zipf_prefix
+    ix = make_index(mode=0, max_nodes=4096, max_tokens=2 * capacity, max_batch=max(batch, 64), max_key_len=4 * L)
+    orc = PortRadixCache(1)
+    docs = None
+    vc = 0
+    n_evicted = 0
+    for b in range(n_batches):
+        seqs, docs = zipf_prefix(seed * 100 + b, n_docs, batch, L, vocab=50, docs=docs)
+        vals = np.arange(vc, vc + batch * L, dtype=np.int64)
+        vc += batch * L
+        offs = np.arange(0, (batch + 1) * L, L, dtype=np.int64)
+        if ix.sizes().arena_used + batch * L > 2 * capacity:
+            ix.compact()
+        got = ix.insert_host(seqs.reshape(-1).copy(), vals, offs)
+        exp = [orc.insert(r.tolist(), vals[i * L:(i + 1) * L]) for i, r in enumerate(seqs)]
+        assert got.tolist() == exp
+        ix.check_device_error()
+        while orc.evictable_size() + orc.protected_size() > 0.9 * capacity:
+            s = ix.sizes()
+            assert (s.evictable, s.protected_) == (orc.evictable_size(), orc.protected_size())
+            before = len(orc.freed)
+            orc.evict(batch * L // 4)
+            _, eo, el = ix.evict(batch * L // 4)
+            freed = [ix.read_arena(int(o), int(n))[1].tolist() for o, n in zip(eo, el)]
+            assert freed == orc.freed[before:]
+            n_evicted += len(freed)
+            if not freed:
+                break
+        assert_same_tree(device_canonical(ix), orc.canonical())
+    assert n_evicted > 0
+    ix.close()

@@ -23,3 +23,8 @@ def test_emu_base_longer_keys(seed):
 @pytest.mark.parametrize("seed", range(30))
 def test_emu_batched_match_splits_then_evict_order(seed):
     cases.run_split_evict(make_index, seed)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_emu_streaming_insert_evict_compact(seed):
+    cases.run_stream_evict(make_index, seed)

@@ -95,3 +95,8 @@ def zipf_check(seed, n_docs, L, n_ins, n_q, batch=4096):
 def test_gpu_zipf_c2_reduced():
     """configs[1] shape (Zipf, 4096 docs, L=256) at a size the oracle finishes in seconds."""
     zipf_check(seed=0, n_docs=4096, L=256, n_ins=6000, n_q=8192)
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_gpu_streaming_insert_evict_compact(seed):
+    cases.run_stream_evict(make_index, seed, n_batches=16, batch=96, L=32, n_docs=24, capacity=6000)

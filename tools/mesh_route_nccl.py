@@ -50,8 +50,25 @@ pf = out[0].cpu().numpy(); dc = out[1].cpu().numpy()
 exp_owner = qd % world
 ok_p = bool(np.all(np.where(exp_owner < P, pf == exp_owner, pf == -1)))
 ok_d = bool(np.all(np.where(exp_owner >= P, dc == exp_owner, dc == -1)))
+# phase breakdown on rank 0 (one extra batch, events between the phases)
+import numpy as _np
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+be = ix.be
+ev[0].record()
+dist.broadcast(tok, src=0); dist.broadcast(qo, src=0)
+ev[1].record()
+lens = be.empty(B, _np.int32); nodes = be.empty(B, _np.int32)
+ix.match(tok, qo, B, lens, nodes)
+ev[2].record()
+depths = be.empty(world * B, _np.int32)
+dist.all_gather_into_tensor(depths, lens)
+ev[3].record()
+o4 = [be.empty(B, _np.int32) for _ in range(4)]; e8 = be.empty(B, _np.uint8)
+ix.pick(depths, world, tok, qo, B, o4[0], o4[1], o4[2], o4[3], e8)
+ev[4].record(); torch.cuda.synchronize()
+phases = {n: round(ev[i].elapsed_time(ev[i + 1]), 3) for i, n in enumerate(["broadcast_ms", "walk_ms", "allgather_ms", "pick_md5_ms"])}
 if rank == 0:
-    print(json.dumps({"mesh_route": "sharded trees + allgather + pick", "n_gpus": world, "requests_per_s": B * K / (ms.item() * 1e-3),
+    print(json.dumps({"phases": phases, "mesh_route": "sharded trees + allgather + pick", "n_gpus": world, "requests_per_s": B * K / (ms.item() * 1e-3),
                       "tree_lookups_per_s": world * B * K / (ms.item() * 1e-3), "ms_per_batch": ms.item() / K, "batch": B,
                       "request_len": Lq, "owner_pick_correct": ok_p and ok_d}))
 dist.destroy_process_group()
