@@ -24,6 +24,7 @@ using std::min;
 #define __forceinline__ inline
 #define __restrict__
 #define __launch_bounds__(...)
+#define __shared__ static   /* threads run one after another: a static buffer indexed by threadIdx works */
 #define __align__(n) __attribute__((aligned(n)))
 
 struct rm_emu_dim3 { unsigned x, y, z; };

@@ -18,53 +18,95 @@
 int rm_launch_router_match(rm_index* idx, const int* tokens, const i64* offsets, int B, int* out_len, int* out_node,
                            int* out_prefill, int* out_decode, unsigned char* out_err, cudaStream_t s);
 
+// MD5 (RFC 1321) streamed per thread.  The message words of the current 64-byte block live in shared
+// memory, one column per thread (wsm[word][thread]: conflict free), because they are written at a
+// run-time index while the text is rendered and read at compile-time indices by the unrolled rounds; the
+// first version kept them in a per-thread array (local memory, one read-modify-write per BYTE) and took
+// 4.7 ms for 16K 2K-token requests.  Bytes are gathered four at a time in a 64-bit shift register.
 struct RmMd5 {
   unsigned a, b, c, d;
-  unsigned w[16];   // current 64-byte block as little-endian words
-  unsigned fill;    // bytes in the block
-  u64 total;        // bytes hashed so far
 };
 
 __device__ __forceinline__ unsigned rm_rotl(unsigned x, int s) { return (x << s) | (x >> (32 - s)); }
 
-__device__ void rm_md5_block(RmMd5& m) {
-  // RFC 1321 round constants and shifts
-  const unsigned K[64] = {
-      0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501,
-      0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821,
-      0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8,
-      0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a,
-      0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70,
-      0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665,
-      0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1,
-      0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
-  const int S[64] = {7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 5, 9,  14, 20, 5, 9,
-                     14, 20, 5, 9,  14, 20, 5, 9,  14, 20, 4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23,
-                     4, 11, 16, 23, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21};
+#define RM_MD5_STEP(f, a, b, c, d, x, k, s) \
+  a = b + rm_rotl(a + (f) + (x) + (k), s)
+
+template <class W>
+__device__ __forceinline__ void rm_md5_block(RmMd5& m, const W& w) {
   unsigned a = m.a, b = m.b, c = m.c, d = m.d;
-#pragma unroll
-  for (int i = 0; i < 64; ++i) {
-    unsigned f;
-    int g;
-    if (i < 16) {
-      f = (b & c) | (~b & d);
-      g = i;
-    } else if (i < 32) {
-      f = (d & b) | (~d & c);
-      g = (5 * i + 1) & 15;
-    } else if (i < 48) {
-      f = b ^ c ^ d;
-      g = (3 * i + 5) & 15;
-    } else {
-      f = c ^ (b | ~d);
-      g = (7 * i) & 15;
-    }
-    unsigned tmp = d;
-    d = c;
-    c = b;
-    b = b + rm_rotl(a + f + K[i] + m.w[g], S[i]);
-    a = tmp;
-  }
+#define F1(x, y, z) ((x & y) | (~x & z))
+#define F2(x, y, z) ((z & x) | (~z & y))
+#define F3(x, y, z) (x ^ y ^ z)
+#define F4(x, y, z) (y ^ (x | ~z))
+  RM_MD5_STEP(F1(b, c, d), a, b, c, d, w(0), 0xd76aa478u, 7);
+  RM_MD5_STEP(F1(a, b, c), d, a, b, c, w(1), 0xe8c7b756u, 12);
+  RM_MD5_STEP(F1(d, a, b), c, d, a, b, w(2), 0x242070dbu, 17);
+  RM_MD5_STEP(F1(c, d, a), b, c, d, a, w(3), 0xc1bdceeeu, 22);
+  RM_MD5_STEP(F1(b, c, d), a, b, c, d, w(4), 0xf57c0fafu, 7);
+  RM_MD5_STEP(F1(a, b, c), d, a, b, c, w(5), 0x4787c62au, 12);
+  RM_MD5_STEP(F1(d, a, b), c, d, a, b, w(6), 0xa8304613u, 17);
+  RM_MD5_STEP(F1(c, d, a), b, c, d, a, w(7), 0xfd469501u, 22);
+  RM_MD5_STEP(F1(b, c, d), a, b, c, d, w(8), 0x698098d8u, 7);
+  RM_MD5_STEP(F1(a, b, c), d, a, b, c, w(9), 0x8b44f7afu, 12);
+  RM_MD5_STEP(F1(d, a, b), c, d, a, b, w(10), 0xffff5bb1u, 17);
+  RM_MD5_STEP(F1(c, d, a), b, c, d, a, w(11), 0x895cd7beu, 22);
+  RM_MD5_STEP(F1(b, c, d), a, b, c, d, w(12), 0x6b901122u, 7);
+  RM_MD5_STEP(F1(a, b, c), d, a, b, c, w(13), 0xfd987193u, 12);
+  RM_MD5_STEP(F1(d, a, b), c, d, a, b, w(14), 0xa679438eu, 17);
+  RM_MD5_STEP(F1(c, d, a), b, c, d, a, w(15), 0x49b40821u, 22);
+  RM_MD5_STEP(F2(b, c, d), a, b, c, d, w(1), 0xf61e2562u, 5);
+  RM_MD5_STEP(F2(a, b, c), d, a, b, c, w(6), 0xc040b340u, 9);
+  RM_MD5_STEP(F2(d, a, b), c, d, a, b, w(11), 0x265e5a51u, 14);
+  RM_MD5_STEP(F2(c, d, a), b, c, d, a, w(0), 0xe9b6c7aau, 20);
+  RM_MD5_STEP(F2(b, c, d), a, b, c, d, w(5), 0xd62f105du, 5);
+  RM_MD5_STEP(F2(a, b, c), d, a, b, c, w(10), 0x02441453u, 9);
+  RM_MD5_STEP(F2(d, a, b), c, d, a, b, w(15), 0xd8a1e681u, 14);
+  RM_MD5_STEP(F2(c, d, a), b, c, d, a, w(4), 0xe7d3fbc8u, 20);
+  RM_MD5_STEP(F2(b, c, d), a, b, c, d, w(9), 0x21e1cde6u, 5);
+  RM_MD5_STEP(F2(a, b, c), d, a, b, c, w(14), 0xc33707d6u, 9);
+  RM_MD5_STEP(F2(d, a, b), c, d, a, b, w(3), 0xf4d50d87u, 14);
+  RM_MD5_STEP(F2(c, d, a), b, c, d, a, w(8), 0x455a14edu, 20);
+  RM_MD5_STEP(F2(b, c, d), a, b, c, d, w(13), 0xa9e3e905u, 5);
+  RM_MD5_STEP(F2(a, b, c), d, a, b, c, w(2), 0xfcefa3f8u, 9);
+  RM_MD5_STEP(F2(d, a, b), c, d, a, b, w(7), 0x676f02d9u, 14);
+  RM_MD5_STEP(F2(c, d, a), b, c, d, a, w(12), 0x8d2a4c8au, 20);
+  RM_MD5_STEP(F3(b, c, d), a, b, c, d, w(5), 0xfffa3942u, 4);
+  RM_MD5_STEP(F3(a, b, c), d, a, b, c, w(8), 0x8771f681u, 11);
+  RM_MD5_STEP(F3(d, a, b), c, d, a, b, w(11), 0x6d9d6122u, 16);
+  RM_MD5_STEP(F3(c, d, a), b, c, d, a, w(14), 0xfde5380cu, 23);
+  RM_MD5_STEP(F3(b, c, d), a, b, c, d, w(1), 0xa4beea44u, 4);
+  RM_MD5_STEP(F3(a, b, c), d, a, b, c, w(4), 0x4bdecfa9u, 11);
+  RM_MD5_STEP(F3(d, a, b), c, d, a, b, w(7), 0xf6bb4b60u, 16);
+  RM_MD5_STEP(F3(c, d, a), b, c, d, a, w(10), 0xbebfbc70u, 23);
+  RM_MD5_STEP(F3(b, c, d), a, b, c, d, w(13), 0x289b7ec6u, 4);
+  RM_MD5_STEP(F3(a, b, c), d, a, b, c, w(0), 0xeaa127fau, 11);
+  RM_MD5_STEP(F3(d, a, b), c, d, a, b, w(3), 0xd4ef3085u, 16);
+  RM_MD5_STEP(F3(c, d, a), b, c, d, a, w(6), 0x04881d05u, 23);
+  RM_MD5_STEP(F3(b, c, d), a, b, c, d, w(9), 0xd9d4d039u, 4);
+  RM_MD5_STEP(F3(a, b, c), d, a, b, c, w(12), 0xe6db99e5u, 11);
+  RM_MD5_STEP(F3(d, a, b), c, d, a, b, w(15), 0x1fa27cf8u, 16);
+  RM_MD5_STEP(F3(c, d, a), b, c, d, a, w(2), 0xc4ac5665u, 23);
+  RM_MD5_STEP(F4(b, c, d), a, b, c, d, w(0), 0xf4292244u, 6);
+  RM_MD5_STEP(F4(a, b, c), d, a, b, c, w(7), 0x432aff97u, 10);
+  RM_MD5_STEP(F4(d, a, b), c, d, a, b, w(14), 0xab9423a7u, 15);
+  RM_MD5_STEP(F4(c, d, a), b, c, d, a, w(5), 0xfc93a039u, 21);
+  RM_MD5_STEP(F4(b, c, d), a, b, c, d, w(12), 0x655b59c3u, 6);
+  RM_MD5_STEP(F4(a, b, c), d, a, b, c, w(3), 0x8f0ccc92u, 10);
+  RM_MD5_STEP(F4(d, a, b), c, d, a, b, w(10), 0xffeff47du, 15);
+  RM_MD5_STEP(F4(c, d, a), b, c, d, a, w(1), 0x85845dd1u, 21);
+  RM_MD5_STEP(F4(b, c, d), a, b, c, d, w(8), 0x6fa87e4fu, 6);
+  RM_MD5_STEP(F4(a, b, c), d, a, b, c, w(15), 0xfe2ce6e0u, 10);
+  RM_MD5_STEP(F4(d, a, b), c, d, a, b, w(6), 0xa3014314u, 15);
+  RM_MD5_STEP(F4(c, d, a), b, c, d, a, w(13), 0x4e0811a1u, 21);
+  RM_MD5_STEP(F4(b, c, d), a, b, c, d, w(4), 0xf7537e82u, 6);
+  RM_MD5_STEP(F4(a, b, c), d, a, b, c, w(11), 0xbd3af235u, 10);
+  RM_MD5_STEP(F4(d, a, b), c, d, a, b, w(2), 0x2ad7d2bbu, 15);
+  RM_MD5_STEP(F4(c, d, a), b, c, d, a, w(9), 0xeb86d391u, 21);
+#undef F1
+#undef F2
+#undef F3
+#undef F4
   m.a += a;
   m.b += b;
   m.c += c;
@@ -76,69 +118,107 @@ __device__ __forceinline__ void rm_md5_init(RmMd5& m) {
   m.b = 0xefcdab89u;
   m.c = 0x98badcfeu;
   m.d = 0x10325476u;
-  m.fill = 0;
-  m.total = 0;
-#pragma unroll
-  for (int i = 0; i < 16; ++i) m.w[i] = 0;
 }
 
-__device__ __forceinline__ void rm_md5_put(RmMd5& m, unsigned char ch) {
-  const unsigned wi = m.fill >> 2, sh = (m.fill & 3) * 8;
-  // w[] is indexed with a runtime value only here; keep it simple (local memory is fine for a
-  // fallback path that runs once per missed request)
-  m.w[wi] |= (unsigned)ch << sh;
-  ++m.fill;
-  ++m.total;
-  if (m.fill == 64) {
-    rm_md5_block(m);
-    m.fill = 0;
+// word column of the calling thread in the block's shared message buffer
+struct RmMd5Words {
+  unsigned* col;     // &wsm[0][threadIdx.x]
+  int stride;        // threads per block
+  __device__ __forceinline__ unsigned operator()(int i) const { return col[i * stride]; }
+  __device__ __forceinline__ void set(int i, unsigned v) const { col[i * stride] = v; }
+};
+
+// ConsistentHash._hash(key) for key = list of ints (cache_aware_router.py:110-118): MD5 of Python's
+// str(list) rendering "[t0, t1, ...]", first four digest bytes big-endian.
+//
+// Shape of the loop (it matters: the 32 requests of a warp render numbers of different widths, and a
+// version that compressed "whenever this lane's block filled up" ran the 64-step compression once per
+// LANE instead of once per warp, 4.2 ms for 16K 2K-token requests).  Each lane owns a byte queue of up
+// to 16 pending bytes (mlo/mhi).  The inner loop only renders tokens and moves whole words from the
+// queue into the lane's block; it ends when the block is full.  The compression sits after it, at a
+// point where the lanes of a warp have reconverged.
+__device__ unsigned rm_hash_token_list(const int* __restrict__ key, int n, const RmMd5Words& w) {
+  RmMd5 m;
+  rm_md5_init(m);
+  u64 mlo = (u64)'[', mhi = 0;   // pending bytes, little-endian (first byte lowest)
+  int pend = 1;                  // number of pending bytes
+  u64 total = 1;
+  int i = 0;
+  bool closed = false;
+  int widx = 0;
+  while (true) {
+    // One body for every lane and every iteration: (1) if fewer than 4 bytes are pending and input is
+    // left, render one item (a token with its separator, or the closing bracket); (2) move as many whole
+    // words as the block still takes.  No lane-dependent branch apart from the digit count.
+    while (widx < 16) {
+      if (pend < 4) {
+        u64 tlo = 0, thi = 0;
+        int len = 0;
+        if (i < n) {
+          // decimal digits, least significant first; shifting what is there up by a byte puts the most
+          // significant digit in the lowest byte, i.e. first in the text
+          const int v = key[i];
+          unsigned ux = v < 0 ? (unsigned)(-(long long)v) : (unsigned)v;
+          do {
+            thi = (thi << 8) | (tlo >> 56);
+            tlo = (tlo << 8) | (u64)('0' + (ux % 10u));
+            ux /= 10u;
+            ++len;
+          } while (ux);
+          if (v < 0) {
+            thi = (thi << 8) | (tlo >> 56);
+            tlo = (tlo << 8) | (u64)'-';
+            ++len;
+          }
+          if (i) {               // ", " separator in front
+            thi = (thi << 16) | (tlo >> 48);
+            tlo = (tlo << 16) | ((u64)' ' << 8) | (u64)',';
+            len += 2;
+          }
+          ++i;
+        } else if (!closed) {
+          tlo = (u64)']';
+          len = 1;
+          closed = true;
+        } else {
+          break;                 // input exhausted, fewer than 4 bytes pending
+        }
+        const int sh = 8 * pend;
+        mhi = (thi << sh) | (sh ? (tlo >> (64 - sh)) : 0ull);
+        mlo |= tlo << sh;
+        pend += len;
+        total += (u64)len;
+      }
 #pragma unroll
-    for (int i = 0; i < 16; ++i) m.w[i] = 0;
+      for (int k = 0; k < 4; ++k) {
+        if (pend >= 4 && widx < 16) {
+          w.set(widx++, (unsigned)mlo);
+          mlo = (mlo >> 32) | (mhi << 32);
+          mhi >>= 32;
+          pend -= 4;
+        }
+      }
+    }
+    if (widx < 16) break;
+    rm_md5_block(m, w);
+    widx = 0;
   }
-}
-
-__device__ unsigned rm_md5_finish_u32be(RmMd5& m) {
-  const u64 bits = m.total * 8ull;
-  rm_md5_put(m, 0x80);
-  while (m.fill != 56) rm_md5_put(m, 0);
-  m.w[14] = (unsigned)(bits & 0xffffffffu);
-  m.w[15] = (unsigned)(bits >> 32);
-  rm_md5_block(m);
+  // padding: 0x80, zeros to 56 mod 64, the bit length (RFC 1321 3.1-3.2)
+  const u64 bits = total * 8ull;
+  mlo |= (u64)0x80 << (8 * pend);
+  w.set(widx++, (unsigned)mlo);          // pend < 4: the 0x80 completes at most one word
+  if (widx > 14) {
+    while (widx < 16) w.set(widx++, 0u);
+    rm_md5_block(m, w);
+    widx = 0;
+  }
+  while (widx < 14) w.set(widx++, 0u);
+  w.set(14, (unsigned)(bits & 0xffffffffu));
+  w.set(15, (unsigned)(bits >> 32));
+  rm_md5_block(m, w);
   // digest bytes 0..3 are the little-endian bytes of `a`; the reference reads them big-endian
   const unsigned a = m.a;
   return ((a & 0xffu) << 24) | ((a & 0xff00u) << 8) | ((a >> 8) & 0xff00u) | (a >> 24);
-}
-
-// str(int) for a Python int, appended to the hash
-__device__ __forceinline__ void rm_md5_put_int(RmMd5& m, int v) {
-  char buf[12];
-  int n = 0;
-  long long x = v;
-  if (x < 0) {
-    rm_md5_put(m, '-');
-    x = -x;
-  }
-  do {
-    buf[n++] = (char)('0' + (int)(x % 10));
-    x /= 10;
-  } while (x);
-  while (n) rm_md5_put(m, (unsigned char)buf[--n]);
-}
-
-// ConsistentHash._hash(key) for key = list of ints (cache_aware_router.py:110-118)
-__device__ unsigned rm_hash_token_list(const int* key, int n) {
-  RmMd5 m;
-  rm_md5_init(m);
-  rm_md5_put(m, '[');
-  for (int i = 0; i < n; ++i) {
-    if (i) {
-      rm_md5_put(m, ',');
-      rm_md5_put(m, ' ');
-    }
-    rm_md5_put_int(m, key[i]);
-  }
-  rm_md5_put(m, ']');
-  return rm_md5_finish_u32be(m);
 }
 
 // bisect.bisect(ring, h) % len(ring) (cache_aware_router.py:106-108)
@@ -157,6 +237,8 @@ rm_route_finish_kernel(RmTree t, const int* __restrict__ qtok, const i64* __rest
                        int* __restrict__ prefill, int* __restrict__ decode, unsigned char* __restrict__ err,
                        int* __restrict__ paddr, int* __restrict__ daddr, const unsigned* ring_p, const int* ring_p_owner,
                        int ring_p_n, const unsigned* ring_d, const int* ring_d_owner, int ring_d_n) {
+  __shared__ unsigned wsm[16 * RM_RT_TPB];
+  const RmMd5Words words = {wsm + threadIdx.x, RM_RT_TPB};
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= B) return;
   int pf = -1, dc = -1;
@@ -173,7 +255,7 @@ rm_route_finish_kernel(RmTree t, const int* __restrict__ qtok, const i64* __rest
   if (e == 0) {
     const bool need_hash = pf == -1 || dc == -1;
     unsigned h = 0;
-    if (need_hash) h = rm_hash_token_list(qtok + qoff[q], (int)(qoff[q + 1] - qoff[q]));
+    if (need_hash) h = rm_hash_token_list(qtok + qoff[q], (int)(qoff[q + 1] - qoff[q]), words);
     if (pf != -1) {
       // prefill_cache_nodes[rank]: a decode rank here is the reference's IndexError (radix_mesh.py:451)
       if (pf >= t.n_prefill) e = 2;

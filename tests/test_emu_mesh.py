@@ -39,3 +39,28 @@ def test_emu_consistent_hash_vectors():
         assert [addrs[i] for i in outs[2].tolist()] == [q["node"] for q in case["queries"]]
         assert err.tolist() == [0] * n
         ix.close()
+
+
+def test_emu_md5_awkward_inputs():
+    """Device MD5 of str(list) against hashlib: negative and 10-digit ints, lengths around the 64-byte block
+    and padding edges, the empty list, a 2K-token request."""
+    import random
+    import numpy as np
+    from oracle.radix_port import PortConsistentHash
+    from tests.parity import pack
+    addrs = [f"n{i}:1" for i in range(7)]
+    h = PortConsistentHash(addrs)
+    ix = make_index(mode=3, n_prefill=7, n_decode=7, max_nodes=64, max_tokens=64, max_batch=512, max_key_len=4096)
+    pts = np.asarray(h.ring, dtype=np.uint32)
+    own = np.asarray([addrs.index(h.owner[p]) for p in h.ring], dtype=np.int32)
+    ix.set_rings(pts, own, pts, own)
+    rnd = random.Random(5)
+    pool = [0, 7, 10, 99, 100, 31999, 32000, 123456, 2147483647, -1, -2147483648, 999999, 1000000]
+    keys = [[rnd.choice(pool) for _ in range(n)] for n in list(range(0, 40)) + [55, 56, 57, 63, 64, 65, 119, 120, 121, 500, 2176]]
+    tk, offs = pack(keys)
+    n = len(keys)
+    outs = [np.zeros(n, np.int32) for _ in range(4)]
+    err = np.zeros(n, np.uint8)
+    ix.route(tk, offs, n, False, outs[0], outs[1], outs[2], outs[3], err)
+    assert outs[2].tolist() == [addrs.index(h.get_node(k)) for k in keys]
+    ix.close()
