@@ -222,6 +222,10 @@ int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, 
 /* Read `n` tokens / values of the edge arenas starting at token offset `off` into HOST buffers. */
 int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream);
 
+/* Parity aid: the per-position owner map of the edge arena (node id, bit 30 = contiguous child of the node
+ * owning the previous position, -1 = free) for `n` positions from `off`, to HOST.  Synchronises. */
+int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void* stream);
+
 /*
  * Measurement aids (no counterpart in the reference, which has no instrumentation).
  * rm_launch_count: kernels this library has launched in this process.

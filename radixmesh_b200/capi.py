@@ -62,6 +62,7 @@ _PROTOS = {
     "rm_sizes": (C.c_int, [_P, C.POINTER(RmSizes), _P]),
     "rm_dump": (C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "rm_read_arena": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
+    "rm_read_segments": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P]),
     "rm_launch_count": (C.c_uint64, []),
     "rm_profile": (C.c_int, [_P, C.c_int]),
     "rm_profile_read": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
@@ -276,6 +277,12 @@ class DeviceIndex:
                                          ptr(a["nchild"]), ptr(a["gen"]), ptr(a["parked"]), C.addressof(out_n), self._s()))
         a["n"] = n
         return a
+
+    def read_segments(self, off: int, n: int) -> np.ndarray:
+        seg = np.zeros(n, np.int32)
+        with self._mutex:
+            self._check(self.lib.rm_read_segments(self._h, int(off), int(n), ptr(seg), self._s()))
+        return seg
 
     def profile(self, enable: bool) -> None:
         self._check(self.lib.rm_profile(self._h, 1 if enable else 0))

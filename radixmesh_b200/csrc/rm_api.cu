@@ -91,7 +91,7 @@ int rm_destroy(rm_index* idx) {
   RmTree& t = idx->t;
   RmScratch& sc = idx->sc;
   void* ptrs[] = {t.table, t.parent, t.edge_off, t.edge_len, t.lock_ref, t.stamp, t.rank, t.depth_end, t.nchild,
-                  t.gen, t.parked, t.tok, t.val, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
+                  t.gen, t.parked, t.tok, t.val, t.seg, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
                   sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.hist, sc.ev_key[0], sc.ev_key[1],
                   sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.lock_first, sc.lock_cnt, sc.lock_flag,
                   sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b,
@@ -158,8 +158,9 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&t.nchild, N));
   A(rm_dalloc(&t.gen, N));
   A(rm_dalloc(&t.parked, N));
-  A(rm_dalloc(&t.tok, (size_t)cfg->max_tokens));
-  A(rm_dalloc(&t.val, with_values ? (size_t)cfg->max_tokens : 1));
+  A(rm_dalloc(&t.tok, (size_t)cfg->max_tokens + RM_ARENA_PAD));
+  A(rm_dalloc(&t.val, with_values ? (size_t)cfg->max_tokens + RM_ARENA_PAD : 1));
+  A(rm_dalloc(&t.seg, (size_t)cfg->max_tokens + RM_ARENA_PAD));
   A(rm_dalloc(&t.free_ids, N));
   A(rm_dalloc(&t.ctr, 1));
   A(rm_dalloc(&t.dup_key, dcap));
@@ -410,6 +411,15 @@ int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, 
   D(gen_h, t.gen, int);
   D(parked_h, t.parked, int);
 #undef D
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
+int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void* stream) {
+  if (!idx || off < 0 || n < 0 || off + n > idx->t.max_tokens || !seg_h) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RM_CUDA(cudaMemcpyAsync(seg_h, idx->t.seg + off, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));
   return RM_OK;
 }

@@ -40,6 +40,14 @@ struct __align__(32) RmSlot {
                       // Zipf workload once first-sight splits have happened) are verified from the slot alone
 };
 #define RM_MAX_EDGE_LEN 0xFFFFFF
+// seg[a] = owner node id of arena position a, with RM_SEG_CONT set on the FIRST position of a node that is the
+// contiguous child of the node owning position a-1 (the lower half of a split).  A walk that has matched a
+// node in full can then carry on along the same arena run, comparing tokens and reading seg[] side by side,
+// without a child-table probe per node: first-sight splits turn hot prefixes into long chains of one-token
+// nodes, but those chains stay contiguous in the arena.
+#define RM_SEG_CONT 0x40000000
+#define RM_ARENA_PAD 64    // walks read up to a warp's width past a run
+__device__ __forceinline__ int rm_seg_owner(int sg) { return sg < 0 ? -1 : (sg & 0x3FFFFFFF); }
 __device__ __forceinline__ int rm_slot_len(unsigned w) { return (int)(w & 0xFFFFFFu); }
 __device__ __forceinline__ int rm_slot_rank(unsigned w) { return (int)(w >> 24) - 1; }
 __device__ __forceinline__ unsigned rm_slot_pack(int len, int rank) { return ((unsigned)len & 0xFFFFFFu) | ((unsigned)(rank + 1) << 24); }
@@ -79,6 +87,7 @@ struct RmTree {
   int* parked;     // tree node: most recently parked predecessor (or -1); parked node: the one parked before it
   int* tok;
   i64* val;
+  int* seg;        // per arena position: id of the node whose edge covers it (-1 = free), see RM_SEG_CONT
   int* free_ids;
   RmCounters* ctr;
   int max_nodes;

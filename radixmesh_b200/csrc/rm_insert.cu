@@ -182,7 +182,11 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
         apos = g.bcast(apos, 0);
         if (apos == ~0ull) break;
         const int u = rm_free_id_at(t, apos);
+        // owner map: [eoff, eoff+m) now belongs to u (the first position keeps its flag), c starts at
+        // eoff+m as the contiguous child of u
+        for (int x = g.lane; x < m; x += G) t.seg[eoff + x] = x == 0 ? ((t.seg[eoff] & RM_SEG_CONT) | u) : u;
         if (g.lane == 0) {
+          t.seg[eoff + m] = c | RM_SEG_CONT;
           const int par = t.parent[c];
           t.parent[u] = par;
           t.edge_off[u] = eoff;
@@ -242,6 +246,12 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
             for (int x = g.lane; x < m; x += G) {
               t.tok[noff + x] = __ldcg(t.tok + eoff + x);
               t.val[noff + x] = val[pos + x];
+              t.seg[noff + x] = target;     // moved away from its parent's run: no contiguity flag
+              t.seg[eoff + x] = d;          // the old run stays with the parked node
+            }
+            if (g.lane == 0) {
+              const int nx = t.seg[eoff + m];  // a contiguous child now follows the PARKED run, not its parent
+              if (nx >= 0 && (nx & RM_SEG_CONT)) t.seg[eoff + m] = nx & ~RM_SEG_CONT;
             }
             if (g.lane == 0) {
               t.parent[d] = t.parent[target];
@@ -290,6 +300,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
         const int leaf = rm_free_id_at(t, apos);
         for (int x = g.lane; x < rem; x += G) {
           t.tok[noff + x] = key[pos + x];
+          t.seg[noff + x] = leaf;
           if (MESH != 2) t.val[noff + x] = val[pos + x];
         }
         g.sync();   // the slot's inline tokens are read back from the arena

@@ -68,6 +68,7 @@ int rm_launch_reset(rm_index* idx, cudaStream_t s) {
   RmTree& t = idx->t;
   RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
   RM_CUDA(cudaMemsetAsync(t.dup_key, 0xFF, sizeof(u64) * ((size_t)t.dup_mask + 1), s));
+  RM_CUDA(cudaMemsetAsync(t.seg, 0xFF, sizeof(int) * ((size_t)t.max_tokens + RM_ARENA_PAD), s));
   RmLockScratch ls = rm_lock_scratch(idx);
   RM_CUDA(cudaMemsetAsync(ls.flag, 0, sizeof(int), s));
   int grid = (int)min((i64)1184, ((i64)t.max_nodes + RM_MT_TPB - 1) / RM_MT_TPB);
@@ -313,6 +314,7 @@ __global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sva
   RmSlot s;
   int sidx = rm_find<true>(t, rm_key(par, t.tok[off]), s);
   if (sidx >= 0) *reinterpret_cast<volatile u64*>(&t.table[sidx].key) = RM_TOMB_KEY;
+  for (int k2 = 0; k2 < len; ++k2) t.seg[off + k2] = -1;   // the run is free again
   atomicSub(&t.nchild[par], 1);
   t.parent[x] = -1;
   t.edge_len[x] = 0;
@@ -415,13 +417,25 @@ int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int*
 // Eviction frees node ids and tombstones table slots, but the edge arenas are bump allocated: under
 // streaming inserts at steady occupancy (BASELINE configs[2]) the space of evicted runs has to be
 // reclaimed.  rm_compact slides every live run (tree nodes and parked duplicates) to the front of fresh
-// arenas in node-id order, rewrites edge_off, and rebuilds the child table from the node pool (which
-// also drops the tombstones).  A maintenance call: it allocates the new arenas and synchronises.
-__global__ void rm_compact_len_kernel(RmTree t, int n, i64* __restrict__ len_out) {
+// arenas IN ARENA ORDER (so a split node's halves stay adjacent and the owner map keeps its contiguity
+// flags), rewrites edge_off, and rebuilds the child table from the node pool (which also drops the
+// tombstones).  A maintenance call: it allocates the new arenas and synchronises.
+__device__ __forceinline__ bool rm_node_has_run(const RmTree& t, int x) {
+  return x > 0 && (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
+}
+
+__global__ void rm_compact_keys_kernel(RmTree t, int n, u64* __restrict__ key, unsigned* __restrict__ val) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= n) return;
-  const bool live = x > 0 && (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
-  len_out[x] = live ? (i64)t.edge_len[x] : 0;
+  key[x] = rm_node_has_run(t, x) ? (u64)t.edge_off[x] : ((1ull << 62) - 1ull);
+  val[x] = (unsigned)x;
+}
+
+__global__ void rm_compact_len_kernel(RmTree t, int n, const unsigned* __restrict__ sval, i64* __restrict__ len_out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int x = (int)sval[i];
+  len_out[i] = rm_node_has_run(t, x) ? (i64)t.edge_len[x] : 0;
 }
 
 // exclusive scan of n i64 values in place, one block (maintenance path: simplicity over speed)
@@ -473,32 +487,42 @@ __global__ void rm_scan_i64_kernel(i64* __restrict__ data, int n, i64* __restric
 #endif
 }
 
+// one group of lanes per run, in arena order: copy tokens, values and owner map, then point the node at
+// its new place (only this group reads edge_off[x])
 template <int G>
-__global__ void rm_compact_copy_kernel(RmTree t, int n, const i64* __restrict__ new_off, int* __restrict__ ntok,
-                                       i64* __restrict__ nval, int with_values) {
+__global__ void rm_compact_copy_kernel(RmTree t, int n, const unsigned* __restrict__ sval, const i64* __restrict__ new_off,
+                                       int* __restrict__ ntok, i64* __restrict__ nval, int* __restrict__ nseg,
+                                       int with_values) {
   RmGroup<G> g;
-  const int x = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
-  if (x >= n || x == 0) return;
-  const bool live = (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
-  if (!live) return;
-  const i64 src = t.edge_off[x], dst = new_off[x];
+  const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (i >= n) return;
+  const int x = (int)sval[i];
+  if (!rm_node_has_run(t, x)) return;
+  const i64 src = t.edge_off[x], dst = new_off[i];
   const int len = t.edge_len[x];
   for (int k = g.lane; k < len; k += G) {
     ntok[dst + k] = t.tok[src + k];
+    nseg[dst + k] = t.seg[src + k];
     if (with_values) nval[dst + k] = t.val[src + k];
+  }
+  g.sync();
+  if (g.lane == 0) t.edge_off[x] = dst;
+}
+
+// after the arenas were swapped: one table slot per tree node
+__global__ void rm_compact_relink_kernel(RmTree t, int n) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || !rm_node_has_run(t, x)) return;
+  if (t.gen[x] >= 0) {   // parked duplicates are not reachable from the table
+    const i64 off = t.edge_off[x];
+    rm_table_insert(t, rm_key(t.parent[x], t.tok[off]), x, t.edge_len[x], off, t.rank[x]);
   }
 }
 
-// after the arenas were swapped: new offsets into the node pool, then one table slot per tree node
-__global__ void rm_compact_relink_kernel(RmTree t, int n, const i64* __restrict__ new_off) {
-  int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= n || x == 0) return;
-  const bool live = (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
-  if (!live) return;
-  const i64 off = new_off[x];
-  t.edge_off[x] = off;
-  if (t.gen[x] >= 0)   // parked duplicates are not reachable from the table
-    rm_table_insert(t, rm_key(t.parent[x], t.tok[off]), x, t.edge_len[x], off, t.rank[x]);
+static int rm_bits_u64(u64 v) {
+  int b = 1;
+  while ((v >> b) != 0 && b < 63) ++b;
+  return b;
 }
 
 extern "C" int rm_compact(rm_index* idx, void* stream) {
@@ -506,14 +530,18 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
   RM_CUDA(cudaSetDevice(idx->cfg.device));
   cudaStream_t s = (cudaStream_t)stream;
   RmTree& t = idx->t;
+  RmScratch& sc = idx->sc;
   RmCounters c;
   RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));
   const int n = c.node_hwm;
   const bool with_values = idx->cfg.mode != RM_MODE_ROUTER;
-  i64* new_off = reinterpret_cast<i64*>(idx->sc.ev_key[0]);   // scratch sized max_nodes x 8 bytes
-  i64* total_d = reinterpret_cast<i64*>(idx->sc.ev_key[1]);
-  RM_LAUNCH(rm_compact_len_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, new_off);
+  // runs in arena order
+  RM_LAUNCH(rm_compact_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, sc.ev_key[0], sc.ev_val[0]);
+  const int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, 62, sc.ev_hist, s);
+  i64* new_off = reinterpret_cast<i64*>(sc.ev_key[w ^ 1]);   // the spare ping-pong buffer, n x 8 bytes
+  i64* total_d = reinterpret_cast<i64*>(sc.sufmax);
+  RM_LAUNCH(rm_compact_len_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, sc.ev_val[w], new_off);
 #ifdef RM_EMU
   RM_LAUNCH(rm_scan_i64_kernel, 1, 1, s, new_off, n, total_d);
 #else
@@ -521,8 +549,12 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
 #endif
   int* ntok = nullptr;
   i64* nval = nullptr;
-  RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&ntok), sizeof(int) * (size_t)t.max_tokens));
-  if (with_values) RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&nval), sizeof(i64) * (size_t)t.max_tokens));
+  int* nseg = nullptr;
+  const size_t cap = (size_t)t.max_tokens + RM_ARENA_PAD;
+  RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&ntok), sizeof(int) * cap));
+  RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&nseg), sizeof(int) * cap));
+  if (with_values) RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&nval), sizeof(i64) * cap));
+  RM_CUDA(cudaMemsetAsync(nseg, 0xFF, sizeof(int) * cap, s));
 #ifdef RM_EMU
   auto kc = rm_compact_copy_kernel<1>;
   const long long cthreads = n;
@@ -530,18 +562,21 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
   auto kc = rm_compact_copy_kernel<32>;
   const long long cthreads = (long long)n * 32;
 #endif
-  RM_LAUNCH(kc, (int)((cthreads + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, n, new_off, ntok, nval, with_values ? 1 : 0);
+  RM_LAUNCH(kc, (int)((cthreads + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, n, sc.ev_val[w], new_off, ntok, nval, nseg,
+            with_values ? 1 : 0);
   RM_CUDA(cudaGetLastError());
   RM_CUDA(cudaStreamSynchronize(s));
   // swap the arenas in, drop the old ones
   cudaFree(t.tok);
+  cudaFree(t.seg);
   t.tok = ntok;
+  t.seg = nseg;
   if (with_values) {
     cudaFree(t.val);
     t.val = nval;
   }
   RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
-  RM_LAUNCH(rm_compact_relink_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, new_off);
+  RM_LAUNCH(rm_compact_relink_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n);
   i64 total = 0;
   RM_CUDA(cudaMemcpyAsync(&total, total_d, sizeof(i64), cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));
@@ -549,5 +584,6 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
   RM_CUDA(cudaMemcpyAsync(&t.ctr->arena_top, &top, sizeof(u64), cudaMemcpyHostToDevice, s));
   RM_CUDA(cudaStreamSynchronize(s));
   RM_CUDA(cudaGetLastError());
+  (void)rm_bits_u64;
   return RM_OK;
 }

@@ -10,6 +10,8 @@
 // Partial edge matches in the splitting modes are recorded as (node, split point) requests; K3 sorts
 // them, creates each distinct upper node once and derives every segment's last-access stamp in closed
 // form so that the result equals the reference processing the batch query by query.
+#include <string.h>
+
 #include "rm_internal.h"
 #include "rm_sort.cuh"
 
@@ -412,6 +414,328 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
   }
 }
 
+// K1, run-following form (the default).  First-sight splits turn a hot prefix into a chain of one-token
+// nodes: ~71 hops per 256-token Zipf query on average and ~225 at the tail, each hop a dependent ~0.2 us
+// child-table read, which is what bounded the lane-per-query kernel above at ~0.18 ms per 64K batch.  But a
+// split is zero-copy, so such a chain is still ONE contiguous run of the token arena.  The owner map
+// seg[] (rm_common.cuh) says, per arena position, which node covers it and whether a node is the
+// contiguous child of its predecessor.  A lane therefore probes the child table only where the path
+// really branches (the root, a leaf appended by an insert, the final miss) and otherwise streams along
+// the run, comparing arena tokens with query tokens RM_RUN positions per step and reading node
+// boundaries from seg[] as it goes.  Every node passed is still stamped (its id comes from seg[]), so
+// results and stamps are those of the hop-by-hop walk.
+#define RM_RUN 8
+template <bool SPLIT, bool ROUTER>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_match_run_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
+                    int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
+                    unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
+  const int q = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
+  if (q >= B) return;
+  const i64 o0 = qoff[q];
+  const int L = (int)(qoff[q + 1] - o0);
+  const int* __restrict__ key = qtok + o0;
+  const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
+  const RmSlot* __restrict__ table = t.table;
+  const unsigned tmask = t.table_mask, tshift = t.table_shift;
+  const int* __restrict__ tok = t.tok;
+  const int* __restrict__ seg = t.seg;
+  u64* __restrict__ stamp = t.stamp;
+  const u64 qpol = rm_policy_evict_first();
+
+  int node = 0, pos = 0;               // `node` is matched in full through `pos`
+  u64 req = RM_NO_REQ;
+  int cnt = 0, deepest = -1, last_prefill = -1;
+  bool bad_below = false;
+
+#define RM_ROUTER_SEE(rk)                          \
+  do {                                             \
+    ++cnt;                                         \
+    deepest = (rk);                                \
+    if ((rk) < t.n_prefill) {                      \
+      last_prefill = (rk);                         \
+      bad_below = false;                           \
+    } else if ((rk) >= t.n_prefill + t.n_decode) { \
+      bad_below = true;                            \
+    }                                              \
+  } while (0)
+
+  bool done = L == 0;
+  while (!done) {
+    // ---- enter a child of `node` that starts with key[pos]
+    const int tk = rm_ld_query(key + pos, qpol);
+    int cur = -1;
+    i64 cs = 0;                        // arena position where cur's run starts
+    {
+      // (the contiguous child, if any, was already ruled out when the previous run ended: table probe)
+      unsigned si = rm_hash2((unsigned)node, (unsigned)tk, tshift);
+      while (true) {
+        const RmSlotRegs S = rm_ld_slot(table + si);
+        if ((unsigned)S.a.x == (unsigned)tk && (unsigned)S.a.y == (unsigned)node) {
+          cur = S.a.z;
+          cs = (i64)(((u64)(unsigned)S.b.y << 32) | (unsigned)S.b.x);
+          break;
+        }
+        if ((S.a.x & S.a.y) == -1) break;   // empty slot: no child starts with this token
+        si = (si + 1) & tmask;
+      }
+      if (cur < 0) break;               // the walk ends at `node`
+    }
+    // ---- stream along the arena run from cs: token cs matched key[pos]
+    i64 a = cs + 1;
+    int qi = pos + 1;
+    bool leave = false;                 // back to the outer loop for a table probe
+    while (!leave && !done) {
+      int ta[RM_RUN], sa[RM_RUN], ka[RM_RUN];
+#pragma unroll
+      for (int j = 0; j < RM_RUN; ++j) {
+        ta[j] = __ldg(tok + a + j);
+        sa[j] = __ldg(seg + a + j);
+        ka[j] = (qi + j < L) ? rm_ld_query(key + qi + j, qpol) : 0;
+      }
+#pragma unroll
+      for (int j = 0; j < RM_RUN; ++j) {
+        if (leave || done) break;
+        const int sg = sa[j];
+        const int owner = sg < 0 ? -1 : (sg & 0x3FFFFFFF);
+        if (owner != cur) {
+          // cur's run ends here: cur is matched in full
+          if (!(flags & 1)) atomicMax(stamp + cur, seq);
+          if (ROUTER) {
+            const int rk = t.rank[cur];
+            RM_ROUTER_SEE(rk);
+          }
+          node = cur;
+          pos = qi;
+          if (qi >= L) {
+            done = true;
+          } else if (sg >= 0 && (sg & RM_SEG_CONT) && ta[j] == ka[j]) {
+            cur = owner;                // the contiguous child continues the match
+            cs = a;
+            ++a;
+            ++qi;
+          } else {
+            leave = true;               // not the contiguous child: back to the child table
+          }
+        } else if (qi >= L || ta[j] != ka[j]) {
+          // the query ends, or differs, inside cur: partial match of p = a - cs tokens (>= 1)
+          const int p = (int)(a - cs);
+          if (SPLIT) {
+            // the reference splits cur here and returns the new upper node (radix_cache.py:262-266); K3 does it
+            req = ((u64)(unsigned)cur << len_bits) | (u64)(unsigned)p;
+            pos = qi;
+          } else {
+            if (!(flags & 1)) atomicMax(stamp + cur, seq);
+            if (ROUTER) {
+              const int rk = t.rank[cur];
+              RM_ROUTER_SEE(rk);
+            }
+            node = cur;                 // no-split modes return the partially matched child
+            pos = qi;
+          }
+          done = true;
+        } else {
+          ++a;
+          ++qi;
+        }
+      }
+    }
+  }
+#undef RM_ROUTER_SEE
+  out_len[q] = pos;
+  out_node[q] = node;
+  if (SPLIT && req != RM_NO_REQ && !(flags & 4)) {
+    const int slot = atomicAdd(&t.ctr->n_req, 1);
+    req_key[slot] = req;
+    req_val[slot] = (unsigned)q;
+  }
+  if (ROUTER) {
+    int pf = -1, dc = -1, er = 0;
+    if (cnt == 1) {
+      pf = deepest;
+    } else if (cnt > 1) {
+      if (deepest < t.n_prefill) {
+        pf = deepest;
+      } else if (bad_below || last_prefill < 0) {
+        er = 1;
+      } else {
+        pf = last_prefill;
+        dc = deepest;
+      }
+    }
+    ro.prefill[q] = pf;
+    ro.decode[q] = dc;
+    ro.err[q] = (unsigned char)er;
+  }
+}
+
+// K1, run-following GROUP form: G lanes per query, one arena position per lane and step, so the three
+// streams (arena tokens, owner map, query tokens) are read as coalesced 32..128-byte pieces and a step
+// costs one memory round trip for G positions.  (The one-lane form above issues the same loads as 3*8
+// scattered 4-byte requests per lane and is bound by the load/store unit.)  All lanes of a group carry the
+// same walk state; node boundaries inside a step are resolved with ballots: the first position where the
+// match stops, the nodes that ended before it (each stamped by the lane that sees its end).
+template <int G, bool SPLIT, bool ROUTER>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
+                     int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
+                     unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
+  RmGroup<G> g;
+  const int q = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (q >= B) return;
+  const i64 o0 = qoff[q];
+  const int L = (int)(qoff[q + 1] - o0);
+  const int* __restrict__ key = qtok + o0;
+  const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
+  const RmSlot* __restrict__ table = t.table;
+  const unsigned tmask = t.table_mask, tshift = t.table_shift;
+  const int* __restrict__ tok = t.tok;
+  const int* __restrict__ seg = t.seg;
+  u64* __restrict__ stamp = t.stamp;
+  const u64 qpol = rm_policy_evict_first();
+  const int lane = g.lane;
+
+  int node = 0, pos = 0;               // `node` is matched in full through `pos` (same in every lane)
+  u64 req = RM_NO_REQ;
+  int cnt = 0, deepest = -1, last_prefill = -1;
+  bool bad_below = false;
+  bool done = L == 0;
+
+  while (!done) {
+    // ---- child of `node` that starts with key[pos]: child-table probe (same address in every lane)
+    const int tk = rm_ld_query(key + pos, qpol);
+    int cur = -1;
+    i64 cs = 0;
+    {
+      unsigned si = rm_hash2((unsigned)node, (unsigned)tk, tshift);
+      while (true) {
+        const RmSlotRegs S = rm_ld_slot(table + si);
+        if ((unsigned)S.a.x == (unsigned)tk && (unsigned)S.a.y == (unsigned)node) {
+          cur = S.a.z;
+          cs = (i64)(((u64)(unsigned)S.b.y << 32) | (unsigned)S.b.x);
+          break;
+        }
+        if ((S.a.x & S.a.y) == -1) break;
+        si = (si + 1) & tmask;
+      }
+    }
+    if (cur < 0) break;                 // the walk ends at `node`
+    // ---- stream along the arena run: position a + lane against query token qi + lane
+    i64 a = cs + 1;
+    int qi = pos + 1;
+    bool leave = false;
+    while (!leave && !done) {
+      const i64 ia = a + lane;
+      const int iq = qi + lane;
+      const int tj = __ldg(tok + ia);
+      const int sj = __ldg(seg + ia);
+      const bool inq = iq < L;
+      const int kj = inq ? rm_ld_query(key + iq, qpol) : 0;
+      const int own = sj < 0 ? -1 : (sj & 0x3FFFFFFF);
+      int prev = g.shfl_up(own, 1);
+      if (lane == 0) prev = cur;
+      const bool bnd = own != prev;                                   // node `prev` ends at this position
+      const bool badb = bnd && !(sj >= 0 && (sj & RM_SEG_CONT));      // ... and the chain does not go on
+      const bool stop = badb || !inq || tj != kj;
+      const unsigned sm = g.ballot(stop);
+      const int s = sm ? (__ffs(sm) - 1) : G;                         // first position where the match stops
+      const bool commit = bnd && lane <= s;                           // `prev` is matched in full
+      if (commit && !(flags & 1)) atomicMax(stamp + prev, seq);       // radix_cache.py:260 / radix_mesh.py:257
+      const unsigned cm = g.ballot(commit);
+      if (ROUTER) {
+        const int rk = commit ? t.rank[prev] : 0;
+        const unsigned pm = g.ballot(commit && rk < t.n_prefill);
+        const unsigned im = g.ballot(commit && rk >= t.n_prefill + t.n_decode);
+        if (cm) {
+          const int jd = 31 - __clz((int)cm);
+          cnt += __popc(cm);
+          deepest = g.bcast(rk, jd);
+          if (pm) {
+            const int jp = 31 - __clz((int)pm);
+            last_prefill = g.bcast(rk, jp);
+            const unsigned above = jp >= 31 ? 0u : (~0u << (jp + 1));
+            bad_below = (im & above) != 0;
+          } else if (im) {
+            bad_below = true;
+          }
+        }
+      }
+      int jb = -1;                       // last boundary committed in this step
+      if (cm) {
+        jb = 31 - __clz((int)cm);
+        node = g.bcast(prev, jb);
+        pos = qi + jb;
+        cs = a + jb;                     // the node that starts there is the current one from now on
+        cur = g.bcast(own, jb);
+      }
+      if (s == G) {                      // everything matched: next G positions
+        a += G;
+        qi += G;
+        continue;
+      }
+      // the match stops at relative position s
+      const bool bnd_s = g.bcast(bnd ? 1 : 0, s) != 0;
+      if (bnd_s) {
+        // a node ended exactly there (it is committed); either the query is exhausted or the next node
+        // is not a contiguous match: back to the child table
+        if (qi + s >= L) done = true;
+        else leave = true;
+      } else {
+        // the query ends, or differs, inside the node that covers position s: partial match
+        const int pn = g.bcast(own, s);
+        const int p = (int)(a + s - cs);
+        if (SPLIT) {
+          // the reference splits pn here and returns the new upper node (radix_cache.py:262-266); K3 does it
+          req = ((u64)(unsigned)pn << len_bits) | (u64)(unsigned)p;
+        } else {
+          if (lane == 0 && !(flags & 1)) atomicMax(stamp + pn, seq);
+          if (ROUTER) {
+            const int rk = t.rank[pn];
+            ++cnt;
+            deepest = rk;
+            if (rk < t.n_prefill) {
+              last_prefill = rk;
+              bad_below = false;
+            } else if (rk >= t.n_prefill + t.n_decode) {
+              bad_below = true;
+            }
+          }
+          node = pn;                     // no-split modes return the partially matched child
+        }
+        pos = qi + s;
+        done = true;
+      }
+    }
+  }
+  if (lane == 0) {
+    out_len[q] = pos;
+    out_node[q] = node;
+    if (SPLIT && req != RM_NO_REQ && !(flags & 4)) {
+      const int slot = atomicAdd(&t.ctr->n_req, 1);
+      req_key[slot] = req;
+      req_val[slot] = (unsigned)q;
+    }
+    if (ROUTER) {
+      int pf = -1, dc = -1, er = 0;
+      if (cnt == 1) {
+        pf = deepest;
+      } else if (cnt > 1) {
+        if (deepest < t.n_prefill) {
+          pf = deepest;
+        } else if (bad_below || last_prefill < 0) {
+          er = 1;
+        } else {
+          pf = last_prefill;
+          dc = deepest;
+        }
+      }
+      ro.prefill[q] = pf;
+      ro.decode[q] = dc;
+      ro.err[q] = (unsigned char)er;
+    }
+  }
+}
+
 // K3: one group per edge that received split requests.  `skey` is sorted by (node, split point) and,
 // inside equal keys, by query index (the sort is stable), `sval` holds the query index.
 template <int G>
@@ -518,6 +842,14 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
     t.parked[u] = -1;
     t.stamp[u] = st;
     atomicMax(&t.ctr->node_hwm, u + 1);
+    // owner map of segment [a, p): the first position keeps the edge's own flag (kk == 0) or marks u as the
+    // contiguous child of the previous segment
+    {
+      const int first = kk == 0 ? ((t.seg[off] & RM_SEG_CONT) | u) : (u | RM_SEG_CONT);
+      t.seg[off + a] = first;
+      for (int x = a + 1; x < p; ++x) t.seg[off + x] = u;
+      if (kk == U - 1) t.seg[off + p] = c | RM_SEG_CONT;
+    }
     if (kk == 0) {
       RmSlot s;
       int sidx = rm_find<true>(t, rm_key(par, t.tok[off]), s);
@@ -588,6 +920,9 @@ rm_split_single_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* _
   t.parked[u] = -1;
   t.stamp[u] = st;
   atomicMax(&t.ctr->node_hwm, u + 1);
+  t.seg[off] = (t.seg[off] & RM_SEG_CONT) | u;     // owner map: [off, off+p) is u's, c starts at off+p
+  for (int x = 1; x < p; ++x) t.seg[off + x] = u;
+  t.seg[off + p] = c | RM_SEG_CONT;
   RmSlot s;
   const int sidx = rm_find<true>(t, rm_key(par, tok0), s);
   if (sidx < 0) {
@@ -657,6 +992,20 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
 #ifdef RM_EMU
   // the emulation build runs the lane-per-query kernel (the default on the GPU) unless RM_EMU_GROUP is set
   static const bool emu_group = getenv("RM_EMU_GROUP") != nullptr;
+  static const bool emu_lpq = getenv("RM_EMU_LPQ") != nullptr;
+  static const bool emu_run1 = getenv("RM_EMU_RUN1") != nullptr;
+  if (!emu_group && !emu_lpq) {
+    if (emu_run1) {
+      auto kr = rm_match_run_kernel<SPLIT, ROUTER>;
+      RM_LAUNCH(kr, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+                idx->sc.key[0], idx->sc.val[0], ro, 0);
+    } else {
+      auto kr = rm_match_rung_kernel<1, SPLIT, ROUTER>;
+      RM_LAUNCH(kr, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+                idx->sc.key[0], idx->sc.val[0], ro, 0);
+    }
+    return;
+  }
   if (!emu_group) {
     auto kq = rm_match_lpq_kernel<SPLIT, ROUTER>;
     RM_LAUNCH(kq, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
@@ -673,6 +1022,39 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
     RM_LAUNCH(k, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,          \
               idx->sc.key[0], idx->sc.val[0], ro);                                                               \
   } break;
+  // RM_WALK selects the walk kernel: "run" (default) = run-following, RM_RUN_G lanes per query (default 8);
+  // "lane" = run-following, one lane per query; "table" = hop-by-hop through the child table, RM_MATCH_G lanes
+  // per query (1 = the lane-per-query kernel).  The non-default forms are kept for A/B measurements and tests.
+  static const char* walk = getenv("RM_WALK") ? getenv("RM_WALK") : "run";
+  static const int run_flags = getenv("RM_EXP_FLAGS") ? (atoi(getenv("RM_EXP_FLAGS")) & 1) : 0;
+  if (!strcmp(walk, "run")) {
+    static const int rg = getenv("RM_RUN_G") ? atoi(getenv("RM_RUN_G")) : 8;
+    const long long rthreads = (long long)B * rg;
+    const int rtpb = rthreads >= 148LL * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (rthreads >= 148LL * 8 * 128 ? 128 : 64);
+    const int rgrid = (int)((rthreads + rtpb - 1) / rtpb);
+#define RM_RCASE(GG)                                                                                              \
+  case GG: {                                                                                                      \
+    auto kr = rm_match_rung_kernel<GG, SPLIT, ROUTER>;                                                            \
+    RM_LAUNCH(kr, rgrid, rtpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,        \
+              idx->sc.key[0], idx->sc.val[0], ro, run_flags);                                                     \
+  } break;
+    switch (rg) {
+      RM_RCASE(4)
+      RM_RCASE(16)
+      RM_RCASE(32)
+      default:
+      RM_RCASE(8)
+    }
+#undef RM_RCASE
+    return;
+  }
+  if (!strcmp(walk, "lane")) {
+    const int ltpb = B >= 148 * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (B >= 148 * 8 * 128 ? 128 : 64);
+    auto kr = rm_match_run_kernel<SPLIT, ROUTER>;
+    RM_LAUNCH(kr, (B + ltpb - 1) / ltpb, ltpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
+              idx->sc.key[0], idx->sc.val[0], ro, run_flags);
+    return;
+  }
   switch (G) {
     case 1: {
       auto k = rm_match_lpq_kernel<SPLIT, ROUTER>;
@@ -786,9 +1168,15 @@ int rm_launch_walk_records(rm_index* idx, const int* tokens, const i64* offsets,
 #else
   const int tpb = N >= 148 * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (N >= 148 * 8 * 128 ? 128 : 64);
 #endif
-  auto k = rm_match_lpq_kernel<true, false>;
-  RM_LAUNCH(k, (N + tpb - 1) / tpb, tpb, s, idx->t, tokens, offsets, N, seq_base, idx->len_bits, out_len, out_node,
-            idx->sc.key[0], idx->sc.val[0], ro, 4);
+#ifdef RM_EMU
+  auto k = rm_match_rung_kernel<1, true, false>;
+  const long long wthreads = N;
+#else
+  auto k = rm_match_rung_kernel<8, true, false>;
+  const long long wthreads = (long long)N * 8;
+#endif
+  RM_LAUNCH(k, (int)((wthreads + tpb - 1) / tpb), tpb, s, idx->t, tokens, offsets, N, seq_base, idx->len_bits, out_len,
+            out_node, idx->sc.key[0], idx->sc.val[0], ro, 4);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }

@@ -27,6 +27,7 @@ def device_canonical(ix, with_stamps=True, mesh=False):
             full[z] = base
         return full[x]
 
+    check_owner_map(ix, d, used)
     rows = []
     for x in alive:
         o, l = int(d["edge_off"][x]), int(d["edge_len"][x])
@@ -40,6 +41,34 @@ def device_canonical(ix, with_stamps=True, mesh=False):
     out["_ids"] = {fk(x): x for x in alive}
     out["_dump"] = d
     return out
+
+
+CONT = 0x40000000
+
+
+def check_owner_map(ix, d, used):
+    """Invariants of the per-position owner map (csrc/rm_common.cuh RM_SEG_CONT): every live run (tree nodes and
+    parked duplicates) is owned by its node, the contiguity flag sits only on the first position of a node
+    whose parent's run ends right there, and everything else is free."""
+    if not used:
+        return
+    seg = ix.read_segments(0, used)
+    n = d["n"]
+    covered = np.zeros(used, dtype=bool)
+    for x in range(1, n):
+        live = (d["parent"][x] >= 0 or d["gen"][x] < 0) and d["edge_len"][x] > 0
+        if not live:
+            continue
+        o, l = int(d["edge_off"][x]), int(d["edge_len"][x])
+        run = seg[o:o + l]
+        assert np.all((run & 0x3FFFFFFF) == x) and np.all(run >= 0), f"owner map of node {x}: {run.tolist()}"
+        assert not np.any(run[1:] & CONT), f"contiguity flag inside node {x}"
+        if run[0] & CONT:
+            p = int(d["parent"][x])
+            assert d["gen"][x] >= 0 and p > 0 and int(d["edge_off"][p]) + int(d["edge_len"][p]) == o, \
+                f"node {x} is flagged contiguous but its parent {p} does not end at {o}"
+        covered[o:o + l] = True
+    assert np.all(seg[~covered] == -1), "free arena positions must be unowned"
 
 
 def rank_stamps(rows):

@@ -28,17 +28,21 @@ def test_gpu_batched_match_splits_then_evict_order(seed):
     cases.run_split_evict(make_index, seed)
 
 
-@pytest.mark.parametrize("group", [1, 2, 4, 8, 16, 32])
-def test_gpu_zipf_match_all_group_widths(group, monkeypatch):
-    """Zipf shared-prefix workload at reduced size, device-pointer entry points, every
-    lanes-per-query variant of the match kernel: lengths, last nodes, values and final tree."""
+WALKS = [("run", 4), ("run", 8), ("run", 16), ("run", 32), ("lane", 1), ("table", 1), ("table", 2), ("table", 8), ("table", 32)]
+
+
+@pytest.mark.parametrize("walk,group", WALKS, ids=[f"{w}{g}" for w, g in WALKS])
+def test_gpu_zipf_match_all_walk_kernels(walk, group):
+    """Zipf shared-prefix workload at reduced size, device-pointer entry points, every form of the
+    walk kernel (run-following with 4..32 lanes per query, run-following lane per query, hop-by-hop through
+    the child table with 1..32 lanes per query): lengths, last nodes, values and final tree."""
+    import os
     import subprocess
     import sys
-    # the group width is read once per process: run the check in a child with RM_MATCH_G set
+    # the kernel choice is read once per process: run the check in a child with the environment set
     code = ("import sys; sys.path.insert(0, '.'); from tests.test_gpu_base import zipf_check; "
             "zipf_check(seed=5, n_docs=64, L=96, n_ins=600, n_q=3000)")
-    import os
-    env = dict(os.environ, RM_MATCH_G=str(group))
+    env = dict(os.environ, RM_WALK=walk, RM_RUN_G=str(group), RM_MATCH_G=str(group))
     subprocess.run([sys.executable, "-c", code], check=True, env=env,
                    cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
