@@ -19,6 +19,9 @@ struct RmScratch {
   unsigned* ev_val[2];
   unsigned* ev_hist;
   int* ev_lens;       // value-run lengths of the evicted nodes, in eviction order
+  u64* ev_eff;        // effective (subtree-max) stamps
+  int* ev_rem;        // children still to report, per node
+  int* ev_nch0;       // child counts before the climb
   // lock batches (sized by max_nodes)
   int* lock_first;
   int* lock_cnt;

@@ -222,14 +222,52 @@ __global__ void rm_evict_pin_kernel(RmTree t, int n, int* __restrict__ pinned) {
   while (y > 0 && atomicExch(&pinned[y], 1) == 0) y = t.parent[y];
 }
 
-__global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int* __restrict__ pinned, u64* key,
-                                     unsigned* val) {
+// Lazy stamps.  Walks and inserts stamp only the deepest node(s) they reach (one atomic per operation instead
+// of one per hop); every other node the reference would have stamped is an ancestor of such an endpoint.
+// The stamp the reference holds for a node is therefore the maximum of the raw stamps in its subtree,
+//     eff(x) = max(raw(x), max over children c of eff(c)),
+// which these two kernels compute bottom-up without ordering or spinning: every node counts its children,
+// leaves start climbing, and at each parent only the LAST child to report carries on upward.  (Deleting a
+// node would lower its ancestors' eff, so eviction pushes eff(x) into raw(parent) first.)
+__global__ void rm_evict_eff_init_kernel(RmTree t, int n, u64* __restrict__ eff, int* __restrict__ rem) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n) return;
+  eff[x] = t.stamp[x];
+  if (x > 0 && t.parent[x] > 0 && t.gen[x] >= 0) atomicAdd(&rem[t.parent[x]], 1);
+}
+
+// the child counts are consumed while climbing, so "is a leaf" is taken from a copy made before
+__global__ void rm_evict_eff_leaf_kernel(int n, const int* __restrict__ rem, int* __restrict__ nch0) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x < n) nch0[x] = rem[x];
+}
+
+__global__ void rm_evict_eff_climb_kernel(RmTree t, int n, u64* __restrict__ eff, int* __restrict__ rem,
+                                          const int* __restrict__ nch0) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || x == 0) return;
+  if (t.parent[x] < 0 || t.gen[x] < 0 || nch0[x] != 0) return;   // leaves of the tree only
+  int y = x;
+  u64 v = eff[y];
+  while (true) {
+    const int p = t.parent[y];
+    if (p <= 0) break;                      // the root carries no stamp
+    atomicMax(&eff[p], v);
+    __threadfence();
+    if (atomicSub(&rem[p], 1) != 1) break;  // a sibling subtree is still on its way
+    y = p;
+    v = *reinterpret_cast<volatile u64*>(&eff[p]);
+  }
+}
+
+__global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int* __restrict__ pinned,
+                                     const u64* __restrict__ eff, u64* key, unsigned* val) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= n) return;
   u64 k = RM_NO_REQ;
   if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0 && pinned[x] == 0) {
     u64 dmask = (1ull << depth_bits) - 1ull;
-    k = (t.stamp[x] << depth_bits) | (dmask - (u64)(unsigned)t.depth_end[x]);
+    k = (eff[x] << depth_bits) | (dmask - (u64)(unsigned)t.depth_end[x]);
   }
   key[x] = k;
   val[x] = (unsigned)x;
@@ -299,8 +337,8 @@ __global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, cons
 #endif
 }
 
-__global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sval, int* out_nodes, i64* out_offs,
-                                      int* out_lens) {
+__global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sval, const u64* __restrict__ eff,
+                                      int* out_nodes, i64* out_offs, int* out_lens) {
   const int n = t.ctr->evict_n;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
@@ -315,6 +353,7 @@ __global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sva
   int sidx = rm_find<true>(t, rm_key(par, t.tok[off]), s);
   if (sidx >= 0) *reinterpret_cast<volatile u64*>(&t.table[sidx].key) = RM_TOMB_KEY;
   for (int k2 = 0; k2 < len; ++k2) t.seg[off + k2] = -1;   // the run is free again
+  if (par > 0) atomicMax(&t.stamp[par], eff[x]);            // lazy stamps: the parent keeps what it saw through x
   atomicSub(&t.nchild[par], 1);
   t.parent[x] = -1;
   t.edge_len[x] = 0;
@@ -347,8 +386,12 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
   int* pinned = sc.ev_lens;   // free until rm_evict_apply_kernel writes the evicted lengths
   RM_CUDA(cudaMemsetAsync(pinned, 0, sizeof(int) * (size_t)n, s));
   RM_LAUNCH(rm_evict_pin_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, pinned);
-  RM_LAUNCH(rm_evict_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_key[0],
-            sc.ev_val[0]);
+  RM_CUDA(cudaMemsetAsync(sc.ev_rem, 0, sizeof(int) * (size_t)n, s));
+  RM_LAUNCH(rm_evict_eff_init_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem);
+  RM_LAUNCH(rm_evict_eff_leaf_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, n, sc.ev_rem, sc.ev_nch0);
+  RM_LAUNCH(rm_evict_eff_climb_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem, sc.ev_nch0);
+  RM_LAUNCH(rm_evict_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_eff,
+            sc.ev_key[0], sc.ev_val[0]);
   const int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, bits, sc.ev_hist, s);
 #ifdef RM_EMU
   RM_LAUNCH(rm_evict_cut_kernel, 1, 1, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, cap);
@@ -360,7 +403,8 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
   i64* d_offs = reinterpret_cast<i64*>(sc.ev_key[w ^ 1]);
   int* d_lens = sc.ev_lens;
   const int lim = min(n, cap);
-  RM_LAUNCH(rm_evict_apply_kernel, (lim + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, sc.ev_val[w], d_nodes, d_offs, d_lens);
+  RM_LAUNCH(rm_evict_apply_kernel, (lim + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, sc.ev_val[w], sc.ev_eff, d_nodes, d_offs,
+            d_lens);
   RM_CUDA(cudaGetLastError());
   RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));

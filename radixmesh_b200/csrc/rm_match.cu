@@ -114,7 +114,6 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
     }
     // child c is reached: stamp it (radix_cache.py:260 / radix_mesh.py:257); the max over the batch is
     // the stamp the last query in order leaves behind
-    if (g.lane == 0) atomicMax(&t.stamp[c], seq);
     if (ROUTER) {
       ++cnt;
       deepest = crank;
@@ -134,6 +133,7 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
     si = ni;
   }
   if (g.lane == 0) {
+    if (node > 0) atomicMax(&t.stamp[node], seq);   // endpoint stamp (lazy stamps, see rm_maint.cu rm_evict_eff_*)
     out_len[q] = pos;
     out_node[q] = node;   // K3 overwrites this for queries that asked for a split
     if (SPLIT && req != RM_NO_REQ) {
@@ -228,7 +228,6 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
       want_tok = (unsigned)g1;
       si = rm_hash2((unsigned)c1, want_tok, tshift);
       S = rm_ld_slot(table + si);
-      if (!(flags & 1)) atomicMax(stamp + c1, seq);   // radix_cache.py:260 / radix_mesh.py:257
       if (ROUTER) {
         const int r1 = rm_slot_rank(w1);
         ++cnt;
@@ -304,7 +303,6 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
           si = rm_hash2((unsigned)c, want_tok, tshift);
           S = rm_ld_slot(table + si);
         }
-        if (!(flags & 1)) atomicMax(stamp + c, seq);   // radix_cache.py:260 / radix_mesh.py:257
         if (ROUTER) {
           ++cnt;
           deepest = erank;
@@ -362,7 +360,6 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
       req = ((u64)(unsigned)c << len_bits) | (u64)(unsigned)m;
       break;
     }
-    if (!(flags & 1)) atomicMax(stamp + c, seq);
     if (ROUTER) {
       ++cnt;
       deepest = erank;
@@ -387,6 +384,10 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
     g2 = (pos + 2 < L) ? rm_ld_query(key + pos + 2, qpol) : 0;
     g3 = (pos + 3 < L) ? rm_ld_query(key + pos + 3, qpol) : 0;
   }
+  // Lazy stamps: an operation stamps only the deepest node it reached (radix_cache.py:253-260 stamps the whole
+  // path; every node on it is an ancestor of this one, and eviction takes a node's stamp as the maximum over
+  // its subtree, rm_maint.cu).  One atomic per query instead of one per hop.
+  if (node > 0 && !(flags & 1)) atomicMax(stamp + node, seq);
   out_len[q] = pos;
   out_node[q] = node;
   if (SPLIT && req != RM_NO_REQ && !(flags & 4)) {   // flags bit 2: walk only (insert pre-pass)
@@ -500,7 +501,6 @@ rm_match_run_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
         const int owner = sg < 0 ? -1 : (sg & 0x3FFFFFFF);
         if (owner != cur) {
           // cur's run ends here: cur is matched in full
-          if (!(flags & 1)) atomicMax(stamp + cur, seq);
           if (ROUTER) {
             const int rk = t.rank[cur];
             RM_ROUTER_SEE(rk);
@@ -525,8 +525,7 @@ rm_match_run_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
             req = ((u64)(unsigned)cur << len_bits) | (u64)(unsigned)p;
             pos = qi;
           } else {
-            if (!(flags & 1)) atomicMax(stamp + cur, seq);
-            if (ROUTER) {
+              if (ROUTER) {
               const int rk = t.rank[cur];
               RM_ROUTER_SEE(rk);
             }
@@ -542,6 +541,10 @@ rm_match_run_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
     }
   }
 #undef RM_ROUTER_SEE
+  // Lazy stamps: an operation stamps only the deepest node it reached (radix_cache.py:253-260 stamps the whole
+  // path; every node on it is an ancestor of this one, and eviction takes a node's stamp as the maximum over
+  // its subtree, rm_maint.cu).  One atomic per query instead of one per hop.
+  if (node > 0 && !(flags & 1)) atomicMax(stamp + node, seq);
   out_len[q] = pos;
   out_node[q] = node;
   if (SPLIT && req != RM_NO_REQ && !(flags & 4)) {
@@ -640,7 +643,6 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       const unsigned sm = g.ballot(stop);
       const int s = sm ? (__ffs(sm) - 1) : G;                         // first position where the match stops
       const bool commit = bnd && lane <= s;                           // `prev` is matched in full
-      if (commit && !(flags & 1)) atomicMax(stamp + prev, seq);       // radix_cache.py:260 / radix_mesh.py:257
       const unsigned cm = g.ballot(commit);
       if (ROUTER) {
         const int rk = commit ? t.rank[prev] : 0;
@@ -688,7 +690,6 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
           // the reference splits pn here and returns the new upper node (radix_cache.py:262-266); K3 does it
           req = ((u64)(unsigned)pn << len_bits) | (u64)(unsigned)p;
         } else {
-          if (lane == 0 && !(flags & 1)) atomicMax(stamp + pn, seq);
           if (ROUTER) {
             const int rk = t.rank[pn];
             ++cnt;
@@ -708,6 +709,7 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
     }
   }
   if (lane == 0) {
+    if (node > 0 && !(flags & 1)) atomicMax(stamp + node, seq);   // lazy stamps: the endpoint only
     out_len[q] = pos;
     out_node[q] = node;
     if (SPLIT && req != RM_NO_REQ && !(flags & 4)) {

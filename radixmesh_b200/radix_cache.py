@@ -44,7 +44,7 @@ class TreeNode:
 
     @property
     def last_access_time(self) -> int:
-        return int(self._cache._dump()["stamp"][self._resolved()])
+        return int(self._cache._eff_stamps()[self._resolved()])
 
     @property
     def parent(self) -> Optional["TreeNode"]:
@@ -130,6 +130,21 @@ class RadixCache:
         if self._dump_cache is None:
             self._dump_cache = self._ix.dump()
         return self._dump_cache
+
+    def _eff_stamps(self) -> np.ndarray:
+        """Last-access stamp per node as the reference holds it.  The device stamps only the deepest node an
+        operation reaches; a node's stamp is the maximum over its subtree (DESIGN.md 'lazy stamps')."""
+        d = self._dump()
+        if "eff" not in d:
+            n = d["n"]
+            eff = d["stamp"][:n].astype(np.uint64).copy()
+            live = [x for x in range(1, n) if d["parent"][x] > 0 and d["gen"][x] >= 0]
+            for x in sorted(live, key=lambda z: -int(d["depth"][z])):
+                p = int(d["parent"][x])
+                if eff[x] > eff[p]:
+                    eff[p] = eff[x]
+            d["eff"] = eff
+        return d["eff"]
 
     def _flush(self) -> None:       # RadixMesh stages remote inserts; the base class has nothing pending
         return None

@@ -28,13 +28,19 @@ def device_canonical(ix, with_stamps=True, mesh=False):
         return full[x]
 
     check_owner_map(ix, d, used)
+    # lazy stamps: the stamp the reference holds for a node is the maximum raw stamp in its subtree
+    eff = {x: int(d["stamp"][x]) for x in alive}
+    for x in sorted(alive, key=lambda z: -int(d["depth"][z])):
+        p = int(d["parent"][x])
+        if p > 0:
+            eff[p] = max(eff[p], eff[x])
     rows = []
     for x in alive:
         o, l = int(d["edge_off"][x]), int(d["edge_len"][x])
         v = tuple(int(t) for t in val[o:o + l]) if val is not None else ()
         row = (fk(x), l, v, int(d["rank"][x]), int(d["lock_ref"][x]))
         if not mesh:
-            row = row + (int(d["stamp"][x]) >> 1,)   # 2*op (+1): compare the operation only
+            row = row + (eff[x] >> 1,)   # 2*op (+1): compare the operation only
         rows.append(row)
     rows.sort()
     out = {"nodes": rows, "evictable": int(s.evictable), "protected": int(s.protected_)}
