@@ -320,7 +320,7 @@ def main():
                 "vs_baseline": None, "dtype": "int32", "data": "synthetic",
                 "config": {"workload": wl["name"], "tree_nodes_start": nodes_start, "tree_nodes_end": nodes_end,
                            "inserts_to_build": n_ins, "build_s": round(build_s, 2), "batch": B, "query_len": L,
-                           "mode": "RadixCache (splitting match)", "lanes_per_query": int(os.environ.get("RM_MATCH_G", "1")),
+                           "mode": "RadixCache (splitting match)", "walk": os.environ.get("RM_WALK", "run"), "lanes_per_query": int(os.environ.get("RM_RUN_G", "32")),
                            "l2": f"every step reads a fresh {B * L * 4 >> 20} MiB query batch ({(K + W) * B * L * 4 >> 20} MiB "
                                  "of distinct batches > 126 MB L2); the tree stays warm as in steady-state serving",
                            "parallelism": f"replica x{world}, query batches sharded, no collective"},
@@ -343,7 +343,7 @@ def main():
             except Exception:
                 pass
             line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                "traffic": traffic, "kernel": "rm_match_lpq_kernel (K1 walk)", "peak_source": peak_src,
+                                "traffic": traffic, "kernel": "rm_match_rung_kernel (K1 walk)", "peak_source": peak_src,
                                 "bytes_per_lookup": bpl, "mean_hops": hops, "kernel_ms": walk_ms_mean,
                                 "kernel_share_of_step": walk_ms_mean / (ms / K),
                                 "lookups_per_s_kernel_only": B / (walk_ms_mean * 1e-3)}

@@ -92,7 +92,7 @@ int rm_destroy(rm_index* idx) {
   RmScratch& sc = idx->sc;
   void* ptrs[] = {t.table, t.parent, t.edge_off, t.edge_len, t.lock_ref, t.stamp, t.rank, t.depth_end, t.nchild,
                   t.gen, t.parked, t.tok, t.val, t.seg, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
-                  sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.hist, sc.ev_key[0], sc.ev_key[1],
+                  sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.link, t.req_head, sc.hist, sc.ev_key[0], sc.ev_key[1],
                   sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ev_nch0, sc.lock_first, sc.lock_cnt, sc.lock_flag,
                   sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b,
                   idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner};
@@ -173,6 +173,8 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&sc.krank, B));
   A(rm_dalloc(&sc.uniq_pos, B));
   A(rm_dalloc(&sc.uniq_min, B));
+  A(rm_dalloc(&sc.link, B));
+  A(rm_dalloc(&t.req_head, N));
   A(rm_dalloc(&sc.hist, sc.hist_words));
   A(rm_dalloc(&sc.ev_key[0], N));
   A(rm_dalloc(&sc.ev_key[1], N));

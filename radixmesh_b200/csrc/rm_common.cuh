@@ -87,6 +87,8 @@ struct RmTree {
   int* parked;     // tree node: most recently parked predecessor (or -1); parked node: the one parked before it
   int* tok;
   i64* val;
+  int* req_head;   // per node: last query of the current match batch that asked to split it (-1 between batches)
+  int* req_link;   // per query of the batch: the query that asked for the same node before it (-1 = none)
   int* seg;        // per arena position: id of the node whose edge covers it (-1 = free), see RM_SEG_CONT
   int* free_ids;
   RmCounters* ctr;

@@ -12,6 +12,7 @@ struct RmScratch {
   int* krank;         // per sorted split request: rank of its split point among the edge's distinct points
   int* uniq_pos;      // per edge group: sorted positions of the distinct split points
   unsigned* uniq_min; // per distinct split point: lowest query index that asked for it
+  int* link;          // per query: predecessor in its node's request chain (RmTree.req_link points here)
   unsigned* hist;     // radix-sort histogram table
   size_t hist_words;
   // eviction (sized by max_nodes)

@@ -68,6 +68,7 @@ int rm_launch_reset(rm_index* idx, cudaStream_t s) {
   RmTree& t = idx->t;
   RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
   RM_CUDA(cudaMemsetAsync(t.dup_key, 0xFF, sizeof(u64) * ((size_t)t.dup_mask + 1), s));
+  RM_CUDA(cudaMemsetAsync(t.req_head, 0xFF, sizeof(int) * (size_t)t.max_nodes, s));
   RM_CUDA(cudaMemsetAsync(t.seg, 0xFF, sizeof(int) * ((size_t)t.max_tokens + RM_ARENA_PAD), s));
   RmLockScratch ls = rm_lock_scratch(idx);
   RM_CUDA(cudaMemsetAsync(ls.flag, 0, sizeof(int), s));

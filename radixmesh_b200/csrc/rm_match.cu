@@ -140,6 +140,8 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
       const int slot = atomicAdd(&t.ctr->n_req, 1);   // compact list of split requests
       req_key[slot] = req;
       req_val[slot] = (unsigned)q;
+      // per-node chain of this batch's requests: lets K3 tell at once whether the node has a single request
+      t.req_link[q] = atomicExch(&t.req_head[(int)(req >> len_bits)], q);
     }
     if (ROUTER) {
       int pf = -1, dc = -1, er = 0;
@@ -394,6 +396,8 @@ rm_match_lpq_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
     const int slot = atomicAdd(&t.ctr->n_req, 1);     // compact list of split requests
     req_key[slot] = req;
     req_val[slot] = (unsigned)q;
+    // per-node chain of this batch's requests: lets K3 tell at once whether the node has a single request
+    t.req_link[q] = atomicExch(&t.req_head[(int)(req >> len_bits)], q);
   }
   if (ROUTER) {
     int pf = -1, dc = -1, er = 0;
@@ -551,6 +555,8 @@ rm_match_run_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
     const int slot = atomicAdd(&t.ctr->n_req, 1);
     req_key[slot] = req;
     req_val[slot] = (unsigned)q;
+    // per-node chain of this batch's requests: lets K3 tell at once whether the node has a single request
+    t.req_link[q] = atomicExch(&t.req_head[(int)(req >> len_bits)], q);
   }
   if (ROUTER) {
     int pf = -1, dc = -1, er = 0;
@@ -716,6 +722,8 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       const int slot = atomicAdd(&t.ctr->n_req, 1);
       req_key[slot] = req;
       req_val[slot] = (unsigned)q;
+      // per-node chain of this batch's requests: lets K3 tell at once whether the node has a single request
+      t.req_link[q] = atomicExch(&t.req_head[(int)(req >> len_bits)], q);
     }
     if (ROUTER) {
       int pf = -1, dc = -1, er = 0;
@@ -744,18 +752,17 @@ template <int G>
 __global__ void __launch_bounds__(RM_MATCH_TPB)
 rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int Bmax, int len_bits,
                       u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
-                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min, const int* __restrict__ big_list) {
+                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min) {
   RmGroup<G> g;
-  const int B = min(t.ctr->n_req, Bmax);   // requests were appended compactly by K1, in no particular order
+  const int B = min(t.ctr->n_big, Bmax);   // requests on shared edges only (rm_split_single_kernel did the rest)
   const u64 pmask = (1ull << len_bits) - 1ull;
-  // one group of lanes per edge that received SEVERAL requests (rm_split_single_kernel listed them and
-  // handled the single-request edges itself); grid-stride, the counts live on the device
-  const int n_big = t.ctr->n_big;
+  // one group of lanes per edge, found as the first entry of its run in the sorted list; grid-stride, the
+  // count lives on the device
   const int gstride = (int)((gridDim.x * (unsigned)blockDim.x) / G);
-  for (int w = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G); w < n_big; w += gstride) {
-  const int i = big_list[w];
+  for (int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G); i < B; i += gstride) {
   const u64 ki = skey[i];
   const int c = (int)(ki >> len_bits);
+  if (i > 0 && (int)(skey[i - 1] >> len_bits) == c) continue;   // not the first request of its edge
   // pass 1 (forward): extent of the group, distinct split points, rank of each request's point
   int e = i, U = 0;
   for (int base = i;; base += G) {
@@ -880,24 +887,30 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
 }
 
 // K3, common case: an edge that received exactly ONE split request this batch (in steady state almost
-// all of them: ~10K single requests per 64K-query batch against a handful of shared ones).  One thread per
-// sorted request, so 32 independent splits share every memory round trip of a warp.  Edges with several
-// requests are only listed here; rm_split_apply_kernel takes them a warp each.
+// all of them: ~10K single requests per 64K-query batch against a few hundred shared ones).  One thread per
+// request of K1's compact, unsorted list, so 32 independent splits share every memory round trip of a
+// warp and nothing has to be sorted for them: a request is alone on its node iff it is the head of the
+// node's request chain and has no predecessor.  Requests on shared edges are copied to a second list,
+// which alone goes through the radix sort and rm_split_apply_kernel (a warp per edge).
 __global__ void __launch_bounds__(RM_MATCH_TPB)
-rm_split_single_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int Bmax, int len_bits,
-                       u64 seq_base, int* __restrict__ out_node, int* __restrict__ big_list) {
+rm_split_single_kernel(RmTree t, const u64* __restrict__ rkey, const unsigned* __restrict__ rval, int Bmax, int len_bits,
+                       u64 seq_base, int* __restrict__ out_node, u64* __restrict__ mkey, unsigned* __restrict__ mval) {
   const int B = min(t.ctr->n_req, Bmax);
   const int i = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
   if (i >= B) return;
-  const u64 ki = skey[i];
+  const u64 ki = rkey[i];
   const int c = (int)(ki >> len_bits);
-  if (i > 0 && (int)(skey[i - 1] >> len_bits) == c) return;            // not the first request of its edge
-  if (i + 1 < B && (int)(skey[i + 1] >> len_bits) == c) {              // shared edge: a warp will do it
-    big_list[atomicAdd(&t.ctr->n_big, 1)] = i;
+  const unsigned q = rval[i];
+  const bool is_head = t.req_head[c] == (int)q;
+  const bool alone = is_head && t.req_link[q] < 0;
+  if (is_head) t.req_head[c] = -1;                                      // ready for the next batch
+  if (!alone) {                                                         // shared edge: sorted, then a warp does it
+    const int slot = atomicAdd(&t.ctr->n_big, 1);
+    mkey[slot] = ki;
+    mval[slot] = q;
     return;
   }
   const int p = (int)(ki & ((1ull << len_bits) - 1ull));
-  const unsigned q = sval[i];
   const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
   const u64 apos = rm_alloc_nodes(t, 1);
   if (apos == ~0ull) return;
@@ -1024,13 +1037,13 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
     RM_LAUNCH(k, grid, tpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,          \
               idx->sc.key[0], idx->sc.val[0], ro);                                                               \
   } break;
-  // RM_WALK selects the walk kernel: "run" (default) = run-following, RM_RUN_G lanes per query (default 8);
+  // RM_WALK selects the walk kernel: "run" (default) = run-following, RM_RUN_G lanes per query (default 32);
   // "lane" = run-following, one lane per query; "table" = hop-by-hop through the child table, RM_MATCH_G lanes
   // per query (1 = the lane-per-query kernel).  The non-default forms are kept for A/B measurements and tests.
   static const char* walk = getenv("RM_WALK") ? getenv("RM_WALK") : "run";
   static const int run_flags = getenv("RM_EXP_FLAGS") ? (atoi(getenv("RM_EXP_FLAGS")) & 1) : 0;
   if (!strcmp(walk, "run")) {
-    static const int rg = getenv("RM_RUN_G") ? atoi(getenv("RM_RUN_G")) : 8;
+    static const int rg = getenv("RM_RUN_G") ? atoi(getenv("RM_RUN_G")) : 32;
     const long long rthreads = (long long)B * rg;
     const int rtpb = rthreads >= 148LL * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (rthreads >= 148LL * 8 * 128 ? 128 : 64);
     const int rgrid = (int)((rthreads + rtpb - 1) / rtpb);
@@ -1042,10 +1055,10 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
   } break;
     switch (rg) {
       RM_RCASE(4)
-      RM_RCASE(16)
-      RM_RCASE(32)
-      default:
       RM_RCASE(8)
+      RM_RCASE(16)
+      default:
+      RM_RCASE(32)
     }
 #undef RM_RCASE
     return;
@@ -1100,6 +1113,7 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   if (prof) cudaEventRecord(idx->prof_ev[2 * idx->prof_n], s);
 #endif
   RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_req, 0, sizeof(int), s));
+  idx->t.req_link = idx->sc.link;
   rm_match_dispatch<true, false>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
 #ifndef RM_EMU
   if (prof) {
@@ -1108,24 +1122,23 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   }
 #endif
   RM_CUDA(cudaGetLastError());
-  // group the split requests by (node, split point); their number stays on the device
+  // requests that are alone on their edge are applied straight from K1's list; the rest (requests on
+  // shared edges) are sorted by (node, split point) and applied a warp per edge.  All counts stay on the device.
   RmScratch& sc = idx->sc;
+  RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_big, 0, sizeof(int), s));
+  RM_LAUNCH(rm_split_single_kernel, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B,
+            idx->len_bits, seq_base, out_node, sc.key[1], sc.val[1]);
   const int bits = idx->node_bits + idx->len_bits;
-  const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], B, bits, sc.hist, s, &idx->t.ctr->n_req);
+  const int w = 1 ^ rm_sort_pairs(sc.key[1], sc.val[1], sc.key[0], sc.val[0], B, bits, sc.hist, s, &idx->t.ctr->n_big);
   RM_CUDA(cudaGetLastError());
   const long long threads = (long long)B * RM_WIDE_G;
   int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
 #ifndef RM_EMU
   if (grid > 148 * 8) grid = 148 * 8;    // persistent: 8 blocks of 8 warps per SM, grid-stride inside
 #endif
-  RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_big, 0, sizeof(int), s));
-  // edges with one request: a thread each; the others are listed in the spare half of the value ping-pong
-  int* big_list = reinterpret_cast<int*>(sc.val[w ^ 1]);
-  RM_LAUNCH(rm_split_single_kernel, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w],
-            B, idx->len_bits, seq_base, out_node, big_list);
   auto k3 = rm_split_apply_kernel<RM_WIDE_G>;
   RM_LAUNCH(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
-            sc.krank, sc.uniq_pos, sc.uniq_min, big_list);
+            sc.krank, sc.uniq_pos, sc.uniq_min);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }

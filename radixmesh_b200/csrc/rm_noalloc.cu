@@ -94,6 +94,7 @@ extern "C" int rm_match_batch_static(rm_index* idx, const int32_t* tokens, const
   view.krank = rm_carve<int>(cur, RM_STATIC_MAX_BATCH);
   view.uniq_pos = rm_carve<int>(cur, RM_STATIC_MAX_BATCH);
   view.uniq_min = rm_carve<unsigned>(cur, RM_STATIC_MAX_BATCH);
+  view.link = rm_carve<int>(cur, RM_STATIC_MAX_BATCH);
   view.hist_words = rm_sort_scratch_words(RM_STATIC_MAX_BATCH);
   view.hist = rm_carve<unsigned>(cur, view.hist_words);
   if ((size_t)(cur - base) > (size_t)RM_STATIC_SCRATCH_BYTES) {
