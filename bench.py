@@ -206,6 +206,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=4096, help="queries timed on the CPU oracle (rank 0, N=1)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--stages", action="store_true", help="also time the split stages (3 more CUDA events per step)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
@@ -275,7 +276,7 @@ def main():
     sampler = ClockSampler(local)
     sampler.start()
     time.sleep(0.3)
-    ix.profile(True)
+    ix.profile(2 if args.stages else 1)
     launches0 = ix.lib.rm_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     matched_tokens = torch.zeros((), dtype=torch.int64, device=dev)
@@ -287,6 +288,7 @@ def main():
     barrier()
     ms = ev0.elapsed_time(ev1)
     launches = int(ix.lib.rm_launch_count() - launches0)
+    stage_ms, _ = ix.profile_stages() if args.stages else (None, 0)
     walk_ms, walk_n = ix.profile_read()
     ix.profile(False)
     clocks = sampler.finish()
@@ -328,6 +330,9 @@ def main():
                 "e2e": {"value": e2e, "unit": "lookups/s", "h2d_bytes_per_step": B * L * 4 + (B + 1) * 8,
                         "d2h_bytes_per_step": B * 8},
                 "gpu_launches": launches, "clocks": clocks}
+        if stage_ms:
+            line["stages_ms_per_step"] = dict(zip(("walk", "single_splits", "sort_shared", "shared_splits"),
+                                                  (x / max(walk_n, 1) for x in stage_ms)))
         cpu = None
         if world == 1 and not args.no_cpu:
             v, bpl, hops, mm = cpu_sample(wl, docs, args.cpu_sample)

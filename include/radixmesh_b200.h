@@ -231,11 +231,15 @@ int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void
  * rm_launch_count: kernels this library has launched in this process.
  * rm_profile(idx, 1): record a CUDA-event pair around the walk kernel (K1) of every following
  * rm_match_batch; rm_profile_read returns the summed device time of those kernels and their count,
- * and clears the record (at most 256 batches are kept).  Synchronises.
+ * and clears the record (at most 128 batches are kept).  Synchronises.
+ * rm_profile(idx, 2) + rm_profile_stages (call it before rm_profile_read, which clears): the same sums for
+ * the four stages of a splitting match batch (three more events per batch): stage_ms_h[0] walk (K1), [1] single-request splits, [2] sort of the requests on
+ * shared edges, [3] shared-edge splits.
  */
 unsigned long long rm_launch_count(void);
 int rm_profile(rm_index* idx, int enable);
 int rm_profile_read(rm_index* idx, double* walk_ms_h, int* n_h);
+int rm_profile_stages(rm_index* idx, double* stage_ms_h, int* n_h);
 
 #ifdef __cplusplus
 }

@@ -66,6 +66,7 @@ _PROTOS = {
     "rm_launch_count": (C.c_uint64, []),
     "rm_profile": (C.c_int, [_P, C.c_int]),
     "rm_profile_read": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
+    "rm_profile_stages": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
 }
 EXPORTS = tuple(_PROTOS)
 
@@ -284,8 +285,15 @@ class DeviceIndex:
             self._check(self.lib.rm_read_segments(self._h, int(off), int(n), ptr(seg), self._s()))
         return seg
 
-    def profile(self, enable: bool) -> None:
-        self._check(self.lib.rm_profile(self._h, 1 if enable else 0))
+    def profile(self, enable) -> None:
+        """False/0 off, True/1 time the walk kernel of each match batch, 2 time all four stages."""
+        self._check(self.lib.rm_profile(self._h, int(enable)))
+
+    def profile_stages(self):
+        """(ms summed over the recorded batches for [walk, single splits, sort, shared splits], batches)."""
+        ms, n = (C.c_double * 4)(), C.c_int(0)
+        self._check(self.lib.rm_profile_stages(self._h, ms, C.byref(n)))
+        return list(ms), n.value
 
     def profile_read(self):
         ms, n = C.c_double(0.0), C.c_int(0)

@@ -58,31 +58,50 @@ int rm_profile(rm_index* idx, int enable) {
   if (enable && !idx->prof_ev[0]) {
     for (int i = 0; i < RM_PROF_EVENTS; ++i) RM_CUDA(cudaEventCreate(&idx->prof_ev[i]));
   }
-  idx->prof_on = enable ? 1 : 0;
+  idx->prof_on = enable < 0 ? 0 : enable > 2 ? 2 : enable;   // 1: walk kernel only, 2: all four stages
   idx->prof_n = 0;
 #endif
   return RM_OK;
 }
 
-int rm_profile_read(rm_index* idx, double* walk_ms_h, int* n_h) {
-  if (!idx || !walk_ms_h || !n_h) return RM_E_INVALID;
-  *walk_ms_h = 0.0;
+// per batch: [0] before K1, [1] after K1, [2] after the single-request split kernel, [3] after the sort of the
+// shared-edge requests, [4] after the shared-edge split kernel
+static int rm_profile_sum(rm_index* idx, double* stage_ms, int* n_h) {
+  for (int k = 0; k < RM_PROF_STRIDE - 1; ++k) stage_ms[k] = 0.0;
   *n_h = 0;
 #ifndef RM_EMU
   RM_CUDA(cudaSetDevice(idx->cfg.device));
-  const int n = idx->prof_n < RM_PROF_EVENTS / 2 ? idx->prof_n : RM_PROF_EVENTS / 2;
-  double tot = 0.0;
+  const int cap = RM_PROF_EVENTS / RM_PROF_STRIDE;
+  const int n = idx->prof_n < cap ? idx->prof_n : cap;
+  const int last = idx->prof_on > 1 ? RM_PROF_STRIDE - 1 : 1;
   for (int i = 0; i < n; ++i) {
-    RM_CUDA(cudaEventSynchronize(idx->prof_ev[2 * i + 1]));
-    float ms = 0.f;
-    RM_CUDA(cudaEventElapsedTime(&ms, idx->prof_ev[2 * i], idx->prof_ev[2 * i + 1]));
-    tot += ms;
+    cudaEvent_t* e = idx->prof_ev + RM_PROF_STRIDE * i;
+    RM_CUDA(cudaEventSynchronize(e[last]));
+    for (int k = 0; k < last; ++k) {
+      float ms = 0.f;
+      RM_CUDA(cudaEventElapsedTime(&ms, e[k], e[k + 1]));
+      stage_ms[k] += ms;
+    }
   }
-  *walk_ms_h = tot;
   *n_h = n;
-  idx->prof_n = 0;
 #endif
   return RM_OK;
+}
+
+int rm_profile_stages(rm_index* idx, double* stage_ms_h, int* n_h) {
+  if (!idx || !stage_ms_h || !n_h) return RM_E_INVALID;
+  return rm_profile_sum(idx, stage_ms_h, n_h);
+}
+
+int rm_profile_read(rm_index* idx, double* walk_ms_h, int* n_h) {
+  if (!idx || !walk_ms_h || !n_h) return RM_E_INVALID;
+  double st[RM_PROF_STRIDE - 1];
+  int rc = rm_profile_sum(idx, st, n_h);
+  *walk_ms_h = st[0];
+#ifndef RM_EMU
+  idx->prof_n = 0;
+#endif
+  return rc;
 }
 
 int rm_destroy(rm_index* idx) {
@@ -176,11 +195,13 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&sc.link, B));
   A(rm_dalloc(&t.req_head, N));
   A(rm_dalloc(&sc.hist, sc.hist_words));
+  A(cudaMemset(sc.hist, 0, sizeof(unsigned) * RM_SORT_TABLE_OFF));      // grid-barrier words of the one-launch sort
   A(rm_dalloc(&sc.ev_key[0], N));
   A(rm_dalloc(&sc.ev_key[1], N));
   A(rm_dalloc(&sc.ev_val[0], N));
   A(rm_dalloc(&sc.ev_val[1], N));
   A(rm_dalloc(&sc.ev_hist, rm_sort_scratch_words((int)N)));
+  A(cudaMemset(sc.ev_hist, 0, sizeof(unsigned) * RM_SORT_TABLE_OFF));
   A(rm_dalloc(&sc.ev_lens, N));
   A(rm_dalloc(&sc.ev_eff, N));
   A(rm_dalloc(&sc.ev_rem, N));
@@ -386,7 +407,7 @@ int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream) {
   out_h->op_seq = (int64_t)idx->op_seq;
   out_h->device_error = c.err;
   out_h->pad = c.node_hwm;
-  if (getenv("RM_DEBUG_COUNTERS")) fprintf(stderr, "[rm] n_req %d groups %d max_group %d\n", c.n_req, c.dbg_groups, c.dbg_max_group);
+  if (getenv("RM_DEBUG_COUNTERS")) fprintf(stderr, "[rm] n_req %d on_shared_edges %d groups %d max_group %d\n", c.n_req, c.n_big, c.dbg_groups, c.dbg_max_group);
   return RM_OK;
 }
 

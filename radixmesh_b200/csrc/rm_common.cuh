@@ -63,9 +63,10 @@ struct RmCounters {
   int err;            // sticky rm_status raised on the device
   int n_dups;
   int n_req;          // scratch: split requests of the current match batch
+  int n_big;          // scratch: of those, the requests on edges that more than one query asked to split
+                      // (kept next to n_req: one memset clears both)
   int evict_n;        // scratch: nodes evicted by the current rm_evict
   int pad;
-  int n_big;          // scratch: split-request groups with more than one request (handled a warp each)
   int dbg_max_group;  // largest split-request group seen (diagnostics)
   int dbg_groups;     // split-request groups seen (diagnostics)
 };

@@ -53,9 +53,10 @@ struct rm_index {
   unsigned* ring_d;
   int* ring_d_owner;
   int ring_d_n;
+  // optional CUDA events around the stages of each match batch (rm_profile)
+#define RM_PROF_EVENTS 640
+#define RM_PROF_STRIDE 5
 #ifndef RM_EMU
-  // optional CUDA-event pairs around the walk kernel of each match batch (rm_profile)
-#define RM_PROF_EVENTS 512
   cudaEvent_t prof_ev[RM_PROF_EVENTS];
   int prof_on;
   int prof_n;

@@ -1109,28 +1109,35 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
     return RM_OK;
   }
 #ifndef RM_EMU
-  const bool prof = idx->prof_on && idx->prof_n < RM_PROF_EVENTS / 2;
-  if (prof) cudaEventRecord(idx->prof_ev[2 * idx->prof_n], s);
+  const bool prof = idx->prof_on && idx->prof_n < RM_PROF_EVENTS / RM_PROF_STRIDE;
+  cudaEvent_t* pev = idx->prof_ev + RM_PROF_STRIDE * idx->prof_n;
+#else
+  const bool prof = false;
 #endif
-  RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_req, 0, sizeof(int), s));
+  RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_req, 0, 2 * sizeof(int), s));   // n_req and n_big (adjacent)
   idx->t.req_link = idx->sc.link;
+#ifndef RM_EMU
+  if (prof) cudaEventRecord(pev[0], s);
+#endif
   rm_match_dispatch<true, false>(idx, tokens, offsets, B, seq_base, out_len, out_node, ro, s);
 #ifndef RM_EMU
-  if (prof) {
-    cudaEventRecord(idx->prof_ev[2 * idx->prof_n + 1], s);
-    ++idx->prof_n;
-  }
+  if (prof) cudaEventRecord(pev[1], s);
 #endif
   RM_CUDA(cudaGetLastError());
   // requests that are alone on their edge are applied straight from K1's list; the rest (requests on
   // shared edges) are sorted by (node, split point) and applied a warp per edge.  All counts stay on the device.
   RmScratch& sc = idx->sc;
-  RM_CUDA(cudaMemsetAsync(&idx->t.ctr->n_big, 0, sizeof(int), s));
   RM_LAUNCH(rm_split_single_kernel, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B,
             idx->len_bits, seq_base, out_node, sc.key[1], sc.val[1]);
+#ifndef RM_EMU
+  if (prof && idx->prof_on > 1) cudaEventRecord(pev[2], s);
+#endif
   const int bits = idx->node_bits + idx->len_bits;
   const int w = 1 ^ rm_sort_pairs(sc.key[1], sc.val[1], sc.key[0], sc.val[0], B, bits, sc.hist, s, &idx->t.ctr->n_big);
   RM_CUDA(cudaGetLastError());
+#ifndef RM_EMU
+  if (prof && idx->prof_on > 1) cudaEventRecord(pev[3], s);
+#endif
   const long long threads = (long long)B * RM_WIDE_G;
   int grid = (int)((threads + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
 #ifndef RM_EMU
@@ -1139,6 +1146,12 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   auto k3 = rm_split_apply_kernel<RM_WIDE_G>;
   RM_LAUNCH(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
             sc.krank, sc.uniq_pos, sc.uniq_min);
+#ifndef RM_EMU
+  if (prof) {
+    if (idx->prof_on > 1) cudaEventRecord(pev[4], s);
+    ++idx->prof_n;
+  }
+#endif
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }

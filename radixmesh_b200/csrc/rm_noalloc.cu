@@ -13,10 +13,11 @@
 // The price.  The array is part of the library image: every GPU that loads the library holds
 // RM_STATIC_SCRATCH_BYTES of it until the process exits, used or not.  All calls, on all indexes
 // and streams of a device, share it, so two calls that overlap on the GPU race; issue them on one
-// stream or order them yourself.  It keeps the previous call's bytes; nothing in it has to start at
-// zero (each kernel writes every word it later reads: K1 fills the request arrays for all B
-// queries, the histogram kernel writes every bin of every tile before the scan reads them), so the
-// entry point clears nothing.
+// stream or order them yourself.  It keeps the previous call's bytes and the entry point clears nothing:
+// each kernel writes every word it later reads (K1 fills the request arrays for all B queries, the sort
+// writes every bin of every tile before reading it); the only words that must be zero between calls are
+// the two grid-barrier words of the sort, which start at zero (static storage) and which every sort
+// leaves at zero.
 //
 // First call on a device: looks up the array's device address (cudaGetSymbolAddress) and caches it
 // per device.  In host code the array's name is only a handle for that lookup, never an address a

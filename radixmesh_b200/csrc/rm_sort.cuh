@@ -13,6 +13,10 @@
 #define RM_SORT_WARPS (RM_SORT_TPB / 32)
 #define RM_SORT_MIN_TILE 1024      // 8 warps x 4 rounds x 32 lanes: keeps the histogram table (256 x tiles) small
 #define RM_SORT_MAX_TILE 4096      // 8 warps x 16 rounds x 32 lanes
+#define RM_SORT_ROUNDS (RM_SORT_MAX_TILE / RM_SORT_TPB)   // rounds of 32 items per warp in the largest tile
+#define RM_SORT_SOLO 2048          // up to here one block alone is faster than the grid with its barriers (measured:
+                                   // 2000 items 23 us alone, 4097 items 29 us on the grid; tools/sort_probe.cu)
+#define RM_SORT_TABLE_OFF 8        // hist[0..1]: grid barrier of the one-launch form (zero between launches); tables after
 
 // Items per block: small inputs get small tiles so that the grid still covers the 148 SMs (a 64K-item
 // sort with 4096-item tiles ran on 16 blocks and was latency bound); large inputs get 4096-item tiles.
@@ -30,7 +34,7 @@ static inline size_t rm_sort_scratch_words(int n) {
   size_t nb = nb_small < 148 ? nb_small : 148;
   size_t nb_big = ((size_t)n + RM_SORT_MAX_TILE - 1) / RM_SORT_MAX_TILE;
   if (nb_big > nb) nb = nb_big;
-  return (size_t)256 * (nb + 2) + 8;
+  return (size_t)256 * (nb + 2) + 8 + RM_SORT_TABLE_OFF;
 }
 
 #ifndef RM_EMU
@@ -40,6 +44,7 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_hist_kernel(const 
                                                                   unsigned* __restrict__ ghist, int nblocks, int tile) {
   __shared__ unsigned h[256];
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  if ((int)blockIdx.x * tile >= n) return;   // tiles past the (device-side) count: nothing to do, nothing read later
   h[threadIdx.x] = 0;
   __syncthreads();
   int base = blockIdx.x * tile;
@@ -53,8 +58,12 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_hist_kernel(const 
 // per tile).  One block of 32 warps; warp w owns rows w, w+32, ..., w+224.  The eight rows of a warp are
 // walked together so that their loads are in flight at the same time (a row-after-row version spent
 // 15 us waiting on one L2 round trip after another).
-static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __restrict__ data, int nb) {
+static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __restrict__ data, int nb_stride, int n_max,
+                                                                 const int* __restrict__ n_dev, int tile) {
   __shared__ unsigned tot[256];
+  const int n_items = n_dev ? min(*n_dev, n_max) : n_max;
+  const int nb = (n_items + tile - 1) / tile;   // active tiles; rows keep their stride of nb_stride
+  if (nb == 0) return;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   {
     unsigned s[8];
@@ -62,7 +71,7 @@ static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __re
     for (int r = 0; r < 8; ++r) s[r] = 0;
     for (int j = lane; j < nb; j += 32) {
 #pragma unroll
-      for (int r = 0; r < 8; ++r) s[r] += data[(size_t)(wid + 32 * r) * nb + j];
+      for (int r = 0; r < 8; ++r) s[r] += data[(size_t)(wid + 32 * r) * nb_stride + j];
     }
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
@@ -102,7 +111,7 @@ static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __re
     const int j = j0 + lane;
     unsigned v[8];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) v[r] = j < nb ? data[(size_t)(wid + 32 * r) * nb + j] : 0u;
+    for (int r = 0; r < 8; ++r) v[r] = j < nb ? data[(size_t)(wid + 32 * r) * nb_stride + j] : 0u;
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
       unsigned inc = v[r];
@@ -111,7 +120,7 @@ static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __re
         unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += x;
       }
-      if (j < nb) data[(size_t)(wid + 32 * r) * nb + j] = run[r] + inc - v[r];
+      if (j < nb) data[(size_t)(wid + 32 * r) * nb_stride + j] = run[r] + inc - v[r];
       run[r] += __shfl_sync(0xffffffffu, inc, 31);
     }
   }
@@ -123,6 +132,7 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_scatter_kernel(con
                                                                      const unsigned* __restrict__ gscan, int nblocks, int tile) {
   __shared__ unsigned wcnt[RM_SORT_WARPS][256];
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  if ((int)blockIdx.x * tile >= n) return;
   const int per_warp = tile / RM_SORT_WARPS;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < RM_SORT_WARPS * 256; i += RM_SORT_TPB) (&wcnt[0][0])[i] = 0;
@@ -170,6 +180,150 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_scatter_kernel(con
   }
 }
 
+// All passes in ONE launch, for inputs of at most 148 tiles (every sort of a match or insert batch).
+// A pass of the three-kernel form costs three dependent launches of ~5 us each even when the input is a few
+// hundred items (the split requests on shared edges of a 64K-query batch: 12 launches, 65 us for ~500 items).
+// Here a pass is: per-warp digit counts in shared memory -> tile totals to ghist[tile][256] -> grid barrier ->
+// every block sums the totals it needs itself (digit base + tiles before it; <= 148 coalesced loads per
+// thread) -> stable scatter -> grid barrier.  Inputs of at most RM_SORT_SOLO items (a grid-uniform
+// test on the device-side count) are sorted by block 0 alone with no grid barrier at all.
+// The grid barrier is a counter in hist[0] (arrivals; the blocks of one launch, at most one per SM, are all
+// resident or become resident as soon as an SM is free, and wait for nobody but each other); the last block
+// to leave the kernel puts hist[0] and hist[1] back to zero.  (A cooperative launch costs ~20 us more than a
+// plain one here, which is the whole budget of this sort.)
+static __device__ __forceinline__ void rm_sort_grid_barrier(unsigned* bar, unsigned target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar, 1u);
+    while (*(volatile unsigned*)bar < target) {
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_fused_kernel(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n_max,
+                                                                   const int* n_dev, int passes, unsigned* hist, int tile) {
+  __shared__ unsigned wcnt[RM_SORT_WARPS][256];
+  __shared__ unsigned wtot[RM_SORT_WARPS];
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  if (n <= 0) return;
+  const bool solo = n <= RM_SORT_SOLO;
+  if (solo && blockIdx.x != 0) return;
+  unsigned* ghist = hist + RM_SORT_TABLE_OFF;
+  unsigned arrivals = 0;
+  const int my_tile = solo ? (n + 255) / 256 * 256 : tile;
+  const int nb = solo ? 1 : (n + tile - 1) / tile;
+  const bool active = (int)blockIdx.x < nb;
+  const int per_warp = my_tile / RM_SORT_WARPS;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int wbase = blockIdx.x * my_tile + wid * per_warp;
+  const unsigned lt = (1u << lane) - 1u;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = 8 * p;
+    const u64* kin = (p & 1) ? k1 : k0;
+    const unsigned* vin = (p & 1) ? v1 : v0;
+    u64* kout = (p & 1) ? k0 : k1;
+    unsigned* vout = (p & 1) ? v0 : v1;
+    // this warp's run of the tile, loaded up front: the loads of all rounds are in flight together (round
+    // after round, each waiting for its own L2 round trip, a 4096-item single-block sort took 87 us)
+    u64 kreg[RM_SORT_ROUNDS];
+    unsigned vreg[RM_SORT_ROUNDS];
+#pragma unroll
+    for (int r = 0; r < RM_SORT_ROUNDS; ++r) {
+      const int i = wbase + r * 32 + lane;
+      const bool ok = active && r * 32 < per_warp && i < n;
+      kreg[r] = ok ? __ldcg(kin + i) : 0ull;
+      vreg[r] = ok ? __ldcg(vin + i) : 0u;
+    }
+    for (int i = threadIdx.x; i < RM_SORT_WARPS * 256; i += RM_SORT_TPB) (&wcnt[0][0])[i] = 0;
+    __syncthreads();
+    if (active) {
+#pragma unroll
+      for (int r = 0; r < RM_SORT_ROUNDS; ++r) {
+        if (r * 32 < per_warp) {
+          const int i = wbase + r * 32 + lane;
+          unsigned d = (i < n) ? ((unsigned)(kreg[r] >> shift) & 255u) : 0xFFFFu;
+          unsigned m = __match_any_sync(0xffffffffu, d);
+          if (d != 0xFFFFu && (m & lt) == 0) wcnt[wid][d] += __popc(m);
+          __syncwarp();
+        }
+      }
+    }
+    __syncthreads();
+    const unsigned d = threadIdx.x;
+    unsigned total = 0, before = 0;
+#pragma unroll
+    for (int w = 0; w < RM_SORT_WARPS; ++w) total += wcnt[w][d];
+    if (!solo) {
+      if (active) ghist[blockIdx.x * 256 + d] = total;
+      arrivals += gridDim.x;
+      rm_sort_grid_barrier(hist, arrivals);
+      total = 0;
+#pragma unroll 16
+      for (int j = 0; j < nb; ++j) {
+        unsigned x = __ldcg(ghist + j * 256 + d);
+        total += x;
+        if (j < (int)blockIdx.x) before += x;
+      }
+    }
+    // exclusive scan of the digit totals over the 256 threads
+    unsigned inc = total;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += x;
+    }
+    if (lane == 31) wtot[wid] = inc;
+    __syncthreads();
+    unsigned run = inc - total + before;
+    for (int w = 0; w < wid; ++w) run += wtot[w];
+#pragma unroll
+    for (int w = 0; w < RM_SORT_WARPS; ++w) {
+      unsigned c = wcnt[w][d];
+      wcnt[w][d] = run;
+      run += c;
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll
+      for (int r = 0; r < RM_SORT_ROUNDS; ++r) {
+        if (r * 32 < per_warp) {
+          const int i = wbase + r * 32 + lane;
+          const bool ok = i < n;
+          unsigned dd = ok ? ((unsigned)(kreg[r] >> shift) & 255u) : 0xFFFFu;
+          unsigned m = __match_any_sync(0xffffffffu, dd);
+          unsigned dst = 0;
+          if (ok) dst = wcnt[wid][dd] + __popc(m & lt);
+          __syncwarp();
+          if (ok && (m & lt) == 0) wcnt[wid][dd] += __popc(m);
+          __syncwarp();
+          if (ok) {
+            kout[dst] = kreg[r];
+            vout[dst] = vreg[r];
+          }
+        }
+      }
+    }
+    if (p + 1 < passes) {
+      if (solo) {
+        __syncthreads();
+      } else {
+        arrivals += gridDim.x;
+        rm_sort_grid_barrier(hist, arrivals);
+      }
+    }
+  }
+  if (!solo && threadIdx.x == 0) {   // the last block out re-arms the barrier for the next launch
+    __threadfence();
+    if (atomicAdd(hist + 1, 1u) == gridDim.x - 1) {
+      hist[0] = 0;
+      hist[1] = 0;
+      __threadfence();
+    }
+  }
+}
+
 // Sorts n pairs by the low `bits` bits of the key.  Returns 0 if the result is in (k0, v0), 1 if in
 // (k1, v1).  hist must hold rm_sort_scratch_words(n) u32.  If n_dev is not NULL the item count is read on
 // the device (min(*n_dev, n)) and n only bounds the grid, so no host synchronisation is needed.
@@ -179,6 +333,11 @@ static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, in
   int passes = (bits + 7) / 8;
   int tile = rm_sort_tile(n);
   int nb = (n + tile - 1) / tile;
+  if (nb <= 148) {   // one launch, at most one block per SM
+    RM_LAUNCH(rm_sort_fused_kernel, nb, RM_SORT_TPB, s, k0, v0, k1, v1, n, n_dev, passes, hist, tile);
+    return passes & 1;
+  }
+  hist += RM_SORT_TABLE_OFF;
   int cur = 0;
   for (int p = 0; p < passes; ++p) {
     u64* ki = cur ? k1 : k0;
@@ -186,7 +345,7 @@ static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, in
     u64* ko = cur ? k0 : k1;
     unsigned* vo = cur ? v0 : v1;
     RM_LAUNCH(rm_sort_hist_kernel, nb, RM_SORT_TPB, s, ki, n, n_dev, p * 8, hist, nb, tile);
-    RM_LAUNCH(rm_scan_u32_kernel, 1, 1024, s, hist, nb);
+    RM_LAUNCH(rm_scan_u32_kernel, 1, 1024, s, hist, nb, n, n_dev, tile);
     RM_LAUNCH(rm_sort_scatter_kernel, nb, RM_SORT_TPB, s, ki, vi, ko, vo, n, n_dev, p * 8, hist, nb, tile);
     cur ^= 1;
   }
