@@ -46,7 +46,7 @@ struct __align__(32) RmSlot {
 // without a child-table probe per node: first-sight splits turn hot prefixes into long chains of one-token
 // nodes, but those chains stay contiguous in the arena.
 #define RM_SEG_CONT 0x40000000
-#define RM_ARENA_PAD 64    // walks read up to a warp's width past a run
+#define RM_ARENA_PAD 128   // walks read up to RM_RUN_DEPTH warp widths past a run position (rm_match.cu)
 __device__ __forceinline__ int rm_seg_owner(int sg) { return sg < 0 ? -1 : (sg & 0x3FFFFFFF); }
 __device__ __forceinline__ int rm_slot_len(unsigned w) { return (int)(w & 0xFFFFFFu); }
 __device__ __forceinline__ int rm_slot_rank(unsigned w) { return (int)(w >> 24) - 1; }

@@ -584,8 +584,11 @@ rm_match_run_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restric
 // scattered 4-byte requests per lane and is bound by the load/store unit.)  All lanes of a group carry the
 // same walk state; node boundaries inside a step are resolved with ballots: the first position where the
 // match stops, the nodes that ended before it (each stamped by the lane that sees its end).
+#ifndef RM_RUN_DEPTH
+#define RM_RUN_DEPTH 2   // steps whose loads are in flight together; RM_RUN_DEPTH * 32 <= RM_ARENA_PAD
+#endif
 template <int G, bool SPLIT, bool ROUTER>
-__global__ void __launch_bounds__(RM_MATCH_TPB)
+__global__ void __launch_bounds__(RM_MATCH_TPB, 8)
 rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
                      int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
                      unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
@@ -610,9 +613,12 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
   bool bad_below = false;
   bool done = L == 0;
 
+  int tk_next = 0;                     // key[pos] when the step that ended the previous run already read it
+  bool have_tk = false;
   while (!done) {
     // ---- child of `node` that starts with key[pos]: child-table probe (same address in every lane)
-    const int tk = rm_ld_query(key + pos, qpol);
+    const int tk = have_tk ? tk_next : rm_ld_query(key + pos, qpol);
+    have_tk = false;
     int cur = -1;
     i64 cs = 0;
     {
@@ -634,12 +640,21 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
     int qi = pos + 1;
     bool leave = false;
     while (!leave && !done) {
-      const i64 ia = a + lane;
-      const int iq = qi + lane;
-      const int tj = __ldg(tok + ia);
-      const int sj = __ldg(seg + ia);
-      const bool inq = iq < L;
-      const int kj = inq ? rm_ld_query(key + iq, qpol) : 0;
+      // the loads of RM_RUN_DEPTH steps are issued together: a run is ~68 positions on the C2 tree, and every
+      // step that waits for its own loads adds one memory round trip to the query's dependent chain
+      int tjv[RM_RUN_DEPTH], sjv[RM_RUN_DEPTH], kjv[RM_RUN_DEPTH];
+#pragma unroll
+      for (int u = 0; u < RM_RUN_DEPTH; ++u) {
+        const i64 ia = a + u * G + lane;
+        const int iq = qi + u * G + lane;
+        tjv[u] = __ldg(tok + ia);
+        sjv[u] = __ldg(seg + ia);
+        kjv[u] = iq < L ? rm_ld_query(key + iq, qpol) : 0;
+      }
+#pragma unroll
+      for (int u = 0; u < RM_RUN_DEPTH; ++u) {
+      const int tj = tjv[u], sj = sjv[u], kj = kjv[u];
+      const bool inq = qi + lane < L;
       const int own = sj < 0 ? -1 : (sj & 0x3FFFFFFF);
       int prev = g.shfl_up(own, 1);
       if (lane == 0) prev = cur;
@@ -686,8 +701,13 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       if (bnd_s) {
         // a node ended exactly there (it is committed); either the query is exhausted or the next node
         // is not a contiguous match: back to the child table
-        if (qi + s >= L) done = true;
-        else leave = true;
+        if (qi + s >= L) {
+          done = true;
+        } else {
+          leave = true;
+          tk_next = g.bcast(kj, s);      // key[qi + s]: the token the next probe hashes
+          have_tk = true;
+        }
       } else {
         // the query ends, or differs, inside the node that covers position s: partial match
         const int pn = g.bcast(own, s);
@@ -711,6 +731,8 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
         }
         pos = qi + s;
         done = true;
+      }
+      break;
       }
     }
   }
