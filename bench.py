@@ -37,6 +37,10 @@ WORKLOADS = {
     # north_star target shape
     "target": dict(name="north_star target: 1M-node tree, 64K queries x 512 tokens, Zipf s=1.1 prefix sharing",
                    n_docs=32768, L=512, tree_nodes=1_000_000, B=65536, seed=1),
+    # BASELINE configs[4] at reduced size: 4K-token queries.  The full shape (10 M-node trees) does not fit this
+    # generator: every insert appends ~1,800 fresh tokens (29 KB of arenas), i.e. 144 GB for 5 M inserts.
+    "c5r": dict(name="C5 reduced: 0.5M-node tree, 16K queries x 4096 tokens, Zipf s=1.1 prefix sharing",
+                n_docs=8192, L=4096, tree_nodes=500_000, B=16384, seed=3),
 }
 INSERT_BATCH = 4096
 

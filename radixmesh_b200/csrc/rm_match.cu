@@ -768,6 +768,8 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
   }
 }
 
+#define RM_FILL_COOP 48   // owner-map fills longer than this are done by the whole warp
+
 // K3: one group per edge that received split requests.  `skey` is sorted by (node, split point) and,
 // inside equal keys, by query index (the sort is stable), `sval` holds the query index.
 template <int G>
@@ -847,7 +849,11 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
   const u64 st_c = t.stamp[c];
   g.sync();
   // pass 3: one upper node per distinct split point, chained parent -> u_0 -> ... -> u_{U-1} -> c
-  for (int kk = g.lane; kk < U; kk += G) {
+  for (int kk0 = 0; kk0 < U; kk0 += G) {
+    const int kk = kk0 + g.lane;
+    i64 fill_off = 0;
+    int fill_n = 0, fill_id = 0;
+    if (kk < U) {
     const int j = uniq_pos[i + kk];
     const int p = (int)(skey[j] & pmask);
     const int jprev = kk > 0 ? uniq_pos[i + kk - 1] : -1;
@@ -878,7 +884,9 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
     {
       const int first = kk == 0 ? ((t.seg[off] & RM_SEG_CONT) | u) : (u | RM_SEG_CONT);
       t.seg[off + a] = first;
-      for (int x = a + 1; x < p; ++x) t.seg[off + x] = u;
+      fill_off = off + a;          // positions a+1 .. p-1: filled by the whole group below
+      fill_n = p - a;
+      fill_id = u;
       if (kk == U - 1) t.seg[off + p] = c | RM_SEG_CONT;
     }
     if (kk == 0) {
@@ -901,6 +909,20 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
       u64 smin = ((seq_base + (u64)uniq_min[i + kk]) << 1) | 1ull;
       t.stamp[c] = smin > st_c ? smin : st_c;
     }
+    }
+    if (fill_n <= RM_FILL_COOP) {
+      for (int x = 1; x < fill_n; ++x) t.seg[fill_off + x] = fill_id;
+      fill_n = 0;
+    }
+    unsigned todo = g.ballot(fill_n > 1);
+    while (todo) {
+      const int l = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const i64 o = g.bcast(fill_off, l);
+      const int n = g.bcast(fill_n, l);
+      const int id = g.bcast(fill_id, l);
+      for (int x = 1 + g.lane; x < n; x += G) t.seg[o + x] = id;
+    }
   }
   if (g.lane == 0) rm_add_i64(&t.ctr->n_nodes, (i64)U);
   // pass 4: every request's last node is the upper node that ends at its split point
@@ -919,62 +941,92 @@ rm_split_single_kernel(RmTree t, const u64* __restrict__ rkey, const unsigned* _
                        u64 seq_base, int* __restrict__ out_node, u64* __restrict__ mkey, unsigned* __restrict__ mval) {
   const int B = min(t.ctr->n_req, Bmax);
   const int i = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
-  if (i >= B) return;
-  const u64 ki = rkey[i];
-  const int c = (int)(ki >> len_bits);
-  const unsigned q = rval[i];
-  const bool is_head = t.req_head[c] == (int)q;
-  const bool alone = is_head && t.req_link[q] < 0;
-  if (is_head) t.req_head[c] = -1;                                      // ready for the next batch
-  if (!alone) {                                                         // shared edge: sorted, then a warp does it
-    const int slot = atomicAdd(&t.ctr->n_big, 1);
-    mkey[slot] = ki;
-    mval[slot] = q;
-    return;
+  // owner-map fill of the new upper node, done by the whole warp after the per-thread part (a thread writing
+  // its own p-1 words one after another made this kernel 57 us on 4096-token keys)
+  i64 fill_off = 0;
+  int fill_n = 0, fill_id = 0;
+  if (i < B) {
+    const u64 ki = rkey[i];
+    const int c = (int)(ki >> len_bits);
+    const unsigned q = rval[i];
+    const bool is_head = t.req_head[c] == (int)q;
+    const bool alone = is_head && t.req_link[q] < 0;
+    if (is_head) t.req_head[c] = -1;                                      // ready for the next batch
+    if (!alone) {                                                         // shared edge: sorted, then a warp does it
+      const int slot = atomicAdd(&t.ctr->n_big, 1);
+      mkey[slot] = ki;
+      mval[slot] = q;
+    } else {
+      const int p = (int)(ki & ((1ull << len_bits) - 1ull));
+      const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
+      const u64 apos = rm_alloc_nodes(t, 1);
+      if (apos != ~0ull) {
+        const int u = rm_free_id_at(t, apos);
+        const int par = t.parent[c];
+        const i64 off = t.edge_off[c];
+        const int len = t.edge_len[c];
+        const int dend = t.depth_end[c];
+        const int lk = t.lock_ref[c];
+        const int rk = t.rank[c];
+        const u64 st_c = t.stamp[c];
+        const u64 st = seq > st_c ? seq : st_c;       // the query stamped the whole edge, then split it
+        const int tok0 = t.tok[off], tokp = t.tok[off + p];
+        t.parent[u] = par;
+        t.edge_off[u] = off;
+        t.edge_len[u] = p;
+        t.depth_end[u] = dend - len + p;
+        t.lock_ref[u] = lk;       // radix_cache.py:283
+        t.rank[u] = rk;
+        t.nchild[u] = 1;
+        t.gen[u] = 0;
+        t.parked[u] = -1;
+        t.stamp[u] = st;
+        atomicMax(&t.ctr->node_hwm, u + 1);
+        t.seg[off] = (t.seg[off] & RM_SEG_CONT) | u;     // owner map: [off, off+p) is u's, c starts at off+p
+        t.seg[off + p] = c | RM_SEG_CONT;
+        fill_off = off;
+        fill_n = p;
+        fill_id = u;
+        RmSlot s;
+        const int sidx = rm_find<true>(t, rm_key(par, tok0), s);
+        if (sidx < 0) {
+          atomicMax(&t.ctr->err, (int)RM_E_INVALID);
+        } else {
+          t.table[sidx].child = u;
+          rm_slot_set_len(&t.table[sidx], p);
+        }
+        rm_table_insert(t, rm_key(u, tokp), c, len - p, off + p, rk);
+        t.parent[c] = u;
+        t.edge_off[c] = off + p;
+        t.edge_len[c] = len - p;
+        t.stamp[c] = st;
+        rm_add_i64(&t.ctr->n_nodes, (i64)1);
+        out_node[q] = u;
+      }
+    }
   }
-  const int p = (int)(ki & ((1ull << len_bits) - 1ull));
-  const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
-  const u64 apos = rm_alloc_nodes(t, 1);
-  if (apos == ~0ull) return;
-  const int u = rm_free_id_at(t, apos);
-  const int par = t.parent[c];
-  const i64 off = t.edge_off[c];
-  const int len = t.edge_len[c];
-  const int dend = t.depth_end[c];
-  const int lk = t.lock_ref[c];
-  const int rk = t.rank[c];
-  const u64 st_c = t.stamp[c];
-  const u64 st = seq > st_c ? seq : st_c;       // the query stamped the whole edge, then split it
-  const int tok0 = t.tok[off], tokp = t.tok[off + p];
-  t.parent[u] = par;
-  t.edge_off[u] = off;
-  t.edge_len[u] = p;
-  t.depth_end[u] = dend - len + p;
-  t.lock_ref[u] = lk;       // radix_cache.py:283
-  t.rank[u] = rk;
-  t.nchild[u] = 1;
-  t.gen[u] = 0;
-  t.parked[u] = -1;
-  t.stamp[u] = st;
-  atomicMax(&t.ctr->node_hwm, u + 1);
-  t.seg[off] = (t.seg[off] & RM_SEG_CONT) | u;     // owner map: [off, off+p) is u's, c starts at off+p
-  for (int x = 1; x < p; ++x) t.seg[off + x] = u;
-  t.seg[off + p] = c | RM_SEG_CONT;
-  RmSlot s;
-  const int sidx = rm_find<true>(t, rm_key(par, tok0), s);
-  if (sidx < 0) {
-    atomicMax(&t.ctr->err, (int)RM_E_INVALID);
-  } else {
-    t.table[sidx].child = u;
-    rm_slot_set_len(&t.table[sidx], p);
+#ifdef RM_EMU
+  for (int x = 1; x < fill_n; ++x) t.seg[fill_off + x] = fill_id;
+#else
+  {
+    // short fills stay with their thread (32 of them proceed side by side); only long ones are worth
+    // serialising the warp for
+    if (fill_n <= RM_FILL_COOP) {
+      for (int x = 1; x < fill_n; ++x) t.seg[fill_off + x] = fill_id;
+      fill_n = 0;
+    }
+    const int lane = threadIdx.x & 31;
+    unsigned todo = __ballot_sync(0xffffffffu, fill_n > 1);
+    while (todo) {
+      const int l = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const i64 o = __shfl_sync(0xffffffffu, fill_off, l);
+      const int n = __shfl_sync(0xffffffffu, fill_n, l);
+      const int id = __shfl_sync(0xffffffffu, fill_id, l);
+      for (int x = 1 + lane; x < n; x += 32) t.seg[o + x] = id;
+    }
   }
-  rm_table_insert(t, rm_key(u, tokp), c, len - p, off + p, rk);
-  t.parent[c] = u;
-  t.edge_off[c] = off + p;
-  t.edge_len[c] = len - p;
-  t.stamp[c] = st;
-  rm_add_i64(&t.ctr->n_nodes, (i64)1);
-  out_node[q] = u;
+#endif
 }
 
 // K2: values along the matched path, written back to front by walking parent links from the last
