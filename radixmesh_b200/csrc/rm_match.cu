@@ -1119,7 +1119,10 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
   if (!strcmp(walk, "run")) {
     static const int rg = getenv("RM_RUN_G") ? atoi(getenv("RM_RUN_G")) : 32;
     const long long rthreads = (long long)B * rg;
-    const int rtpb = rthreads >= 148LL * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (rthreads >= 148LL * 8 * 128 ? 128 : 64);
+    static const int rtpb_env = getenv("RM_RUN_TPB") ? atoi(getenv("RM_RUN_TPB")) : 0;
+    // 4 queries per block: a block's warps end at different times and its slots are only handed on when the last
+    // one is done (128 threads: +2 % over 256 on both bench shapes)
+    const int rtpb = rtpb_env ? rtpb_env : (rthreads >= 148LL * 8 * 128 ? 128 : 64);
     const int rgrid = (int)((rthreads + rtpb - 1) / rtpb);
 #define RM_RCASE(GG)                                                                                              \
   case GG: {                                                                                                      \
