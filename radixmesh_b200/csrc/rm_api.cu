@@ -114,7 +114,7 @@ int rm_destroy(rm_index* idx) {
                   sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.link, t.req_head, sc.hist, sc.ev_key[0], sc.ev_key[1],
                   sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ev_nch0, sc.lock_first, sc.lock_cnt, sc.lock_flag,
                   sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b,
-                  idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner};
+                  idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner, idx->route_msg, idx->route_nblk};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   delete idx;

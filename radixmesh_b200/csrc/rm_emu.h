@@ -71,6 +71,7 @@ template <class T> static inline T __ldcg(const T* p) { return *p; }
 template <class T> static inline void __stcg(T* p, T v) { *p = v; }
 struct int4 { int x, y, z, w; };
 struct uint2 { unsigned x, y; };
+struct uint4 { unsigned x, y, z, w; };
 
 // Sequential launcher: one emulated thread per GROUP (RM_G == 1), block by block.
 #define RM_LAUNCH(kernel, grid, block, stream, ...)                                  \

@@ -53,6 +53,9 @@ struct rm_index {
   unsigned* ring_d;
   int* ring_d_owner;
   int ring_d_n;
+  unsigned char* route_msg;   // rendered str(list) messages of a route / pick batch (rm_route.cu); NULL until rings are set
+  size_t route_msg_bytes;
+  int* route_nblk;            // 64-byte blocks per rendered request, 0 = hash it with the streamed form
   // optional CUDA events around the stages of each match batch (rm_profile)
 #define RM_PROF_EVENTS 640
 #define RM_PROF_STRIDE 5

@@ -128,6 +128,38 @@ struct RmMd5Words {
   __device__ __forceinline__ void set(int i, unsigned v) const { col[i * stride] = v; }
 };
 
+// Text of one list item, first character in the lowest byte of (lo, hi): the decimal digits of v ('-' in front
+// of a negative one), preceded by ", " (lead 1) or "[" (lead 2) or nothing (lead 0).  At most 13 bytes.
+__device__ __forceinline__ int rm_render_token(int v, int lead, u64& tlo, u64& thi) {
+  // decimal digits, least significant first; shifting what is there up by a byte puts the most
+  // significant digit in the lowest byte, i.e. first in the text
+  int len = 0;
+  tlo = 0;
+  thi = 0;
+  unsigned ux = v < 0 ? (unsigned)(-(long long)v) : (unsigned)v;
+  do {
+    thi = (thi << 8) | (tlo >> 56);
+    tlo = (tlo << 8) | (u64)('0' + (ux % 10u));
+    ux /= 10u;
+    ++len;
+  } while (ux);
+  if (v < 0) {
+    thi = (thi << 8) | (tlo >> 56);
+    tlo = (tlo << 8) | (u64)'-';
+    ++len;
+  }
+  if (lead == 1) {
+    thi = (thi << 16) | (tlo >> 48);
+    tlo = (tlo << 16) | ((u64)' ' << 8) | (u64)',';
+    len += 2;
+  } else if (lead == 2) {
+    thi = (thi << 8) | (tlo >> 56);
+    tlo = (tlo << 8) | (u64)'[';
+    ++len;
+  }
+  return len;
+}
+
 // ConsistentHash._hash(key) for key = list of ints (cache_aware_router.py:110-118): MD5 of Python's
 // str(list) rendering "[t0, t1, ...]", first four digest bytes big-endian.
 //
@@ -155,26 +187,7 @@ __device__ unsigned rm_hash_token_list(const int* __restrict__ key, int n, const
         u64 tlo = 0, thi = 0;
         int len = 0;
         if (i < n) {
-          // decimal digits, least significant first; shifting what is there up by a byte puts the most
-          // significant digit in the lowest byte, i.e. first in the text
-          const int v = key[i];
-          unsigned ux = v < 0 ? (unsigned)(-(long long)v) : (unsigned)v;
-          do {
-            thi = (thi << 8) | (tlo >> 56);
-            tlo = (tlo << 8) | (u64)('0' + (ux % 10u));
-            ux /= 10u;
-            ++len;
-          } while (ux);
-          if (v < 0) {
-            thi = (thi << 8) | (tlo >> 56);
-            tlo = (tlo << 8) | (u64)'-';
-            ++len;
-          }
-          if (i) {               // ", " separator in front
-            thi = (thi << 16) | (tlo >> 48);
-            tlo = (tlo << 16) | ((u64)' ' << 8) | (u64)',';
-            len += 2;
-          }
+          len = rm_render_token(key[i], i ? 1 : 0, tlo, thi);
           ++i;
         } else if (!closed) {
           tlo = (u64)']';
@@ -221,6 +234,123 @@ __device__ unsigned rm_hash_token_list(const int* __restrict__ key, int n, const
   return ((a & 0xffu) << 24) | ((a & 0xff00u) << 8) | ((a >> 8) & 0xff00u) | (a >> 24);
 }
 
+// ---- two-step form of the same hash, for long requests --------------------------------------------------
+// One thread rendering AND compressing a 2K-token request is ~250 dependent instructions per token at an
+// occupancy of a few warps per SM: 1.4 ms for a batch, however small the batch.  The text of a request is
+// independent per token, so a block renders it in parallel (digit counts -> block prefix sum -> bytes) into
+// a scratch area, padded per RFC 1321; the compression, the only sequential part, then reads 64-byte blocks.
+// Place of request q's message: 64 * ((qoff[q] - qoff[0] + 3) / 4 + 2 q) bytes, which leaves room for 13 bytes
+// per token + brackets + padding without a prefix sum over the requests.  A request that does not fit the
+// scratch keeps nblk = 0 and is hashed by the streamed form above.
+#define RM_RENDER_TPB 128
+
+__device__ __forceinline__ u64 rm_msg_off(i64 rel_tok, int q) { return 64ull * ((u64)((rel_tok + 3) >> 2) + 2ull * (u64)q); }
+
+__device__ __forceinline__ void rm_put_bytes(unsigned char* dst, u64 lo, u64 hi, int len) {
+  for (int b = 0; b < len; ++b) dst[b] = (unsigned char)((b < 8 ? lo >> (8 * b) : hi >> (8 * (b - 8))) & 0xffu);
+}
+
+// closing bracket, 0x80, zeros to 56 mod 64, bit length; returns the number of 64-byte blocks
+__device__ __forceinline__ int rm_msg_finish(unsigned char* dst, u64 total) {
+  dst[total++] = (unsigned char)']';
+  const u64 bits = total * 8ull;
+  dst[total++] = 0x80;
+  while ((total & 63ull) != 56ull) dst[total++] = 0;
+  for (int b = 0; b < 8; ++b) dst[total++] = (unsigned char)((bits >> (8 * b)) & 0xffu);
+  return (int)(total >> 6);
+}
+
+__global__ void __launch_bounds__(RM_RENDER_TPB)
+rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, int warm,
+                       const int* __restrict__ prefill, const int* __restrict__ decode, const unsigned char* __restrict__ err,
+                       unsigned char* __restrict__ msg, u64 msg_bytes, int* __restrict__ nblk) {
+  const int q = blockIdx.x;
+  if (q >= B) return;
+  const bool need = warm ? ((prefill[q] == -1 || decode[q] == -1) && err[q] == 0) : true;
+  const i64 o0 = qoff[q];
+  const int n = (int)(qoff[q + 1] - o0);
+  const u64 base = rm_msg_off(o0 - qoff[0], q);
+  const bool fits = msg != nullptr && rm_msg_off(qoff[q + 1] - qoff[0], q + 1) <= msg_bytes;
+  if (!need || !fits) {
+    if (threadIdx.x == 0) nblk[q] = 0;
+    return;
+  }
+  const int* __restrict__ key = qtok + o0;
+  unsigned char* dst = msg + base;
+#ifdef RM_EMU
+  {
+    u64 total = 0;
+    if (n == 0) dst[total++] = (unsigned char)'[';
+    for (int i = 0; i < n; ++i) {
+      u64 lo, hi;
+      const int len = rm_render_token(key[i], i ? 1 : 2, lo, hi);
+      rm_put_bytes(dst + total, lo, hi, len);
+      total += (u64)len;
+    }
+    nblk[q] = rm_msg_finish(dst, total);
+  }
+#else
+  __shared__ unsigned wsum[RM_RENDER_TPB / 32];
+  __shared__ unsigned chunk_total;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  u64 running = 0;
+  if (n == 0 && threadIdx.x == 0) dst[0] = (unsigned char)'[';
+  if (n == 0) running = 1;
+  for (int c0 = 0; c0 < n; c0 += RM_RENDER_TPB) {
+    const int i = c0 + (int)threadIdx.x;
+    u64 lo = 0, hi = 0;
+    int len = 0;
+    if (i < n) len = rm_render_token(key[i], i ? 1 : 2, lo, hi);
+    unsigned inc = (unsigned)len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += x;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    unsigned before = 0;
+    for (int w = 0; w < wid; ++w) before += wsum[w];
+    if (threadIdx.x == RM_RENDER_TPB - 1) chunk_total = before + inc;
+    rm_put_bytes(dst + running + before + inc - (unsigned)len, lo, hi, len);
+    __syncthreads();
+    running += chunk_total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) nblk[q] = rm_msg_finish(dst, running);
+#endif
+}
+
+struct RmMd5Regs {
+  unsigned m[16];
+  __device__ __forceinline__ unsigned operator()(int i) const { return m[i]; }
+};
+
+// MD5 of a rendered, padded message of nb 64-byte blocks (64-byte aligned); next block loaded while this one
+// is compressed
+__device__ unsigned rm_hash_rendered(const unsigned char* __restrict__ msg, int nb) {
+  RmMd5 m;
+  rm_md5_init(m);
+  const uint4* __restrict__ p = reinterpret_cast<const uint4*>(msg);
+  uint4 x0 = p[0], x1 = p[1], x2 = p[2], x3 = p[3];
+  for (int b = 0; b < nb; ++b) {
+    RmMd5Regs w;
+    w.m[0] = x0.x; w.m[1] = x0.y; w.m[2] = x0.z; w.m[3] = x0.w;
+    w.m[4] = x1.x; w.m[5] = x1.y; w.m[6] = x1.z; w.m[7] = x1.w;
+    w.m[8] = x2.x; w.m[9] = x2.y; w.m[10] = x2.z; w.m[11] = x2.w;
+    w.m[12] = x3.x; w.m[13] = x3.y; w.m[14] = x3.z; w.m[15] = x3.w;
+    if (b + 1 < nb) {
+      x0 = p[4 * (b + 1)];
+      x1 = p[4 * (b + 1) + 1];
+      x2 = p[4 * (b + 1) + 2];
+      x3 = p[4 * (b + 1) + 3];
+    }
+    rm_md5_block(m, w);
+  }
+  const unsigned a = m.a;
+  return ((a & 0xffu) << 24) | ((a & 0xff00u) << 8) | ((a >> 8) & 0xff00u) | (a >> 24);
+}
+
 // bisect.bisect(ring, h) % len(ring) (cache_aware_router.py:106-108)
 __device__ __forceinline__ int rm_ring_owner(const unsigned* ring, const int* owner, int n, unsigned h) {
   int lo = 0, hi = n;
@@ -236,7 +366,8 @@ __global__ void __launch_bounds__(RM_RT_TPB)
 rm_route_finish_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, int warm,
                        int* __restrict__ prefill, int* __restrict__ decode, unsigned char* __restrict__ err,
                        int* __restrict__ paddr, int* __restrict__ daddr, const unsigned* ring_p, const int* ring_p_owner,
-                       int ring_p_n, const unsigned* ring_d, const int* ring_d_owner, int ring_d_n) {
+                       int ring_p_n, const unsigned* ring_d, const int* ring_d_owner, int ring_d_n,
+                       const unsigned char* __restrict__ msg, const int* __restrict__ nblk) {
   __shared__ unsigned wsm[16 * RM_RT_TPB];
   const RmMd5Words words = {wsm + threadIdx.x, RM_RT_TPB};
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -255,7 +386,11 @@ rm_route_finish_kernel(RmTree t, const int* __restrict__ qtok, const i64* __rest
   if (e == 0) {
     const bool need_hash = pf == -1 || dc == -1;
     unsigned h = 0;
-    if (need_hash) h = rm_hash_token_list(qtok + qoff[q], (int)(qoff[q + 1] - qoff[q]), words);
+    if (need_hash) {
+      const int nb = nblk ? nblk[q] : 0;
+      if (nb > 0) h = rm_hash_rendered(msg + rm_msg_off(qoff[q] - qoff[0], q), nb);     // rendered by rm_route_render_kernel
+      else h = rm_hash_token_list(qtok + qoff[q], (int)(qoff[q + 1] - qoff[q]), words);
+    }
     if (pf != -1) {
       // prefill_cache_nodes[rank]: a decode rank here is the reference's IndexError (radix_mesh.py:451)
       if (pf >= t.n_prefill) e = 2;
@@ -278,6 +413,21 @@ rm_route_finish_kernel(RmTree t, const int* __restrict__ qtok, const i64* __rest
   err[q] = e;
 }
 
+// renders the requests that will need the hash (all of them when warm == 0) into the route scratch, if the
+// index has one (rm_route_set_rings allocates it) and the batch is within max_batch
+static bool rm_launch_render(rm_index* idx, const int* tokens, const i64* offsets, int B, int warm, const int* prefill,
+                             const int* decode, const unsigned char* err, cudaStream_t s) {
+  if (!idx->route_nblk || !idx->route_msg || B > idx->cfg.max_batch) return false;
+#ifdef RM_EMU
+  const int tpb = 1;
+#else
+  const int tpb = RM_RENDER_TPB;
+#endif
+  RM_LAUNCH(rm_route_render_kernel, B, tpb, s, tokens, offsets, B, warm, prefill, decode, err, idx->route_msg,
+            (u64)idx->route_msg_bytes, idx->route_nblk);
+  return true;
+}
+
 int rm_launch_route(rm_index* idx, const int* tokens, const i64* offsets, int B, int warm, int* out_prefill,
                     int* out_decode, int* out_paddr, int* out_daddr, unsigned char* out_err, cudaStream_t s) {
   if (B <= 0) return RM_OK;
@@ -288,9 +438,11 @@ int rm_launch_route(rm_index* idx, const int* tokens, const i64* offsets, int B,
   } else {
     RM_CUDA(cudaMemsetAsync(out_err, 0, (size_t)B, s));
   }
+  const bool rendered = rm_launch_render(idx, tokens, offsets, B, warm, out_prefill, out_decode, out_err, s);
   RM_LAUNCH(rm_route_finish_kernel, (B + RM_RT_TPB - 1) / RM_RT_TPB, RM_RT_TPB, s, idx->t, tokens, offsets, B, warm,
             out_prefill, out_decode, out_err, out_paddr, out_daddr, idx->ring_p, idx->ring_p_owner, idx->ring_p_n,
-            idx->ring_d, idx->ring_d_owner, idx->ring_d_n);
+            idx->ring_d, idx->ring_d_owner, idx->ring_d_n, rendered ? idx->route_msg : nullptr,
+            rendered ? idx->route_nblk : nullptr);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }
@@ -349,9 +501,11 @@ extern "C" int rm_pick_batch(rm_index* idx, const int32_t* depths, int32_t n_ran
   cudaStream_t s = (cudaStream_t)stream;
   RM_LAUNCH(rm_pick_kernel, (B + RM_RT_TPB - 1) / RM_RT_TPB, RM_RT_TPB, s, depths, n_ranks, B, idx->cfg.n_prefill,
             idx->cfg.n_decode, out_prefill, out_decode, out_err);
+  const bool rendered = rm_launch_render(idx, tokens, (const i64*)offsets, B, 1, out_prefill, out_decode, out_err, s);
   RM_LAUNCH(rm_route_finish_kernel, (B + RM_RT_TPB - 1) / RM_RT_TPB, RM_RT_TPB, s, idx->t, tokens, (const i64*)offsets, B, 1,
             out_prefill, out_decode, out_err, out_paddr, out_daddr, idx->ring_p, idx->ring_p_owner, idx->ring_p_n,
-            idx->ring_d, idx->ring_d_owner, idx->ring_d_n);
+            idx->ring_d, idx->ring_d_owner, idx->ring_d_n, rendered ? idx->route_msg : nullptr,
+            rendered ? idx->route_nblk : nullptr);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
 }
@@ -377,5 +531,22 @@ extern "C" int rm_route_set_rings(rm_index* idx, const uint32_t* p_points_h, con
   RM_CUDA(cudaSetDevice(idx->cfg.device));
   int rc = rm_set_ring(&idx->ring_p, &idx->ring_p_owner, &idx->ring_p_n, p_points_h, p_owner_h, n_p);
   if (rc) return rc;
-  return rm_set_ring(&idx->ring_d, &idx->ring_d_owner, &idx->ring_d_n, d_points_h, d_owner_h, n_d);
+  rc = rm_set_ring(&idx->ring_d, &idx->ring_d_owner, &idx->ring_d_n, d_points_h, d_owner_h, n_d);
+  if (rc) return rc;
+  // scratch of the rendered hash messages: 16 bytes per token + 128 per request of the largest batch, capped
+  // (RM_ROUTE_SCRATCH_MB, default 1024); requests that do not fit are hashed by the streamed form
+  if (!idx->route_nblk) {
+    size_t cap_mb = 1024;
+    if (const char* e = getenv("RM_ROUTE_SCRATCH_MB")) cap_mb = (size_t)atoll(e);
+    size_t want = (size_t)idx->cfg.max_batch * ((size_t)idx->cfg.max_key_len * 16 + 128) + 64;
+    if (want > (cap_mb << 20)) want = cap_mb << 20;
+    RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&idx->route_nblk), sizeof(int) * (size_t)idx->cfg.max_batch));
+    idx->route_msg = nullptr;
+    idx->route_msg_bytes = 0;
+    if (want >= 256) {
+      RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&idx->route_msg), want));
+      idx->route_msg_bytes = want;
+    }
+  }
+  return RM_OK;
 }

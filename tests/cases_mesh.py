@@ -141,3 +141,13 @@ def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7):
     for ix in ixs:
         ix.close()
     return stats
+
+
+def md5_awkward_keys():
+    """Negative and 10-digit ints, lengths around the 64-byte block and padding edges, the empty list, and enough
+    2K-token requests to overflow a 1 MB message scratch (the rest then takes the streamed form)."""
+    import random
+    rnd = random.Random(5)
+    pool = [0, 7, 10, 99, 100, 31999, 32000, 123456, 2147483647, -1, -2147483648, 999999, 1000000]
+    lens = list(range(0, 40)) + [55, 56, 57, 63, 64, 65, 119, 120, 121, 127, 128, 129, 500] + [2176] * 40
+    return [[rnd.choice(pool) for _ in range(n)] for n in lens]

@@ -41,22 +41,21 @@ def test_emu_consistent_hash_vectors():
         ix.close()
 
 
-def test_emu_md5_awkward_inputs():
-    """Device MD5 of str(list) against hashlib: negative and 10-digit ints, lengths around the 64-byte block
-    and padding edges, the empty list, a 2K-token request."""
-    import random
+@pytest.mark.parametrize("scratch_mb", [None, "0", "1"], ids=["rendered", "streamed", "mixed"])
+def test_emu_md5_awkward_inputs(scratch_mb, monkeypatch):
+    """Device MD5 of str(list) against hashlib, through both forms of the hash (rm_route.cu)."""
     import numpy as np
     from oracle.radix_port import PortConsistentHash
     from tests.parity import pack
+    if scratch_mb is not None:
+        monkeypatch.setenv("RM_ROUTE_SCRATCH_MB", scratch_mb)
     addrs = [f"n{i}:1" for i in range(7)]
     h = PortConsistentHash(addrs)
     ix = make_index(mode=3, n_prefill=7, n_decode=7, max_nodes=64, max_tokens=64, max_batch=512, max_key_len=4096)
     pts = np.asarray(h.ring, dtype=np.uint32)
     own = np.asarray([addrs.index(h.owner[p]) for p in h.ring], dtype=np.int32)
     ix.set_rings(pts, own, pts, own)
-    rnd = random.Random(5)
-    pool = [0, 7, 10, 99, 100, 31999, 32000, 123456, 2147483647, -1, -2147483648, 999999, 1000000]
-    keys = [[rnd.choice(pool) for _ in range(n)] for n in list(range(0, 40)) + [55, 56, 57, 63, 64, 65, 119, 120, 121, 500, 2176]]
+    keys = cases_mesh.md5_awkward_keys()
     tk, offs = pack(keys)
     n = len(keys)
     outs = [np.zeros(n, np.int32) for _ in range(4)]

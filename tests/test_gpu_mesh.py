@@ -64,3 +64,35 @@ def test_gpu_consistent_hash_vectors():
         assert [addrs[i] for i in pa] == [q["node"] for q in case["queries"]]
         assert outs[3].cpu().tolist() == pa and err.cpu().tolist() == [0] * n
         ix.close()
+
+
+@pytest.mark.parametrize("scratch_mb", [None, "0", "1"], ids=["rendered", "streamed", "mixed"])
+def test_gpu_md5_awkward_inputs(scratch_mb, monkeypatch):
+    """Device MD5 of str(list) against hashlib through both forms of the hash: rendered by a block per request
+    and compressed from scratch (default), streamed per thread (no scratch), and a batch that overflows a 1 MB
+    scratch so that both forms run in one launch."""
+    import numpy as np
+    import torch
+    from oracle.radix_port import PortConsistentHash
+    from radixmesh_b200 import capi
+    from tests.parity import pack
+    if scratch_mb is not None:
+        monkeypatch.setenv("RM_ROUTE_SCRATCH_MB", scratch_mb)
+    addrs = [f"n{i}:1" for i in range(7)]
+    h = PortConsistentHash(addrs)
+    ix = capi.DeviceIndex(mode=capi.MODE_ROUTER, n_prefill=7, n_decode=7, max_nodes=64, max_tokens=64, max_batch=512,
+                          max_key_len=4096)
+    pts = np.asarray(h.ring, dtype=np.uint32)
+    own = np.asarray([addrs.index(h.owner[p]) for p in h.ring], dtype=np.int32)
+    ix.set_rings(pts, own, pts, own)
+    keys = cases_mesh.md5_awkward_keys()
+    tk, offs = pack(keys)
+    n = len(keys)
+    dev = torch.device("cuda")
+    outs = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(4)]
+    err = torch.empty(n, dtype=torch.uint8, device=dev)
+    ix.route(torch.from_numpy(tk).to(dev), torch.from_numpy(offs).to(dev), n, False, outs[0], outs[1], outs[2], outs[3], err)
+    exp = [addrs.index(h.get_node(k)) for k in keys]
+    assert outs[2].cpu().tolist() == exp and outs[3].cpu().tolist() == exp
+    assert err.cpu().tolist() == [0] * n
+    ix.close()

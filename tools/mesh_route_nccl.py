@@ -35,40 +35,51 @@ q = np.concatenate([prompts[qd], np.random.default_rng(8).integers(0, 32000, (B,
 Lq = q.shape[1]
 tok = torch.from_numpy(q.reshape(-1).copy()).to(dev) if rank == 0 else torch.zeros(B * Lq, dtype=torch.int32, device=dev)
 qo = torch.arange(0, (B + 1) * Lq, Lq, dtype=torch.int64, device=dev)
-r = ShardedMeshRouter(ix, rank, world)
-for _ in range(3):
-    out = r.route(tok, qo, B)
-torch.cuda.synchronize(); dist.barrier()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-K = 10
-e0.record()
-for _ in range(K):
-    out = r.route(tok, qo, B)
-e1.record(); torch.cuda.synchronize()
-ms = torch.tensor([e0.elapsed_time(e1)], device=dev); dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+def timed(router, K=10):
+    for _ in range(3):
+        out = router.route(tok, qo, B)
+    torch.cuda.synchronize(); dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        out = router.route(tok, qo, B)
+    e1.record(); torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev); dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return out, ms.item() / K
+
+out, ms_batch = timed(ShardedMeshRouter(ix, rank, world))
+out_full, ms_full = timed(ShardedMeshRouter(ix, rank, world, shard_pick=False))
 pf = out[0].cpu().numpy(); dc = out[1].cpu().numpy()
+same = all(bool((a.cpu() == b.cpu()).all()) for a, b in zip(out, out_full))
 exp_owner = qd % world
 ok_p = bool(np.all(np.where(exp_owner < P, pf == exp_owner, pf == -1)))
 ok_d = bool(np.all(np.where(exp_owner >= P, dc == exp_owner, dc == -1)))
-# phase breakdown on rank 0 (one extra batch, events between the phases)
+# phase breakdown on rank 0 (one extra batch, events between the phases; the sharded-pick pipeline)
 import numpy as _np
-ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
 be = ix.be
+Bs = (B + world - 1) // world
+bounds = [min(j * Bs, B) for j in range(world + 1)]
+lo, n = bounds[rank], bounds[rank + 1] - bounds[rank]
 ev[0].record()
 dist.broadcast(tok, src=0); dist.broadcast(qo, src=0)
 ev[1].record()
 lens = be.empty(B, _np.int32); nodes = be.empty(B, _np.int32)
 ix.match(tok, qo, B, lens, nodes)
 ev[2].record()
-depths = be.empty(world * B, _np.int32)
-dist.all_gather_into_tensor(depths, lens)
+depths = be.empty(world * n, _np.int32)
+dist.all_to_all_single(depths, lens, [n] * world, [bounds[j + 1] - bounds[j] for j in range(world)])
 ev[3].record()
-o4 = [be.empty(B, _np.int32) for _ in range(4)]; e8 = be.empty(B, _np.uint8)
-ix.pick(depths, world, tok, qo, B, o4[0], o4[1], o4[2], o4[3], e8)
-ev[4].record(); torch.cuda.synchronize()
-phases = {n: round(ev[i].elapsed_time(ev[i + 1]), 3) for i, n in enumerate(["broadcast_ms", "walk_ms", "allgather_ms", "pick_md5_ms"])}
+loc = be.empty(4 * Bs, _np.int32); e8 = be.empty(Bs, _np.uint8)
+ix.pick(depths, world, tok, qo[lo:], n, loc[0:Bs], loc[Bs:2 * Bs], loc[2 * Bs:3 * Bs], loc[3 * Bs:4 * Bs], e8)
+ev[4].record()
+g = be.empty(world * 4 * Bs, _np.int32); ge = be.empty(world * Bs, _np.uint8)
+dist.all_gather_into_tensor(g, loc); dist.all_gather_into_tensor(ge, e8)
+ev[5].record(); torch.cuda.synchronize()
+phases = {nm: round(ev[i].elapsed_time(ev[i + 1]), 3) for i, nm in enumerate(["broadcast_ms", "walk_ms", "all_to_all_ms", "pick_md5_slice_ms", "allgather_results_ms"])}
 if rank == 0:
-    print(json.dumps({"phases": phases, "mesh_route": "sharded trees + allgather + pick", "n_gpus": world, "requests_per_s": B * K / (ms.item() * 1e-3),
-                      "tree_lookups_per_s": world * B * K / (ms.item() * 1e-3), "ms_per_batch": ms.item() / K, "batch": B,
-                      "request_len": Lq, "owner_pick_correct": ok_p and ok_d}))
+    print(json.dumps({"phases": phases, "mesh_route": "sharded trees + all-to-all of matched lengths + sharded pick + all-gather of results",
+                      "n_gpus": world, "requests_per_s": B / (ms_batch * 1e-3), "tree_lookups_per_s": world * B / (ms_batch * 1e-3),
+                      "ms_per_batch": ms_batch, "ms_per_batch_unsharded_pick": ms_full, "same_result_as_unsharded_pick": same,
+                      "batch": B, "request_len": Lq, "owner_pick_correct": ok_p and ok_d}))
 dist.destroy_process_group()
