@@ -211,14 +211,17 @@ class DeviceIndex:
 
     def evict(self, num_tokens: int, cap: Optional[int] = None):
         cap = int(cap or self.cfg.max_nodes)
-        nodes = np.zeros(cap, dtype=np.int32)
-        offs = np.zeros(cap, dtype=np.int64)
-        lens = np.zeros(cap, dtype=np.int32)
         n = C.c_int32(0)
         with self._mutex:
+            # result buffers are kept (zeroing three max_nodes-sized arrays per call cost more than the eviction)
+            bufs = getattr(self, "_evict_bufs", None)
+            if bufs is None or len(bufs[0]) < cap:
+                bufs = (np.empty(cap, dtype=np.int32), np.empty(cap, dtype=np.int64), np.empty(cap, dtype=np.int32))
+                self._evict_bufs = bufs
+            nodes, offs, lens = bufs
             self._check(self.lib.rm_evict(self._h, int(num_tokens), cap, ptr(nodes), ptr(offs), ptr(lens), C.addressof(n), self._s()))
-        k = n.value
-        return nodes[:k], offs[:k], lens[:k]
+            k = n.value
+            return nodes[:k].copy(), offs[:k].copy(), lens[:k].copy()
 
     def compact(self) -> None:
         with self._mutex:

@@ -69,6 +69,8 @@ struct RmCounters {
   int pad;
   int dbg_max_group;  // largest split-request group seen (diagnostics)
   int dbg_groups;     // split-request groups seen (diagnostics)
+  int ev_total;       // scratch: eviction candidates (leaves up to the frontier key + the parents they expose)
+  u64 ev_k0;          // scratch: frontier key of the current rm_evict (rm_maint.cu)
 };
 
 struct RmTree {

@@ -227,51 +227,84 @@ __global__ void rm_evict_pin_kernel(RmTree t, int n, int* __restrict__ pinned) {
 // of one per hop); every other node the reference would have stamped is an ancestor of such an endpoint.
 // The stamp the reference holds for a node is therefore the maximum of the raw stamps in its subtree,
 //     eff(x) = max(raw(x), max over children c of eff(c)),
-// which these two kernels compute bottom-up without ordering or spinning: every node counts its children,
-// leaves start climbing, and at each parent only the LAST child to report carries on upward.  (Deleting a
-// node would lower its ancestors' eff, so eviction pushes eff(x) into raw(parent) first.)
-__global__ void rm_evict_eff_init_kernel(RmTree t, int n, u64* __restrict__ eff, int* __restrict__ rem) {
+// (deleting a node would lower its ancestors' eff, so eviction pushes eff(x) into raw(parent) first).
+//
+// Computing eff for the whole tree bottom-up is a chain of dependent atomics as long as the tree is deep
+// (0.5 ms on a 1 M-node tree).  Only the nodes that CAN be evicted by this call need it:
+//   1. order the evictable LEAVES alone by (raw stamp, deeper first) - a leaf's eff is its raw stamp - and
+//      find the frontier key K0 where their lengths reach num_tokens;
+//   2. the true cut lies at or before K0 (inner nodes only add tokens earlier), and a node's key is never
+//      below a descendant's, so every node the call can evict has its whole subtree at keys <= K0;
+//   3. so: the leaves up to K0 climb; a parent joins the candidates when ALL its children have reported
+//      (they are candidates themselves) and its own key is still <= K0, and carries on upward;
+//   4. candidates are sorted again and cut exactly.
+// The climbs are as short as the evicted region is shallow.
+__global__ void rm_evict_count_kernel(RmTree t, int n, u64* __restrict__ eff, int* __restrict__ rem) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= n) return;
   eff[x] = t.stamp[x];
   if (x > 0 && t.parent[x] > 0 && t.gen[x] >= 0) atomicAdd(&rem[t.parent[x]], 1);
 }
 
-// the child counts are consumed while climbing, so "is a leaf" is taken from a copy made before
-__global__ void rm_evict_eff_leaf_kernel(int n, const int* __restrict__ rem, int* __restrict__ nch0) {
-  int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x < n) nch0[x] = rem[x];
+__device__ __forceinline__ u64 rm_evict_key(u64 stamp, int depth_end, int depth_bits) {
+  const u64 dmask = (1ull << depth_bits) - 1ull;
+  return (stamp << depth_bits) | (dmask - (u64)(unsigned)depth_end);
 }
 
-__global__ void rm_evict_eff_climb_kernel(RmTree t, int n, u64* __restrict__ eff, int* __restrict__ rem,
-                                          const int* __restrict__ nch0) {
-  int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= n || x == 0) return;
-  if (t.parent[x] < 0 || t.gen[x] < 0 || nch0[x] != 0) return;   // leaves of the tree only
-  int y = x;
-  u64 v = eff[y];
-  while (true) {
-    const int p = t.parent[y];
-    if (p <= 0) break;                      // the root carries no stamp
-    atomicMax(&eff[p], v);
-    __threadfence();
-    if (atomicSub(&rem[p], 1) != 1) break;  // a sibling subtree is still on its way
-    y = p;
-    v = *reinterpret_cast<volatile u64*>(&eff[p]);
-  }
-}
-
+// keys of the evictable leaves (everything else sorts last)
 __global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int* __restrict__ pinned,
-                                     const u64* __restrict__ eff, u64* key, unsigned* val) {
+                                     const int* __restrict__ rem, u64* key, unsigned* val) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= n) return;
   u64 k = RM_NO_REQ;
-  if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0 && pinned[x] == 0) {
-    u64 dmask = (1ull << depth_bits) - 1ull;
-    k = (eff[x] << depth_bits) | (dmask - (u64)(unsigned)t.depth_end[x]);
-  }
+  if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0 && pinned[x] == 0 && rem[x] == 0)
+    k = rm_evict_key(t.stamp[x], t.depth_end[x], depth_bits);
   key[x] = k;
   val[x] = (unsigned)x;
+}
+
+// after the cut over the leaves: frontier key, number of leaves at or below it (ties included)
+__global__ void rm_evict_frontier_kernel(RmTree t, const u64* __restrict__ skey, int n) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  int m = t.ctr->evict_n;
+  u64 k0 = 0;
+  if (m > 0) {
+    if (m >= n || skey[m] == RM_NO_REQ) {
+      k0 = RM_NO_REQ - 1;            // every evictable leaf is taken: nothing bounds the climb
+    } else {
+      k0 = skey[m - 1];
+      while (m < n && skey[m] == k0) ++m;
+    }
+  }
+  t.ctr->ev_total = m;
+  t.ctr->ev_k0 = k0;
+}
+
+// step 3: parents exposed by the candidate leaves are appended behind them
+__global__ void rm_evict_climb_kernel(RmTree t, int n, int depth_bits, const int* __restrict__ pinned, u64* __restrict__ eff,
+                                      int* __restrict__ rem, u64* skey, unsigned* sval, int m_leaves) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m_leaves) return;
+  const u64 k0 = t.ctr->ev_k0;
+  int y = (int)sval[i];
+  u64 v = eff[y];
+  while (true) {
+    const int p = t.parent[y];
+    if (p <= 0) break;                      // the root is never evicted
+    atomicMax(&eff[p], v);
+    __threadfence();
+    if (atomicSub(&rem[p], 1) != 1) break;  // a sibling subtree is not (or not yet) among the candidates
+    if (t.lock_ref[p] != 0 || pinned[p] != 0) break;
+    v = *reinterpret_cast<volatile u64*>(&eff[p]);
+    const u64 kp = rm_evict_key(v, t.depth_end[p], depth_bits);
+    if (kp > k0) break;
+    const int slot = atomicAdd(&t.ctr->ev_total, 1);
+    if (slot < n) {
+      skey[slot] = kp;
+      sval[slot] = (unsigned)p;
+    }
+    y = p;
+  }
 }
 
 // One block: walk the sorted candidates in chunks, prefix-sum their value lengths, stop at the first
@@ -385,25 +418,41 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
   const int depth_bits = idx->len_bits;
   const int bits = rm_bits_for(idx->op_seq * 2 + 1) + depth_bits + 1;
   int* pinned = sc.ev_lens;   // free until rm_evict_apply_kernel writes the evicted lengths
-  RM_CUDA(cudaMemsetAsync(pinned, 0, sizeof(int) * (size_t)n, s));
-  RM_LAUNCH(rm_evict_pin_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, pinned);
-  RM_CUDA(cudaMemsetAsync(sc.ev_rem, 0, sizeof(int) * (size_t)n, s));
-  RM_LAUNCH(rm_evict_eff_init_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem);
-  RM_LAUNCH(rm_evict_eff_leaf_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, n, sc.ev_rem, sc.ev_nch0);
-  RM_LAUNCH(rm_evict_eff_climb_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem, sc.ev_nch0);
-  RM_LAUNCH(rm_evict_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_eff,
-            sc.ev_key[0], sc.ev_val[0]);
-  const int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, bits, sc.ev_hist, s);
+  const int grid_n = (n + RM_MT_TPB - 1) / RM_MT_TPB;
 #ifdef RM_EMU
-  RM_LAUNCH(rm_evict_cut_kernel, 1, 1, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, cap);
+  const int cut_tpb = 1;
 #else
-  RM_LAUNCH(rm_evict_cut_kernel, 1, 1024, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, cap);
+  const int cut_tpb = 1024;
 #endif
+  RM_CUDA(cudaMemsetAsync(pinned, 0, sizeof(int) * (size_t)n, s));
+  RM_LAUNCH(rm_evict_pin_kernel, grid_n, RM_MT_TPB, s, t, n, pinned);
+  RM_CUDA(cudaMemsetAsync(sc.ev_rem, 0, sizeof(int) * (size_t)n, s));
+  RM_LAUNCH(rm_evict_count_kernel, grid_n, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem);
+  RM_LAUNCH(rm_evict_keys_kernel, grid_n, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_rem, sc.ev_key[0], sc.ev_val[0]);
+  // 1. leaves alone, frontier
+  int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, bits, sc.ev_hist, s);
+  RM_LAUNCH(rm_evict_cut_kernel, 1, cut_tpb, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, n);
+  RM_LAUNCH(rm_evict_frontier_kernel, 1, 1, s, t, sc.ev_key[w], n);
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  const int m_leaves = c.ev_total;
+  if (m_leaves <= 0) return RM_OK;
+  // 3. climb, 4. exact order and cut over the candidates
+  RM_LAUNCH(rm_evict_climb_kernel, (m_leaves + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_eff,
+            sc.ev_rem, sc.ev_key[w], sc.ev_val[w], m_leaves);
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  const int m_all = c.ev_total < n ? c.ev_total : n;
+  if (m_all > m_leaves) {
+    const int w2 = rm_sort_pairs(sc.ev_key[w], sc.ev_val[w], sc.ev_key[w ^ 1], sc.ev_val[w ^ 1], m_all, bits, sc.ev_hist, s);
+    w ^= w2;
+  }
+  RM_LAUNCH(rm_evict_cut_kernel, 1, cut_tpb, s, t, sc.ev_key[w], sc.ev_val[w], m_all, num_tokens, cap);
   // outputs are staged in the other ping-pong buffer (large enough: n entries of 8/4 bytes)
   int* d_nodes = reinterpret_cast<int*>(sc.ev_val[w ^ 1]);
   i64* d_offs = reinterpret_cast<i64*>(sc.ev_key[w ^ 1]);
   int* d_lens = sc.ev_lens;
-  const int lim = min(n, cap);
+  const int lim = min(m_all, cap);
   RM_LAUNCH(rm_evict_apply_kernel, (lim + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, sc.ev_val[w], sc.ev_eff, d_nodes, d_offs,
             d_lens);
   RM_CUDA(cudaGetLastError());

@@ -16,6 +16,9 @@
 #define RM_SORT_ROUNDS (RM_SORT_MAX_TILE / RM_SORT_TPB)   // rounds of 32 items per warp in the largest tile
 #define RM_SORT_SOLO 2048          // up to here one block alone is faster than the grid with its barriers (measured:
                                    // 2000 items 23 us alone, 4097 items 29 us on the grid; tools/sort_probe.cu)
+#ifndef RM_SORT_FUSED_TILES
+#define RM_SORT_FUSED_TILES 148    // largest grid of the one-launch form (blocks must be resident together)
+#endif
 #define RM_SORT_TABLE_OFF 8        // hist[0..1]: grid barrier of the one-launch form (zero between launches); tables after
 
 // Items per block: small inputs get small tiles so that the grid still covers the 148 SMs (a 64K-item
@@ -54,76 +57,39 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_hist_kernel(const 
   ghist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// Exclusive scan, in place, of the digit-major histogram table data[256][nb] (row d = counts of digit d
-// per tile).  One block of 32 warps; warp w owns rows w, w+32, ..., w+224.  The eight rows of a warp are
-// walked together so that their loads are in flight at the same time (a row-after-row version spent
-// 15 us waiting on one L2 round trip after another).
-static __global__ void __launch_bounds__(1024) rm_scan_u32_kernel(unsigned* __restrict__ data, int nb_stride, int n_max,
-                                                                 const int* __restrict__ n_dev, int tile) {
-  __shared__ unsigned tot[256];
+// Exclusive scan, in place, of every ROW of the digit-major histogram table data[256][nb] (row d = counts of
+// digit d per tile), one block per row, and the row's total into data[256 * nb_stride + d].  The scatter
+// kernel adds the digit bases itself (an exclusive scan of the 256 totals, per block).  (One block scanning
+// the whole table took 24 us per pass at 254 tiles: five passes of a 1 M-key sort spent 120 of 245 us there.)
+static __global__ void __launch_bounds__(RM_SORT_TPB) rm_scan_rows_kernel(unsigned* __restrict__ data, int nb_stride, int n_max,
+                                                                  const int* __restrict__ n_dev, int tile) {
+  __shared__ unsigned wtot[RM_SORT_WARPS];
+  __shared__ unsigned carry_s;
   const int n_items = n_dev ? min(*n_dev, n_max) : n_max;
   const int nb = (n_items + tile - 1) / tile;   // active tiles; rows keep their stride of nb_stride
-  if (nb == 0) return;
+  unsigned* __restrict__ row = data + (size_t)blockIdx.x * nb_stride;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  {
-    unsigned s[8];
-#pragma unroll
-    for (int r = 0; r < 8; ++r) s[r] = 0;
-    for (int j = lane; j < nb; j += 32) {
-#pragma unroll
-      for (int r = 0; r < 8; ++r) s[r] += data[(size_t)(wid + 32 * r) * nb_stride + j];
-    }
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      unsigned v = s[r];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) tot[wid + 32 * r] = v;
-    }
-  }
+  if (threadIdx.x == 0) carry_s = 0;
   __syncthreads();
-  if (wid == 0) {
-    // lane l owns digits 8l .. 8l+7
-    unsigned v[8], sum = 0;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      v[k] = tot[lane * 8 + k];
-      sum += v[k];
-    }
-    unsigned inc = sum;
+  for (int j0 = 0; j0 < nb; j0 += RM_SORT_TPB) {
+    const int j = j0 + (int)threadIdx.x;
+    const unsigned v = j < nb ? row[j] : 0u;
+    unsigned inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= o) inc += x;
     }
-    unsigned run = inc - sum;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      tot[lane * 8 + k] = run;
-      run += v[k];
-    }
+    if (lane == 31) wtot[wid] = inc;
+    __syncthreads();
+    unsigned before = carry_s;
+    for (int w = 0; w < wid; ++w) before += wtot[w];
+    if (j < nb) row[j] = before + inc - v;
+    __syncthreads();
+    if (threadIdx.x == RM_SORT_TPB - 1) carry_s = before + inc;
+    __syncthreads();
   }
-  __syncthreads();
-  unsigned run[8];
-#pragma unroll
-  for (int r = 0; r < 8; ++r) run[r] = tot[wid + 32 * r];
-  for (int j0 = 0; j0 < nb; j0 += 32) {
-    const int j = j0 + lane;
-    unsigned v[8];
-#pragma unroll
-    for (int r = 0; r < 8; ++r) v[r] = j < nb ? data[(size_t)(wid + 32 * r) * nb_stride + j] : 0u;
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      unsigned inc = v[r];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += x;
-      }
-      if (j < nb) data[(size_t)(wid + 32 * r) * nb_stride + j] = run[r] + inc - v[r];
-      run[r] += __shfl_sync(0xffffffffu, inc, 31);
-    }
-  }
+  if (threadIdx.x == 0) data[(size_t)256 * nb_stride + blockIdx.x] = carry_s;
 }
 
 static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_scatter_kernel(const u64* __restrict__ kin, const unsigned* __restrict__ vin,
@@ -148,10 +114,22 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_scatter_kernel(con
     __syncwarp();
   }
   __syncthreads();
-  // phase 2: thread d turns the per-warp counts of digit d into global start positions
+  // phase 2: thread d turns the per-warp counts of digit d into global start positions: digit base (exclusive
+  // scan of the row totals) + the digit's count in the tiles before this one
   {
+    __shared__ unsigned dtot[RM_SORT_WARPS];
     unsigned d = threadIdx.x;
-    unsigned run = gscan[d * nblocks + blockIdx.x];
+    const unsigned tot = gscan[(size_t)256 * nblocks + d];
+    unsigned inc = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += x;
+    }
+    if (lane == 31) dtot[wid] = inc;
+    __syncthreads();
+    unsigned run = inc - tot + gscan[d * nblocks + blockIdx.x];
+    for (int w = 0; w < wid; ++w) run += dtot[w];
 #pragma unroll
     for (int w = 0; w < RM_SORT_WARPS; ++w) {
       unsigned c = wcnt[w][d];
@@ -333,7 +311,7 @@ static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, in
   int passes = (bits + 7) / 8;
   int tile = rm_sort_tile(n);
   int nb = (n + tile - 1) / tile;
-  if (nb <= 148) {   // one launch, at most one block per SM
+  if (nb <= RM_SORT_FUSED_TILES) {   // one launch, all blocks resident
     RM_LAUNCH(rm_sort_fused_kernel, nb, RM_SORT_TPB, s, k0, v0, k1, v1, n, n_dev, passes, hist, tile);
     return passes & 1;
   }
@@ -345,7 +323,7 @@ static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, in
     u64* ko = cur ? k0 : k1;
     unsigned* vo = cur ? v0 : v1;
     RM_LAUNCH(rm_sort_hist_kernel, nb, RM_SORT_TPB, s, ki, n, n_dev, p * 8, hist, nb, tile);
-    RM_LAUNCH(rm_scan_u32_kernel, 1, 1024, s, hist, nb, n, n_dev, tile);
+    RM_LAUNCH(rm_scan_rows_kernel, 256, RM_SORT_TPB, s, hist, nb, n, n_dev, tile);
     RM_LAUNCH(rm_sort_scatter_kernel, nb, RM_SORT_TPB, s, ki, vi, ko, vo, n, n_dev, p * 8, hist, nb, tile);
     cur ^= 1;
   }

@@ -104,3 +104,20 @@ def test_gpu_zipf_c2_reduced():
 @pytest.mark.parametrize("seed", range(3))
 def test_gpu_streaming_insert_evict_compact(seed):
     cases.run_stream_evict(make_index, seed, n_batches=16, batch=96, L=32, n_docs=24, capacity=6000)
+
+
+def test_gpu_radix_sort_all_forms():
+    """tools/sort_probe.cu (built by __graft_entry__.build()): the device radix sort against std::stable_sort for
+    item counts from 0 to 1 M with the count read on the device - one block alone, the one-launch grid form, and
+    the three-kernels-per-pass form (bound > 148 tiles)."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "build", "sort_probe")
+    if not os.path.exists(exe):
+        pytest.skip("build/sort_probe not built (run __graft_entry__.build())")
+    for args in (["65536", "30"], ["1100000", "40"]):
+        out = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr
+        lines = [ln for ln in out.stdout.splitlines() if ln.startswith("n ")]
+        assert len(lines) >= 10 and all(ln.rstrip().endswith("ok") for ln in lines), out.stdout
