@@ -16,6 +16,7 @@ import numpy as np
 
 from . import capi
 from .host import CacheOplog, CacheOplogType, NodeKey, RadixMode, RingPolicy
+from .oplog_codec import IngestBuffer, deserialize_any, with_header
 from .radix_cache import MatchResult, RadixCache, TreeNode
 
 
@@ -63,8 +64,8 @@ class RadixMesh(RadixCache):
         self.communicator = communicator
         self.router_communicators = routers
         self.logic_op_counter = 0
-        self._pending: List[tuple] = []
         self._pending_lock = threading.Lock()
+        self._ingest = IngestBuffer(with_values=self.mode != RadixMode.ROUTER)
         self.tick_received: Dict[int, int] = {}
         backend = index_kwargs.pop("_backend", None)
         library = index_kwargs.pop("_library", None)
@@ -107,21 +108,25 @@ class RadixMesh(RadixCache):
 
     def _insert(self, key, value, owner_rank: int) -> int:
         with self._pending_lock:
-            self._pending.append((key, value, owner_rank))
+            self._ingest.add(key, value, owner_rank)
         ret = self._flush()
         self.send_insert_event(key, value, owner_rank)
         return ret
 
     def _flush(self):
-        """Apply the staged INSERTs, in arrival order, as one ordered device batch."""
+        """Apply the staged INSERTs, in arrival order, as ordered device batches (rm_insert_batch_h)."""
         with self._pending_lock:
-            recs, self._pending = self._pending, []
-        if not recs:
-            return 0
+            if len(self._ingest) == 0:
+                return 0
+            tok, val, offs, ranks = self._ingest.take()
         out = None
-        step = int(self._ix.cfg.max_batch)
-        for i in range(0, len(recs), step):
-            out = self._insert_records(recs[i:i + step])
+        n, step = len(ranks), int(self._ix.cfg.max_batch)
+        for i in range(0, n, step):
+            j = min(i + step, n)
+            a, b = int(offs[i]), int(offs[j])
+            out = self._ix.insert_host(tok[a:b], val[a:b] if val is not None else None, offs[i:j + 1] - offs[i], ranks[i:j])
+        self._invalidate()
+        self._ix.check_device_error()
         return int(out[-1])
 
     def send_insert_event(self, key, value, owner_rank: int) -> None:
@@ -150,12 +155,36 @@ class RadixMesh(RadixCache):
             return None
         if t == CacheOplogType.INSERT:
             with self._pending_lock:
-                self._pending.append((list(oplog.key), oplog.value, oplog.node_rank))
+                self._ingest.add(oplog.key, oplog.value, oplog.node_rank)
             self.send_insert_event(oplog.key, oplog.value, oplog.node_rank)   # re-forward with a fresh ttl
         elif t == CacheOplogType.RESET:
             RadixCache.reset(self)
         elif t != CacheOplogType.DELETE:
             assert False, "unknown oplog type"
+        return None
+
+    def oplog_received_wire(self, buf, size=None) -> None:
+        """Addition: an inbound message as it came off the socket.  An INSERT - packed
+        (oplog_codec.PackedSerializer) or the reference's JSON - is gated on its header fields and its payload
+        copied straight into the staging arrays of the next ordered insert batch; anything else (TICK, RESET, GC,
+        unusual JSON) is decoded and goes through oplog_received.  Re-forwarding re-uses the same bytes with a
+        fresh ttl and logic id."""
+        with self._pending_lock:
+            what, oplog, _ttl = self._ingest.feed_wire(buf, size, self._global_node_rank)
+        if what == "other":
+            return self.oplog_received(oplog)
+        if what == "insert" and self.mode != RadixMode.ROUTER and self.communicator is not None:
+            raw = bytes(memoryview(buf)[:size] if size is not None else buf)
+            self.logic_op_counter += 1
+            fwd = with_header(raw, self.sync_algo.ttl(self.args), self.logic_op_counter)
+            send_raw = getattr(self.communicator, "send_raw", None)
+            if send_raw is not None:
+                send_raw(fwd)
+            else:
+                self.communicator.send(deserialize_any(fwd))
+            if self._global_node_rank == self.sync_algo.master_node_rank() and self.router_communicators:
+                for r in self.router_communicators:
+                    (getattr(r, "send_raw", None) or (lambda b, r=r: r.send(deserialize_any(b))))(fwd)
         return None
 
     def dec_lock_ref(self, node: TreeNode) -> int:

@@ -138,3 +138,33 @@ def test_consistent_hash_matches_reference():
         for _ in range(200):
             key = [rnd.randrange(0, 32000) for _ in range(rnd.randrange(1, 40))]
             assert a.get_node(key) == b.get_node(key)
+
+
+def test_oplog_wire_matches_reference():
+    """The reference's JsonSerializer, the oracle's restatement of its decode and the product's JSON codec agree on
+    the same bytes, both ways (communication/serializer.py:20-35, radix/cache_oplog.py:48-66)."""
+    ref_harness.load()
+    from src.communication.serializer import JsonSerializer as RefSer
+    from src.radix.cache_oplog import CacheOplog as RefOplog, CacheOplogType as RefType
+    from oracle.oplog_port import port_deserialize
+    from radixmesh_b200.oplog_codec import JsonSerializer, PackedSerializer
+    rnd = random.Random(11)
+    ref, ours, packed = RefSer(), JsonSerializer(), PackedSerializer()
+    for _ in range(200):
+        n = rnd.choice([0, 1, 3, 17, 200])
+        typ = rnd.choice([RefType.INSERT, RefType.INSERT, RefType.TICK, RefType.RESET, RefType.DELETE])
+        op = RefOplog(oplog_type=typ, node_rank=rnd.randrange(0, 8), local_logic_id=rnd.randrange(0, 1 << 40),
+                      key=[rnd.randrange(0, 1 << 31) for _ in range(n)], value=[rnd.randrange(0, 1 << 50) for _ in range(n)],
+                      ttl=rnd.randrange(0, 9))
+        wire = ref.serialize(op)
+        a = ref.deserialize(bytearray(wire), len(wire))
+        b = port_deserialize(bytearray(wire), len(wire))
+        c = ours.deserialize(bytearray(wire), len(wire))
+        for x in (b, c):
+            assert (int(x.oplog_type), x.node_rank, x.local_logic_id, list(x.key), list(x.value), x.ttl) == \
+                   (int(a.oplog_type), a.node_rank, a.local_logic_id, list(a.key), list(a.value), a.ttl)
+        assert ours.serialize(c) == wire                      # same bytes on the way out
+        d = ref.deserialize(bytearray(ours.serialize(c)), len(wire))
+        assert d.to_dict() == a.to_dict()
+        e = packed.deserialize(packed.serialize(c))
+        assert e.to_dict() == a.to_dict()

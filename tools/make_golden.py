@@ -199,10 +199,38 @@ def hash_vectors():
     return out
 
 
+def oplog_wire():
+    """Messages exactly as the reference's JsonSerializer puts them on the wire (communication/serializer.py:20-35),
+    with the fields CacheOplog.model_validate_json gives back (radix/cache_oplog.py:48-66)."""
+    ref_harness.load()
+    from src.communication.serializer import JsonSerializer
+    from src.radix.cache_oplog import CacheOplog, CacheOplogType
+    rnd = random.Random(7)
+    ser = JsonSerializer()
+    out = []
+    for i in range(60):
+        typ = rnd.choice([CacheOplogType.INSERT] * 6 + [CacheOplogType.TICK, CacheOplogType.RESET, CacheOplogType.DELETE])
+        n = rnd.choice([0, 1, 2, 7, 64, 300]) if typ == CacheOplogType.INSERT else 0
+        key = [rnd.randrange(0, 32000) for _ in range(n)]
+        val = [rnd.randrange(0, 1 << 40) for _ in range(n)]
+        op = CacheOplog(oplog_type=typ, node_rank=rnd.randrange(0, 6), local_logic_id=rnd.randrange(0, 1 << 30), key=key,
+                        value=val, ttl=rnd.randrange(1, 7))
+        wire = ser.serialize(op)
+        back = ser.deserialize(bytearray(wire), len(wire))
+        out.append({"wire": wire.decode("utf-8"),
+                    "fields": {"oplog_type": int(back.oplog_type), "node_rank": back.node_rank,
+                               "local_logic_id": back.local_logic_id, "key": list(back.key), "value": list(back.value),
+                               "ttl": back.ttl}})
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    only = set(sys.argv[1:])
     for name, fn in [("base_sequences", base_sequences), ("correctness_blocks", correctness_blocks),
-                     ("mesh_sequences", mesh_sequences), ("consistent_hash", hash_vectors)]:
+                     ("mesh_sequences", mesh_sequences), ("consistent_hash", hash_vectors), ("oplog_wire", oplog_wire)]:
+        if only and name not in only:
+            continue
         data = fn()
         with open(os.path.join(OUT, name + ".json"), "w") as f:
             json.dump(data, f, separators=(",", ":"))
