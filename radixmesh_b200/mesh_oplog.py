@@ -1,0 +1,114 @@
+"""Intra-box oplog transport over NVLink.
+
+The reference forwards every INSERT hop by hop around a TCP ring (`policy/sync_algo.py:57-75`,
+`radix/radix_mesh.py:339-347`, `communication/communicator.py:183-210`): P + D sequential hops of JSON per insert,
+one tree insert per hop.  Inside one box the mesh nodes are GPUs on NVSwitch, so the records of a round travel as
+packed arrays in ONE exchange and every replica applies the same ordered batches:
+
+    stage()               local inserts of this rank (owner rank = this rank), packed on the host (IngestBuffer)
+    exchange_and_apply()  all-gather of (records, tokens) counts, then of the padded token / value / length arrays;
+                          every rank applies the records of rank 0, 1, ..., W-1 in that order, each rank's records in
+                          their local order, through rm_insert_batch (device pointers, the conflict rule of
+                          radix_mesh.py:273-323 on the device).
+
+All replicas see one total order, so they end identical (the ring gives every node a different interleaving and
+relies on the lowest-rank-wins rule to converge; the same rule runs here, the order is just no longer a variable).
+Cross-box traffic stays on the reference's TCP path: feed what arrives there through RadixMesh.oplog_received_wire.
+
+One process per GPU, `torch.distributed` (NCCL on the GPUs; gloo with the host-emulation backend in the CPU tests).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import numpy as np
+
+from . import capi
+from .oplog_codec import IngestBuffer
+
+
+def _as_torch(x):
+    import torch
+    return x if isinstance(x, torch.Tensor) else torch.from_numpy(x)
+
+
+class NvlinkOplogExchange:
+    """`indexes`: the device indexes of THIS rank that replicate the mesh tree (its P/D tree, optionally a ROUTER
+    tree as well); every one of them receives every record."""
+
+    def __init__(self, indexes: List[capi.DeviceIndex], rank: int, world: int, group=None):
+        self.ixs, self.rank, self.world, self.group = list(indexes), rank, world, group
+        self.be = self.ixs[0].be
+        self._stage = IngestBuffer(with_values=True)
+        self.applied = 0
+
+    def stage(self, key, value) -> None:
+        """A local insert (RadixMesh.insert on this node): applied, here and everywhere, at the next exchange."""
+        self._stage.add(key, value, self.rank)
+
+    def exchange_and_apply(self) -> int:
+        """Collective.  Returns the number of records applied (the same on every rank)."""
+        import torch
+        import torch.distributed as dist
+        be, W = self.be, self.world
+        tok, val, offs, _ = self._stage.take()
+        lens = np.diff(offs).astype(np.int32)
+        mine = be.to_device(np.asarray([len(lens), int(offs[-1])], dtype=np.int64))
+        counts = be.empty(2 * W, np.int64)
+        if W > 1:
+            dist.all_gather_into_tensor(_as_torch(counts), _as_torch(mine), group=self.group)
+        else:
+            _as_torch(counts).copy_(_as_torch(mine))
+        cnt = be.to_host(counts).reshape(W, 2)
+        max_rec, max_tok = int(cnt[:, 0].max()), int(cnt[:, 1].max())
+        total = int(cnt[:, 0].sum())
+        if total == 0:
+            return 0
+        # padded send buffers (the pad is never read: every rank's true counts are known)
+        s_tok = np.zeros(max(max_tok, 1), dtype=np.int32)
+        s_val = np.zeros(max(max_tok, 1), dtype=np.int64)
+        s_len = np.zeros(max(max_rec, 1), dtype=np.int32)
+        s_tok[:len(tok)] = tok
+        s_val[:len(val)] = val
+        s_len[:len(lens)] = lens
+        d_tok, d_val, d_len = be.to_device(s_tok), be.to_device(s_val), be.to_device(s_len)
+        g_tok = be.empty(W * s_tok.size, np.int32)
+        g_val = be.empty(W * s_val.size, np.int64)
+        g_len = be.empty(W * s_len.size, np.int32)
+        if W > 1:
+            dist.all_gather_into_tensor(_as_torch(g_tok), _as_torch(d_tok), group=self.group)
+            dist.all_gather_into_tensor(_as_torch(g_val), _as_torch(d_val), group=self.group)
+            dist.all_gather_into_tensor(_as_torch(g_len), _as_torch(d_len), group=self.group)
+        else:
+            _as_torch(g_tok).copy_(_as_torch(d_tok))
+            _as_torch(g_val).copy_(_as_torch(d_val))
+            _as_torch(g_len).copy_(_as_torch(d_len))
+        t_len = _as_torch(g_len)
+        for r in range(W):
+            n_r = int(cnt[r, 0])
+            if n_r == 0:
+                continue
+            # offsets of rank r's records inside its slice: exclusive prefix sum of its lengths, on the device
+            l_r = t_len[r * s_len.size:r * s_len.size + n_r].to(torch.int64)
+            o_r = torch.zeros(n_r + 1, dtype=torch.int64, device=l_r.device)
+            torch.cumsum(l_r, 0, out=o_r[1:])
+            ranks = torch.full((n_r,), r, dtype=torch.int32, device=l_r.device)
+            tok_r = _as_torch(g_tok)[r * s_tok.size:(r + 1) * s_tok.size]
+            val_r = _as_torch(g_val)[r * s_val.size:(r + 1) * s_val.size]
+            step = min(int(ix.cfg.max_batch) for ix in self.ixs)
+            for a in range(0, n_r, step):
+                b = min(a + step, n_r)
+                o_ab = (o_r[a:b + 1] - o_r[a]).contiguous()
+                lo = int(o_r[a].item()) if a else 0
+                out = torch.empty(b - a, dtype=torch.int32, device=l_r.device)
+                for ix in self.ixs:
+                    v = None if ix.mode == capi.MODE_ROUTER else self._arr(val_r[lo:])
+                    ix.insert(self._arr(tok_r[lo:]), v, self._arr(o_ab), self._arr(ranks[a:b]), b - a, self._arr(out))
+        for ix in self.ixs:
+            ix.check_device_error()
+        self.applied += total
+        return total
+
+    def _arr(self, t):
+        """torch tensor -> what the index's backend takes (numpy view for the host-emulation backend)."""
+        return t if getattr(self.be, "name", "") == "cuda" else t.numpy()
