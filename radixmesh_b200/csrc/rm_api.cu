@@ -110,9 +110,9 @@ int rm_destroy(rm_index* idx) {
   RmTree& t = idx->t;
   RmScratch& sc = idx->sc;
   void* ptrs[] = {t.table, t.parent, t.edge_off, t.edge_len, t.lock_ref, t.stamp, t.rank, t.depth_end, t.nchild,
-                  t.gen, t.parked, t.tok, t.val, t.seg, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
+                  t.gen, t.parked, t.born, t.tok, t.val, t.seg, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
                   sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.link, t.req_head, sc.hist, sc.ev_key[0], sc.ev_key[1],
-                  sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ev_nch0, sc.lock_first, sc.lock_cnt, sc.lock_flag,
+                  sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ins_mark, sc.lock_first, sc.lock_cnt, sc.lock_flag,
                   sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b,
                   idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner, idx->route_msg, idx->route_nblk};
   for (void* p : ptrs)
@@ -177,6 +177,7 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&t.nchild, N));
   A(rm_dalloc(&t.gen, N));
   A(rm_dalloc(&t.parked, N));
+  A(rm_dalloc(&t.born, N));
   A(rm_dalloc(&t.tok, (size_t)cfg->max_tokens + RM_ARENA_PAD));
   A(rm_dalloc(&t.val, with_values ? (size_t)cfg->max_tokens + RM_ARENA_PAD : 1));
   A(rm_dalloc(&t.seg, (size_t)cfg->max_tokens + RM_ARENA_PAD));
@@ -205,7 +206,7 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&sc.ev_lens, N));
   A(rm_dalloc(&sc.ev_eff, N));
   A(rm_dalloc(&sc.ev_rem, N));
-  A(rm_dalloc(&sc.ev_nch0, N));
+  A(rm_dalloc(&sc.ins_mark, N));
   A(rm_dalloc(&sc.lock_first, N));
   A(rm_dalloc(&sc.lock_cnt, N));
   A(rm_dalloc(&sc.lock_flag, 1));
@@ -407,7 +408,7 @@ int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream) {
   out_h->op_seq = (int64_t)idx->op_seq;
   out_h->device_error = c.err;
   out_h->pad = c.node_hwm;
-  if (getenv("RM_DEBUG_COUNTERS")) fprintf(stderr, "[rm] n_req %d on_shared_edges %d groups %d max_group %d\n", c.n_req, c.n_big, c.dbg_groups, c.dbg_max_group);
+  if (getenv("RM_DEBUG_COUNTERS")) fprintf(stderr, "[rm] n_req %d on_shared_edges %d groups %d max_group %d  insert records ordered %llu resumed %llu\n", c.n_req, c.n_big, c.dbg_groups, c.dbg_max_group, c.ins_ordered, c.ins_resumed);
   return RM_OK;
 }
 

@@ -71,6 +71,8 @@ struct RmCounters {
   int dbg_groups;     // split-request groups seen (diagnostics)
   int ev_total;       // scratch: eviction candidates (leaves up to the frontier key + the parents they expose)
   u64 ev_k0;          // scratch: frontier key of the current rm_evict (rm_maint.cu)
+  u64 ins_ordered;    // diagnostics: mesh insert records applied on the ordered (first-token) path
+  u64 ins_resumed;    // diagnostics: mesh insert records applied on the resumed (divergence-group) path
 };
 
 struct RmTree {
@@ -88,6 +90,7 @@ struct RmTree {
   int* nchild;
   int* gen;        // generation of the object a tree id stands for (bumped by a locked swap); parked: -(gen)-1
   int* parked;     // tree node: most recently parked predecessor (or -1); parked node: the one parked before it
+  u64* born;       // op seq of the insert record that created the node (0 = older than any batch in flight)
   int* tok;
   i64* val;
   int* req_head;   // per node: last query of the current match batch that asked to split it (-1 between batches)

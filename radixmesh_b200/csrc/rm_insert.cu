@@ -92,6 +92,9 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
   const u64 gk = skey[i];
   if (i > 0 && skey[i - 1] == gk) return;  // one group per distinct key
   if (start != nullptr && gk == 0) return;  // records the pre-pass finished
+  // mesh modes mix both kinds of groups in one launch: keys with bit 40 are first-token groups that must be
+  // applied from the root in arrival order (a record of the group replaces a stored value)
+  const bool resume = start != nullptr && (gk >> 40) == 0;
   if (start == nullptr && gk == (1ull << 32)) {
     // empty keys: insert returns 0 and only stamps the root (radix_cache.py:297-299)
     for (int j = i + g.lane; j < N; j += G) out_prefix[sval[j]] = 0;
@@ -119,7 +122,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       continue;
     }
     int node = 0, pos = 0, total = 0;
-    if (start != nullptr) {
+    if (resume) {
       node = start[r];
       pos = total = node > 0 ? t.depth_end[node] : 0;
     }
@@ -197,6 +200,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.nchild[u] = 1;
           t.gen[u] = 0;
           t.parked[u] = -1;
+          t.born[u] = seq_base + (u64)r;
           t.stamp[u] = c_before > seq ? c_before : seq;   // later records that passed c in full pass u as well
           atomicMax(&t.ctr->node_hwm, u + 1);
           t.table[sidx].child = u;
@@ -262,6 +266,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
               t.rank[d] = old_rank;
               t.nchild[d] = 0;
               t.gen[d] = -(t.gen[target] + 1);   // parked marker: -(generation it was known under) - 1
+              t.born[d] = seq_base + (u64)r;
               t.stamp[d] = t.stamp[target];
               atomicMax(&t.ctr->node_hwm, d + 1);
               t.edge_off[target] = noff;
@@ -314,6 +319,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.nchild[leaf] = 0;
           t.gen[leaf] = 0;
           t.parked[leaf] = -1;
+          t.born[leaf] = seq_base + (u64)r;
           t.stamp[leaf] = seq;
           atomicMax(&t.ctr->node_hwm, leaf + 1);
           atomicAdd(&t.nchild[node], 1);
@@ -327,6 +333,164 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       g.sync();
     }
     if (g.lane == 0) out_prefix[r] = total;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Mesh modes, two-phase apply.  Grouping by first token alone serialises a Zipf-skewed stream on its hottest
+// prompt (one warp applies every record that starts with it: 21 K records/s measured), so the mesh modes use the
+// same scheme as RadixCache semantics - read-only pre-pass to the deepest fully matched node, groups keyed by
+// (that node, next token), walk resumed there - wherever the conflict rule allows it:
+//   * a record whose value DIFFERS from a stored node it passes either LOSES there (stored rank <= its own:
+//     nothing in the tree changes, dup_nodes gets (node, its rank), radix_mesh.py:300-310) or REPLACES the stored
+//     value (_swap_node, radix_mesh.py:466-495).  A replacement changes what every later record of the same first
+//     token compares against, so a first-token group that contains one keeps the ordered path from the root
+//     (marked through its root child; such groups and the resumed ones touch disjoint subtrees).
+//   * all other records resume at their divergence node.  Their losses are booked AFTER the apply
+//     (rm_insert_lost_kernel), walking up from the divergence node: an upper node created by a split of this same
+//     batch counts as a node of its own only if the record that made it came EARLIER (born[] holds the creating
+//     record's op seq); made later, it was still part of the node below it when this record passed, so its
+//     comparison is folded into that node's.  Values on the path cannot change meanwhile (no replacement in a
+//     resumed group reaches a node older than the batch).
+template <int G, int MESH>
+__device__ __forceinline__ bool rm_ins_differs(const RmTree& t, const RmGroup<G>& g, int v, const i64* __restrict__ val, int owner) {
+  if (MESH == 2) return t.rank[v] != owner;
+  const int e = t.edge_len[v];
+  const i64 off = t.edge_off[v];
+  const int at = t.depth_end[v] - e;
+  for (int base = 0; base < e; base += G) {
+    const int x = base + g.lane;
+    const bool ne = x < e && __ldcg(t.val + off + x) != val[at + x];
+    if (g.ballot(ne)) return true;
+  }
+  return false;
+}
+
+template <int G, int MESH>
+__global__ void __launch_bounds__(RM_INS_TPB)
+rm_insert_classify_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__ rval, const i64* __restrict__ roff,
+                          const int* __restrict__ rrank, int N, const int* __restrict__ xnode, int* __restrict__ c0s,
+                          int* __restrict__ mark) {
+  RmGroup<G> g;
+  const int r = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (r >= N) return;
+  const i64 o = roff[r];
+  const int n = (int)(roff[r + 1] - o);
+  const int* __restrict__ key = rtok + o;
+  const i64* __restrict__ val = (MESH == 2) ? nullptr : (rval + o);
+  const int owner = rrank ? rrank[r] : t.self_rank;
+  const int x = xnode[r];
+  int c0 = 0;
+  bool swap = false;
+  if (n <= t.max_key_len) {
+    const int pos = x > 0 ? t.depth_end[x] : 0;
+    if (pos < n) {                       // the edge the record leaves the tree on, matched in part
+      RmSlot sl;
+      const int sidx = rm_find<true>(t, rm_key(x, key[pos]), sl);
+      if (sidx >= 0) {
+        const int elen = rm_slot_len(sl.len_rank);
+        const int srank = rm_slot_rank(sl.len_rank);
+        const i64 eoff = sl.edge_off;
+        const int lim = min(elen, n - pos);
+        int m = lim;
+        for (int base = 1; base < lim; base += G) {
+          const int xx = base + g.lane;
+          const bool ne = xx < lim && __ldcg(t.tok + eoff + xx) != key[pos + xx];
+          const unsigned mb = g.ballot(ne);
+          if (mb) {
+            m = base + __ffs(mb) - 1;
+            break;
+          }
+        }
+        bool diff = false;
+        if (MESH == 2) {
+          diff = srank != owner;
+        } else {
+          for (int base = 0; base < m; base += G) {
+            const int xx = base + g.lane;
+            const bool ne = xx < m && __ldcg(t.val + eoff + xx) != val[pos + xx];
+            if (g.ballot(ne)) {
+              diff = true;
+              break;
+            }
+          }
+        }
+        if (diff && srank > owner) swap = true;
+        if (x == 0) c0 = sl.child;
+      }
+    }
+    for (int v = x; v > 0;) {            // the nodes it matched in full, bottom-up
+      if (!swap && rm_ins_differs<G, MESH>(t, g, v, val, owner) && t.rank[v] > owner) swap = true;
+      const int par = t.parent[v];
+      if (par == 0) c0 = v;
+      v = par;
+    }
+  }
+  if (g.lane == 0) {
+    c0s[r] = c0;
+    if (swap && c0 > 0) mark[c0] = 1;
+  }
+}
+
+// group keys after the classification: bit 40 | first token for the groups that stay on the ordered path,
+// else the hash of (divergence node, next token) + 1, or 0 when the whole key is in the tree already
+__global__ void rm_insert_keys3_kernel(RmTree t, const int* __restrict__ tok, const i64* __restrict__ off, int N,
+                                       const int* __restrict__ xnode, const int* __restrict__ c0s, const int* __restrict__ mark,
+                                       u64* __restrict__ key, unsigned* __restrict__ val, int* __restrict__ out_prefix,
+                                       unsigned char* __restrict__ ordered) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  const i64 o = off[r];
+  const int n = (int)(off[r + 1] - o);
+  const int c0 = c0s[r];
+  u64 k = 0;
+  const bool slow = c0 > 0 && mark[c0] != 0;
+  if (slow) {
+    k = (1ull << 40) | (u64)(unsigned)tok[o];
+  } else {
+    const int x = xnode[r];
+    const int pos = x > 0 ? t.depth_end[x] : 0;
+    if (n > t.max_key_len) k = (1ull << 40) | (1ull << 33);              // error record: the kernel reports it
+    else if (pos < n) k = 1ull + (u64)(rm_hash2((unsigned)x, (unsigned)tok[o + pos], 0) >> 12);
+    else out_prefix[r] = n;
+  }
+  ordered[r] = slow ? 1 : 0;
+  atomicAdd(slow ? &t.ctr->ins_ordered : &t.ctr->ins_resumed, 1ull);
+  key[r] = k;
+  val[r] = (unsigned)r;
+}
+
+__global__ void rm_insert_unmark_kernel(int N, const int* __restrict__ c0s, int* __restrict__ mark) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < N && c0s[r] > 0) mark[c0s[r]] = 0;
+}
+
+// losses of the resumed records, booked on the tree as the apply left it (see above)
+template <int G, int MESH>
+__global__ void __launch_bounds__(RM_INS_TPB)
+rm_insert_lost_kernel(RmTree t, const i64* __restrict__ rval, const i64* __restrict__ roff, const int* __restrict__ rrank,
+                      int N, const int* __restrict__ xnode, const unsigned char* __restrict__ ordered, u64 seq_base) {
+  RmGroup<G> g;
+  const int r = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (r >= N || ordered[r]) return;
+  const i64 o = roff[r];
+  const int n = (int)(roff[r + 1] - o);
+  if (n > t.max_key_len) return;
+  const i64* __restrict__ val = (MESH == 2) ? nullptr : (rval + o);
+  const int owner = rrank ? rrank[r] : t.self_rank;
+  const u64 mine = seq_base + (u64)r;
+  int v = xnode[r];
+  while (v > 0) {
+    const int base = v;
+    const int rk = t.rank[base];
+    bool diff = rm_ins_differs<G, MESH>(t, g, v, val, owner);
+    int p = t.parent[v];
+    while (p > 0 && t.born[p] > mine) {          // made by a later record: still part of `base` when this one passed
+      if (!diff) diff = rm_ins_differs<G, MESH>(t, g, p, val, owner);
+      p = t.parent[p];
+    }
+    if (diff && rk <= owner && g.lane == 0) rm_dup_put(t, base, owner, -1);
+    v = p;
   }
 }
 
@@ -357,18 +521,39 @@ int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const 
     RM_CUDA(cudaGetLastError());
     return RM_OK;
   }
-  RM_LAUNCH(rm_insert_keys_kernel, (N + 255) / 256, 256, s, tokens, offsets, N, sc.key[0], sc.val[0]);
+  // mesh modes: pre-pass, conflict classification, one launch for both kinds of groups, losses of the resumed ones
+  int* xnode = sc.krank;
+  int* xlen = sc.uniq_pos;
+  int* c0s = reinterpret_cast<int*>(sc.uniq_min);
+  unsigned char* ordered = reinterpret_cast<unsigned char*>(sc.sufmax);
+  int rc = rm_launch_walk_records(idx, tokens, offsets, N, seq_base, xlen, xnode, s);
+  if (rc) return rc;
+  const bool router = idx->cfg.mode == RM_MODE_ROUTER;
+  if (router) {
+    auto kc = rm_insert_classify_kernel<RM_INS_G, 2>;
+    RM_LAUNCH(kc, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, xnode, c0s, sc.ins_mark);
+  } else {
+    auto kc = rm_insert_classify_kernel<RM_INS_G, 1>;
+    RM_LAUNCH(kc, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, xnode, c0s, sc.ins_mark);
+  }
+  RM_LAUNCH(rm_insert_keys3_kernel, (N + 255) / 256, 256, s, idx->t, tokens, offsets, N, xnode, c0s, sc.ins_mark, sc.key[0],
+            sc.val[0], out_prefix_len, ordered);
+  RM_LAUNCH(rm_insert_unmark_kernel, (N + 255) / 256, 256, s, N, c0s, sc.ins_mark);
   RM_CUDA(cudaGetLastError());
-  const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], N, 33, sc.hist, s);
+  const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], N, 41, sc.hist, s);
   RM_CUDA(cudaGetLastError());
-  if (idx->cfg.mode == RM_MODE_ROUTER) {
+  if (router) {
     auto k = rm_insert_kernel<RM_INS_G, 2>;
     RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base,
-              out_prefix_len, (const int*)nullptr);
+              out_prefix_len, xnode);
+    auto kl = rm_insert_lost_kernel<RM_INS_G, 2>;
+    RM_LAUNCH(kl, grid, RM_INS_TPB, s, idx->t, values, offsets, ranks, N, xnode, ordered, seq_base);
   } else {
     auto k = rm_insert_kernel<RM_INS_G, 1>;
     RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base,
-              out_prefix_len, (const int*)nullptr);
+              out_prefix_len, xnode);
+    auto kl = rm_insert_lost_kernel<RM_INS_G, 1>;
+    RM_LAUNCH(kl, grid, RM_INS_TPB, s, idx->t, values, offsets, ranks, N, xnode, ordered, seq_base);
   }
   RM_CUDA(cudaGetLastError());
   return RM_OK;

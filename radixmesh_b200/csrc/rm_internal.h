@@ -22,7 +22,7 @@ struct RmScratch {
   int* ev_lens;       // value-run lengths of the evicted nodes, in eviction order
   u64* ev_eff;        // effective (subtree-max) stamps
   int* ev_rem;        // children still to report, per node
-  int* ev_nch0;       // child counts before the climb
+  int* ins_mark;      // per node, zero between insert batches: root child whose first-token group stays on the ordered path
   // lock batches (sized by max_nodes)
   int* lock_first;
   int* lock_cnt;

@@ -30,6 +30,7 @@ __global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
     t.nchild[x] = 0;
     t.gen[x] = 0;
     t.parked[x] = -1;
+    t.born[x] = 0;
     lock_first[x] = RM_INT_MAX;
     lock_cnt[x] = 0;
   }
@@ -50,6 +51,10 @@ __global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
     c.n_big = 0;
     c.dbg_max_group = 0;
     c.dbg_groups = 0;
+    c.ev_total = 0;
+    c.ev_k0 = 0;
+    c.ins_ordered = 0;
+    c.ins_resumed = 0;
     *t.ctr = c;
   }
 }
@@ -69,6 +74,7 @@ int rm_launch_reset(rm_index* idx, cudaStream_t s) {
   RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
   RM_CUDA(cudaMemsetAsync(t.dup_key, 0xFF, sizeof(u64) * ((size_t)t.dup_mask + 1), s));
   RM_CUDA(cudaMemsetAsync(t.req_head, 0xFF, sizeof(int) * (size_t)t.max_nodes, s));
+  RM_CUDA(cudaMemsetAsync(idx->sc.ins_mark, 0, sizeof(int) * (size_t)t.max_nodes, s));
   RM_CUDA(cudaMemsetAsync(t.seg, 0xFF, sizeof(int) * ((size_t)t.max_tokens + RM_ARENA_PAD), s));
   RmLockScratch ls = rm_lock_scratch(idx);
   RM_CUDA(cudaMemsetAsync(ls.flag, 0, sizeof(int), s));

@@ -29,7 +29,7 @@ def rings(addrs):
     return pts, own
 
 
-def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7):
+def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7, max_recs=5):
     rnd = random.Random(seed)
     port = PortMesh(P, D, R)
     ixs = []
@@ -45,7 +45,7 @@ def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7):
         kind = rnd.choice(["ins", "ins", "ins", "match", "route", "lock", "unlock"])
         if kind == "ins":
             recs = []
-            for _ in range(rnd.randrange(1, 6)):
+            for _ in range(rnd.randrange(1, max_recs + 1)):
                 rank = rnd.randrange(P + D)
                 key = [rnd.randrange(vocab) for _ in range(rnd.randrange(1, maxlen))]
                 variant = rnd.randrange(2)

@@ -16,6 +16,13 @@ def test_emu_mesh_binary_vocab(seed):
     cases_mesh.run_mesh_sequence(make_index, 500 + seed, n_steps=30, vocab=2, maxlen=6)
 
 
+@pytest.mark.parametrize("seed", range(30))
+def test_emu_mesh_big_batches(seed):
+    """Up to 48 records per insert batch: records of one batch lose against, replace and split the same nodes, in
+    resumed groups and in groups that stay on the ordered path (rm_insert.cu, two-phase mesh apply)."""
+    cases_mesh.run_mesh_sequence(make_index, 9000 + seed, n_steps=12, vocab=2 + seed % 2, maxlen=6 + seed % 4, max_recs=48)
+
+
 def test_emu_consistent_hash_vectors():
     """ConsistentHash golden vectors (recorded from the reference) through the MD5 fallback kernel."""
     import numpy as np
