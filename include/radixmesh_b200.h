@@ -173,6 +173,27 @@ int rm_compact(rm_index* idx, void* stream);
 int rm_gc_candidates(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h, void* stream);
 /* All dup_nodes entries (tree node id, rank, parked node id or -1, parked lock_ref or 0).  Synchronises. */
 int rm_dup_entries(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h, void* stream);
+/*
+ * Duplicate-node GC between replicas: RadixMesh._gc_handle (radix_mesh.py:362-389).  A key crosses replicas as
+ * (full key tokens, rank) = ImmutableNodeKey (cache_oplog.py:25-40); every call here takes HOST pointers, locates
+ * the keys read-only and synchronises (control plane: a handful of keys every gc_interval_second).
+ *   rm_gc_keys_h   full keys of tree nodes (the node ids rm_gc_candidates returns): row i of out_tokens_h
+ *                  (stride tokens per row) and out_lens_h[i]; a key longer than stride only reports its length.
+ *   rm_gc_agree_h  out_agree_h[i] = 1 iff the key is in dup_nodes here and its entry is None or has
+ *                  lock_ref == 0 (:386-387), else 0 (also when the key's node does not exist here).
+ *   rm_gc_exec_h   GC_EXEC: dup_nodes.pop(key, None) (:363-366).  With free_parked != 0 (the replica that asked,
+ *                  :371-377) a parked node held by the entry is released and its arena run returned in
+ *                  out_off_h[i] / out_len_h[i] (else -1 / 0): read the KV indices with rm_read_arena and hand them
+ *                  to token_to_kv_pool_allocator.free, as :376-377 does.
+ * The all-reduce that replaces the GC_QUERY ring pass on one box is host code (radixmesh_b200/mesh_gc.py); the
+ * reference's own ring pass cannot complete because CacheOplog.to_dict drops gc_query / gc_exec.
+ */
+int rm_gc_keys_h(rm_index* idx, const int32_t* nodes_h, int32_t n, int32_t stride, int32_t* out_tokens_h,
+                 int32_t* out_lens_h, void* stream);
+int rm_gc_agree_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offsets_h, const int32_t* ranks_h, int32_t n,
+                  uint8_t* out_agree_h, void* stream);
+int rm_gc_exec_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offsets_h, const int32_t* ranks_h, int32_t n,
+                 int32_t free_parked, int64_t* out_off_h, int32_t* out_len_h, void* stream);
 
 /*
  * Router pick: RadixMesh.match_prefix in ROUTER mode (radix_mesh.py:219-238) fused with

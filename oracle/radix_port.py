@@ -619,6 +619,17 @@ class PortRadixMesh(PortRadixCache):
         # radix_mesh.py:386-388
         return k in self.dup_nodes and (self.dup_nodes[k] is None or self.dup_nodes[k].lock_ref == 0)
 
+    def gc_exec(self, keys, origin: bool) -> list:
+        # radix_mesh.py:363-377: GC_EXEC pops the keys everywhere; the node that asked first frees the KV indices
+        # of the parked nodes it holds for them (token_to_kv_pool_allocator.free(value.value.tolist()))
+        freed = []
+        for k in keys:
+            n = self.dup_nodes.get(k)
+            if origin and n is not None:
+                freed.append([int(x) for x in self._raw(n.value)])
+            self.dup_nodes.pop(k, None)
+        return freed
+
     def dup_canonical(self) -> dict:
         return {k: (None if n is None else n.lock_ref) for k, n in self.dup_nodes.items()}
 

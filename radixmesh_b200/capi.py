@@ -64,6 +64,9 @@ _PROTOS = {
     "rm_read_arena": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
     "rm_read_segments": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P]),
     "rm_launch_count": (C.c_uint64, []),
+    "rm_gc_keys_h": (C.c_int, [_P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
+    "rm_gc_agree_h": (C.c_int, [_P, _P, _P, _P, C.c_int32, _P, _P]),
+    "rm_gc_exec_h": (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
     "rm_profile": (C.c_int, [_P, C.c_int]),
     "rm_profile_read": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
     "rm_profile_stages": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
@@ -235,6 +238,47 @@ class DeviceIndex:
         with self._mutex:
             self._check(fn(self._h, cap, ptr(out), C.addressof(n), self._s()))
         return out[:n.value]
+
+    # ---- duplicate-node GC between replicas (host arrays; radix_mesh.py:362-389)
+    def gc_keys(self, nodes: np.ndarray):
+        """Full keys (token lists) of tree nodes, e.g. column 0 of dup_entries(only_candidates=True)."""
+        nodes = np.ascontiguousarray(nodes, dtype=np.int32)
+        n = len(nodes)
+        if n == 0:
+            return []
+        stride = int(self.cfg.max_key_len)
+        tok = np.zeros((n, stride), dtype=np.int32)
+        lens = np.zeros(n, dtype=np.int32)
+        with self._mutex:
+            self._check(self.lib.rm_gc_keys_h(self._h, ptr(nodes), n, stride, ptr(tok), ptr(lens), self._s()))
+        return [tok[i, :lens[i]].tolist() for i in range(n)]
+
+    def _gc_pack(self, keys, ranks):
+        offs = np.zeros(len(keys) + 1, dtype=np.int64)
+        np.cumsum([len(k) for k in keys], out=offs[1:])
+        tok = np.asarray([t for k in keys for t in k], dtype=np.int32) if offs[-1] else np.zeros(1, np.int32)
+        return tok, offs, np.ascontiguousarray(ranks, dtype=np.int32)
+
+    def gc_agree(self, keys, ranks) -> np.ndarray:
+        n = len(keys)
+        out = np.zeros(max(n, 1), dtype=np.uint8)
+        if n:
+            tok, offs, rk = self._gc_pack(keys, ranks)
+            with self._mutex:
+                self._check(self.lib.rm_gc_agree_h(self._h, ptr(tok), ptr(offs), ptr(rk), n, ptr(out), self._s()))
+        return out[:n].astype(bool)
+
+    def gc_exec(self, keys, ranks, free_parked: bool):
+        """Pops the keys; returns (arena offsets, lengths) of the parked runs released (-1 / 0 where none)."""
+        n = len(keys)
+        off = np.full(max(n, 1), -1, dtype=np.int64)
+        ln = np.zeros(max(n, 1), dtype=np.int32)
+        if n:
+            tok, offs, rk = self._gc_pack(keys, ranks)
+            with self._mutex:
+                self._check(self.lib.rm_gc_exec_h(self._h, ptr(tok), ptr(offs), ptr(rk), n, 1 if free_parked else 0,
+                                                  ptr(off), ptr(ln), self._s()))
+        return off[:n], ln[:n]
 
     def route(self, tokens, offsets, B, warm, out_prefill, out_decode, out_paddr, out_daddr, out_err) -> None:
         with self._mutex:

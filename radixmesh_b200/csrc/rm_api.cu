@@ -393,6 +393,28 @@ int rm_dup_entries(rm_index* idx, int32_t cap, int32_t* out_h, int32_t* out_n_h,
   return rm_launch_dups(idx, 0, cap, out_h, out_n_h, (cudaStream_t)stream);
 }
 
+int rm_gc_keys_h(rm_index* idx, const int32_t* nodes_h, int32_t n, int32_t stride, int32_t* out_tokens_h,
+                 int32_t* out_lens_h, void* stream) {
+  if (!idx || n < 0 || stride <= 0 || (n > 0 && (!nodes_h || !out_tokens_h || !out_lens_h))) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_gc_keys(idx, nodes_h, n, stride, out_tokens_h, out_lens_h, (cudaStream_t)stream);
+}
+
+int rm_gc_agree_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offsets_h, const int32_t* ranks_h, int32_t n,
+                  uint8_t* out_agree_h, void* stream) {
+  if (!idx || n < 0 || (n > 0 && (!tokens_h || !offsets_h || !ranks_h || !out_agree_h))) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_gc_agree(idx, tokens_h, (const i64*)offsets_h, ranks_h, n, out_agree_h, (cudaStream_t)stream);
+}
+
+int rm_gc_exec_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offsets_h, const int32_t* ranks_h, int32_t n,
+                 int32_t free_parked, int64_t* out_off_h, int32_t* out_len_h, void* stream) {
+  if (!idx || n < 0 || (n > 0 && (!tokens_h || !offsets_h || !ranks_h || !out_off_h || !out_len_h))) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_gc_exec(idx, tokens_h, (const i64*)offsets_h, ranks_h, n, free_parked, (i64*)out_off_h, out_len_h,
+                           (cudaStream_t)stream);
+}
+
 int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream) {
   if (!idx || !out_h) return RM_E_INVALID;
   RM_CUDA(cudaSetDevice(idx->cfg.device));

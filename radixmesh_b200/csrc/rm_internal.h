@@ -93,3 +93,9 @@ int rm_launch_lock_g(rm_index* idx, const int* nodes, const int* gens, int B, in
 int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
                     int* out_n_h, cudaStream_t s);
 int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int* out_n_h, cudaStream_t s);
+int rm_launch_gc_agree(rm_index* idx, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n,
+                       unsigned char* out_agree_h, cudaStream_t s);
+int rm_launch_gc_exec(rm_index* idx, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n, int free_parked,
+                      i64* out_off_h, int* out_len_h, cudaStream_t s);
+int rm_launch_gc_keys(rm_index* idx, const int* nodes_h, int n, int stride, int* out_tokens_h, int* out_lens_h,
+                      cudaStream_t s);

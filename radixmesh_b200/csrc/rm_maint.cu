@@ -4,6 +4,8 @@
 //   K5      inc_lock_ref / dec_lock_ref          radix_cache.py:204-230, radix_mesh.py:168-179
 //   K6      evict + _collect_leaves + _delete_leaf   radix_cache.py:179-202, 366-377, 347-352
 //   K7      RadixMesh._gc candidate scan         radix_mesh.py:151-156
+#include <vector>
+
 #include "rm_internal.h"
 #include "rm_sort.cuh"
 
@@ -480,7 +482,7 @@ __global__ void rm_dup_scan_kernel(RmTree t, int only_candidates, int cap, int* 
   unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i > t.dup_mask) return;
   u64 k = t.dup_key[i];
-  if (k == RM_EMPTY_KEY) return;
+  if (k == RM_EMPTY_KEY || k == RM_TOMB_KEY) return;   // tombstone: an entry rm_gc_exec_h removed
   int parked = t.dup_parked[i];
   int lk = parked >= 0 ? t.lock_ref[parked] : 0;
   if (only_candidates && !(parked >= 0 && lk == 0)) return;   // radix_mesh.py:152-156
@@ -510,6 +512,203 @@ int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int*
     RM_CUDA(cudaStreamSynchronize(s));
   }
   *out_n_h = n;
+  return RM_OK;
+}
+
+// ------------------------------------------------------------------ duplicate-node GC: agree / execute
+// RadixMesh._gc_handle (radix_mesh.py:362-389).  A key travels between replicas as (full key tokens, rank); on a
+// replica it is located read-only (the walk kernel, no stamps, no split requests) and stands for (tree node id, rank)
+// in the duplicate table.
+__device__ int rm_dup_find(const RmTree& t, int node, int rank) {
+  const u64 key = ((u64)(unsigned)node << 32) | (unsigned)(rank + 1);
+  unsigned i = (rm_hash2((unsigned)(key >> 32), (unsigned)key, 0) >> 7) & t.dup_mask;
+  for (unsigned probes = 0; probes <= t.dup_mask; ++probes) {
+    const u64 cur = *reinterpret_cast<volatile u64*>(&t.dup_key[i]);
+    if (cur == key) return (int)i;
+    if (cur == RM_EMPTY_KEY) return -1;
+    i = (i + 1) & t.dup_mask;
+  }
+  return -1;
+}
+
+// the node whose full key IS the query (matched to its end, at a node boundary), else -1
+__global__ void rm_gc_locate_kernel(RmTree t, const i64* __restrict__ off, int n, const int* __restrict__ wlen,
+                                    const int* __restrict__ wnode, int* __restrict__ out_node) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int L = (int)(off[i + 1] - off[i]);
+  const int node = wnode[i];
+  out_node[i] = (L > 0 && wlen[i] == L && node > 0 && t.depth_end[node] == L) ? node : -1;
+}
+
+// radix_mesh.py:386-387: key in dup_nodes and (entry is None or entry.lock_ref == 0)
+__global__ void rm_gc_agree_kernel(RmTree t, const int* __restrict__ nodes, const int* __restrict__ ranks, int n,
+                                   unsigned char* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  unsigned char a = 0;
+  if (nodes[i] > 0) {
+    const int sl = rm_dup_find(t, nodes[i], ranks[i]);
+    if (sl >= 0) {
+      const int parked = t.dup_parked[sl];
+      a = (parked < 0 || t.lock_ref[parked] == 0) ? 1 : 0;
+    }
+  }
+  out[i] = a;
+}
+
+// GC_EXEC: dup_nodes.pop(k, None) (radix_mesh.py:363-366).  On the replica that asked (free_parked), the parked
+// node's run is handed back (the caller frees its KV indices, :375-377) and the node is released.  One thread:
+// a GC round is a handful of keys, and keys of one tree node share its chain of parked nodes.
+__global__ void rm_gc_exec_kernel(RmTree t, const int* __restrict__ nodes, const int* __restrict__ ranks, int n,
+                                  int free_parked, i64* __restrict__ out_off, int* __restrict__ out_len) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  for (int i = 0; i < n; ++i) {
+    out_off[i] = -1;
+    out_len[i] = 0;
+    if (nodes[i] <= 0) continue;
+    const int sl = rm_dup_find(t, nodes[i], ranks[i]);
+    if (sl < 0) continue;
+    const int d = t.dup_parked[sl];
+    t.dup_key[sl] = RM_TOMB_KEY;
+    t.dup_parked[sl] = -1;
+    t.ctr->n_dups -= 1;
+    if (d < 0 || !free_parked) continue;
+    const i64 off = t.edge_off[d];
+    const int len = t.edge_len[d];
+    out_off[i] = off;
+    out_len[i] = len;
+    // unlink d from the chain of parked predecessors of its tree node
+    for (int x = nodes[i], guard = 0; x >= 0 && guard < t.max_nodes; ++guard) {
+      const int nx = t.parked[x];
+      if (nx == d) {
+        t.parked[x] = t.parked[d];
+        break;
+      }
+      x = nx;
+    }
+    for (int k = 0; k < len; ++k)
+      if ((t.seg[off + k] & 0x3FFFFFFF) == d) t.seg[off + k] = -1;
+    t.parked[d] = -1;
+    t.parent[d] = -1;
+    t.edge_len[d] = 0;
+    t.gen[d] = 0;
+    const u64 pos = atomicAdd(&t.ctr->free_tail, 1ull);
+    t.free_ids[pos % (u64)t.max_nodes] = d;
+  }
+}
+
+// full key of tree nodes, one row of `stride` tokens per node
+__global__ void rm_node_key_kernel(RmTree t, const int* __restrict__ nodes, int n, int stride, int* __restrict__ out_tok,
+                                   int* __restrict__ out_len) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int v = nodes[i];
+  const int L = (v > 0 && t.parent[v] >= 0) ? t.depth_end[v] : 0;
+  out_len[i] = L;
+  if (L > stride) return;
+  int* __restrict__ row = out_tok + (size_t)i * stride;
+  while (v > 0) {
+    const int e = t.edge_len[v];
+    const i64 off = t.edge_off[v];
+    const int at = t.depth_end[v] - e;
+    for (int k = 0; k < e; ++k) row[at + k] = t.tok[off + k];
+    v = t.parent[v];
+  }
+}
+
+int rm_launch_walk_readonly(rm_index* idx, const int* tokens, const i64* offsets, int N, int* out_len, int* out_node,
+                            cudaStream_t s);
+
+struct RmTmp {          // device scratch of a control-plane call (GC rounds are rare: plain cudaMalloc / cudaFree)
+  void* p[8];
+  int n = 0;
+  template <class T>
+  cudaError_t get(T** out, size_t count) {
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(out), sizeof(T) * (count ? count : 1));
+    if (e == cudaSuccess) p[n++] = *out;
+    return e;
+  }
+  ~RmTmp() {
+    for (int i = 0; i < n; ++i) cudaFree(p[i]);
+  }
+};
+
+// tokens/offsets/ranks on the host -> device copies + located node ids
+static int rm_gc_stage(rm_index* idx, RmTmp& tmp, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n,
+                       int** d_nodes, int** d_ranks, cudaStream_t s) {
+  const i64 total = offsets_h[n] - offsets_h[0];
+  int *d_tok, *d_len;
+  i64* d_off;
+  RM_CUDA(tmp.get(&d_tok, (size_t)total));
+  RM_CUDA(tmp.get(&d_off, (size_t)n + 1));
+  RM_CUDA(tmp.get(&d_len, (size_t)n));
+  RM_CUDA(tmp.get(d_nodes, (size_t)n));
+  RM_CUDA(tmp.get(d_ranks, (size_t)n));
+  int* d_wnode;
+  RM_CUDA(tmp.get(&d_wnode, (size_t)n));
+  RM_CUDA(cudaMemcpyAsync(d_tok, tokens_h + offsets_h[0], sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, s));
+  std::vector<i64> rel((size_t)n + 1);
+  for (int i = 0; i <= n; ++i) rel[i] = offsets_h[i] - offsets_h[0];
+  RM_CUDA(cudaMemcpyAsync(d_off, rel.data(), sizeof(i64) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
+  RM_CUDA(cudaMemcpyAsync(*d_ranks, ranks_h, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
+  RM_CUDA(cudaStreamSynchronize(s));     // rel[] goes out of scope
+  int rc = rm_launch_walk_readonly(idx, d_tok, d_off, n, d_len, d_wnode, s);
+  if (rc) return rc;
+  RM_LAUNCH(rm_gc_locate_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, idx->t, d_off, n, d_len, d_wnode, *d_nodes);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
+int rm_launch_gc_agree(rm_index* idx, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n,
+                       unsigned char* out_agree_h, cudaStream_t s) {
+  if (n <= 0) return RM_OK;
+  RmTmp tmp;
+  int *d_nodes, *d_ranks;
+  int rc = rm_gc_stage(idx, tmp, tokens_h, offsets_h, ranks_h, n, &d_nodes, &d_ranks, s);
+  if (rc) return rc;
+  unsigned char* d_out;
+  RM_CUDA(tmp.get(&d_out, (size_t)n));
+  RM_LAUNCH(rm_gc_agree_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, idx->t, d_nodes, d_ranks, n, d_out);
+  RM_CUDA(cudaGetLastError());
+  RM_CUDA(cudaMemcpyAsync(out_agree_h, d_out, (size_t)n, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
+int rm_launch_gc_exec(rm_index* idx, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n, int free_parked,
+                      i64* out_off_h, int* out_len_h, cudaStream_t s) {
+  if (n <= 0) return RM_OK;
+  RmTmp tmp;
+  int *d_nodes, *d_ranks;
+  int rc = rm_gc_stage(idx, tmp, tokens_h, offsets_h, ranks_h, n, &d_nodes, &d_ranks, s);
+  if (rc) return rc;
+  i64* d_off;
+  int* d_len;
+  RM_CUDA(tmp.get(&d_off, (size_t)n));
+  RM_CUDA(tmp.get(&d_len, (size_t)n));
+  RM_LAUNCH(rm_gc_exec_kernel, 1, 1, s, idx->t, d_nodes, d_ranks, n, free_parked, d_off, d_len);
+  RM_CUDA(cudaGetLastError());
+  RM_CUDA(cudaMemcpyAsync(out_off_h, d_off, sizeof(i64) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaMemcpyAsync(out_len_h, d_len, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
+int rm_launch_gc_keys(rm_index* idx, const int* nodes_h, int n, int stride, int* out_tokens_h, int* out_lens_h,
+                      cudaStream_t s) {
+  if (n <= 0) return RM_OK;
+  RmTmp tmp;
+  int *d_nodes, *d_tok, *d_len;
+  RM_CUDA(tmp.get(&d_nodes, (size_t)n));
+  RM_CUDA(tmp.get(&d_tok, (size_t)n * (size_t)stride));
+  RM_CUDA(tmp.get(&d_len, (size_t)n));
+  RM_CUDA(cudaMemcpyAsync(d_nodes, nodes_h, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
+  RM_LAUNCH(rm_node_key_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, idx->t, d_nodes, n, stride, d_tok, d_len);
+  RM_CUDA(cudaGetLastError());
+  RM_CUDA(cudaMemcpyAsync(out_tokens_h, d_tok, sizeof(int) * (size_t)n * (size_t)stride, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaMemcpyAsync(out_lens_h, d_len, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
   return RM_OK;
 }
 

@@ -1264,8 +1264,8 @@ int rm_launch_router_match(rm_index* idx, const int* tokens, const i64* offsets,
 // Read-only pre-pass of the ordered insert (rm_insert.cu): walk every record of the batch against the
 // tree as it stands, stamp the nodes it matches in full, and report the deepest such node.  Same kernel
 // as the splitting match, with the split requests switched off.
-int rm_launch_walk_records(rm_index* idx, const int* tokens, const i64* offsets, int N, u64 seq_base, int* out_len,
-                           int* out_node, cudaStream_t s) {
+static int rm_launch_walk_flags(rm_index* idx, const int* tokens, const i64* offsets, int N, u64 seq_base, int* out_len,
+                                int* out_node, int walk_flags, cudaStream_t s) {
   if (N <= 0) return RM_OK;
   RmRouteOut ro = {nullptr, nullptr, nullptr};
 #ifdef RM_EMU
@@ -1281,7 +1281,18 @@ int rm_launch_walk_records(rm_index* idx, const int* tokens, const i64* offsets,
   const long long wthreads = (long long)N * 8;
 #endif
   RM_LAUNCH(k, (int)((wthreads + tpb - 1) / tpb), tpb, s, idx->t, tokens, offsets, N, seq_base, idx->len_bits, out_len,
-            out_node, idx->sc.key[0], idx->sc.val[0], ro, 4);
+            out_node, idx->sc.key[0], idx->sc.val[0], ro, walk_flags);
   RM_CUDA(cudaGetLastError());
   return RM_OK;
+}
+
+int rm_launch_walk_records(rm_index* idx, const int* tokens, const i64* offsets, int N, u64 seq_base, int* out_len,
+                           int* out_node, cudaStream_t s) {
+  return rm_launch_walk_flags(idx, tokens, offsets, N, seq_base, out_len, out_node, 4, s);
+}
+
+// the same walk with nothing written to the tree at all (no stamp, no split request): locating GC keys
+int rm_launch_walk_readonly(rm_index* idx, const int* tokens, const i64* offsets, int N, int* out_len, int* out_node,
+                            cudaStream_t s) {
+  return rm_launch_walk_flags(idx, tokens, offsets, N, 0, out_len, out_node, 4 | 1, s);
 }

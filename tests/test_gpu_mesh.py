@@ -96,3 +96,40 @@ def test_gpu_md5_awkward_inputs(scratch_mb, monkeypatch):
     assert outs[2].cpu().tolist() == exp and outs[3].cpu().tolist() == exp
     assert err.cpu().tolist() == [0] * n
     ix.close()
+
+
+def test_gpu_gc_keys_agree_exec():
+    """rm_gc_keys_h / rm_gc_agree_h / rm_gc_exec_h on the GPU: two replicas in one process (the exchange itself is
+    host code, tests/test_mesh_gc.py), against the oracle's restatement of _gc_handle (radix_mesh.py:362-389)."""
+    from oracle.radix_port import MODE_DECODE, MODE_PREFILL, PortRadixMesh
+    from radixmesh_b200 import capi
+    from tests.test_mesh_gc import _apply_device, _apply_oracle, _dup_state, _script
+    ixs, ports = [], []
+    for r in range(2):
+        ix = capi.DeviceIndex(mode=MODE_PREFILL if r == 0 else MODE_DECODE, self_rank=r, n_prefill=1, n_decode=1,
+                              max_nodes=256, max_tokens=4096, max_batch=16, max_key_len=32, max_dups=64)
+        _apply_device(ix, _script(r))
+        ixs.append(ix)
+        p = PortRadixMesh(MODE_PREFILL if r == 0 else MODE_DECODE, r, 1, 1)
+        _apply_oracle(p, _script(r))
+        ports.append(p)
+    for o in range(2):
+        cand = ixs[o].dup_entries(only_candidates=True)
+        keys = ixs[o].gc_keys(cand[:, 0])
+        q = sorted(zip(map(tuple, keys), cand[:, 1].tolist()))
+        assert q == sorted(ports[o].gc_candidates())
+        peer = 1 - o
+        agree = ixs[peer].gc_agree([list(k) for k, _ in q], [r for _, r in q]).tolist()
+        assert agree == [ports[peer].gc_agrees(k) for k in q]
+        assert ixs[peer].gc_agree([[9, 9, 9], [1, 2]], [0, 1]).tolist() == [False, False]   # unknown key, inner prefix
+        ok = [k for k, a in zip(q, agree) if a]
+        off, ln = ixs[o].gc_exec([list(k) for k, _ in ok], [r for _, r in ok], free_parked=True)
+        freed = sorted(ixs[o].read_arena(int(a), int(n))[1].tolist() for a, n in zip(off, ln) if a >= 0)
+        assert freed == sorted(ports[o].gc_exec(ok, origin=True))
+        ixs[peer].gc_exec([list(k) for k, _ in ok], [r for _, r in ok], free_parked=False)
+        ports[peer].gc_exec(ok, origin=False)
+        for r in range(2):
+            assert _dup_state(ixs[r]) == sorted((k, rk, v) for (k, rk), v in ports[r].dup_canonical().items())
+            ixs[r].check_device_error()
+    for ix in ixs:
+        ix.close()
