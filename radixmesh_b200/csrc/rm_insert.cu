@@ -55,23 +55,43 @@ __global__ void rm_insert_keys2_kernel(RmTree t, const int* __restrict__ tok, co
 // Record a duplicate-node entry: dup_nodes[(full_key(node), rank)] = parked (radix_mesh.py:310, 476, 493).
 // The tree node id stands for its full key (stable under splits: the lower half keeps the id).
 __device__ __forceinline__ void rm_dup_put(const RmTree& t, int node, int rank, int parked) {
-  u64 key = ((u64)(unsigned)node << 32) | (unsigned)(rank + 1);
-  unsigned i = (rm_hash2((unsigned)(key >> 32), (unsigned)key, 0) >> 7) & t.dup_mask;
-  for (unsigned probes = 0; probes <= t.dup_mask; ++probes) {
-    u64 cur = *reinterpret_cast<volatile u64*>(&t.dup_key[i]);
-    if (cur == key) {
-      t.dup_parked[i] = parked;  // dict assignment overwrites
-      return;
-    }
-    if (cur == RM_EMPTY_KEY) {
-      u64 old = atomicCAS(&t.dup_key[i], RM_EMPTY_KEY, key);
-      if (old == RM_EMPTY_KEY || old == key) {
-        t.dup_parked[i] = parked;
-        if (old == RM_EMPTY_KEY) atomicAdd(&t.ctr->n_dups, 1);
+  const u64 key = ((u64)(unsigned)node << 32) | (unsigned)(rank + 1);
+  const unsigned home = (rm_hash2((unsigned)(key >> 32), (unsigned)key, 0) >> 7) & t.dup_mask;
+  for (int attempt = 0; attempt < 64; ++attempt) {
+    unsigned i = home;
+    int tomb = -1;                 // first slot an rm_gc_exec_h removal left behind: reused before a fresh one
+    bool retry = false;
+    for (unsigned probes = 0; probes <= t.dup_mask; ++probes) {
+      const u64 cur = *reinterpret_cast<volatile u64*>(&t.dup_key[i]);
+      if (cur == key) {
+        t.dup_parked[i] = parked;  // dict assignment overwrites
         return;
       }
+      if (cur == RM_TOMB_KEY && tomb < 0) tomb = (int)i;
+      if (cur == RM_EMPTY_KEY) {
+        const unsigned at = tomb >= 0 ? (unsigned)tomb : i;
+        const u64 expect = tomb >= 0 ? RM_TOMB_KEY : RM_EMPTY_KEY;
+        const u64 old = atomicCAS(&t.dup_key[at], expect, key);
+        if (old == expect || old == key) {
+          t.dup_parked[at] = parked;
+          if (old == expect) atomicAdd(&t.ctr->n_dups, 1);
+          return;
+        }
+        retry = true;              // somebody else took the slot: look again from the start (it may hold this key)
+        break;
+      }
+      i = (i + 1) & t.dup_mask;
     }
-    i = (i + 1) & t.dup_mask;
+    if (!retry && tomb >= 0) {     // no empty slot anywhere, but a removed one
+      const u64 old = atomicCAS(&t.dup_key[tomb], RM_TOMB_KEY, key);
+      if (old == RM_TOMB_KEY || old == key) {
+        t.dup_parked[tomb] = parked;
+        if (old == RM_TOMB_KEY) atomicAdd(&t.ctr->n_dups, 1);
+        return;
+      }
+      retry = true;
+    }
+    if (!retry) break;             // the table is full
   }
   atomicMax(&t.ctr->err, (int)RM_E_NOSPACE);
 }
