@@ -127,3 +127,29 @@ def test_two_replica_gc_round_matches_oracle():
         assert freed == exp_freed[r] and len(freed) == 2
         assert after == exp_after[r], f"replica {r}: duplicate table after the round"
         assert again == ([], []) and n_dups == len(exp_after[r])
+
+
+def test_single_replica_round_and_slot_reuse():
+    """World of one: every candidate is agreed and freed; the duplicate-table slots the round vacated are used again
+    by later conflicts (same keys), and the table still equals the oracle's dup_nodes."""
+    from radixmesh_b200.mesh_gc import GcRound
+    from tests.emu.emu_backend import make_index
+    ix = make_index(mode=MODE_DECODE, self_rank=1, n_prefill=1, n_decode=1, max_nodes=256, max_tokens=4096, max_batch=16,
+                    max_key_len=32, max_dups=8)
+    port = PortRadixMesh(MODE_DECODE, 1, 1, 1)
+    ops = [op for op in _script(0) if op[0] != "unlock"] + [("unlock", i) for i in range(len(KEYS))]
+    _apply_device(ix, ops)
+    _apply_oracle(port, ops)
+    removed, freed = GcRound(ix, 0, 1).run()
+    cand = sorted(port.gc_candidates())
+    assert removed == cand and len(cand) == len(KEYS)
+    assert sorted(freed) == sorted(port.gc_exec(cand, origin=True))
+    assert _dup_state(ix) == sorted((k, r, v) for (k, r), v in port.dup_canonical().items())
+    assert int(ix.sizes().n_dups) == len(port.dup_nodes)
+    for rnd in range(3):                                # rank 1 loses against rank 0's values again and again
+        more = [("ins", 1, k, [7000 + 100 * rnd + 10 * i + j for j in range(len(k))]) for i, k in enumerate(KEYS)]
+        _apply_device(ix, more)
+        _apply_oracle(port, more)
+        assert _dup_state(ix) == sorted((k, r, v) for (k, r), v in port.dup_canonical().items())
+        assert int(ix.sizes().n_dups) == len(port.dup_nodes)
+    ix.check_device_error()
