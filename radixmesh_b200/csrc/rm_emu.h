@@ -73,6 +73,10 @@ struct int4 { int x, y, z, w; };
 struct uint2 { unsigned x, y; };
 struct uint4 { unsigned x, y, z, w; };
 
+#define RM_LAUNCH_PDL RM_LAUNCH
+static inline void rm_grid_dependency_wait() {}
+static inline void rm_grid_dependency_trigger() {}
+
 // Sequential launcher: one emulated thread per GROUP (RM_G == 1), block by block.
 #define RM_LAUNCH(kernel, grid, block, stream, ...)                                  \
   do {                                                                               \

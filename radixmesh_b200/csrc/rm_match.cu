@@ -593,6 +593,7 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
                      int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
                      unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
   RmGroup<G> g;
+  rm_grid_dependency_trigger();        // the split kernels that follow may be scheduled now; they wait for this grid
   const int q = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
   if (q >= B) return;
   const i64 o0 = qoff[q];
@@ -778,6 +779,7 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
                       u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
                       int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min) {
   RmGroup<G> g;
+  rm_grid_dependency_wait();               // launched while the sort may still be running (RM_LAUNCH_PDL)
   const int B = min(t.ctr->n_big, Bmax);   // requests on shared edges only (rm_split_single_kernel did the rest)
   const u64 pmask = (1ull << len_bits) - 1ull;
   // one group of lanes per edge, found as the first entry of its run in the sorted list; grid-stride, the
@@ -939,6 +941,8 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
 __global__ void __launch_bounds__(RM_MATCH_TPB)
 rm_split_single_kernel(RmTree t, const u64* __restrict__ rkey, const unsigned* __restrict__ rval, int Bmax, int len_bits,
                        u64 seq_base, int* __restrict__ out_node, u64* __restrict__ mkey, unsigned* __restrict__ mval) {
+  rm_grid_dependency_trigger();
+  rm_grid_dependency_wait();               // launched while the walk kernel may still be running (RM_LAUNCH_PDL)
   const int B = min(t.ctr->n_req, Bmax);
   const int i = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
   // owner-map fill of the new upper node, done by the whole warp after the per-thread part (a thread writing
@@ -1204,7 +1208,7 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   // requests that are alone on their edge are applied straight from K1's list; the rest (requests on
   // shared edges) are sorted by (node, split point) and applied a warp per edge.  All counts stay on the device.
   RmScratch& sc = idx->sc;
-  RM_LAUNCH(rm_split_single_kernel, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B,
+  RM_LAUNCH_PDL(rm_split_single_kernel, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B,
             idx->len_bits, seq_base, out_node, sc.key[1], sc.val[1]);
 #ifndef RM_EMU
   if (prof && idx->prof_on > 1) cudaEventRecord(pev[2], s);
@@ -1221,7 +1225,7 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   if (grid > 148 * 8) grid = 148 * 8;    // persistent: 8 blocks of 8 warps per SM, grid-stride inside
 #endif
   auto k3 = rm_split_apply_kernel<RM_WIDE_G>;
-  RM_LAUNCH(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
+  RM_LAUNCH_PDL(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
             sc.krank, sc.uniq_pos, sc.uniq_min);
 #ifndef RM_EMU
   if (prof) {

@@ -184,6 +184,8 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_fused_kernel(u64* 
                                                                    const int* n_dev, int passes, unsigned* hist, int tile) {
   __shared__ unsigned wcnt[RM_SORT_WARPS][256];
   __shared__ unsigned wtot[RM_SORT_WARPS];
+  rm_grid_dependency_trigger();
+  rm_grid_dependency_wait();     // RM_LAUNCH_PDL: the producer of the items may still be running
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   if (n <= 0) return;
   const bool solo = n <= RM_SORT_SOLO;
@@ -312,7 +314,7 @@ static inline int rm_sort_pairs(u64* k0, unsigned* v0, u64* k1, unsigned* v1, in
   int tile = rm_sort_tile(n);
   int nb = (n + tile - 1) / tile;
   if (nb <= RM_SORT_FUSED_TILES) {   // one launch, all blocks resident
-    RM_LAUNCH(rm_sort_fused_kernel, nb, RM_SORT_TPB, s, k0, v0, k1, v1, n, n_dev, passes, hist, tile);
+    RM_LAUNCH_PDL(rm_sort_fused_kernel, nb, RM_SORT_TPB, s, k0, v0, k1, v1, n, n_dev, passes, hist, tile);
     return passes & 1;
   }
   hist += RM_SORT_TABLE_OFF;
