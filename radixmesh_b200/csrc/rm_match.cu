@@ -773,14 +773,24 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
 
 // K3: one group per edge that received split requests.  `skey` is sorted by (node, split point) and,
 // inside equal keys, by query index (the sort is stable), `sval` holds the query index.
+// (a device function: the stand-alone kernel and the one-launch form rm_split_fused_kernel share it.  The sorted
+// list may have been written earlier in the SAME launch, by other blocks: it is read with ld.cg.)
 template <int G>
-__global__ void __launch_bounds__(RM_MATCH_TPB)
-rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int Bmax, int len_bits,
-                      u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
-                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min) {
+__device__ __forceinline__ void rm_split_apply_body(const RmTree& t, const u64* skey_, const unsigned* sval_, int Bmax, int len_bits,
+                                                    u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax,
+                                                    int* __restrict__ krank, int* __restrict__ uniq_pos,
+                                                    unsigned* __restrict__ uniq_min) {
   RmGroup<G> g;
-  rm_grid_dependency_wait();               // launched while the sort may still be running (RM_LAUNCH_PDL)
-  const int B = min(t.ctr->n_big, Bmax);   // requests on shared edges only (rm_split_single_kernel did the rest)
+  struct CgU64 {
+    const u64* p;
+    __device__ __forceinline__ u64 operator[](int i) const { return __ldcg(p + i); }
+  } skey = {skey_};
+  struct CgU32 {
+    const unsigned* p;
+    __device__ __forceinline__ unsigned operator[](int i) const { return __ldcg(p + i); }
+  } sval = {sval_};
+  const int nbig_now = *(volatile int*)&t.ctr->n_big;
+  const int B = min(nbig_now, Bmax);   // requests on shared edges only (the single-request ones are done)
   const u64 pmask = (1ull << len_bits) - 1ull;
   // one group of lanes per edge, found as the first entry of its run in the sorted list; grid-stride, the
   // count lives on the device
@@ -932,19 +942,25 @@ rm_split_apply_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __
   }
 }
 
+template <int G>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_split_apply_kernel(RmTree t, const u64* skey, const unsigned* sval, int Bmax, int len_bits, u64 seq_base,
+                      int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
+                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min) {
+  rm_grid_dependency_wait();               // launched while the sort may still be running (RM_LAUNCH_PDL)
+  rm_split_apply_body<G>(t, skey, sval, Bmax, len_bits, seq_base, out_node, sufmax, krank, uniq_pos, uniq_min);
+}
+
 // K3, common case: an edge that received exactly ONE split request this batch (in steady state almost
 // all of them: ~10K single requests per 64K-query batch against a few hundred shared ones).  One thread per
 // request of K1's compact, unsorted list, so 32 independent splits share every memory round trip of a
 // warp and nothing has to be sorted for them: a request is alone on its node iff it is the head of the
 // node's request chain and has no predecessor.  Requests on shared edges are copied to a second list,
 // which alone goes through the radix sort and rm_split_apply_kernel (a warp per edge).
-__global__ void __launch_bounds__(RM_MATCH_TPB)
-rm_split_single_kernel(RmTree t, const u64* __restrict__ rkey, const unsigned* __restrict__ rval, int Bmax, int len_bits,
-                       u64 seq_base, int* __restrict__ out_node, u64* __restrict__ mkey, unsigned* __restrict__ mval) {
-  rm_grid_dependency_trigger();
-  rm_grid_dependency_wait();               // launched while the walk kernel may still be running (RM_LAUNCH_PDL)
-  const int B = min(t.ctr->n_req, Bmax);
-  const int i = (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x);
+// (device function, one call per request index i < B; every thread of a warp must make the call, also for i >= B)
+__device__ __forceinline__ void rm_split_single_body(const RmTree& t, const u64* rkey, const unsigned* rval, int B, int i,
+                                                     int len_bits, u64 seq_base, int* __restrict__ out_node, u64* mkey,
+                                                     unsigned* mval) {
   // owner-map fill of the new upper node, done by the whole warp after the per-thread part (a thread writing
   // its own p-1 words one after another made this kernel 57 us on 4096-token keys)
   i64 fill_off = 0;
@@ -1032,6 +1048,66 @@ rm_split_single_kernel(RmTree t, const u64* __restrict__ rkey, const unsigned* _
   }
 #endif
 }
+
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_split_single_kernel(RmTree t, const u64* rkey, const unsigned* rval, int Bmax, int len_bits, u64 seq_base,
+                       int* __restrict__ out_node, u64* mkey, unsigned* mval) {
+  rm_grid_dependency_trigger();
+  rm_grid_dependency_wait();               // launched while the walk kernel may still be running (RM_LAUNCH_PDL)
+  const int B = min(t.ctr->n_req, Bmax);
+  rm_split_single_body(t, rkey, rval, B, (int)(blockIdx.x * (unsigned)blockDim.x + threadIdx.x), len_bits, seq_base, out_node,
+                       mkey, mval);
+}
+
+#ifndef RM_EMU
+// K3 in ONE launch: single-request splits, grid barrier, sort of the requests on shared edges, grid barrier,
+// shared-edge splits.  Three dependent launches of ~10 us each (most of it launch and drain latency: each stage is
+// a few microseconds of work on a few thousand requests) become one launch with two barriers of ~2 us.  The grid
+// is sized to be resident as a whole (the barrier is a counter the blocks wait on, rm_sort.cuh).
+// Measured (C2): 0.105 ms per step against 0.101-0.104 for the three launches with programmatic dependent launch:
+// what a stage costs is its own chain of dependent memory round trips, not the launch.  Kept behind RM_FUSED_SPLIT=1.
+static_assert(RM_MATCH_TPB == RM_SORT_TPB, "rm_sort_body is written for blocks of RM_SORT_TPB threads");
+template <int G>
+__global__ void __launch_bounds__(RM_MATCH_TPB)
+rm_split_fused_kernel(RmTree t, u64* rkey, unsigned* rval, u64* mkey, unsigned* mval, int Bmax, int len_bits, int passes,
+                      u64 seq_base, int* __restrict__ out_node, u64* __restrict__ sufmax, int* __restrict__ krank,
+                      int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min, unsigned* hist, int tile) {
+  rm_grid_dependency_wait();               // launched while the walk kernel may still be running (RM_LAUNCH_PDL)
+  unsigned arrivals = 0;
+  const int n_req = min(t.ctr->n_req, Bmax);
+  const int gthreads = (int)(gridDim.x * blockDim.x);
+  for (int base = (int)(blockIdx.x * blockDim.x); base < n_req; base += gthreads)
+    rm_split_single_body(t, rkey, rval, n_req, base + (int)threadIdx.x, len_bits, seq_base, out_node, mkey, mval);
+  arrivals += gridDim.x;
+  rm_sort_grid_barrier(hist, arrivals);
+  const int nbig_now = *(volatile int*)&t.ctr->n_big;
+  const int nbig = min(nbig_now, Bmax);
+  if (nbig > 0) rm_sort_body(mkey, mval, rkey, rval, nbig, passes, hist, tile, (int)blockIdx.x, (int)gridDim.x, arrivals);
+  arrivals += gridDim.x;
+  rm_sort_grid_barrier(hist, arrivals);
+  const bool in_r = (passes & 1) != 0;     // where rm_sort_body left the result
+  rm_split_apply_body<G>(t, in_r ? rkey : mkey, in_r ? rval : mval, Bmax, len_bits, seq_base, out_node, sufmax, krank,
+                         uniq_pos, uniq_min);
+  rm_sort_barrier_rearm(hist, (int)gridDim.x);
+}
+
+// blocks of rm_split_fused_kernel that are resident together on this device (0: do not use it)
+static int rm_split_fused_grid() {
+  static int grid = -1;
+  if (grid < 0) {
+    const char* e = getenv("RM_FUSED_SPLIT");
+    int per_sm = 0, dev = 0, sms = 0;
+    auto k = rm_split_fused_kernel<32>;
+    if (!(e && e[0] == '1') || cudaGetDevice(&dev) != cudaSuccess ||   // opt-in: measured no faster than the three PDL launches
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, RM_MATCH_TPB, 0) != cudaSuccess)
+      grid = 0;
+    else
+      grid = sms * (per_sm > 2 ? 2 : per_sm);
+  }
+  return grid;
+}
+#endif
 
 // K2: values along the matched path, written back to front by walking parent links from the last
 // node; depth_end gives each node's place in the output without a prefix sum.
@@ -1208,12 +1284,33 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   // requests that are alone on their edge are applied straight from K1's list; the rest (requests on
   // shared edges) are sorted by (node, split point) and applied a warp per edge.  All counts stay on the device.
   RmScratch& sc = idx->sc;
+  const int bits = idx->node_bits + idx->len_bits;
+#ifndef RM_EMU
+  {
+    const int fgrid = rm_split_fused_grid();
+    const int tile = rm_sort_tile(B);
+    if (B > 1 && fgrid > 0 && (B + tile - 1) / tile <= min(fgrid, RM_SORT_FUSED_TILES)) {
+      auto kf = rm_split_fused_kernel<RM_WIDE_G>;
+      RM_LAUNCH_PDL(kf, fgrid, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], sc.key[1], sc.val[1], B, idx->len_bits, (bits + 7) / 8,
+                    seq_base, out_node, sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.hist, tile);
+      if (prof) {
+        if (idx->prof_on > 1) {
+          cudaEventRecord(pev[2], s);
+          cudaEventRecord(pev[3], s);
+          cudaEventRecord(pev[4], s);
+        }
+        ++idx->prof_n;
+      }
+      RM_CUDA(cudaGetLastError());
+      return RM_OK;
+    }
+  }
+#endif
   RM_LAUNCH_PDL(rm_split_single_kernel, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B,
-            idx->len_bits, seq_base, out_node, sc.key[1], sc.val[1]);
+                idx->len_bits, seq_base, out_node, sc.key[1], sc.val[1]);
 #ifndef RM_EMU
   if (prof && idx->prof_on > 1) cudaEventRecord(pev[2], s);
 #endif
-  const int bits = idx->node_bits + idx->len_bits;
   const int w = 1 ^ rm_sort_pairs(sc.key[1], sc.val[1], sc.key[0], sc.val[0], B, bits, sc.hist, s, &idx->t.ctr->n_big);
   RM_CUDA(cudaGetLastError());
 #ifndef RM_EMU
@@ -1226,7 +1323,7 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
 #endif
   auto k3 = rm_split_apply_kernel<RM_WIDE_G>;
   RM_LAUNCH_PDL(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base, out_node, sc.sufmax,
-            sc.krank, sc.uniq_pos, sc.uniq_min);
+                sc.krank, sc.uniq_pos, sc.uniq_min);
 #ifndef RM_EMU
   if (prof) {
     if (idx->prof_on > 1) cudaEventRecord(pev[4], s);

@@ -180,24 +180,23 @@ static __device__ __forceinline__ void rm_sort_grid_barrier(unsigned* bar, unsig
   }
   __syncthreads();
 }
-static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_fused_kernel(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n_max,
-                                                                   const int* n_dev, int passes, unsigned* hist, int tile) {
+// The sort proper, run by the blocks `bid` = 0..nblk-1 of RM_SORT_TPB threads of ONE launch (all resident).  With
+// n <= RM_SORT_SOLO only bid 0 works and no barrier is used.  `arrivals` is the caller's running count of barrier
+// arrivals on hist[0] (a kernel that has other phases around the sort shares the barrier with it).
+static __device__ __forceinline__ void rm_sort_body(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n, int passes,
+                                                    unsigned* hist, int tile, const int bid, const int nblk,
+                                                    unsigned& arrivals) {
   __shared__ unsigned wcnt[RM_SORT_WARPS][256];
   __shared__ unsigned wtot[RM_SORT_WARPS];
-  rm_grid_dependency_trigger();
-  rm_grid_dependency_wait();     // RM_LAUNCH_PDL: the producer of the items may still be running
-  const int n = n_dev ? min(*n_dev, n_max) : n_max;
-  if (n <= 0) return;
   const bool solo = n <= RM_SORT_SOLO;
-  if (solo && blockIdx.x != 0) return;
+  if (solo && bid != 0) return;
   unsigned* ghist = hist + RM_SORT_TABLE_OFF;
-  unsigned arrivals = 0;
   const int my_tile = solo ? (n + 255) / 256 * 256 : tile;
   const int nb = solo ? 1 : (n + tile - 1) / tile;
-  const bool active = (int)blockIdx.x < nb;
+  const bool active = bid < nb;
   const int per_warp = my_tile / RM_SORT_WARPS;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int wbase = blockIdx.x * my_tile + wid * per_warp;
+  const int wbase = bid * my_tile + wid * per_warp;
   const unsigned lt = (1u << lane) - 1u;
   for (int p = 0; p < passes; ++p) {
     const int shift = 8 * p;
@@ -236,15 +235,15 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_fused_kernel(u64* 
 #pragma unroll
     for (int w = 0; w < RM_SORT_WARPS; ++w) total += wcnt[w][d];
     if (!solo) {
-      if (active) ghist[blockIdx.x * 256 + d] = total;
-      arrivals += gridDim.x;
+      if (active) ghist[bid * 256 + d] = total;
+      arrivals += (unsigned)nblk;
       rm_sort_grid_barrier(hist, arrivals);
       total = 0;
 #pragma unroll 16
       for (int j = 0; j < nb; ++j) {
         unsigned x = __ldcg(ghist + j * 256 + d);
         total += x;
-        if (j < (int)blockIdx.x) before += x;
+        if (j < bid) before += x;
       }
     }
     // exclusive scan of the digit totals over the 256 threads
@@ -289,19 +288,34 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_fused_kernel(u64* 
       if (solo) {
         __syncthreads();
       } else {
-        arrivals += gridDim.x;
+        arrivals += (unsigned)nblk;
         rm_sort_grid_barrier(hist, arrivals);
       }
     }
   }
-  if (!solo && threadIdx.x == 0) {   // the last block out re-arms the barrier for the next launch
+}
+
+// the last block out of a launch that used the barrier puts hist[0] and hist[1] back to zero
+static __device__ __forceinline__ void rm_sort_barrier_rearm(unsigned* hist, int nblk) {
+  if (threadIdx.x == 0) {
     __threadfence();
-    if (atomicAdd(hist + 1, 1u) == gridDim.x - 1) {
+    if (atomicAdd(hist + 1, 1u) == (unsigned)nblk - 1) {
       hist[0] = 0;
       hist[1] = 0;
       __threadfence();
     }
   }
+}
+
+static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_fused_kernel(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n_max,
+                                                                   const int* n_dev, int passes, unsigned* hist, int tile) {
+  rm_grid_dependency_trigger();
+  rm_grid_dependency_wait();     // RM_LAUNCH_PDL: the producer of the items may still be running
+  const int n = n_dev ? min(*n_dev, n_max) : n_max;
+  if (n <= 0) return;
+  unsigned arrivals = 0;
+  rm_sort_body(k0, v0, k1, v1, n, passes, hist, tile, (int)blockIdx.x, (int)gridDim.x, arrivals);
+  if (n > RM_SORT_SOLO) rm_sort_barrier_rearm(hist, (int)gridDim.x);
 }
 
 // Sorts n pairs by the low `bits` bits of the key.  Returns 0 if the result is in (k0, v0), 1 if in

@@ -47,6 +47,17 @@ def test_gpu_zipf_match_all_walk_kernels(walk, group):
                    cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
+def test_gpu_zipf_match_one_launch_split_stage():
+    """The same check with the three split-stage kernels fused into one launch with grid barriers (RM_FUSED_SPLIT=1)."""
+    import os
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, '.'); from tests.test_gpu_base import zipf_check; "
+            "zipf_check(seed=7, n_docs=64, L=96, n_ins=600, n_q=3000)")
+    subprocess.run([sys.executable, "-c", code], check=True, env=dict(os.environ, RM_FUSED_SPLIT="1"),
+                   cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
 def test_gpu_zipf_match_without_dependent_launch():
     """The same check with programmatic dependent launch turned off (RM_PDL=0): the split-stage kernels then start
     only after their predecessor has finished, as plain stream order gives."""
