@@ -969,8 +969,19 @@ __device__ __forceinline__ void rm_split_single_body(const RmTree& t, const u64*
     const u64 ki = rkey[i];
     const int c = (int)(ki >> len_bits);
     const unsigned q = rval[i];
-    const bool is_head = t.req_head[c] == (int)q;
-    const bool alone = is_head && t.req_link[q] < 0;
+    // everything that depends only on (c, q) is loaded at once, before any of it is tested: one memory round trip
+    // instead of four in a row (chain head, chain link, node record, edge tokens)
+    const int head = t.req_head[c];
+    const int link = t.req_link[q];
+    const int par = t.parent[c];
+    const i64 off = t.edge_off[c];
+    const int len = t.edge_len[c];
+    const int dend = t.depth_end[c];
+    const int lk = t.lock_ref[c];
+    const int rk = t.rank[c];
+    const u64 st_c = t.stamp[c];
+    const bool is_head = head == (int)q;
+    const bool alone = is_head && link < 0;
     if (is_head) t.req_head[c] = -1;                                      // ready for the next batch
     if (!alone) {                                                         // shared edge: sorted, then a warp does it
       const int slot = atomicAdd(&t.ctr->n_big, 1);
@@ -979,18 +990,16 @@ __device__ __forceinline__ void rm_split_single_body(const RmTree& t, const u64*
     } else {
       const int p = (int)(ki & ((1ull << len_bits) - 1ull));
       const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
+      // second round trip: the id allocation, the edge's tokens and its owner word, together
+      const int tok0 = t.tok[off], tokp = t.tok[off + p];
+      const int seg0 = t.seg[off];
       const u64 apos = rm_alloc_nodes(t, 1);
       if (apos != ~0ull) {
+        // third: the new id and the parent's slot
+        RmSlot s;
+        const int sidx = rm_find<true>(t, rm_key(par, tok0), s);
         const int u = rm_free_id_at(t, apos);
-        const int par = t.parent[c];
-        const i64 off = t.edge_off[c];
-        const int len = t.edge_len[c];
-        const int dend = t.depth_end[c];
-        const int lk = t.lock_ref[c];
-        const int rk = t.rank[c];
-        const u64 st_c = t.stamp[c];
         const u64 st = seq > st_c ? seq : st_c;       // the query stamped the whole edge, then split it
-        const int tok0 = t.tok[off], tokp = t.tok[off + p];
         t.parent[u] = par;
         t.edge_off[u] = off;
         t.edge_len[u] = p;
@@ -1002,13 +1011,11 @@ __device__ __forceinline__ void rm_split_single_body(const RmTree& t, const u64*
         t.parked[u] = -1;
         t.stamp[u] = st;
         atomicMax(&t.ctr->node_hwm, u + 1);
-        t.seg[off] = (t.seg[off] & RM_SEG_CONT) | u;     // owner map: [off, off+p) is u's, c starts at off+p
+        t.seg[off] = (seg0 & RM_SEG_CONT) | u;           // owner map: [off, off+p) is u's, c starts at off+p
         t.seg[off + p] = c | RM_SEG_CONT;
         fill_off = off;
         fill_n = p;
         fill_id = u;
-        RmSlot s;
-        const int sidx = rm_find<true>(t, rm_key(par, tok0), s);
         if (sidx < 0) {
           atomicMax(&t.ctr->err, (int)RM_E_INVALID);
         } else {
