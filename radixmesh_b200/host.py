@@ -33,6 +33,8 @@ class CacheOplog:                     # radix/cache_oplog.py:48-66 (fields the t
     local_logic_id: int = 0
     key: list = dataclasses.field(default_factory=list)
     value: list = dataclasses.field(default_factory=list)
+    gc_query: list = dataclasses.field(default_factory=list)   # of GCQuery; like the reference, NOT part of to_dict
+    gc_exec: list = dataclasses.field(default_factory=list)    # of NodeKey
 
     def to_dict(self) -> dict:
         return {"oplog_type": int(self.oplog_type), "node_rank": self.node_rank, "local_logic_id": self.local_logic_id,
@@ -81,3 +83,9 @@ class RingPolicy:                     # policy/sync_algo.py:50-110 (the few fact
 class NodeKey:                        # radix/cache_oplog.py:25-40 (ImmutableNodeKey)
     key: tuple
     node_rank: int
+
+
+@dataclasses.dataclass
+class GCQuery:                        # radix/cache_oplog.py:43-45
+    key: NodeKey
+    agree: int = 1

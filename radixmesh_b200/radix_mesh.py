@@ -15,7 +15,7 @@ from typing import Dict, List, Optional
 import numpy as np
 
 from . import capi
-from .host import CacheOplog, CacheOplogType, NodeKey, RadixMode, RingPolicy
+from .host import CacheOplog, CacheOplogType, GCQuery, NodeKey, RadixMode, RingPolicy
 from .oplog_codec import IngestBuffer, deserialize_any, with_header
 from .radix_cache import MatchResult, RadixCache, TreeNode
 
@@ -150,7 +150,7 @@ class RadixMesh(RadixCache):
             self.tick_received[oplog.node_rank] = self.tick_received.get(oplog.node_rank, 0) + 1
             return None
         if t in (CacheOplogType.GC_QUERY, CacheOplogType.GC_EXEC):
-            return None                       # the GC protocol is a 'next' row
+            return self._gc_handle(oplog)
         if oplog.node_rank == self._global_node_rank or oplog.ttl <= 0:
             return None
         if t == CacheOplogType.INSERT:
@@ -218,6 +218,61 @@ class RadixMesh(RadixCache):
         self._flush()
         return [NodeKey(tuple(self.full_key(TreeNode(self, n, -1))), r)
                 for n, r, _, _ in self._ix.dup_entries(only_candidates=True).tolist()]
+
+    # ------------------------------------------------------------------ duplicate-node GC (radix_mesh.py:148-166, 362-389)
+    def _send(self, oplog) -> None:
+        # radix_mesh.py:339-347
+        if self.mode == RadixMode.ROUTER or self.communicator is None:
+            return
+        self.communicator.send(oplog)
+        if self._global_node_rank == self.sync_algo.master_node_rank() and self.router_communicators:
+            for r in self.router_communicators:
+                r.send(oplog)
+
+    def gc_scan_send(self) -> int:
+        """One iteration of the reference's `_gc` loop (radix_mesh.py:148-166; the thread and its sleep stay with the
+        caller): ask the ring about every parked, unlocked duplicate.  Returns the number of keys asked about."""
+        assert self.mode != RadixMode.ROUTER, "only mode ref node need gc"
+        query = [GCQuery(key=k) for k in self.gc_candidates()]
+        if query:
+            self._send(CacheOplog(oplog_type=CacheOplogType.GC_QUERY, node_rank=self._global_node_rank,
+                                  ttl=self.sync_algo.ttl(self.args), gc_query=query))
+        return len(query)
+
+    def _gc_handle(self, oplog) -> None:
+        """radix_mesh.py:362-389 on the device duplicate table (rm_gc_agree_h / rm_gc_exec_h).  Two departures from
+        the letter of the reference, both its evident intent (its own version cannot run: CacheOplog.to_dict drops the
+        payload): the node that asked also pops its own entries when it frees them (the reference would
+        ask about them again on the next scan and free the same KV indices twice), and GC_EXEC is forwarded until its
+        ttl runs out (the reference stops it at the first hop, so only one peer would ever pop)."""
+        self._flush()
+        if int(oplog.oplog_type) == CacheOplogType.GC_EXEC:
+            keys = list(oplog.gc_exec)
+            if keys:
+                self._ix.gc_exec([list(k.key) for k in keys], [k.node_rank for k in keys], free_parked=False)
+                self._invalidate()
+            if oplog.node_rank != self._global_node_rank and oplog.ttl > 0:
+                self._send(oplog)
+            return None
+        if oplog.node_rank == self._global_node_rank:
+            full = self.sync_algo.ttl(self.args)
+            keys = [q.key for q in oplog.gc_query if q.agree == full]
+            if keys:
+                off, ln = self._ix.gc_exec([list(k.key) for k in keys], [k.node_rank for k in keys], free_parked=True)
+                for a, n in zip(off.tolist(), ln.tolist()):
+                    if a >= 0 and n > 0 and self.token_to_kv_pool_allocator is not None:
+                        self.token_to_kv_pool_allocator.free(self._tensor(self._ix.read_arena(a, n)[1]))
+                self._invalidate()
+                self._send(CacheOplog(oplog_type=CacheOplogType.GC_EXEC, node_rank=self._global_node_rank,
+                                      ttl=self.sync_algo.ttl(self.args), gc_exec=keys))
+            return None
+        if oplog.gc_query:
+            agree = self._ix.gc_agree([list(q.key.key) for q in oplog.gc_query], [q.key.node_rank for q in oplog.gc_query])
+            for q, a in zip(oplog.gc_query, agree.tolist()):
+                if a:
+                    q.agree += 1
+        self._send(oplog)
+        return None
 
     # ------------------------------------------------------------------ router side (used by CacheAwareRouter)
     def _route_keys(self, keys, warm: bool):

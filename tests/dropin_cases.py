@@ -45,7 +45,7 @@ class FakeAllocator:
         self.freed.append([int(x) for x in t.tolist()])
 
 
-def build_mesh(kw):
+def build_mesh(kw, with_allocators=False):
     """3 prefill + 2 decode in a ring, 1 router fed by rank 0 (policy/sync_algo.py:57-75)."""
     ring = [LoopComm() for _ in range(5)]
     to_router, router_in = LoopComm(), LoopComm()
@@ -61,7 +61,8 @@ def build_mesh(kw):
         small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64, max_dups=512)
         small.update(kw)
         if rank < 5:
-            nodes.append(RadixMesh(args, communicator=ring[rank], routers=[to_router] if rank == 0 else None, **small))
+            nodes.append(RadixMesh(args, communicator=ring[rank], routers=[to_router] if rank == 0 else None,
+                                   token_to_kv_pool_allocator=FakeAllocator() if with_allocators else None, **small))
         else:
             nodes.append(RadixMesh(args, communicator=router_in, **small))
     for i in range(5):
