@@ -133,3 +133,9 @@ def test_gpu_gc_keys_agree_exec():
             ixs[r].check_device_error()
     for ix in ixs:
         ix.close()
+
+
+def test_gpu_gc_round_over_the_ring():
+    """GC_QUERY / GC_EXEC through the drop-in RadixMesh on a 3P+2D+1R mesh, device indexes on the GPU."""
+    dc.run_gc_ring({})
+
