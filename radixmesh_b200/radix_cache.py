@@ -104,8 +104,19 @@ class RadixCache:
                  enable_kv_cache_events: bool = False, *, max_nodes: int = 1 << 20, max_tokens: int = 1 << 26,
                  max_batch: int = 1 << 16, max_key_len: int = 1 << 15, max_dups: int = 1 << 12, device: int = 0,
                  _index_kwargs: Optional[dict] = None, _backend=None, _library=None):
-        if page_size != 1:
-            raise NotImplementedError("radixmesh_b200: page_size > 1 is a 'next' row (SURVEY.md 8f-4); RadixMesh uses 1")
+        if page_size < 1 or (page_size != 1 and self.MODE != capi.MODE_BASE):
+            raise ValueError("page_size > 1 is a RadixCache feature; RadixMesh hard-codes 1 (radix_mesh.py:87)")
+        # Paged keys (radix_cache.py:23-32, 109-114: child key = first page, keys compared a page at a time, splits at
+        # page multiples).  A paged radix tree over tokens IS a radix tree over page symbols, so the device index runs
+        # unchanged on symbols: this class keeps the exact dictionary page -> symbol on the host, stores one row of
+        # page_size KV indices per symbol in a host value store (the device value is the row id) and scales every
+        # length by page_size.  Host-side adapter: correct, Python-paced; the page_size == 1 path is untouched.
+        self._P = int(page_size)
+        self._page_id: dict = {}
+        self._page_tok: list = []
+        self._vs = np.zeros((1024, self._P), dtype=np.int64) if self._P > 1 else None
+        self._vs_free: list = []
+        self._vs_top = 0
         self.req_to_token_pool = req_to_token_pool
         self.token_to_kv_pool_allocator = token_to_kv_pool_allocator
         self.page_size = page_size
@@ -172,6 +183,8 @@ class RadixCache:
             return []
         d = self._dump()
         tok, _ = self._ix.read_arena(int(d["edge_off"][x]), int(d["edge_len"][x]), values=False)
+        if self._P > 1:
+            return [t for sid in tok.tolist() for t in self._page_tok[sid]]
         return tok.tolist()
 
     def _node_value(self, x: int):
@@ -180,24 +193,73 @@ class RadixCache:
             return []
         d = self._dump()
         _, val = self._ix.read_arena(int(d["edge_off"][x]), int(d["edge_len"][x]))
+        if self._P > 1:
+            val = self._rows_values(val)
         return torch.from_numpy(val)
 
     def _tensor(self, a):
         import torch
         return a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
 
+    # ------------------------------------------------------------------ paged keys: symbols and the value store
+    def _symbols(self, key, create: bool) -> List[int]:
+        P = self._P
+        out = []
+        for i in range(0, len(key) // P * P, P):
+            page = tuple(int(t) for t in key[i:i + P])
+            sid = self._page_id.get(page)
+            if sid is None:
+                if not create:
+                    break                      # a page the tree has never seen: nothing can match from here on
+                sid = len(self._page_tok)
+                self._page_id[page] = sid
+                self._page_tok.append(page)
+            out.append(sid)
+        return out
+
+    def _rows_alloc(self, n: int) -> np.ndarray:
+        rows = np.empty(n, dtype=np.int64)
+        k = min(n, len(self._vs_free))
+        for i in range(k):
+            rows[i] = self._vs_free.pop()
+        if n > k:
+            need = self._vs_top + (n - k)
+            if need > self._vs.shape[0]:
+                grown = np.zeros((max(need, 2 * self._vs.shape[0]), self._P), dtype=np.int64)
+                grown[:self._vs.shape[0]] = self._vs
+                self._vs = grown
+            rows[k:] = np.arange(self._vs_top, need)
+            self._vs_top = need
+        return rows
+
+    def _rows_values(self, rows) -> np.ndarray:
+        rows = np.asarray(rows, dtype=np.int64)
+        return self._vs[rows].reshape(-1) if len(rows) else np.zeros(0, dtype=np.int64)
+
+    def _no_paged_batch(self) -> None:
+        if self._P > 1:
+            raise NotImplementedError("the *_batch additions take tokens as they are: page_size 1 only")
+
     # ------------------------------------------------------------------ public API (radix_cache.py:117-248)
     def reset(self) -> None:
         self._ix.reset()
         self._invalidate()
+        self._page_id, self._page_tok, self._vs_free, self._vs_top = {}, [], [], 0
 
     def match_prefix(self, key: List[int], **kwargs) -> MatchResult:
         import torch
         if self.disable or len(key) == 0:
             return MatchResult(torch.empty((0,), dtype=torch.int64), self.root_node, self.root_node)
+        if self._P > 1:
+            key = self._symbols(key, create=False)       # page aligned (radix_cache.py:148-150), in symbols
+            if not key:
+                return MatchResult(torch.empty((0,), dtype=torch.int64), self.root_node, self.root_node)
         lens, nodes, vals, offs = self._match_keys([key])
         node = self._handle(int(nodes[0]))
-        return MatchResult(self._tensor(vals[:int(lens[0])]), node, node)
+        got = vals[:int(lens[0])]
+        if self._P > 1:
+            got = self._rows_values(self._be.to_host(got))
+        return MatchResult(self._tensor(got), node, node)
 
     def _match_keys(self, keys):
         """Host lists -> (lens, nodes, values, value offsets) as host arrays."""
@@ -219,6 +281,7 @@ class RadixCache:
     def match_prefix_batch(self, tokens, offsets, out_len=None, out_node=None):
         """Addition: device tensors in, device tensors out (int32 lengths, int32 last-node ids), equal to
         match_prefix on each query in order."""
+        self._no_paged_batch()
         self._flush()
         B = int(offsets.shape[0]) - 1
         out_len = out_len if out_len is not None else self._be.empty(B, np.int32)
@@ -229,6 +292,7 @@ class RadixCache:
 
     def gather_values_batch(self, nodes, lens, out_offsets, out_values):
         """Addition: the torch.cat of match_prefix for a whole batch (ragged, caller-provided offsets)."""
+        self._no_paged_batch()
         self._ix.gather(nodes, lens, out_offsets, int(nodes.shape[0]), out_values)
         return out_values
 
@@ -237,6 +301,21 @@ class RadixCache:
             return 0
         if value is None:
             value = [x for x in key]
+        if self._P > 1:
+            P = self._P
+            if len(key) % P != 0:
+                # the reference would store a ragged last page in the leaf (radix_cache.py:296-326 never aligns);
+                # its callers insert page-aligned keys, and so must the callers of this class
+                raise ValueError(f"paged insert: key of {len(key)} tokens is not a multiple of page_size {P}")
+            sym = self._symbols(key, create=True)
+            if not sym:
+                return 0
+            v = value.cpu().numpy() if hasattr(value, "cpu") else np.asarray(value)
+            rows = self._rows_alloc(len(sym))
+            self._vs[rows] = v.astype(np.int64, copy=False).reshape(len(sym), P)
+            m = int(self._insert_records([(sym, rows, -1)])[0])
+            self._vs_free.extend(int(r) for r in rows[:m])      # pages the tree already held: their rows stay unused
+            return m * P
         return int(self._insert_records([(list(key), value, -1)])[0])
 
     def _insert_records(self, recs) -> np.ndarray:
@@ -257,6 +336,7 @@ class RadixCache:
 
     def insert_batch(self, tokens, values, offsets, ranks=None, out_prefix_len=None):
         """Addition: ordered batch of inserts on device tensors (rm_insert_batch)."""
+        self._no_paged_batch()
         self._flush()
         N = int(offsets.shape[0]) - 1
         out = out_prefix_len if out_prefix_len is not None else self._be.empty(N, np.int32)
@@ -268,10 +348,15 @@ class RadixCache:
         if self.disable:
             return
         self._flush()
-        nodes, offs, lens = self._ix.evict(int(num_tokens))
+        P = self._P
+        nodes, offs, lens = self._ix.evict((int(num_tokens) + P - 1) // P)   # sum(len * P) >= n  <=>  sum(len) >= ceil(n / P)
         self._invalidate()
         for o, n in zip(offs.tolist(), lens.tolist()):
             _, val = self._ix.read_arena(o, n)
+            if P > 1:
+                rows = val
+                val = self._rows_values(rows)
+                self._vs_free.extend(int(r) for r in rows)
             if self.token_to_kv_pool_allocator is not None:
                 self.token_to_kv_pool_allocator.free(self._tensor(val))      # radix_cache.py:195
 
@@ -282,7 +367,7 @@ class RadixCache:
         self._ix.lock(be.to_device(np.asarray([node.id], np.int32)), be.to_device(np.asarray([node._gen], np.int32)),
                       1, direction, d_out)
         self._invalidate()
-        return int(be.to_host(d_out)[0])
+        return int(be.to_host(d_out)[0]) * self._P
 
     def inc_lock_ref(self, node: TreeNode) -> int:
         return 0 if self.disable else self._lock(node, +1)
@@ -292,17 +377,17 @@ class RadixCache:
 
     def evictable_size(self) -> int:
         self._flush()
-        return int(self._ix.sizes().evictable)
+        return int(self._ix.sizes().evictable) * self._P
 
     def protected_size(self) -> int:
         self._flush()
-        return int(self._ix.sizes().protected_)
+        return int(self._ix.sizes().protected_) * self._P
 
     def total_size(self) -> int:
         d = self._dump()
         live = (d["parent"][:d["n"]] >= 0) & (d["gen"][:d["n"]] >= 0)
         live[0] = False
-        return int(d["edge_len"][:d["n"]][live].sum())
+        return int(d["edge_len"][:d["n"]][live].sum()) * self._P
 
     def all_values_flatten(self):
         """All values of the tree; node order is by pool id, not the reference's dict order."""

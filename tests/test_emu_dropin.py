@@ -27,3 +27,26 @@ def test_base_sequences(case):
 
 def test_gc_round_over_the_ring():
     dc.run_gc_ring(kw())
+
+
+@pytest.mark.parametrize("case", dc.golden("paged_sequences"), ids=lambda c: f"seed{c['seed']}-page{c['page']}")
+def test_paged_sequences(case):
+    """RadixCache(page_size > 1) recorded from the reference: the drop-in runs the device index on page symbols."""
+    dc.replay_base_sequence(case, kw())
+
+
+
+def test_paged_restrictions():
+    import torch
+    from radixmesh_b200 import RadixCache, RadixMesh, ServerArgs
+    t = RadixCache(None, None, 4, max_nodes=256, max_tokens=4096, max_batch=16, max_key_len=64, **kw())
+    with pytest.raises(ValueError):
+        t.insert([1, 2, 3, 4, 5], torch.arange(5))                 # not a multiple of the page
+    assert t.insert([1, 2, 3, 4, 5, 6, 7, 8], torch.arange(8)) == 0
+    assert t.match_prefix([1, 2, 3, 4, 5, 6, 7]).device_indices.tolist() == [0, 1, 2, 3]   # page aligned (radix_cache.py:148-150)
+    assert t.match_prefix([1, 2, 3]).device_indices.tolist() == []
+    assert (t.evictable_size(), t.total_size()) == (8, 8)
+    with pytest.raises(NotImplementedError):
+        t.match_prefix_batch(None, None)
+    t.reset()
+    assert t.total_size() == 0 and t.match_prefix([1, 2, 3, 4]).device_indices.tolist() == []

@@ -139,3 +139,9 @@ def test_gpu_gc_round_over_the_ring():
     """GC_QUERY / GC_EXEC through the drop-in RadixMesh on a 3P+2D+1R mesh, device indexes on the GPU."""
     dc.run_gc_ring({})
 
+
+@pytest.mark.parametrize("case", dc.golden("paged_sequences"), ids=lambda c: f"seed{c['seed']}-page{c['page']}")
+def test_paged_sequences(case):
+    """RadixCache(page_size > 1) recorded from the reference: the drop-in runs the device index on page symbols."""
+    dc.replay_base_sequence(case, {})
+

@@ -68,6 +68,63 @@ def base_sequences():
     return out
 
 
+def paged_sequences():
+    """The same kind of sequences on RadixCache(page_size 2 / 4): keys matched a page at a time, page-aligned
+    inserts (what the reference's callers do), radix_cache.py:23-32, 109-114, 148-150."""
+    out = []
+    for seed in range(8):
+        rnd = random.Random(700 + seed)
+        page = rnd.choice([2, 4])
+        vocab = rnd.choice([2, 3, 5])
+        maxlen = rnd.choice([9, 17, 26])
+        ref = ref_harness.RefCache(page)
+        held, ops, vc = [], [], 0
+
+        def alive(node):
+            # a handle to a node that has been evicted since is outside the contract (the reference would still
+            # count on the detached object; the device has recycled the id)
+            while node is not ref.tree.root_node:
+                par = node.parent
+                if par is None or par.children.get(ref.tree.get_child_key_fn(node.key)) is not node:
+                    return False
+                node = par
+            return True
+
+        for _ in range(rnd.randrange(25, 70)):
+            kind = rnd.choice(["ins", "ins", "match", "match", "lock", "unlock", "evict"])
+            key = [rnd.randrange(vocab) for _ in range(rnd.randrange(0, maxlen))]
+            if kind == "ins":
+                key = key[:len(key) // page * page]
+                val = list(range(vc, vc + len(key)))
+                vc += len(key)
+                ops.append({"op": "ins", "key": key, "val": val, "ret": ref.insert(key, val)})
+            elif kind == "match":
+                r = ref.match_prefix(key)
+                held.append(r.last_device_node)
+                ops.append({"op": "match", "key": key, "idx": r.device_indices.tolist(),
+                            "last": ref.full_key(r.last_device_node)})
+            elif kind == "lock" and held:
+                i = rnd.randrange(len(held))
+                if not alive(held[i]):
+                    continue
+                ops.append({"op": "lock", "h": i, "ret": ref.tree.inc_lock_ref(held[i])})
+                held.append(held[i])
+            elif kind == "unlock" and held:
+                i = rnd.randrange(len(held))
+                if alive(held[i]) and held[i].lock_ref > 0 and held[i] is not ref.tree.root_node:
+                    ops.append({"op": "unlock", "h": i, "ret": ref.tree.dec_lock_ref(held[i])})
+            elif kind == "evict":
+                n = rnd.randrange(0, 14)
+                before = len(ref.alloc.freed)
+                ref.evict(n)
+                ops.append({"op": "evict", "n": n, "freed": ref.alloc.freed[before:]})
+            else:
+                continue
+            ops[-1]["state"] = canon_json(ref.canonical())
+        out.append({"seed": seed, "page": page, "ops": ops})
+    return out
+
+
 def correctness_blocks():
     """The four known-answer blocks of the reference's own test/correctness.py (:41-70, :77-103,
     :147-174, :178-211) replayed on the in-process 3P+2D+1R mesh."""
@@ -228,7 +285,8 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     only = set(sys.argv[1:])
     for name, fn in [("base_sequences", base_sequences), ("correctness_blocks", correctness_blocks),
-                     ("mesh_sequences", mesh_sequences), ("consistent_hash", hash_vectors), ("oplog_wire", oplog_wire)]:
+                     ("mesh_sequences", mesh_sequences), ("consistent_hash", hash_vectors), ("oplog_wire", oplog_wire),
+                     ("paged_sequences", paged_sequences)]:
         if only and name not in only:
             continue
         data = fn()
