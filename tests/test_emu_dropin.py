@@ -50,3 +50,38 @@ def test_paged_restrictions():
         t.match_prefix_batch(None, None)
     t.reset()
     assert t.total_size() == 0 and t.match_prefix([1, 2, 3, 4]).device_indices.tolist() == []
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_paged_random_against_oracle(seed):
+    """Random insert / match / evict on RadixCache(page_size 2..4) against the oracle's paged RadixCache."""
+    import random
+    import numpy as np
+    import torch
+    from oracle.radix_port import PortRadixCache
+    from radixmesh_b200 import RadixCache
+    rnd = random.Random(4200 + seed)
+    page = rnd.choice([2, 3, 4])
+    alloc = dc.FakeAllocator()
+    t = RadixCache(None, alloc, page, max_nodes=1 << 12, max_tokens=1 << 15, max_batch=16, max_key_len=64, **kw())
+    orc = PortRadixCache(page)
+    vc = 0
+    for _ in range(80):
+        kind = rnd.choice(["ins", "ins", "match", "match", "evict"])
+        key = [rnd.randrange(3) for _ in range(rnd.randrange(0, 20))]
+        if kind == "ins":
+            key = key[:len(key) // page * page]
+            val = list(range(vc, vc + len(key)))
+            vc += len(key)
+            assert t.insert(key, torch.tensor(val, dtype=torch.int64)) == orc.insert(list(key), np.asarray(val, dtype=np.int64))
+        elif kind == "match":
+            a, b = t.match_prefix(key), orc.match_prefix(list(key))
+            assert a.device_indices.tolist() == b.indices.tolist()
+            assert t.full_key(a.last_device_node) == orc.full_key(b.last_node)
+        else:
+            n = rnd.randrange(0, 10)
+            before_d, before_o = len(alloc.freed), len(orc.freed)
+            t.evict(n)
+            orc.evict(n)
+            assert alloc.freed[before_d:] == orc.freed[before_o:]
+        assert (t.evictable_size(), t.total_size()) == (orc.evictable, orc.total_size())
