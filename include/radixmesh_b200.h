@@ -104,8 +104,8 @@ int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offs
  * scratch of the match pipeline (split-request arrays, sort buffers, histograms) lives in a fixed
  * 256 KiB array inside the library image instead of memory sized by rm_config.max_batch, so an index
  * created with max_batch = 1 can still serve batches here.  For engines that gave all of HBM to their
- * KV pool (a later cudaMalloc can fail), for request-path threads that cannot take cudaMalloc's
- * device-wide synchronisation, and for code running while a stream is captured.
+ * KV pool (a later cudaMalloc can fail) and for request-path threads that cannot take cudaMalloc's
+ * device-wide synchronisation.
  *   - at most 4096 queries per call, else RM_E_TOO_LARGE;
  *   - makes no cudaMalloc / cudaFree / allocating call;
  *   - the first call on each device looks the array's address up (cudaGetSymbolAddress): make it

@@ -4,9 +4,9 @@
 // Who needs it.  An index is normally created once, with scratch sized for rm_config.max_batch, and
 // every later call reuses that scratch.  Some hosts of this library cannot size that up front and
 // cannot call cudaMalloc afterwards either: a serving engine hands almost all of HBM to its KV pool
-// at start-up, so a later device allocation can simply fail; a scheduler or an oplog receive
-// thread on the request path cannot afford cudaMalloc's implicit device-wide synchronisation; and
-// nothing may allocate while a stream is being captured.  Such a caller creates its index with a
+// at start-up, so a later device allocation can simply fail; and a scheduler or an oplog
+// receive thread on the request path cannot afford cudaMalloc's implicit device-wide
+// synchronisation.  Such a caller creates its index with a
 // minimal max_batch and sends its match batches (up to RM_STATIC_MAX_BATCH queries) through this
 // entry point: no cudaMalloc, cudaFree or other allocating call is made, here or below.
 //
@@ -22,6 +22,9 @@
 // First call on a device: looks up the array's device address (cudaGetSymbolAddress) and caches it
 // per device.  In host code the array's name is only a handle for that lookup, never an address a
 // kernel may be given.  Make this first call before any stream capture begins.
+//
+// Like every entry point, calls on one index must be serialised by the caller: for the duration of the
+// call the index's scratch view points into the static array.
 #include <mutex>
 
 #include "rm_internal.h"

@@ -64,7 +64,9 @@ class RadixMesh(RadixCache):
         self.communicator = communicator
         self.router_communicators = routers
         self.logic_op_counter = 0
-        self._pending_lock = threading.Lock()
+        # One lock for staging, taking and applying records: the reference holds _tree_lock across the whole
+        # _insert_helper (radix_mesh.py:198-199).  Re-entrant, because _flush is reached from code that holds it.
+        self._pending_lock = threading.RLock()
         self._ingest = IngestBuffer(with_values=self.mode != RadixMode.ROUTER)
         self.tick_received: Dict[int, int] = {}
         backend = index_kwargs.pop("_backend", None)
@@ -107,27 +109,37 @@ class RadixMesh(RadixCache):
         return self._insert(list(key), value, self._global_node_rank)
 
     def _insert(self, key, value, owner_rank: int) -> int:
+        # staged and applied under ONE hold of the lock: nobody can add or take records in between, so the
+        # caller's record is the last one of the batch and batches reach the device in arrival order
         with self._pending_lock:
             self._ingest.add(key, value, owner_rank)
-        ret = self._flush()
+            ret = self._flush()
         self.send_insert_event(key, value, owner_rank)
         return ret
 
     def _flush(self):
-        """Apply the staged INSERTs, in arrival order, as ordered device batches (rm_insert_batch_h)."""
+        """Apply the staged INSERTs, in arrival order, as ordered device batches (rm_insert_batch_h).  Returns the
+        prefix length of the LAST staged record (what _insert needs: it holds the lock across add + flush)."""
         with self._pending_lock:
             if len(self._ingest) == 0:
                 return 0
             tok, val, offs, ranks = self._ingest.take()
-        out = None
-        n, step = len(ranks), int(self._ix.cfg.max_batch)
-        for i in range(0, n, step):
-            j = min(i + step, n)
-            a, b = int(offs[i]), int(offs[j])
-            out = self._ix.insert_host(tok[a:b], val[a:b] if val is not None else None, offs[i:j + 1] - offs[i], ranks[i:j])
-        self._invalidate()
-        self._ix.check_device_error()
-        return int(out[-1])
+            out = None
+            n, step = len(ranks), int(self._ix.cfg.max_batch)
+            for i in range(0, n, step):
+                j = min(i + step, n)
+                a, b = int(offs[i]), int(offs[j])
+                out = self._ix.insert_host(tok[a:b], val[a:b] if val is not None else None, offs[i:j + 1] - offs[i], ranks[i:j])
+            self._invalidate()
+            self._ix.check_device_error()
+            return int(out[-1])
+
+    def reset(self) -> None:
+        """radix_mesh.py:240-245.  INSERTs that arrived before the reset and are still staged must not outlive it:
+        the reference has applied them already when it resets, so they are gone with the tree."""
+        with self._pending_lock:
+            self._ingest.take()
+            RadixCache.reset(self)
 
     def send_insert_event(self, key, value, owner_rank: int) -> None:
         # radix_mesh.py:325-347: routers never send; rank 0 also feeds the routers
@@ -146,8 +158,11 @@ class RadixMesh(RadixCache):
         # radix_mesh.py:391-423
         oplog.ttl -= 1
         t = int(oplog.oplog_type)
-        if t == CacheOplogType.TICK:
+        if t == CacheOplogType.TICK:                              # _tick_handle, radix_mesh.py:356-360
             self.tick_received[oplog.node_rank] = self.tick_received.get(oplog.node_rank, 0) + 1
+            if oplog.ttl <= 0:
+                return None
+            self._send(oplog)
             return None
         if t in (CacheOplogType.GC_QUERY, CacheOplogType.GC_EXEC):
             return self._gc_handle(oplog)
@@ -158,7 +173,7 @@ class RadixMesh(RadixCache):
                 self._ingest.add(oplog.key, oplog.value, oplog.node_rank)
             self.send_insert_event(oplog.key, oplog.value, oplog.node_rank)   # re-forward with a fresh ttl
         elif t == CacheOplogType.RESET:
-            RadixCache.reset(self)
+            self.reset()                                          # also drops INSERTs staged before the reset
         elif t != CacheOplogType.DELETE:
             assert False, "unknown oplog type"
         return None

@@ -226,3 +226,47 @@ def run_gc_ring(kw):
 def _key(key, rank):
     from radixmesh_b200.host import NodeKey
     return NodeKey(tuple(key), rank)
+
+
+def run_reset_drops_staged(kw):
+    """An INSERT oplog followed by a RESET with no read in between: the reference has applied the insert when the
+    reset arrives, so nothing of it survives (radix_mesh.py:411-420); the staged record must go with the tree."""
+    from radixmesh_b200.host import CacheOplog, CacheOplogType
+    nodes = build_mesh(kw)
+    n2 = nodes[2]
+    n2.oplog_received(CacheOplog(oplog_type=CacheOplogType.INSERT, node_rank=1, key=[1, 2, 3], value=[10, 11, 12], ttl=5))
+    n2.oplog_received(CacheOplog(oplog_type=CacheOplogType.RESET, node_rank=1, ttl=5))
+    assert n2.match_prefix([1, 2, 3]).device_indices.tolist() == []
+    assert n2.evictable_size() == 0
+    # the same through a local reset()
+    n2.oplog_received(CacheOplog(oplog_type=CacheOplogType.INSERT, node_rank=1, key=[4, 5], value=[40, 41], ttl=5))
+    n2.reset()
+    assert n2.match_prefix([4, 5]).device_indices.tolist() == []
+    # and the tree still works afterwards
+    assert n2.insert([4, 5], torch.tensor([70, 71])) == 0
+    assert n2.match_prefix([4, 5, 6]).device_indices.tolist() == [70, 71]
+
+
+def run_tick_ring(kw):
+    """A TICK is counted and forwarded while its ttl lasts (_tick_handle, radix_mesh.py:356-360): with the ticker's
+    two-round ttl 2*(P+D) every replica of the ring counts the origin twice (the _wait_all_nodes_ready condition)."""
+    from radixmesh_b200.host import CacheOplog, CacheOplogType
+    nodes = build_mesh(kw)
+    ttl = 2 * 5
+    nodes[3]._send(CacheOplog(oplog_type=CacheOplogType.TICK, node_rank=3, ttl=ttl))
+    for r in range(5):
+        assert nodes[r].tick_received.get(3, 0) == 2, f"replica {r} saw {nodes[r].tick_received}"
+    # rank 0 also feeds the router, once per pass through rank 0's _send (radix_mesh.py:344-347)
+    assert nodes[5].tick_received.get(3, 0) >= 1
+
+
+def run_insert_returns_own_prefix(kw):
+    """insert() returns the prefix length of the caller's own record although remote records were staged ahead of it
+    (they are applied first, in arrival order: radix_mesh.py:197-201)."""
+    from radixmesh_b200.host import CacheOplog, CacheOplogType
+    nodes = build_mesh(kw)
+    n1 = nodes[1]
+    n1.oplog_received(CacheOplog(oplog_type=CacheOplogType.INSERT, node_rank=0, key=[1, 2, 3, 4], value=[1, 2, 3, 4], ttl=5))
+    n1.oplog_received(CacheOplog(oplog_type=CacheOplogType.INSERT, node_rank=0, key=[9], value=[9], ttl=5))
+    assert n1.insert([1, 2, 3, 4, 5, 6], torch.tensor([1, 2, 3, 4, 55, 66])) == 4
+    assert n1.insert([7, 7], torch.tensor([5, 6])) == 0

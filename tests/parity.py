@@ -124,3 +124,69 @@ def zipf_prefix(seed, n_docs, n_seq, L, s=1.1, vocab=32000, docs=None):
     mask = cols < cut[:, None]
     out[mask] = docs[d][mask]
     return out, docs
+
+
+# ---- large trees: digests instead of full-key tuples ---------------------------------------------------------------
+# A node's digest chains its parent's digest with its own key and value bytes, so two trees have the same multiset
+# of (digest, edge length, lock_ref, stamp order) rows iff they have the same nodes with the same boundaries, keys,
+# values, locks and eviction order.  Costs O(tokens) instead of O(nodes * depth).
+def _dg(parent_digest: bytes, tok: np.ndarray, val) -> bytes:
+    import hashlib
+    h = hashlib.blake2b(parent_digest, digest_size=16)
+    h.update(np.ascontiguousarray(tok, dtype=np.int32).tobytes())
+    if val is not None:
+        h.update(np.ascontiguousarray(val, dtype=np.int64).tobytes())
+    return h.digest()
+
+
+def device_digest(ix):
+    """{"rows": sorted (digest, len, lock_ref, effective stamp >> 1), "by_id": {node id: digest}, sizes} of a DeviceIndex."""
+    d = ix.dump()
+    s = ix.sizes()
+    n = d["n"]
+    used = int(s.arena_used)
+    tok, val = ix.read_arena(0, used) if used else (np.zeros(0, np.int32), np.zeros(0, np.int64))
+    parent, off, ln, depth = d["parent"][:n], d["edge_off"][:n], d["edge_len"][:n], d["depth"][:n]
+    alive = np.nonzero((parent >= 0) & (d["gen"][:n] >= 0))[0]
+    alive = alive[alive != 0]
+    order = alive[np.argsort(depth[alive], kind="stable")]        # parents before children
+    dig = {0: b""}
+    for x in order.tolist():
+        o, l = int(off[x]), int(ln[x])
+        dig[x] = _dg(dig[int(parent[x])], tok[o:o + l], val[o:o + l] if val is not None else None)
+    eff = d["stamp"][:n].astype(np.uint64).copy()
+    for x in order[::-1].tolist():                                 # children before parents
+        p = int(parent[x])
+        if p > 0 and eff[x] > eff[p]:
+            eff[p] = eff[x]
+    rows = sorted((dig[x], int(ln[x]), int(d["lock_ref"][x]), int(eff[x]) >> 1) for x in order.tolist())
+    return {"rows": rows, "by_id": dig, "evictable": int(s.evictable), "protected": int(s.protected_),
+            "val": val, "dump": d}
+
+
+def oracle_digest(orc):
+    """The same rows for a PortRadixCache, plus {Node: digest}."""
+    from oracle.radix_port import SUB_BITS
+    dig = {orc.root: b""}
+    rows = []
+    stack = [orc.root]
+    while stack:
+        nd = stack.pop()
+        for c in nd.children.values():
+            dig[c] = _dg(dig[nd], np.asarray(c.key, dtype=np.int32), np.asarray(c.value, dtype=np.int64))
+            rows.append((dig[c], len(c.key), c.lock_ref, c.stamp >> SUB_BITS))
+            stack.append(c)
+    rows.sort()
+    return {"rows": rows, "by_node": dig, "evictable": orc.evictable, "protected": orc.protected}
+
+
+def assert_same_digest(dev, orc):
+    a, b = dev["rows"], orc["rows"]
+    assert len(a) == len(b), f"node count {len(a)} != {len(b)}"
+    # stamps: only the order matters; nodes compare in (digest) order, stamps by dense rank
+    ra = {s: i for i, s in enumerate(sorted({r[3] for r in a}))}
+    rb = {s: i for i, s in enumerate(sorted({r[3] for r in b}))}
+    for x, y in zip(a, b):
+        assert x[:3] == y[:3], f"node differs: dev {x[0].hex()} len {x[1]} lock {x[2]} / orc {y[0].hex()} len {y[1]} lock {y[2]}"
+        assert ra[x[3]] == rb[y[3]], f"stamp order differs at node {x[0].hex()}: {ra[x[3]]} vs {rb[y[3]]}"
+    assert dev["evictable"] == orc["evictable"] and dev["protected"] == orc["protected"]

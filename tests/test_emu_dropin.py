@@ -29,6 +29,18 @@ def test_gc_round_over_the_ring():
     dc.run_gc_ring(kw())
 
 
+def test_reset_drops_staged_inserts():
+    dc.run_reset_drops_staged(kw())
+
+
+def test_tick_is_forwarded_around_the_ring():
+    dc.run_tick_ring(kw())
+
+
+def test_insert_returns_its_own_prefix_length():
+    dc.run_insert_returns_own_prefix(kw())
+
+
 @pytest.mark.parametrize("case", dc.golden("paged_sequences"), ids=lambda c: f"seed{c['seed']}-page{c['page']}")
 def test_paged_sequences(case):
     """RadixCache(page_size > 1) recorded from the reference: the drop-in runs the device index on page symbols."""

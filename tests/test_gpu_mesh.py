@@ -140,6 +140,13 @@ def test_gpu_gc_round_over_the_ring():
     dc.run_gc_ring({})
 
 
+def test_gpu_reset_tick_and_own_prefix():
+    """Host-side oplog rules of the drop-in RadixMesh with the indexes on the GPU."""
+    dc.run_reset_drops_staged({})
+    dc.run_tick_ring({})
+    dc.run_insert_returns_own_prefix({})
+
+
 @pytest.mark.parametrize("case", dc.golden("paged_sequences"), ids=lambda c: f"seed{c['seed']}-page{c['page']}")
 def test_paged_sequences(case):
     """RadixCache(page_size > 1) recorded from the reference: the drop-in runs the device index on page symbols."""
