@@ -335,8 +335,7 @@ def main():
                         "d2h_bytes_per_step": B * 8},
                 "gpu_launches": launches, "clocks": clocks}
         if stage_ms:
-            line["stages_ms_per_step"] = dict(zip(("walk", "single_splits", "sort_shared", "shared_splits"),
-                                                  (x / max(walk_n, 1) for x in stage_ms)))
+            line["stages_ms_per_step"] = dict(zip(("walk", "split_stage"), (x / max(walk_n, 1) for x in stage_ms[:2])))
         cpu = None
         if world == 1 and not args.no_cpu:
             v, bpl, hops, mm = cpu_sample(wl, docs, args.cpu_sample)

@@ -101,7 +101,7 @@ int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offs
 /*
  * rm_match_batch for callers that must not allocate device memory.  No counterpart in the reference
  * (a Python dict tree has no device scratch).  Same arguments and results as rm_match_batch, but the
- * scratch of the match pipeline (split-request arrays, sort buffers, histograms) lives in a fixed
+ * scratch of the match pipeline (split-request arrays, chain links, the lists of its sorted path) lives in a fixed
  * 256 KiB array inside the library image instead of memory sized by rm_config.max_batch, so an index
  * created with max_batch = 1 can still serve batches here.  For engines that gave all of HBM to their
  * KV pool (a later cudaMalloc can fail) and for request-path threads that cannot take cudaMalloc's
@@ -253,9 +253,9 @@ int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void
  * rm_profile(idx, 1): record a CUDA-event pair around the walk kernel (K1) of every following
  * rm_match_batch; rm_profile_read returns the summed device time of those kernels and their count,
  * and clears the record (at most 128 batches are kept).  Synchronises.
- * rm_profile(idx, 2) + rm_profile_stages (call it before rm_profile_read, which clears): the same sums for
- * the four stages of a splitting match batch (three more events per batch): stage_ms_h[0] walk (K1), [1] single-request splits, [2] sort of the requests on
- * shared edges, [3] shared-edge splits.
+ * rm_profile(idx, 2) + rm_profile_stages (call it before rm_profile_read, which clears): the same sums for the
+ * stages of a splitting match batch (one more event per batch): stage_ms_h[0] walk (K1), [1] split stage (K3);
+ * [2] and [3] are reserved and read 0.
  */
 unsigned long long rm_launch_count(void);
 int rm_profile(rm_index* idx, int enable);

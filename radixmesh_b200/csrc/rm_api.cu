@@ -58,16 +58,15 @@ int rm_profile(rm_index* idx, int enable) {
   if (enable && !idx->prof_ev[0]) {
     for (int i = 0; i < RM_PROF_EVENTS; ++i) RM_CUDA(cudaEventCreate(&idx->prof_ev[i]));
   }
-  idx->prof_on = enable < 0 ? 0 : enable > 2 ? 2 : enable;   // 1: walk kernel only, 2: all four stages
+  idx->prof_on = enable < 0 ? 0 : enable > 2 ? 2 : enable;   // 1: walk kernel only, 2: walk and split stage
   idx->prof_n = 0;
 #endif
   return RM_OK;
 }
 
-// per batch: [0] before K1, [1] after K1, [2] after the single-request split kernel, [3] after the sort of the
-// shared-edge requests, [4] after the shared-edge split kernel
+// per batch: [0] before K1, [1] after K1, [2] after the split kernel
 static int rm_profile_sum(rm_index* idx, double* stage_ms, int* n_h) {
-  for (int k = 0; k < RM_PROF_STRIDE - 1; ++k) stage_ms[k] = 0.0;
+  for (int k = 0; k < 4; ++k) stage_ms[k] = 0.0;
   *n_h = 0;
 #ifndef RM_EMU
   RM_CUDA(cudaSetDevice(idx->cfg.device));
@@ -95,7 +94,7 @@ int rm_profile_stages(rm_index* idx, double* stage_ms_h, int* n_h) {
 
 int rm_profile_read(rm_index* idx, double* walk_ms_h, int* n_h) {
   if (!idx || !walk_ms_h || !n_h) return RM_E_INVALID;
-  double st[RM_PROF_STRIDE - 1];
+  double st[4];
   int rc = rm_profile_sum(idx, st, n_h);
   *walk_ms_h = st[0];
 #ifndef RM_EMU
@@ -110,7 +109,7 @@ int rm_destroy(rm_index* idx) {
   RmTree& t = idx->t;
   RmScratch& sc = idx->sc;
   void* ptrs[] = {t.table, t.parent, t.edge_off, t.edge_len, t.lock_ref, t.stamp, t.rank, t.depth_end, t.nchild,
-                  t.gen, t.parked, t.born, t.tok, t.val, t.seg, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
+                  t.gen, t.parked, t.born, t.ts, t.val, t.req_cnt, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
                   sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.link, t.req_head, sc.hist, sc.ev_key[0], sc.ev_key[1],
                   sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ins_mark, sc.lock_first, sc.lock_cnt, sc.lock_flag,
                   sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b,
@@ -178,9 +177,8 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&t.gen, N));
   A(rm_dalloc(&t.parked, N));
   A(rm_dalloc(&t.born, N));
-  A(rm_dalloc(&t.tok, (size_t)cfg->max_tokens + RM_ARENA_PAD));
+  A(rm_dalloc(&t.ts, (size_t)cfg->max_tokens + RM_ARENA_PAD));
   A(rm_dalloc(&t.val, with_values ? (size_t)cfg->max_tokens + RM_ARENA_PAD : 1));
-  A(rm_dalloc(&t.seg, (size_t)cfg->max_tokens + RM_ARENA_PAD));
   A(rm_dalloc(&t.free_ids, N));
   A(rm_dalloc(&t.ctr, 1));
   A(rm_dalloc(&t.dup_key, dcap));
@@ -195,6 +193,7 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&sc.uniq_min, B));
   A(rm_dalloc(&sc.link, B));
   A(rm_dalloc(&t.req_head, N));
+  A(rm_dalloc(&t.req_cnt, N));
   A(rm_dalloc(&sc.hist, sc.hist_words));
   A(cudaMemset(sc.hist, 0, sizeof(unsigned) * RM_SORT_TABLE_OFF));      // grid-barrier words of the one-launch sort
   A(rm_dalloc(&sc.ev_key[0], N));
@@ -464,20 +463,41 @@ int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, 
   return RM_OK;
 }
 
+// one component (0 = token, 1 = owner word) of `n` arena records from `off`, to HOST.  Tokens and owner words are
+// interleaved on the device; the records are copied as they are and taken apart here.
+static int rm_read_arena_component(rm_index* idx, i64 off, i64 n, int which, int* out_h, cudaStream_t s) {
+  const i64 chunk = 1 << 20;
+  int2* tmp = (int2*)malloc(sizeof(int2) * (size_t)(n < chunk ? (n > 0 ? n : 1) : chunk));
+  if (!tmp) return RM_E_NOSPACE;
+  for (i64 a = 0; a < n; a += chunk) {
+    const i64 m = n - a < chunk ? n - a : chunk;
+    cudaError_t e = cudaMemcpyAsync(tmp, idx->t.ts + off + a, sizeof(int2) * (size_t)m, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) {
+      free(tmp);
+      rm_set_error("arena read failed: %s", cudaGetErrorString(e));
+      return RM_E_CUDA;
+    }
+    for (i64 k = 0; k < m; ++k) out_h[a + k] = which ? tmp[k].y : tmp[k].x;
+  }
+  free(tmp);
+  return RM_OK;
+}
+
 int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void* stream) {
   if (!idx || off < 0 || n < 0 || off + n > idx->t.max_tokens || !seg_h) return RM_E_INVALID;
   RM_CUDA(cudaSetDevice(idx->cfg.device));
-  cudaStream_t s = (cudaStream_t)stream;
-  RM_CUDA(cudaMemcpyAsync(seg_h, idx->t.seg + off, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
-  RM_CUDA(cudaStreamSynchronize(s));
-  return RM_OK;
+  return rm_read_arena_component(idx, off, n, 1, seg_h, (cudaStream_t)stream);
 }
 
 int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream) {
   if (!idx || off < 0 || n < 0 || off + n > idx->t.max_tokens) return RM_E_INVALID;
   RM_CUDA(cudaSetDevice(idx->cfg.device));
   cudaStream_t s = (cudaStream_t)stream;
-  if (tokens_h) RM_CUDA(cudaMemcpyAsync(tokens_h, idx->t.tok + off, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  if (tokens_h) {
+    int rc = rm_read_arena_component(idx, off, n, 0, tokens_h, s);
+    if (rc) return rc;
+  }
   if (values_h && idx->cfg.mode != RM_MODE_ROUTER)
     RM_CUDA(cudaMemcpyAsync(values_h, idx->t.val + off, sizeof(i64) * (size_t)n, cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));

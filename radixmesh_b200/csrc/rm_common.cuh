@@ -5,9 +5,10 @@
 //                a slot carries everything one hop of a walk needs: child id, edge length, edge
 //                offset, owner rank.  Replaces TreeNode.children (radix_cache.py:39).
 //   node pool    structure of arrays indexed by node id (TreeNode fields, radix_cache.py:35-53).
-//   edge arenas  tok[i32] and val[i64] in parallel: a node's key and value are the same
+//   edge arenas  ts[{tok i32, seg i32}] and val[i64] in parallel: a node's key and value are the same
 //                [edge_off, edge_off+edge_len) run of both, so _split_node (radix_cache.py:277-294)
-//                is zero-copy.
+//                is zero-copy.  A position's token and its owner word (seg, below) sit in one 8-byte
+//                record: a step of the walk reads both with ONE 64-bit load per lane.
 #pragma once
 #include <stdint.h>
 #ifdef RM_EMU
@@ -95,7 +96,7 @@ struct RmCounters {
   int n_big;          // scratch: of those, the requests on edges that more than one query asked to split
                       // (kept next to n_req: one memset clears both)
   int evict_n;        // scratch: nodes evicted by the current rm_evict
-  int pad;
+  unsigned split_done; // scratch: blocks of the split kernel that have finished (the last one runs the rare big groups)
   int dbg_max_group;  // largest split-request group seen (diagnostics)
   int dbg_groups;     // split-request groups seen (diagnostics)
   int ev_total;       // scratch: eviction candidates (leaves up to the frontier key + the parents they expose)
@@ -120,11 +121,11 @@ struct RmTree {
   int* gen;        // generation of the object a tree id stands for (bumped by a locked swap); parked: -(gen)-1
   int* parked;     // tree node: most recently parked predecessor (or -1); parked node: the one parked before it
   u64* born;       // op seq of the insert record that created the node (0 = older than any batch in flight)
-  int* tok;
+  int2* ts;        // per arena position: .x = token, .y = seg = id of the node whose edge covers it (-1 = free), see RM_SEG_CONT
   i64* val;
-  int* req_head;   // per node: last query of the current match batch that asked to split it (-1 between batches)
-  int* req_link;   // per query of the batch: the query that asked for the same node before it (-1 = none)
-  int* seg;        // per arena position: id of the node whose edge covers it (-1 = free), see RM_SEG_CONT
+  int* req_head;   // per node: last split request of the current match batch on it (an index into the batch's request list; -1 between batches)
+  int* req_cnt;    // per node: how many split requests of the current match batch it received (0 between batches)
+  int* req_link;   // per request of the batch: the request on the same node before it (-1 = none)
   int* free_ids;
   RmCounters* ctr;
   int max_nodes;
@@ -135,6 +136,11 @@ struct RmTree {
   int* dup_parked;
   unsigned dup_mask;
 };
+
+// arena accessors (coherent loads: the kernels that call them may have written the arena themselves)
+__device__ __forceinline__ int rm_tok(const RmTree& t, i64 a) { return __ldcg(&t.ts[a].x); }
+__device__ __forceinline__ int rm_seg(const RmTree& t, i64 a) { return __ldcg(&t.ts[a].y); }
+__device__ __forceinline__ void rm_set_seg(const RmTree& t, i64 a, int v) { t.ts[a].y = v; }
 
 // Table hash of (parent id, first token): Fibonacci-style multiplicative hash, top bits.  It sits on
 // the dependent chain of every hop of the walk, so it is two independent IMADs, an add and a shift
@@ -265,8 +271,8 @@ __device__ __forceinline__ void rm_slot_store(const RmTree& t, RmSlot* s, u64 ke
   s->child = child;
   s->len_rank = rm_slot_pack(edge_len, rank);
   s->edge_off = edge_off;
-  s->tok1 = edge_len > 1 ? __ldcg(t.tok + edge_off + 1) : 0;   // the edge's tokens are in the arena already
-  s->tok2 = edge_len > 2 ? __ldcg(t.tok + edge_off + 2) : 0;
+  s->tok1 = edge_len > 1 ? rm_tok(t, edge_off + 1) : 0;   // the edge's tokens are in the arena already
+  s->tok2 = edge_len > 2 ? rm_tok(t, edge_off + 2) : 0;
   *reinterpret_cast<volatile u64*>(&s->key) = key;
 }
 // in-place edits of a live slot (its key and edge start do not change, so the inline tokens stay valid)

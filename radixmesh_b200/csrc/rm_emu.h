@@ -66,10 +66,13 @@ static inline int __popc(unsigned v) { return __builtin_popcount(v); }
 static inline int __clz(int v) { return v ? __builtin_clz((unsigned)v) : 32; }
 static inline void __syncwarp(unsigned = 0xffffffffu) {}
 static inline void __threadfence() {}
+static inline void __syncthreads() {}
 template <class T> static inline T __ldg(const T* p) { return *p; }
 template <class T> static inline T __ldcg(const T* p) { return *p; }
 template <class T> static inline void __stcg(T* p, T v) { *p = v; }
 struct int4 { int x, y, z, w; };
+struct int2 { int x, y; };
+static inline int2 make_int2(int x, int y) { return int2{x, y}; }
 struct uint2 { unsigned x, y; };
 struct uint4 { unsigned x, y, z, w; };
 

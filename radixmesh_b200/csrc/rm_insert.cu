@@ -159,7 +159,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       int m = lim;
       for (int base = 1; base < lim; base += G) {
         int x = base + g.lane;
-        bool ne = x < lim && __ldcg(t.tok + eoff + x) != key[pos + x];
+        bool ne = x < lim && rm_tok(t, eoff + x) != key[pos + x];
         unsigned mb = g.ballot(ne);
         if (mb) {
           m = base + __ffs(mb) - 1;
@@ -207,9 +207,9 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
         const int u = rm_free_id_at(t, apos);
         // owner map: [eoff, eoff+m) now belongs to u (the first position keeps its flag), c starts at
         // eoff+m as the contiguous child of u
-        for (int x = g.lane; x < m; x += G) t.seg[eoff + x] = x == 0 ? ((t.seg[eoff] & RM_SEG_CONT) | u) : u;
+        for (int x = g.lane; x < m; x += G) rm_set_seg(t, eoff + x, x == 0 ? ((rm_seg(t, eoff) & RM_SEG_CONT) | u) : u);
         if (g.lane == 0) {
-          t.seg[eoff + m] = c | RM_SEG_CONT;
+          rm_set_seg(t, eoff + m, c | RM_SEG_CONT);
           const int par = t.parent[c];
           t.parent[u] = par;
           t.edge_off[u] = eoff;
@@ -225,7 +225,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           atomicMax(&t.ctr->node_hwm, u + 1);
           t.table[sidx].child = u;
           rm_slot_set_len(&t.table[sidx], m);
-          rm_table_insert(t, rm_key(u, __ldcg(t.tok + eoff + m)), c, elen - m, eoff + m, srank);
+          rm_table_insert(t, rm_key(u, rm_tok(t, eoff + m)), c, elen - m, eoff + m, srank);
           t.parent[c] = u;
           t.edge_off[c] = eoff + m;
           t.edge_len[c] = elen - m;
@@ -268,14 +268,13 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
             if (apos == ~0ull || noff < 0) break;
             const int d = rm_free_id_at(t, apos);
             for (int x = g.lane; x < m; x += G) {
-              t.tok[noff + x] = __ldcg(t.tok + eoff + x);
+              t.ts[noff + x] = make_int2(rm_tok(t, eoff + x), target);   // moved away from its parent's run: no contiguity flag
               t.val[noff + x] = val[pos + x];
-              t.seg[noff + x] = target;     // moved away from its parent's run: no contiguity flag
-              t.seg[eoff + x] = d;          // the old run stays with the parked node
+              rm_set_seg(t, eoff + x, d);   // the old run stays with the parked node
             }
             if (g.lane == 0) {
-              const int nx = t.seg[eoff + m];  // a contiguous child now follows the PARKED run, not its parent
-              if (nx >= 0 && (nx & RM_SEG_CONT)) t.seg[eoff + m] = nx & ~RM_SEG_CONT;
+              const int nx = rm_seg(t, eoff + m);  // a contiguous child now follows the PARKED run, not its parent
+              if (nx >= 0 && (nx & RM_SEG_CONT)) rm_set_seg(t, eoff + m, nx & ~RM_SEG_CONT);
             }
             if (g.lane == 0) {
               t.parent[d] = t.parent[target];
@@ -324,8 +323,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       if (apos != ~0ull && noff >= 0) {
         const int leaf = rm_free_id_at(t, apos);
         for (int x = g.lane; x < rem; x += G) {
-          t.tok[noff + x] = key[pos + x];
-          t.seg[noff + x] = leaf;
+          t.ts[noff + x] = make_int2(key[pos + x], leaf);
           if (MESH != 2) t.val[noff + x] = val[pos + x];
         }
         g.sync();   // the slot's inline tokens are read back from the arena
@@ -415,7 +413,7 @@ rm_insert_classify_kernel(RmTree t, const int* __restrict__ rtok, const i64* __r
         int m = lim;
         for (int base = 1; base < lim; base += G) {
           const int xx = base + g.lane;
-          const bool ne = xx < lim && __ldcg(t.tok + eoff + xx) != key[pos + xx];
+          const bool ne = xx < lim && rm_tok(t, eoff + xx) != key[pos + xx];
           const unsigned mb = g.ballot(ne);
           if (mb) {
             m = base + __ffs(mb) - 1;

@@ -57,8 +57,8 @@ struct rm_index {
   size_t route_msg_bytes;
   int* route_nblk;            // 64-byte blocks per rendered request, 0 = hash it with the streamed form
   // optional CUDA events around the stages of each match batch (rm_profile)
-#define RM_PROF_EVENTS 640
-#define RM_PROF_STRIDE 5
+#define RM_PROF_EVENTS 384
+#define RM_PROF_STRIDE 3
 #ifndef RM_EMU
   cudaEvent_t prof_ev[RM_PROF_EVENTS];
   int prof_on;

@@ -49,7 +49,7 @@ __global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
     c.n_dups = 0;
     c.n_req = 0;
     c.evict_n = 0;
-    c.pad = 0;
+    c.split_done = 0;
     c.n_big = 0;
     c.dbg_max_group = 0;
     c.dbg_groups = 0;
@@ -77,7 +77,8 @@ int rm_launch_reset(rm_index* idx, cudaStream_t s) {
   RM_CUDA(cudaMemsetAsync(t.dup_key, 0xFF, sizeof(u64) * ((size_t)t.dup_mask + 1), s));
   RM_CUDA(cudaMemsetAsync(t.req_head, 0xFF, sizeof(int) * (size_t)t.max_nodes, s));
   RM_CUDA(cudaMemsetAsync(idx->sc.ins_mark, 0, sizeof(int) * (size_t)t.max_nodes, s));
-  RM_CUDA(cudaMemsetAsync(t.seg, 0xFF, sizeof(int) * ((size_t)t.max_tokens + RM_ARENA_PAD), s));
+  RM_CUDA(cudaMemsetAsync(t.ts, 0xFF, sizeof(int2) * ((size_t)t.max_tokens + RM_ARENA_PAD), s));   // token -1, owner -1 (free)
+  RM_CUDA(cudaMemsetAsync(t.req_cnt, 0, sizeof(int) * (size_t)t.max_nodes, s));
   RmLockScratch ls = rm_lock_scratch(idx);
   RM_CUDA(cudaMemsetAsync(ls.flag, 0, sizeof(int), s));
   int grid = (int)min((i64)1184, ((i64)t.max_nodes + RM_MT_TPB - 1) / RM_MT_TPB);
@@ -392,9 +393,9 @@ __global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sva
   out_offs[k] = off;
   out_lens[k] = len;
   RmSlot s;
-  int sidx = rm_find<true>(t, rm_key(par, t.tok[off]), s);
+  int sidx = rm_find<true>(t, rm_key(par, rm_tok(t, off)), s);
   if (sidx >= 0) *reinterpret_cast<volatile u64*>(&t.table[sidx].key) = RM_TOMB_KEY;
-  for (int k2 = 0; k2 < len; ++k2) t.seg[off + k2] = -1;   // the run is free again
+  for (int k2 = 0; k2 < len; ++k2) rm_set_seg(t, off + k2, -1);   // the run is free again
   if (par > 0) atomicMax(&t.stamp[par], eff[x]);            // lazy stamps: the parent keeps what it saw through x
   atomicSub(&t.nchild[par], 1);
   t.parent[x] = -1;
@@ -588,7 +589,7 @@ __global__ void rm_gc_exec_kernel(RmTree t, const int* __restrict__ nodes, const
       x = nx;
     }
     for (int k = 0; k < len; ++k)
-      if ((t.seg[off + k] & 0x3FFFFFFF) == d) t.seg[off + k] = -1;
+      if ((rm_seg(t, off + k) & 0x3FFFFFFF) == d) rm_set_seg(t, off + k, -1);
     t.parked[d] = -1;
     t.parent[d] = -1;
     t.edge_len[d] = 0;
@@ -612,7 +613,7 @@ __global__ void rm_node_key_kernel(RmTree t, const int* __restrict__ nodes, int 
     const int e = t.edge_len[v];
     const i64 off = t.edge_off[v];
     const int at = t.depth_end[v] - e;
-    for (int k = 0; k < e; ++k) row[at + k] = t.tok[off + k];
+    for (int k = 0; k < e; ++k) row[at + k] = rm_tok(t, off + k);
     v = t.parent[v];
   }
 }
@@ -790,8 +791,7 @@ __global__ void rm_scan_i64_kernel(i64* __restrict__ data, int n, i64* __restric
 // its new place (only this group reads edge_off[x])
 template <int G>
 __global__ void rm_compact_copy_kernel(RmTree t, int n, const unsigned* __restrict__ sval, const i64* __restrict__ new_off,
-                                       int* __restrict__ ntok, i64* __restrict__ nval, int* __restrict__ nseg,
-                                       int with_values) {
+                                       int2* __restrict__ nts, i64* __restrict__ nval, int with_values) {
   RmGroup<G> g;
   const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
   if (i >= n) return;
@@ -800,8 +800,7 @@ __global__ void rm_compact_copy_kernel(RmTree t, int n, const unsigned* __restri
   const i64 src = t.edge_off[x], dst = new_off[i];
   const int len = t.edge_len[x];
   for (int k = g.lane; k < len; k += G) {
-    ntok[dst + k] = t.tok[src + k];
-    nseg[dst + k] = t.seg[src + k];
+    nts[dst + k] = t.ts[src + k];
     if (with_values) nval[dst + k] = t.val[src + k];
   }
   g.sync();
@@ -814,7 +813,7 @@ __global__ void rm_compact_relink_kernel(RmTree t, int n) {
   if (x >= n || !rm_node_has_run(t, x)) return;
   if (t.gen[x] >= 0) {   // parked duplicates are not reachable from the table
     const i64 off = t.edge_off[x];
-    rm_table_insert(t, rm_key(t.parent[x], t.tok[off]), x, t.edge_len[x], off, t.rank[x]);
+    rm_table_insert(t, rm_key(t.parent[x], rm_tok(t, off)), x, t.edge_len[x], off, t.rank[x]);
   }
 }
 
@@ -846,14 +845,12 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
 #else
   RM_LAUNCH(rm_scan_i64_kernel, 1, 1024, s, new_off, n, total_d);
 #endif
-  int* ntok = nullptr;
+  int2* nts = nullptr;
   i64* nval = nullptr;
-  int* nseg = nullptr;
   const size_t cap = (size_t)t.max_tokens + RM_ARENA_PAD;
-  RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&ntok), sizeof(int) * cap));
-  RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&nseg), sizeof(int) * cap));
+  RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&nts), sizeof(int2) * cap));
   if (with_values) RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&nval), sizeof(i64) * cap));
-  RM_CUDA(cudaMemsetAsync(nseg, 0xFF, sizeof(int) * cap, s));
+  RM_CUDA(cudaMemsetAsync(nts, 0xFF, sizeof(int2) * cap, s));
 #ifdef RM_EMU
   auto kc = rm_compact_copy_kernel<1>;
   const long long cthreads = n;
@@ -861,15 +858,12 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
   auto kc = rm_compact_copy_kernel<32>;
   const long long cthreads = (long long)n * 32;
 #endif
-  RM_LAUNCH(kc, (int)((cthreads + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, n, sc.ev_val[w], new_off, ntok, nval, nseg,
-            with_values ? 1 : 0);
+  RM_LAUNCH(kc, (int)((cthreads + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, n, sc.ev_val[w], new_off, nts, nval, with_values ? 1 : 0);
   RM_CUDA(cudaGetLastError());
   RM_CUDA(cudaStreamSynchronize(s));
   // swap the arenas in, drop the old ones
-  cudaFree(t.tok);
-  cudaFree(t.seg);
-  t.tok = ntok;
-  t.seg = nseg;
+  cudaFree(t.ts);
+  t.ts = nts;
   if (with_values) {
     cudaFree(t.val);
     t.val = nval;

@@ -14,10 +14,9 @@
 // RM_STATIC_SCRATCH_BYTES of it until the process exits, used or not.  All calls, on all indexes
 // and streams of a device, share it, so two calls that overlap on the GPU race; issue them on one
 // stream or order them yourself.  It keeps the previous call's bytes and the entry point clears nothing:
-// each kernel writes every word it later reads (K1 fills the request arrays for all B queries, the sort
-// writes every bin of every tile before reading it); the only words that must be zero between calls are
-// the two grid-barrier words of the sort, which start at zero (static storage) and which every sort
-// leaves at zero.
+// each kernel writes every word it later reads (K1 fills the request arrays and chain links of every
+// request it counts; the split stage reads only those, and its rare sorted path writes its lists before
+// reading them), so nothing in the array has to start at zero.
 //
 // First call on a device: looks up the array's device address (cudaGetSymbolAddress) and caches it
 // per device.  In host code the array's name is only a handle for that lookup, never an address a
@@ -99,8 +98,6 @@ extern "C" int rm_match_batch_static(rm_index* idx, const int32_t* tokens, const
   view.uniq_pos = rm_carve<int>(cur, RM_STATIC_MAX_BATCH);
   view.uniq_min = rm_carve<unsigned>(cur, RM_STATIC_MAX_BATCH);
   view.link = rm_carve<int>(cur, RM_STATIC_MAX_BATCH);
-  view.hist_words = rm_sort_scratch_words(RM_STATIC_MAX_BATCH);
-  view.hist = rm_carve<unsigned>(cur, view.hist_words);
   if ((size_t)(cur - base) > (size_t)RM_STATIC_SCRATCH_BYTES) {
     rm_set_error("rm_match_batch_static: internal layout exceeds the static array");
     return RM_E_INVALID;

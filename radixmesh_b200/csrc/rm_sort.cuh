@@ -295,6 +295,101 @@ static __device__ __forceinline__ void rm_sort_body(u64* k0, unsigned* v0, u64* 
   }
 }
 
+// The same stable LSD sort run by ONE block of RM_SORT_TPB threads on any number of items, with shared memory as
+// its only scratch: per pass a digit histogram of all items, an exclusive scan, then tile after tile (2048 items) the
+// warp-level stable multisplit with running digit bases.  For the rare big groups of the split stage (rm_match.cu),
+// where the block that sorts is the last one alive of its launch.  Returns 0 if the result is in (k0, v0), 1 if in
+// (k1, v1).  Ends with a __syncthreads().
+static __device__ __forceinline__ int rm_sort_block(u64* k0, unsigned* v0, u64* k1, unsigned* v1, int n, int passes) {
+  __shared__ unsigned wcnt[RM_SORT_WARPS][256];
+  __shared__ unsigned base[256];
+  __shared__ unsigned wtot[RM_SORT_WARPS];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  const int tile = RM_SORT_TPB * 8;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = 8 * p;
+    const u64* kin = (p & 1) ? k1 : k0;
+    const unsigned* vin = (p & 1) ? v1 : v0;
+    u64* kout = (p & 1) ? k0 : k1;
+    unsigned* vout = (p & 1) ? v0 : v1;
+    base[threadIdx.x] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += RM_SORT_TPB) atomicAdd(&base[(unsigned)(__ldcg(kin + i) >> shift) & 255u], 1u);
+    __syncthreads();
+    {
+      const unsigned total = base[threadIdx.x];
+      unsigned inc = total;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += x;
+      }
+      if (lane == 31) wtot[wid] = inc;
+      __syncthreads();
+      unsigned run = inc - total;
+      for (int w = 0; w < wid; ++w) run += wtot[w];
+      base[threadIdx.x] = run;
+    }
+    __syncthreads();
+    for (int t0 = 0; t0 < n; t0 += tile) {
+      const int wbase = t0 + wid * (tile / RM_SORT_WARPS);
+      for (int i = threadIdx.x; i < RM_SORT_WARPS * 256; i += RM_SORT_TPB) (&wcnt[0][0])[i] = 0;
+      __syncthreads();
+      u64 kreg[8];
+      unsigned vreg[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int i = wbase + r * 32 + lane;
+        const bool ok = i < n;
+        kreg[r] = ok ? __ldcg(kin + i) : 0ull;
+        vreg[r] = ok ? __ldcg(vin + i) : 0u;
+      }
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int i = wbase + r * 32 + lane;
+        unsigned d = (i < n) ? ((unsigned)(kreg[r] >> shift) & 255u) : 0xFFFFu;
+        unsigned m = __match_any_sync(0xffffffffu, d);
+        if (d != 0xFFFFu && (m & lt) == 0) wcnt[wid][d] += __popc(m);
+        __syncwarp();
+      }
+      __syncthreads();
+      {
+        const unsigned d = threadIdx.x;
+        unsigned run = base[d];
+#pragma unroll
+        for (int w = 0; w < RM_SORT_WARPS; ++w) {
+          unsigned c = wcnt[w][d];
+          wcnt[w][d] = run;
+          run += c;
+        }
+        base[d] = run;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int i = wbase + r * 32 + lane;
+        const bool ok = i < n;
+        unsigned dd = ok ? ((unsigned)(kreg[r] >> shift) & 255u) : 0xFFFFu;
+        unsigned m = __match_any_sync(0xffffffffu, dd);
+        unsigned dst = 0;
+        if (ok) dst = wcnt[wid][dd] + __popc(m & lt);
+        __syncwarp();
+        if (ok && (m & lt) == 0) wcnt[wid][dd] += __popc(m);
+        __syncwarp();
+        if (ok) {
+          kout[dst] = kreg[r];
+          vout[dst] = vreg[r];
+        }
+      }
+      __syncthreads();
+    }
+    __threadfence_block();
+    __syncthreads();
+  }
+  return passes & 1;
+}
+
 // the last block out of a launch that used the barrier puts hist[0] and hist[1] back to zero
 static __device__ __forceinline__ void rm_sort_barrier_rearm(unsigned* hist, int nblk) {
   if (threadIdx.x == 0) {

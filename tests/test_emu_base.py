@@ -28,3 +28,16 @@ def test_emu_batched_match_splits_then_evict_order(seed):
 @pytest.mark.parametrize("seed", range(6))
 def test_emu_streaming_insert_evict_compact(seed):
     cases.run_stream_evict(make_index, seed)
+
+
+@pytest.mark.parametrize("small_max", ["1", "3"])
+def test_emu_split_stage_sorted_path(small_max):
+    """The split stage orders up to 32 requests per edge in registers and sorts only beyond that; with the bound cut to
+    1 or 3 the same scenarios push nearly every shared edge through the sorted path."""
+    import os
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, '.'); from tests import cases; from tests.emu.emu_backend import make_index; "
+            "[cases.run_split_evict(make_index, 200 + s) for s in range(10)]")
+    subprocess.run([sys.executable, "-c", code], check=True, env=dict(os.environ, RM_SPLIT_SMALL_MAX=small_max),
+                   cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

@@ -28,14 +28,15 @@ def test_gpu_batched_match_splits_then_evict_order(seed):
     cases.run_split_evict(make_index, seed)
 
 
-WALKS = [("run", 4), ("run", 8), ("run", 16), ("run", 32), ("lane", 1), ("table", 1), ("table", 2), ("table", 8), ("table", 32)]
+WALKS = [("run", 4), ("run", 8), ("run", 16), ("run", 32), ("table", 2), ("table", 8), ("table", 32)]
 
 
 @pytest.mark.parametrize("walk,group", WALKS, ids=[f"{w}{g}" for w, g in WALKS])
 def test_gpu_zipf_match_all_walk_kernels(walk, group):
     """Zipf shared-prefix workload at reduced size, device-pointer entry points, every form of the
-    walk kernel (run-following with 4..32 lanes per query, run-following lane per query, hop-by-hop through
-    the child table with 1..32 lanes per query): lengths, last nodes, values and final tree."""
+    walk kernel (run-following with 4..32 lanes per query - 32 is the product path, with the query staged in shared
+    memory - and hop-by-hop through the child table with 2..32 lanes per query): lengths, last nodes, values and
+    final tree."""
     import os
     import subprocess
     import sys
@@ -47,15 +48,70 @@ def test_gpu_zipf_match_all_walk_kernels(walk, group):
                    cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def test_gpu_zipf_match_one_launch_split_stage():
-    """The same check with the three split-stage kernels fused into one launch with grid barriers (RM_FUSED_SPLIT=1)."""
+@pytest.mark.parametrize("env", [{"RM_RUN_STAGE": "0"}, {"RM_RUN_DEPTH": "2"}, {"RM_RUN_DEPTH": "4"}, {"RM_RUN_MINB": "16"},
+                                 {"RM_SPLIT_SMALL_MAX": "1"}, {"RM_SPLIT_SMALL_MAX": "3"}],
+                         ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
+def test_gpu_zipf_match_kernel_options(env):
+    """The same check with the product walk's options (query read from global memory instead of staged, 2 or 4 steps
+    in flight, 16 blocks per SM) and with the split stage's in-register path cut down, so that edges with more than
+    1 or 3 requests go through its sorted path (run by the last block of the same launch)."""
     import os
     import subprocess
     import sys
     code = ("import sys; sys.path.insert(0, '.'); from tests.test_gpu_base import zipf_check; "
             "zipf_check(seed=7, n_docs=64, L=96, n_ins=600, n_q=3000)")
-    subprocess.run([sys.executable, "-c", code], check=True, env=dict(os.environ, RM_FUSED_SPLIT="1"),
+    subprocess.run([sys.executable, "-c", code], check=True, env=dict(os.environ, **env),
                    cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+@pytest.mark.parametrize("small_max", [None, "1", "5"])
+def test_gpu_split_stage_paths(small_max):
+    """Split/evict scenarios (tens of requests per edge) with every request-count class of the split stage in play."""
+    import os
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, '.'); from tests import cases; from tests.test_gpu_base import make_index; "
+            "[cases.run_split_evict(make_index, 100 + s) for s in range(6)]")
+    env = dict(os.environ) if small_max is None else dict(os.environ, RM_SPLIT_SMALL_MAX=small_max)
+    subprocess.run([sys.executable, "-c", code], check=True, env=env,
+                   cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def test_gpu_many_requests_on_one_edge():
+    """A batch that meets a long unsplit edge for the first time: thousands of requests on ONE edge (and a second
+    edge with a few hundred), far beyond what a warp orders in registers - the sorted path of the split stage, more
+    than one tile of its single-block sort."""
+    import torch
+    from oracle.radix_port import PortRadixCache
+    from tests.parity import assert_same_digest, device_digest, oracle_digest
+    rng = np.random.default_rng(5)
+    L = 600
+    docs = rng.integers(0, 32000, (3, L), dtype=np.int32)
+    ix = make_index(mode=0, max_nodes=1 << 14, max_tokens=1 << 16, max_batch=8192, max_key_len=1024)
+    orc = PortRadixCache(1)
+    vals = np.arange(3 * L, dtype=np.int64)
+    got = ix.insert_host(docs.reshape(-1).copy(), vals, np.arange(0, 4 * L, L, dtype=np.int64))
+    assert got.tolist() == [orc.insert(d.tolist(), vals[i * L:(i + 1) * L]) for i, d in enumerate(docs)]
+    for rnd in range(2):
+        qs = []
+        for _ in range(6000):
+            d = 0 if rng.random() < 0.9 else (1 if rng.random() < 0.9 else 2)
+            cut = int(rng.integers(1, L + 1))
+            qs.append(docs[d, :cut].tolist() + [40000])
+        tk, offs = pack(qs)
+        ol = np.zeros(len(qs), np.int32)
+        on = np.zeros(len(qs), np.int32)
+        ix.match_host(tk, offs, ol, on)
+        exp = [orc.match_prefix(k) for k in qs]
+        assert ol.tolist() == [len(m.indices) for m in exp]
+        dd, od = device_digest(ix), oracle_digest(orc)
+        assert_same_digest(dd, od)
+        assert [dd["by_id"][x] for x in on.tolist()] == [od["by_node"][m.last_node] for m in exp]
+    ix.check_device_error()
+    _, eo, el = ix.evict(1 << 30)
+    orc.evict(1 << 30)
+    assert el.tolist() == [len(r) for r in orc.freed]
+    ix.close()
 
 
 def test_gpu_zipf_match_without_dependent_launch():
