@@ -36,8 +36,11 @@ typedef enum {
   RM_E_CUDA = 2,        /* a CUDA runtime call failed; rm_last_error() has the text */
   RM_E_NOSPACE = 3,     /* node pool / edge arena / scratch exhausted (the reference cannot produce this) */
   RM_E_TOO_LARGE = 4,   /* batch larger than rm_config.max_batch */
-  RM_E_MODE = 5         /* operation not allowed in this mode (e.g. insert on a ROUTER index,
+  RM_E_MODE = 5,        /* operation not allowed in this mode (e.g. insert on a ROUTER index,
                            radix/radix_mesh.py:194) */
+  RM_E_TABLE = 6        /* a child-table probe visited every slot: no empty slot is left (tombstones of evicted
+                           nodes took them).  rm_evict rebuilds the table long before that; rm_compact does too.
+                           Raised on the device (sticky, rm_sizes.device_error) instead of spinning. */
 } rm_status;
 
 /* Tree semantics selector.  BASE = RadixCache (radix/sglang/srt/mem_cache/radix_cache.py:87);
@@ -67,8 +70,10 @@ typedef struct {
   int64_t arena_used;    /* tokens handed out of the edge arena (monotonic until rm_compact) */
   int64_t n_dups;        /* live entries in the duplicate-node table */
   int64_t op_seq;        /* operations applied so far (the logical clock) */
-  int32_t device_error;  /* sticky rm_status raised inside a kernel (RM_E_NOSPACE) */
-  int32_t pad;
+  int32_t device_error;  /* sticky rm_status raised inside a kernel (RM_E_NOSPACE, RM_E_TABLE) */
+  int32_t node_hwm;      /* high-water node id + 1 */
+  int32_t table_slots;   /* child-table capacity (a power of two >= 2 * max_nodes) */
+  int32_t table_tombs;   /* of those, tombstones left by evicted nodes (rm_evict rebuilds the table at a quarter) */
 } rm_sizes_t;
 
 const char* rm_last_error(void);

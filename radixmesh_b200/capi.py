@@ -15,7 +15,7 @@ import numpy as np
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "_lib", "libradixmesh_b200.so")
 
-RM_OK, RM_E_INVALID, RM_E_CUDA, RM_E_NOSPACE, RM_E_TOO_LARGE, RM_E_MODE = range(6)
+RM_OK, RM_E_INVALID, RM_E_CUDA, RM_E_NOSPACE, RM_E_TOO_LARGE, RM_E_MODE, RM_E_TABLE = range(7)
 MODE_BASE, MODE_PREFILL, MODE_DECODE, MODE_ROUTER = range(4)
 
 
@@ -29,7 +29,8 @@ class RmConfig(C.Structure):
 class RmSizes(C.Structure):
     _fields_ = [("evictable", C.c_int64), ("protected_", C.c_int64), ("n_nodes", C.c_int64),
                 ("arena_used", C.c_int64), ("n_dups", C.c_int64), ("op_seq", C.c_int64),
-                ("device_error", C.c_int32), ("node_hwm", C.c_int32)]
+                ("device_error", C.c_int32), ("node_hwm", C.c_int32), ("table_slots", C.c_int32),
+                ("table_tombs", C.c_int32)]
 
 
 class RadixMeshError(RuntimeError):

@@ -428,7 +428,9 @@ int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream) {
   out_h->n_dups = c.n_dups;
   out_h->op_seq = (int64_t)idx->op_seq;
   out_h->device_error = c.err;
-  out_h->pad = c.node_hwm;
+  out_h->node_hwm = c.node_hwm;
+  out_h->table_slots = (int32_t)(idx->t.table_mask + 1);
+  out_h->table_tombs = c.n_tomb;
   if (getenv("RM_DEBUG_COUNTERS")) fprintf(stderr, "[rm] n_req %d on_shared_edges %d groups %d max_group %d  insert records ordered %llu resumed %llu\n", c.n_req, c.n_big, c.dbg_groups, c.dbg_max_group, c.ins_ordered, c.ins_resumed);
   return RM_OK;
 }

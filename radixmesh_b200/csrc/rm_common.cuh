@@ -97,6 +97,7 @@ struct RmCounters {
                       // (kept next to n_req: one memset clears both)
   int evict_n;        // scratch: nodes evicted by the current rm_evict
   unsigned split_done; // scratch: blocks of the split kernel that have finished (the last one runs the rare big groups)
+  int n_tomb;         // tombstoned child-table slots (evicted nodes); empty slots = capacity - n_nodes - n_tomb
   int dbg_max_group;  // largest split-request group seen (diagnostics)
   int dbg_groups;     // split-request groups seen (diagnostics)
   int ev_total;       // scratch: eviction candidates (leaves up to the frontier key + the parents they expose)
@@ -243,10 +244,13 @@ __device__ __forceinline__ int rm_ld_query(const int* p, u64 pol) {
 // Probe the child table for `key`.  Returns the slot index or -1.  Every lane of the calling
 // group passes the same key, so the loads are broadcasts (one 32-byte sector per probe step).
 // COHERENT = true reads through L2 (ld.cg) for kernels that mutate the table themselves.
+// A probe sequence ends at an EMPTY slot; tombstones do not end it.  Every loop over the table is bounded by the
+// table size and raises the sticky RM_E_TABLE instead of spinning if it has seen every slot (rm_evict rebuilds the
+// table when tombstones have taken a quarter of it, so this is a safety net, not a code path).
 template <bool COHERENT>
 __device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
   unsigned i = rm_hash(key, t.table_shift);
-  while (true) {
+  for (unsigned steps = 0; steps <= t.table_mask; ++steps) {
     const int4* p = reinterpret_cast<const int4*>(t.table + i);
     int4 a = COHERENT ? __ldcg(p) : __ldg(p);
     u64 k = ((u64)(unsigned)a.y << 32) | (unsigned)a.x;
@@ -263,6 +267,8 @@ __device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
     if (k == RM_EMPTY_KEY) return -1;
     i = (i + 1) & t.table_mask;
   }
+  atomicMax(&t.ctr->err, (int)RM_E_TABLE);
+  return -1;
 }
 
 __device__ __forceinline__ void rm_slot_store(const RmTree& t, RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank) {
@@ -283,20 +289,23 @@ __device__ __forceinline__ void rm_slot_set_rank(RmSlot* s, int rank) { s->len_r
 // not present.  One lane calls this.
 __device__ __forceinline__ void rm_table_insert(const RmTree& t, u64 key, int child, int edge_len, i64 edge_off, int rank) {
   unsigned i = rm_hash(key, t.table_shift);
-  while (true) {
+  for (unsigned steps = 0; steps <= t.table_mask;) {
     u64* kp = &t.table[i].key;
     u64 cur = *reinterpret_cast<volatile u64*>(kp);
     if (cur == RM_EMPTY_KEY || cur == RM_TOMB_KEY) {
       // reserve with a key nobody looks up (parent id 0xFFFFFFFD never exists), then publish
       u64 reserve = 0xFFFFFFFD00000000ull | (unsigned)child;
       if (atomicCAS(kp, cur, reserve) == cur) {
+        if (cur == RM_TOMB_KEY) atomicSub(&t.ctr->n_tomb, 1);
         rm_slot_store(t, &t.table[i], key, child, edge_len, edge_off, rank);
         return;
       }
       continue;  // lost the race for this slot: look at it again
     }
     i = (i + 1) & t.table_mask;
+    ++steps;
   }
+  atomicMax(&t.ctr->err, (int)RM_E_TABLE);   // every slot is taken: the node stays unreachable, the error is sticky
 }
 
 // Pop `n` node ids from the free ring.  One lane calls this; returns the ring position of the

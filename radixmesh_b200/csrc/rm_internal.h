@@ -92,6 +92,7 @@ int rm_launch_lock(rm_index* idx, const int* nodes, int B, int dir, i64* out_del
 int rm_launch_lock_g(rm_index* idx, const int* nodes, const int* gens, int B, int dir, i64* out_delta, cudaStream_t s);
 int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
                     int* out_n_h, cudaStream_t s);
+int rm_table_rebuild(rm_index* idx, int n_nodes_hwm, cudaStream_t s);
 int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int* out_n_h, cudaStream_t s);
 int rm_launch_gc_agree(rm_index* idx, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n,
                        unsigned char* out_agree_h, cudaStream_t s);

@@ -50,6 +50,7 @@ __global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
     c.n_req = 0;
     c.evict_n = 0;
     c.split_done = 0;
+    c.n_tomb = 0;
     c.n_big = 0;
     c.dbg_max_group = 0;
     c.dbg_groups = 0;
@@ -394,7 +395,10 @@ __global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sva
   out_lens[k] = len;
   RmSlot s;
   int sidx = rm_find<true>(t, rm_key(par, rm_tok(t, off)), s);
-  if (sidx >= 0) *reinterpret_cast<volatile u64*>(&t.table[sidx].key) = RM_TOMB_KEY;
+  if (sidx >= 0) {
+    *reinterpret_cast<volatile u64*>(&t.table[sidx].key) = RM_TOMB_KEY;
+    atomicAdd(&t.ctr->n_tomb, 1);
+  }
   for (int k2 = 0; k2 < len; ++k2) rm_set_seg(t, off + k2, -1);   // the run is free again
   if (par > 0) atomicMax(&t.stamp[par], eff[x]);            // lazy stamps: the parent keeps what it saw through x
   atomicSub(&t.nchild[par], 1);
@@ -475,6 +479,7 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
     RM_CUDA(cudaStreamSynchronize(s));
   }
   *out_n_h = k;
+  if ((u64)c.n_tomb * 4 > (u64)t.table_mask + 1) return rm_table_rebuild(idx, c.node_hwm, s);
   return RM_OK;
 }
 
@@ -817,6 +822,18 @@ __global__ void rm_compact_relink_kernel(RmTree t, int n) {
   }
 }
 
+// Rebuild the child table from the node pool: one slot per live tree node, no tombstones.  The reference deletes a
+// child from a dict (radix_cache.py:347-352) and the dict shrinks; an open-addressed table only gets its empty slots
+// back this way.  rm_evict calls it once tombstones hold a quarter of the table; rm_compact always does.
+int rm_table_rebuild(rm_index* idx, int n_nodes_hwm, cudaStream_t s) {
+  RmTree& t = idx->t;
+  RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
+  RM_CUDA(cudaMemsetAsync(&t.ctr->n_tomb, 0, sizeof(int), s));
+  if (n_nodes_hwm > 0) RM_LAUNCH(rm_compact_relink_kernel, (n_nodes_hwm + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n_nodes_hwm);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
 static int rm_bits_u64(u64 v) {
   int b = 1;
   while ((v >> b) != 0 && b < 63) ++b;
@@ -869,6 +886,7 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
     t.val = nval;
   }
   RM_CUDA(cudaMemsetAsync(t.table, 0xFF, sizeof(RmSlot) * ((size_t)t.table_mask + 1), s));
+  RM_CUDA(cudaMemsetAsync(&t.ctr->n_tomb, 0, sizeof(int), s));
   RM_LAUNCH(rm_compact_relink_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n);
   i64 total = 0;
   RM_CUDA(cudaMemcpyAsync(&total, total_d, sizeof(i64), cudaMemcpyDeviceToHost, s));

@@ -74,7 +74,11 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
   while (have) {
     // resolve the probe: linear probing past foreign keys (rare at load factor <= 0.5)
     u64 k = ((u64)(unsigned)sa.y << 32) | (unsigned)sa.x;
-    while (k != want && k != RM_EMPTY_KEY) {
+    for (unsigned steps = 0; k != want && k != RM_EMPTY_KEY; ++steps) {
+      if (steps > t.table_mask) {          // saw every slot: no empty one is left (see rm_find)
+        atomicMax(&t.ctr->err, (int)RM_E_TABLE);
+        break;
+      }
       si = (si + 1) & t.table_mask;
       const int4* p = reinterpret_cast<const int4*>(t.table + si);
       sa = __ldg(p);
@@ -277,6 +281,7 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
     i64 cs = 0;
     {
       unsigned si = rm_hash2((unsigned)node, (unsigned)tk, tshift);
+      unsigned steps = 0;
       while (true) {
         const RmSlotRegs S = rm_ld_slot(table + si);
         if ((unsigned)S.a.x == (unsigned)tk && (unsigned)S.a.y == (unsigned)node) {
@@ -286,6 +291,10 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
         }
         if ((S.a.x & S.a.y) == -1) break;
         si = (si + 1) & tmask;
+        if (++steps > tmask) {             // saw every slot: no empty one is left (see rm_find)
+          atomicMax(&t.ctr->err, (int)RM_E_TABLE);
+          break;
+        }
       }
     }
     if (cur < 0) break;                 // the walk ends at `node`

@@ -190,3 +190,52 @@ def run_stream_evict(make_index, seed, n_batches=12, batch=48, L=24, n_docs=12, 
         assert_same_tree(device_canonical(ix), orc.canonical())
     assert n_evicted > 0
     ix.close()
+
+
+def run_tombstone_pressure(make_index, seed, rounds=60):
+    """A small index under a long insert / match (splitting) / evict stream: every eviction tombstones a child-table
+    slot and every insert or split takes a free one, so without a rebuild the empty slots of the table run out (the
+    256-slot table here sees well over 256 evictions) and every miss probe would walk the whole table.  rm_evict rebuilds
+    the table when tombstones hold a quarter of it; results must stay identical to the oracle's throughout and the
+    sticky RM_E_TABLE must never be raised."""
+    rnd = random.Random(seed)
+    ix = make_index(mode=0, max_nodes=128, max_tokens=1 << 14, max_batch=64, max_key_len=64)
+    orc = PortRadixCache(1)
+    vc = 0
+    n_evicted = 0
+    max_tombs = 0
+    for r in range(rounds):
+        keys = [[rnd.randrange(3) for _ in range(rnd.randrange(4, 14))] for _ in range(rnd.randrange(2, 6))]
+        vals = []
+        for k in keys:
+            vals.append(list(range(vc, vc + len(k))))
+            vc += len(k)
+        if ix.sizes().arena_used + sum(len(k) for k in keys) > (1 << 14) - 256:
+            ix.compact()
+        tk, offs = pack(keys)
+        vv, _ = pack(vals, np.int64)
+        got = ix.insert_host(tk, vv, offs)
+        assert got.tolist() == [orc.insert(list(k), np.asarray(v, dtype=np.int64)) for k, v in zip(keys, vals)]
+        for _ in range(2):      # matches that split, then misses that probe for absent children
+            qs = [[rnd.randrange(3) for _ in range(rnd.randrange(1, 12))] + [7] for _ in range(rnd.randrange(2, 10))]
+            tk, offs = pack(qs)
+            ol = np.zeros(len(qs), np.int32)
+            on = np.zeros(len(qs), np.int32)
+            ix.match_host(tk, offs, ol, on)
+            assert ol.tolist() == [len(orc.match_prefix(list(k)).indices) for k in qs]
+        n = orc.evictable_size() - rnd.randrange(0, 12)
+        before = len(orc.freed)
+        orc.evict(n)
+        _, eo, el = ix.evict(n)
+        assert [ix.read_arena(int(o), int(l))[1].tolist() for o, l in zip(eo, el)] == orc.freed[before:]
+        n_evicted += len(eo)
+        ix.check_device_error()
+        s = ix.sizes()
+        assert s.table_slots == 256 and 0 <= s.table_tombs <= s.table_slots // 4, (s.table_slots, s.table_tombs)
+        max_tombs = max(max_tombs, s.table_tombs)
+        if r % 10 == 9:
+            assert_same_tree(device_canonical(ix), orc.canonical())
+    assert n_evicted > 256, n_evicted          # more evictions than the table has slots ...
+    assert max_tombs > 0                       # ... and tombstones were seen and kept in check
+    assert_same_tree(device_canonical(ix), orc.canonical())
+    ix.close()

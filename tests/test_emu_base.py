@@ -30,6 +30,11 @@ def test_emu_streaming_insert_evict_compact(seed):
     cases.run_stream_evict(make_index, seed)
 
 
+@pytest.mark.parametrize("seed", range(3))
+def test_emu_tombstone_pressure_rebuilds_the_table(seed):
+    cases.run_tombstone_pressure(make_index, seed)
+
+
 @pytest.mark.parametrize("small_max", ["1", "3"])
 def test_emu_split_stage_sorted_path(small_max):
     """The split stage orders up to 32 requests per edge in registers and sorts only beyond that; with the bound cut to

@@ -185,6 +185,11 @@ def test_gpu_streaming_insert_evict_compact(seed):
     cases.run_stream_evict(make_index, seed, n_batches=16, batch=96, L=32, n_docs=24, capacity=6000)
 
 
+@pytest.mark.parametrize("seed", range(2))
+def test_gpu_tombstone_pressure_rebuilds_the_table(seed):
+    cases.run_tombstone_pressure(make_index, seed)
+
+
 def test_gpu_radix_sort_all_forms():
     """tools/sort_probe.cu (built by __graft_entry__.build()): the device radix sort against std::stable_sort for
     item counts from 0 to 1 M with the count read on the device - one block alone, the one-launch grid form, and
