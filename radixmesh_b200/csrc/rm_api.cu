@@ -32,6 +32,10 @@ static cudaError_t rm_dalloc(T** p, size_t n) {
   return cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * (n ? n : 1));
 }
 
+#ifndef RM_EMU
+static __global__ void rm_policy_kernel(u64* out) { *out = rm_policy_evict_first(); }
+#endif
+
 extern "C" {
 
 const char* rm_last_error(void) { return g_err; }
@@ -221,6 +225,17 @@ int rm_create(const rm_config* cfg, rm_index** out) {
     rm_destroy(idx);
     return RM_E_NOSPACE;
   }
+#ifndef RM_EMU
+  {
+    // the counters block is free until the reset below fills it: borrow its first word
+    rm_policy_kernel<<<1, 1>>>(reinterpret_cast<u64*>(t.ctr));
+    if (cudaMemcpy(&t.qpol, t.ctr, sizeof(u64), cudaMemcpyDeviceToHost) != cudaSuccess) {
+      rm_set_error("rm_create: cache policy set-up failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rm_destroy(idx);
+      return RM_E_CUDA;
+    }
+  }
+#endif
   int rc = rm_launch_reset(idx, 0);
   if (rc == RM_OK && cudaStreamSynchronize(0) != cudaSuccess) rc = RM_E_CUDA;
   if (rc != RM_OK) {

@@ -132,6 +132,7 @@ struct RmTree {
   int max_nodes;
   i64 max_tokens;
   int mode, n_prefill, n_decode, self_rank;
+  u64 qpol;        // L2 evict-first cache-policy descriptor for query loads (createpolicy, evaluated once at rm_create)
   // duplicate-node table (RadixMesh.dup_nodes): open addressed, key (tree node << 32 | rank+1)
   u64* dup_key;
   int* dup_parked;
@@ -195,6 +196,16 @@ struct RmGroup {
     if (G == 1) return v;
     return __shfl_up_sync(mask, v, d, G);
 #endif
+  }
+  __device__ __forceinline__ int reduce_max(int v) const {
+#ifndef RM_EMU
+#pragma unroll
+    for (int d = G >> 1; d > 0; d >>= 1) {
+      const int o = __shfl_xor_sync(mask, v, d, G);
+      v = o > v ? o : v;
+    }
+#endif
+    return v;
   }
   __device__ __forceinline__ void sync() const {
     if (G > 1) __syncwarp(mask);
@@ -271,34 +282,41 @@ __device__ __forceinline__ int rm_find(const RmTree& t, u64 key, RmSlot& out) {
   return -1;
 }
 
-__device__ __forceinline__ void rm_slot_store(const RmTree& t, RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank) {
+__device__ __forceinline__ void rm_slot_store_toks(RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank, int tok1, int tok2) {
   // payload first, key last.  No fence: inside one kernel only the warp that inserts a key looks it
   // up again (program order + __syncwarp cover that); every other reader runs in a later kernel.
   s->child = child;
   s->len_rank = rm_slot_pack(edge_len, rank);
   s->edge_off = edge_off;
-  s->tok1 = edge_len > 1 ? rm_tok(t, edge_off + 1) : 0;   // the edge's tokens are in the arena already
-  s->tok2 = edge_len > 2 ? rm_tok(t, edge_off + 2) : 0;
+  s->tok1 = tok1;
+  s->tok2 = tok2;
   *reinterpret_cast<volatile u64*>(&s->key) = key;
+}
+__device__ __forceinline__ void rm_slot_store(const RmTree& t, RmSlot* s, u64 key, int child, int edge_len, i64 edge_off, int rank) {
+  // the edge's tokens are in the arena already
+  rm_slot_store_toks(s, key, child, edge_len, edge_off, rank, edge_len > 1 ? rm_tok(t, edge_off + 1) : 0,
+                     edge_len > 2 ? rm_tok(t, edge_off + 2) : 0);
 }
 // in-place edits of a live slot (its key and edge start do not change, so the inline tokens stay valid)
 __device__ __forceinline__ void rm_slot_set_len(RmSlot* s, int len) { s->len_rank = (s->len_rank & 0xFF000000u) | ((unsigned)len & 0xFFFFFFu); }
 __device__ __forceinline__ void rm_slot_set_rank(RmSlot* s, int rank) { s->len_rank = (s->len_rank & 0xFFFFFFu) | ((unsigned)(rank + 1) << 24); }
 
-// Claim a free (empty or tombstoned) slot for `key` and fill it.  Caller guarantees the key is
-// not present.  One lane calls this.
-__device__ __forceinline__ void rm_table_insert(const RmTree& t, u64 key, int child, int edge_len, i64 edge_off, int rank) {
+// Claim a free (empty or tombstoned) slot for `key` and return it reserved: the caller fills it (rm_slot_store*).
+// Caller guarantees the key is not present.  One lane calls this.  The claim is the FIRST access to a slot: a
+// compare-and-swap that expects EMPTY (most probes end there at load factor <= 0.5) and tells what the slot holds
+// otherwise, so the common case is one memory round trip, not a load followed by the swap.
+__device__ __forceinline__ RmSlot* rm_table_claim(const RmTree& t, u64 key, int child) {
   unsigned i = rm_hash(key, t.table_shift);
+  // reserve with a key nobody looks up (parent id 0xFFFFFFFD never exists), then publish
+  const u64 reserve = 0xFFFFFFFD00000000ull | (unsigned)child;
   for (unsigned steps = 0; steps <= t.table_mask;) {
     u64* kp = &t.table[i].key;
-    u64 cur = *reinterpret_cast<volatile u64*>(kp);
-    if (cur == RM_EMPTY_KEY || cur == RM_TOMB_KEY) {
-      // reserve with a key nobody looks up (parent id 0xFFFFFFFD never exists), then publish
-      u64 reserve = 0xFFFFFFFD00000000ull | (unsigned)child;
-      if (atomicCAS(kp, cur, reserve) == cur) {
-        if (cur == RM_TOMB_KEY) atomicSub(&t.ctr->n_tomb, 1);
-        rm_slot_store(t, &t.table[i], key, child, edge_len, edge_off, rank);
-        return;
+    u64 cur = atomicCAS(kp, RM_EMPTY_KEY, reserve);
+    if (cur == RM_EMPTY_KEY) return &t.table[i];
+    if (cur == RM_TOMB_KEY) {
+      if (atomicCAS(kp, RM_TOMB_KEY, reserve) == RM_TOMB_KEY) {
+        atomicSub(&t.ctr->n_tomb, 1);
+        return &t.table[i];
       }
       continue;  // lost the race for this slot: look at it again
     }
@@ -306,6 +324,16 @@ __device__ __forceinline__ void rm_table_insert(const RmTree& t, u64 key, int ch
     ++steps;
   }
   atomicMax(&t.ctr->err, (int)RM_E_TABLE);   // every slot is taken: the node stays unreachable, the error is sticky
+  return nullptr;
+}
+__device__ __forceinline__ void rm_table_insert(const RmTree& t, u64 key, int child, int edge_len, i64 edge_off, int rank) {
+  RmSlot* s = rm_table_claim(t, key, child);
+  if (s) rm_slot_store(t, s, key, child, edge_len, edge_off, rank);
+}
+__device__ __forceinline__ void rm_table_insert_toks(const RmTree& t, u64 key, int child, int edge_len, i64 edge_off, int rank,
+                                                     int tok1, int tok2) {
+  RmSlot* s = rm_table_claim(t, key, child);
+  if (s) rm_slot_store_toks(s, key, child, edge_len, edge_off, rank, tok1, tok2);
 }
 
 // Pop `n` node ids from the free ring.  One lane calls this; returns the ring position of the

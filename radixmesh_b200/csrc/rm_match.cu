@@ -211,7 +211,7 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
   const unsigned tmask = t.table_mask, tshift = t.table_shift;
   const int2* __restrict__ ts = t.ts;
   u64* __restrict__ stamp = t.stamp;
-  const u64 qpol = rm_policy_evict_first();
+  const u64 qpol = t.qpol;               // L2 evict-first descriptor, made once per index: a kernel parameter stays in uniform registers
   const int lane = g.lane;
 
   // ---- query staging (STAGE only)
@@ -229,8 +229,7 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       const int nb = min(16, (qend - t0) * 4);
       if (nb > 0) {
         const unsigned dst = (unsigned)__cvta_generic_to_shared(qbuf + (t0 & (2 * RM_QCH - 1)));
-        asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2, %3;" ::"r"(dst), "l"(qbase + t0), "r"(nb),
-                     "l"(rm_policy_evict_first())
+        asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2, %3;" ::"r"(dst), "l"(qbase + t0), "r"(nb), "l"(qpol)
                      : "memory");
       }
     }
@@ -298,31 +297,32 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       }
     }
     if (cur < 0) break;                 // the walk ends at `node`
-    // ---- stream along the arena run: position a + lane against query token qi + lane
-    i64 a = cs + 1;
+    // ---- stream along the arena run: position a + lane against query token qi + lane.  Per-lane running
+    // pointers: a round costs DEPTH loads with immediate offsets, not DEPTH 64-bit address computations.
+    const int2* __restrict__ tp = ts + (cs + 1 + lane);
     int qi = pos + 1;
-    int lastown = cur;                  // owner of position a - 1
+    int lastown = cur;                  // owner of the position before the round
     bool leave = false;
     while (!leave && !done) {
       int2 tv[DEPTH];
       int kjv[DEPTH];
 #pragma unroll
-      for (int u = 0; u < DEPTH; ++u) tv[u] = __ldg(ts + (a + u * G + lane));
+      for (int u = 0; u < DEPTH; ++u) tv[u] = __ldg(tp + u * G);
 #ifndef RM_EMU
       if (STAGE) q_ensure(qi, DEPTH * G);
 #endif
+      const int lim = L - qi - lane;    // this lane's position u*G is inside the query iff u*G < lim
       if (!STAGE) {
+        const int* __restrict__ kp = key + qi + lane;
 #pragma unroll
-        for (int u = 0; u < DEPTH; ++u) {
-          const int iq = qi + u * G + lane;
-          kjv[u] = iq < L ? rm_ld_query(key + iq, qpol) : 0;
-        }
+        for (int u = 0; u < DEPTH; ++u) kjv[u] = u * G < lim ? rm_ld_query(kp + u * G, qpol) : 0;
       }
+      bool all = true;
 #pragma unroll
       for (int u = 0; u < DEPTH; ++u) {
         const int tj = tv[u].x, sj = tv[u].y;
-        const bool inq = qi + lane < L;
-        const int kj = STAGE ? (inq ? ldq(qi + lane) : 0) : kjv[u];
+        const bool inq = u * G < lim;
+        const int kj = STAGE ? (inq ? ldq(qi + u * G + lane) : 0) : kjv[u];
         const int own = sj < 0 ? -1 : (sj & 0x3FFFFFFF);
         int prev = g.shfl_up(own, 1);
         if (lane == 0) prev = lastown;
@@ -352,15 +352,14 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
           }
         }
         if (s == G) {                      // everything matched: next G positions
-          a += G;
-          qi += G;
           lastown = g.bcast(own, G - 1);
           continue;
         }
-        // the match stops at relative position s
+        // the match stops at position s of step u
+        all = false;
         const int own_s = g.bcast(own, s);
         const int prev_s = g.bcast(prev, s);
-        pos = qi + s;
+        pos = qi + u * G + s;
         if (own_s != prev_s) {
           // node prev_s ended exactly there and is matched in full; either the query is exhausted or the next node
           // is not a contiguous match: back to the child table
@@ -379,7 +378,8 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
             // Until then the walk's endpoint is the node above.
             node = t.parent[own_s];
             const i64 eo = t.edge_off[own_s];
-            req = ((u64)(unsigned)own_s << len_bits) | (u64)(unsigned)(a + s - eo);
+            const i64 apos = (i64)((tp - lane) - ts) + u * G + s;      // arena position of the stop
+            req = ((u64)(unsigned)own_s << len_bits) | (u64)(unsigned)(apos - eo);
           } else {
             if (ROUTER) {
               const int rk = t.rank[own_s];
@@ -397,6 +397,10 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
           done = true;
         }
         break;
+      }
+      if (all) {
+        tp += DEPTH * G;
+        qi += DEPTH * G;
       }
     }
   }
@@ -430,7 +434,8 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
 }
 
 #define RM_FILL_COOP 48   // owner-map fills longer than this are done by the whole warp
-#define RM_SMALL_MAX 32   // requests on one edge that a warp orders in registers (more: the sorted path)
+#define RM_SMALL_MAX 32   // requests on one edge that a warp orders among its lanes (more: the sorted path)
+#define RM_THREAD_MAX 8   // requests on one edge that a single thread orders by itself
 
 
 // K3: one group per edge that received split requests.  `skey` is sorted by (node, split point) and,
@@ -766,7 +771,7 @@ __device__ __forceinline__ void rm_split_small_group(const RmTree& t, const u64*
 // That last block also zeroes the batch counters, so a match batch needs no memset.
 template <int G>
 __global__ void __launch_bounds__(RM_MATCH_TPB)
-rm_split_kernel(RmTree t, u64* rkey, unsigned* rval, int Bmax, int len_bits, int passes, int small_max, u64 seq_base,
+rm_split_kernel(RmTree t, u64* rkey, unsigned* rval, int Bmax, int len_bits, int passes, int small_max, int thread_max, u64 seq_base,
                 int* __restrict__ out_node, u64* mkey, unsigned* mval, u64* __restrict__ sufmax, int* __restrict__ krank,
                 int* __restrict__ uniq_pos, unsigned* __restrict__ uniq_min) {
   __shared__ int sp[RM_MATCH_TPB / 32 > 0 ? RM_MATCH_TPB / 32 : 1][RM_SMALL_MAX];
@@ -777,85 +782,116 @@ rm_split_kernel(RmTree t, u64* rkey, unsigned* rval, int Bmax, int len_bits, int
   const int wid = G == 1 ? 0 : (int)(threadIdx.x >> 5);
   const int n_req_now = *(volatile int*)&t.ctr->n_req;
   const int B = min(n_req_now, Bmax);
-  const int gthreads = (int)(gridDim.x * blockDim.x);
-  for (int base = (int)(blockIdx.x * blockDim.x); base < B; base += gthreads) {
+  // Two roles when the grid allows it: even blocks apply the single requests, odd blocks the small groups - each set
+  // walks the whole request list, so a group's chain of dependent memory round trips (about twice a single's) runs
+  // beside the singles instead of after them in the same threads.
+  const bool roles = thread_max > 1 && gridDim.x >= 2 && (gridDim.x & 1) == 0 && G > 1;
+  const int role = roles ? (int)(blockIdx.x & 1) : -1;            // 0: singles, 1: groups, -1: both
+  const int gthreads = (int)((roles ? gridDim.x >> 1 : gridDim.x) * blockDim.x);
+  for (int base = (int)((roles ? blockIdx.x >> 1 : blockIdx.x) * blockDim.x); base < B; base += gthreads) {
     const int i = base + (int)threadIdx.x;
     // owner-map fill of a single split's upper node, done by the whole warp after the per-thread part (a thread
     // writing its own p-1 words one after another made this stage 57 us on 4096-token keys)
     i64 fill_off = 0;
     int fill_n = 0, fill_id = 0;
     int grp_c = -1, grp_n = 0;             // set by the head of a small group
+    // ---- per request: classify
+    bool single = false;
+    u64 ki = 0;
+    int c = 0, par = 0, len = 0, dend = 0, lk = 0, rk = 0;
+    unsigned q = 0;
+    i64 off = 0;
+    u64 st_c = 0;
     if (i < B) {
-      const u64 ki = rkey[i];
-      const int c = (int)(ki >> len_bits);
-      const unsigned q = rval[i];
+      ki = rkey[i];
+      c = (int)(ki >> len_bits);
+      q = rval[i];
       // everything that depends only on (c, q) is loaded at once, before any of it is tested: one memory round trip
       const int head = t.req_head[c];
       const int n = t.req_cnt[c];
-      const int par = t.parent[c];
-      const i64 off = t.edge_off[c];
-      const int len = t.edge_len[c];
-      const int dend = t.depth_end[c];
-      const int lk = t.lock_ref[c];
-      const int rk = t.rank[c];
-      const u64 st_c = t.stamp[c];
+      par = t.parent[c];
+      off = t.edge_off[c];
+      len = t.edge_len[c];
+      dend = t.depth_end[c];
+      lk = t.lock_ref[c];
+      rk = t.rank[c];
+      st_c = t.stamp[c];
       const bool is_head = head == i;
-      if (is_head) {
-        t.req_head[c] = -1;                                                 // ready for the next batch
-        if (n <= small_max) t.req_cnt[c] = 0;                               // (the sorted path resets its own)
-      }
       if (n > small_max && n > 1) {                                         // many: sorted, then a warp per edge
-        const int slot = atomicAdd(&t.ctr->n_big, 1);
-        mkey[slot] = ki;
-        mval[slot] = q;
+        if (role != 1) {                                                    // (that path re-arms head and count itself)
+          const int slot = atomicAdd(&t.ctr->n_big, 1);
+          mkey[slot] = ki;
+          mval[slot] = q;
+        }
       } else if (n > 1) {
-        if (is_head) {
+        if (is_head && role != 0) {
           grp_c = c;
           grp_n = n;
+          t.req_head[c] = -1;                                               // ready for the next batch
+          t.req_cnt[c] = 0;
         }
-      } else if (is_head) {
+      } else if (is_head && n == 1 && role != 1) {
+        single = true;
+        t.req_head[c] = -1;
+        t.req_cnt[c] = 0;
+      }
+    }
+    // ---- single requests: node ids for the whole warp with ONE atomic on the free ring (the counters are single
+    // words in L2; an atomic per request on each of them serialised the stage)
+    const unsigned smask = g.ballot(single);
+    int made_hwm = 0;
+    if (smask) {
+      const int leader = __ffs(smask) - 1;
+      u64 wbase = 0;
+      if (g.lane == leader) wbase = rm_alloc_nodes(t, __popc(smask));
+      wbase = g.bcast(wbase, leader);
+      if (single && wbase != ~0ull) {
+        const u64 apos = wbase + (u64)__popc(smask & ((1u << g.lane) - 1u));
         const int p = (int)(ki & ((1ull << len_bits) - 1ull));
         const u64 seq = ((seq_base + (u64)q) << 1) | 1ull;
-        // second round trip: the id allocation, the edge's tokens and its owner word, together
+        // second round trip: the new id, the edge's tokens and its owner word, together
         const int2 r0 = __ldcg(t.ts + off);
         const int tokp = rm_tok(t, off + p);
-        const u64 apos = rm_alloc_nodes(t, 1);
-        if (apos != ~0ull) {
-          // third: the new id and the parent's slot
-          RmSlot s;
-          const int sidx = rm_find<true>(t, rm_key(par, r0.x), s);
-          const int u = rm_free_id_at(t, apos);
-          const u64 st = seq > st_c ? seq : st_c;       // the query stamped the whole edge, then split it
-          t.parent[u] = par;
-          t.edge_off[u] = off;
-          t.edge_len[u] = p;
-          t.depth_end[u] = dend - len + p;
-          t.lock_ref[u] = lk;       // radix_cache.py:283
-          t.rank[u] = rk;
-          t.nchild[u] = 1;
-          t.gen[u] = 0;
-          t.parked[u] = -1;
-          t.stamp[u] = st;
-          atomicMax(&t.ctr->node_hwm, u + 1);
-          rm_set_seg(t, off, (r0.y & RM_SEG_CONT) | u);          // owner map: [off, off+p) is u's, c starts at off+p
-          rm_set_seg(t, off + p, c | RM_SEG_CONT);
-          fill_off = off;
-          fill_n = p;
-          fill_id = u;
-          if (sidx < 0) {
-            atomicMax(&t.ctr->err, (int)RM_E_INVALID);
-          } else {
-            t.table[sidx].child = u;
-            rm_slot_set_len(&t.table[sidx], p);
-          }
-          rm_table_insert(t, rm_key(u, tokp), c, len - p, off + p, rk);
-          t.parent[c] = u;
-          t.edge_off[c] = off + p;
-          t.edge_len[c] = len - p;
-          t.stamp[c] = st;
-          rm_add_i64(&t.ctr->n_nodes, (i64)1);
-          out_node[q] = u;
+        const int tokp1 = len - p > 1 ? rm_tok(t, off + p + 1) : 0;     // inline tokens of the lower node's new slot
+        const int tokp2 = len - p > 2 ? rm_tok(t, off + p + 2) : 0;
+        const int u = rm_free_id_at(t, apos);
+        // third: the parent's slot
+        RmSlot s;
+        const int sidx = rm_find<true>(t, rm_key(par, r0.x), s);
+        const u64 st = seq > st_c ? seq : st_c;       // the query stamped the whole edge, then split it
+        t.parent[u] = par;
+        t.edge_off[u] = off;
+        t.edge_len[u] = p;
+        t.depth_end[u] = dend - len + p;
+        t.lock_ref[u] = lk;       // radix_cache.py:283
+        t.rank[u] = rk;
+        t.nchild[u] = 1;
+        t.gen[u] = 0;
+        t.parked[u] = -1;
+        t.stamp[u] = st;
+        made_hwm = u + 1;
+        rm_set_seg(t, off, (r0.y & RM_SEG_CONT) | u);          // owner map: [off, off+p) is u's, c starts at off+p
+        rm_set_seg(t, off + p, c | RM_SEG_CONT);
+        fill_off = off;
+        fill_n = p;
+        fill_id = u;
+        if (sidx < 0) {
+          atomicMax(&t.ctr->err, (int)RM_E_INVALID);
+        } else {
+          t.table[sidx].child = u;
+          rm_slot_set_len(&t.table[sidx], p);
         }
+        rm_table_insert_toks(t, rm_key(u, tokp), c, len - p, off + p, rk, tokp1, tokp2);
+        t.parent[c] = u;
+        t.edge_off[c] = off + p;
+        t.edge_len[c] = len - p;
+        t.stamp[c] = st;
+        out_node[q] = u;
+      }
+      const int hw = g.reduce_max(made_hwm);
+      if (g.lane == leader && wbase != ~0ull) {
+        rm_add_i64(&t.ctr->n_nodes, (i64)__popc(smask));
+        atomicMax(&t.ctr->node_hwm, hw);
       }
     }
     // short fills stay with their thread (32 of them proceed side by side); only long ones are worth
@@ -873,7 +909,18 @@ rm_split_kernel(RmTree t, u64* rkey, unsigned* rval, int Bmax, int len_bits, int
       const int id = g.bcast(fill_id, l);
       for (int x = 1 + g.lane; x < fn; x += G) rm_set_seg(t, o + x, id);
     }
-    // nodes with a few requests: the warp takes them one after another
+    // nodes with a handful of requests (2..thread_max, nearly all shared edges of a served tree): the head's own
+    // thread orders them, one lane working like a group of one, so the heads of a warp - they cluster at the end of
+    // the request list, being the last of their node to finish the walk - proceed side by side instead of queueing
+    // for the warp
+    if (G > 1 && grp_n > 0 && grp_n <= thread_max) {
+      int lsp[RM_THREAD_MAX];
+      unsigned lsq[RM_THREAD_MAX];
+      unsigned char lrep[RM_THREAD_MAX];
+      rm_split_small_group<1>(t, rkey, rval, grp_c, i, grp_n, len_bits, seq_base, out_node, lsp, lsq, lrep);
+      grp_n = 0;
+    }
+    // up to small_max requests: the warp takes the nodes one after another
     todo = g.ballot(grp_n > 0);
     while (todo) {
       const int l = __ffs(todo) - 1;
@@ -1020,7 +1067,11 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
         case 4: RM_RLAUNCH(4, 2, false); break;
         case 8: RM_RLAUNCH(8, 2, false); break;
         case 16: RM_RLAUNCH(16, 2, false); break;
-        default: RM_RLAUNCH(32, 2, false); break;
+        default:
+          if (depth_env == 3) RM_RLAUNCH(32, 3, false);
+          else if (depth_env == 4) RM_RLAUNCH(32, 4, false);
+          else RM_RLAUNCH(32, 2, false);
+          break;
       }
     }
     return;
@@ -1084,11 +1135,16 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   const int bits = idx->node_bits + idx->len_bits;
 #ifndef RM_EMU
   static const int small_env = getenv("RM_SPLIT_SMALL_MAX") ? atoi(getenv("RM_SPLIT_SMALL_MAX")) : RM_SMALL_MAX;
+  static const int thread_env = getenv("RM_SPLIT_THREAD_MAX") ? atoi(getenv("RM_SPLIT_THREAD_MAX")) : RM_THREAD_MAX;
   const int small_max = small_env < 1 ? 1 : (small_env > RM_SMALL_MAX ? RM_SMALL_MAX : small_env);
-  int grid = (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB;
+  const int thread_max = thread_env < 1 ? 1 : (thread_env > RM_THREAD_MAX ? RM_THREAD_MAX : thread_env);
+  static const int roles_env = getenv("RM_SPLIT_ROLES") ? atoi(getenv("RM_SPLIT_ROLES")) : 1;
+  int grid = 2 * ((B + RM_MATCH_TPB - 1) / RM_MATCH_TPB);
   if (grid > 148) grid = 148;            // grid-stride inside; one block per SM keeps the walk kernel's tail unobstructed
+  if (!roles_env) grid |= 1;             // an odd grid runs without the role split (A/B)
+  if (grid > 148) grid = 147;
   auto k3 = rm_split_kernel<RM_WIDE_G>;
-  RM_LAUNCH_PDL(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B, idx->len_bits, (bits + 7) / 8, small_max, seq_base,
+  RM_LAUNCH_PDL(k3, grid, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B, idx->len_bits, (bits + 7) / 8, small_max, thread_max, seq_base,
                 out_node, sc.key[1], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min);
   if (prof) {
     cudaEventRecord(pev[2], s);
@@ -1099,7 +1155,7 @@ int rm_launch_match(rm_index* idx, const int* tokens, const i64* offsets, int B,
   const int small_max = small_env < 1 ? 1 : (small_env > RM_SMALL_MAX ? RM_SMALL_MAX : small_env);
   auto k3 = rm_split_kernel<RM_WIDE_G>;
   RM_LAUNCH(k3, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[0], sc.val[0], B, idx->len_bits,
-            (bits + 7) / 8, small_max, seq_base, out_node, sc.key[1], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min);
+            (bits + 7) / 8, small_max, 1, seq_base, out_node, sc.key[1], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min);
   const int w = 1 ^ rm_sort_pairs(sc.key[1], sc.val[1], sc.key[0], sc.val[0], B, bits, sc.hist, s, &idx->t.ctr->n_big);
   auto k4 = rm_split_apply_kernel<RM_WIDE_G>;
   RM_LAUNCH(k4, (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB, RM_MATCH_TPB, s, idx->t, sc.key[w], sc.val[w], B, idx->len_bits, seq_base,
