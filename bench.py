@@ -136,10 +136,11 @@ def build_oracle_tree(wl, docs, n_nodes):
             return t, count
 
 
-def cpu_sample(wl, docs, n_queries, rank=0):
-    """(lookups/s of the oracle on one core, mean algorithmic bytes per lookup, mean hops, mean match)."""
+def cpu_sample(wl, docs, n_queries, rank=0, step=0):
+    """(lookups/s of the oracle on one core, mean algorithmic bytes per lookup, mean hops, mean match, matched lengths)
+    on the first n_queries queries of device batch `step`."""
     t, _ = build_oracle_tree(wl, docs, wl["tree_nodes"])
-    qs = gen_batch(query_seed(wl, rank, 0, 0), wl["B"], wl["L"], docs)[:n_queries]
+    qs = gen_batch(query_seed(wl, rank, 0, step), wl["B"], wl["L"], docs)[:n_queries]
     lists = [r.tolist() for r in qs]
     L = wl["L"]
     bytes_tot = hops_tot = m_tot = 0
@@ -155,7 +156,7 @@ def cpu_sample(wl, docs, n_queries, rank=0):
         hops_tot += h
         m_tot += m
     n = len(lists)
-    return n / dt, bytes_tot / n, hops_tot / n, m_tot / n
+    return n / dt, bytes_tot / n, hops_tot / n, m_tot / n, np.asarray([m for m, _ in res], dtype=np.int32)
 
 
 def _ref_worker(args):
@@ -210,7 +211,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=4096, help="queries timed on the CPU oracle (rank 0, N=1)")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--stages", action="store_true", help="also time the split stages (3 more CUDA events per step)")
+    ap.add_argument("--stages", action="store_true", help="also time the split stage (one more CUDA event per step)")
+    ap.add_argument("--no-compact", action="store_true", help="skip rm_compact after the build (A/B of the arena layout)")
+    ap.add_argument("--no-blocks", action="store_true", help="headline only: no target / c3 / mesh_route blocks")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
@@ -251,6 +254,8 @@ def main():
         n_ins += INSERT_BATCH
         if ix.sizes().n_nodes >= wl["tree_nodes"]:
             break
+    if not args.no_compact:
+        ix.compact()       # index maintenance, untimed: reclaims nothing here, lays heavy paths out contiguously (csrc/rm_maint.cu)
     torch.cuda.synchronize()
     build_s = time.perf_counter() - t_build0
     ix.check_device_error()
@@ -263,7 +268,8 @@ def main():
     host_batches = [torch.from_numpy(gen_batch(query_seed(wl, rank, 1, s), B, L, docs).reshape(-1)).pin_memory()
                     for s in range(K + W)]
     offs_h = torch.arange(0, (B + 1) * L, L, dtype=torch.int64).pin_memory()
-    out_len = torch.empty(B, dtype=torch.int32, device=dev)
+    out_lens = torch.empty((K, B), dtype=torch.int32, device=dev)   # every timed step keeps its result (parity_check reads step 0)
+    out_len = out_lens[K - 1]
     out_node = torch.empty(B, dtype=torch.int32, device=dev)
     out_len_h = torch.empty(B, dtype=torch.int32).pin_memory()
     out_node_h = torch.empty(B, dtype=torch.int32).pin_memory()
@@ -287,7 +293,7 @@ def main():
     barrier()
     ev0.record()
     for s in range(W, W + K):
-        ix.match(dev_batches[s], offs_q, B, out_len, out_node)
+        ix.match(dev_batches[s], offs_q, B, out_lens[s - W], out_node)
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -297,9 +303,6 @@ def main():
     ix.profile(False)
     clocks = sampler.finish()
     ix.check_device_error()
-    # matched tokens/s (second half of the metric): one extra untimed pass result is enough for the mean
-    mean_match = float(out_len.to(torch.float64).mean().item())
-    nodes_end = int(ix.sizes().n_nodes)
 
     # ---- end to end through the host-buffer C ABI ----------------------------------------------
     for s in range(W):
@@ -317,6 +320,20 @@ def main():
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
     ms, e2e_ms, walk_ms_mean = [float(x) for x in t_ms.cpu()]
 
+    # ---- secondary blocks (tools/bench_blocks.py): every rank takes part in the collective ones
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_blocks as blocks
+    h2d_gbs = blocks.h2d_probe(torch, world)
+    mean_match = float(out_len.to(torch.float64).mean().item())
+    nodes_end = int(ix.sizes().n_nodes)
+    first_lens = out_lens[0, :args.cpu_sample].cpu().numpy()
+    ix.close()
+    del dev_batches, host_batches
+    torch.cuda.empty_cache()
+    mesh = None
+    if not args.no_blocks and args.workload == "c2":
+        mesh = blocks.mesh_route_block(torch, capi, rank, world)
+
     if rank == 0:
         value = world * B * K / (ms * 1e-3)
         e2e = world * B * K / (e2e_ms * 1e-3)
@@ -325,6 +342,7 @@ def main():
                 "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "int32", "data": "synthetic",
                 "config": {"workload": wl["name"], "tree_nodes_start": nodes_start, "tree_nodes_end": nodes_end,
+                           "layout": "bump-allocated arenas as built" if args.no_compact else "rm_compact after the build (heavy paths contiguous)",
                            "inserts_to_build": n_ins, "build_s": round(build_s, 2), "batch": B, "query_len": L,
                            "mode": "RadixCache (splitting match)", "walk": os.environ.get("RM_WALK", "run"), "lanes_per_query": int(os.environ.get("RM_RUN_G", "32")),
                            "l2": f"every step reads a fresh {B * L * 4 >> 20} MiB query batch ({(K + W) * B * L * 4 >> 20} MiB "
@@ -332,26 +350,39 @@ def main():
                            "parallelism": f"replica x{world}, query batches sharded, no collective"},
                 "matched_tokens_per_s": value * mean_match, "mean_matched_len": mean_match,
                 "e2e": {"value": e2e, "unit": "lookups/s", "h2d_bytes_per_step": B * L * 4 + (B + 1) * 8,
-                        "d2h_bytes_per_step": B * 8},
+                        "d2h_bytes_per_step": B * 8,
+                        "h2d_GBps": world * (B * L * 4 + (B + 1) * 8) / (e2e_ms * 1e-3 / K) / 1e9,
+                        "h2d_ceiling_GBps": h2d_gbs, "frac_of_h2d_ceiling": world * (B * L * 4 + (B + 1) * 8) / (e2e_ms * 1e-3 / K) / 1e9 / h2d_gbs,
+                        "h2d_ceiling_how": f"pinned 256 MiB cudaMemcpyAsync host-to-device on all {world} GPU(s) at once, aggregate"},
                 "gpu_launches": launches, "clocks": clocks}
         if stage_ms:
             line["stages_ms_per_step"] = dict(zip(("walk", "split_stage"), (x / max(walk_n, 1) for x in stage_ms[:2])))
         cpu = None
         if world == 1 and not args.no_cpu:
-            v, bpl, hops, mm = cpu_sample(wl, docs, args.cpu_sample)
+            v, bpl, hops, mm, cpu_lens = cpu_sample(wl, docs, args.cpu_sample, rank, W)
+            got = first_lens
+            mism = int((got != cpu_lens).sum())
+            line["parity_check"] = {"queries": int(len(cpu_lens)), "mismatches": mism,
+                                    "what": "matched lengths of the first timed batch against the CPU port on its replica of the tree"}
+            if mism:
+                sys.stderr.write(json.dumps({"error": "parity_check failed: no value reported", "parity_check": line["parity_check"]}) + "\n")
+                raise SystemExit(3)
             cpu = {"value": v, "unit": "lookups/s", "cores": 1, "kind": "port",
                    "sample": f"first {args.cpu_sample} queries of the first timed batch on the oracle's replica of the tree "
                              f"(pure-Python port of the reference's RadixCache, like the reference itself)"}
             line["cpu_baseline"] = cpu
             achieved = bpl * B / (walk_ms_mean * 1e-3) / 1e9
             traffic = None
+            traffic_src = None
             try:
                 with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                    traffic = json.load(f).get(args.workload, {}).get("walk_kernel_dram_bytes_per_launch")
+                    tj = json.load(f).get(args.workload, {})
+                    traffic = tj.get("walk_kernel_dram_bytes_per_launch")
+                    traffic_src = "profiles/traffic.json <- " + str(tj.get("source"))
             except Exception:
                 pass
             line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                "traffic": traffic, "kernel": "rm_match_rung_kernel (K1 walk)", "peak_source": peak_src,
+                                "traffic": traffic, "traffic_source": traffic_src, "kernel": "rm_match_rung_kernel (K1 walk)", "peak_source": peak_src,
                                 "bytes_per_lookup": bpl, "mean_hops": hops, "kernel_ms": walk_ms_mean,
                                 "kernel_share_of_step": walk_ms_mean / (ms / K),
                                 "lookups_per_s_kernel_only": B / (walk_ms_mean * 1e-3),
@@ -362,6 +393,20 @@ def main():
                                         "and reads a 4-byte owner word per position instead of node records, and the tree is "
                                         "largely L2 resident, so DRAM traffic (traffic, dram_achieved, dram_frac; ncu) is well "
                                         "below the algorithmic figure and frac can pass 1"}
+        if mesh is not None:
+            line["mesh_route"] = mesh
+            if mesh["parity_check"]["mismatches"]:
+                sys.stderr.write(json.dumps({"error": "mesh_route parity_check failed", "parity_check": mesh["parity_check"]}) + "\n")
+                raise SystemExit(3)
+        if world == 1 and not args.no_blocks and not args.no_cpu and args.workload == "c2":
+            tb, tix, tstate = blocks.target_block(sys.modules[__name__], torch, capi, peak)
+            line["target"] = tb
+            if tb["parity_check"]["mismatches"]:
+                sys.stderr.write(json.dumps({"error": "target parity_check failed", "parity_check": tb["parity_check"]}) + "\n")
+                raise SystemExit(3)
+            hpt = tb["roofline"]["mean_hops"] / max(tb["mean_matched_len"], 1.0)
+            line["c3"] = blocks.c3_block(sys.modules[__name__], torch, capi, peak, tix, tstate, hpt)
+            tix.close()
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

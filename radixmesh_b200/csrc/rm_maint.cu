@@ -721,19 +721,55 @@ int rm_launch_gc_keys(rm_index* idx, const int* nodes_h, int n, int stride, int*
 // ------------------------------------------------------------------ arena compaction + table rebuild
 // Eviction frees node ids and tombstones table slots, but the edge arenas are bump allocated: under
 // streaming inserts at steady occupancy (BASELINE configs[2]) the space of evicted runs has to be
-// reclaimed.  rm_compact slides every live run (tree nodes and parked duplicates) to the front of fresh
-// arenas IN ARENA ORDER (so a split node's halves stay adjacent and the owner map keeps its contiguity
-// flags), rewrites edge_off, and rebuilds the child table from the node pool (which also drops the
-// tombstones).  A maintenance call: it allocates the new arenas and synchronises.
+// reclaimed.  rm_compact moves every live run (tree nodes and parked duplicates) to the front of fresh
+// arenas, heavy paths contiguous (below), rewrites edge_off and the owner map, and rebuilds the child
+// table from the node pool (which also drops the tombstones).  A maintenance call: it allocates the new arenas and synchronises.
 __device__ __forceinline__ bool rm_node_has_run(const RmTree& t, int x) {
   return x > 0 && (t.parent[x] >= 0 || t.gen[x] < 0) && t.edge_len[x] > 0;
 }
 
-__global__ void rm_compact_keys_kernel(RmTree t, int n, u64* __restrict__ key, unsigned* __restrict__ val) {
+// Layout of the new arenas: HEAVY PATHS are contiguous.  A walk follows the arena for as long as the next node of
+// its path starts where the previous one ended (RM_SEG_CONT) and goes back to the child table otherwise; bump
+// allocation only gives that adjacency to the halves of a split, so a query that runs down a hot document pays a
+// table probe at every point where a later insert extended it.  Compaction therefore lays every node out directly
+// behind its parent when it is the parent's heaviest child (most nodes below it: where most lookups go), top-down
+// along each such chain, and flags it contiguous.  Three passes over the node pool: subtree weights (every node adds
+// itself to its ancestors), heaviest child per node (atomic max of (weight, id)), chain head per node (climb while I
+// am the heaviest child).  The sort key (chain head, depth) then puts chains together, top first.
+__device__ __forceinline__ bool rm_is_tree_node(const RmTree& t, int x) { return x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0; }
+
+__global__ void rm_compact_weight_kernel(RmTree t, int n, int* __restrict__ weight) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || !rm_is_tree_node(t, x)) return;
+  atomicAdd(&weight[x], 1);
+  for (int p = t.parent[x], guard = 0; p > 0 && guard < t.max_nodes; p = t.parent[p], ++guard) atomicAdd(&weight[p], 1);
+}
+
+__global__ void rm_compact_heavy_kernel(RmTree t, int n, const int* __restrict__ weight, u64* __restrict__ best) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || !rm_is_tree_node(t, x)) return;
+  const int p = t.parent[x];
+  if (p > 0) atomicMax(&best[p], ((u64)(unsigned)weight[x] << 32) | (unsigned)x);
+}
+
+__device__ __forceinline__ bool rm_is_heavy_child(const RmTree& t, const u64* __restrict__ best, int x) {
+  const int p = t.parent[x];
+  return p > 0 && (int)(unsigned)best[p] == x;
+}
+
+__global__ void rm_compact_keys_kernel(RmTree t, int n, const u64* __restrict__ best, u64* __restrict__ key,
+                                       unsigned* __restrict__ val) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= n) return;
-  key[x] = rm_node_has_run(t, x) ? (u64)t.edge_off[x] : ((1ull << 62) - 1ull);
   val[x] = (unsigned)x;
+  if (!rm_node_has_run(t, x)) {
+    key[x] = (1ull << 62) - 1ull;
+    return;
+  }
+  int head = x;
+  if (rm_is_tree_node(t, x))
+    for (int guard = 0; rm_is_heavy_child(t, best, head) && guard < t.max_nodes; ++guard) head = t.parent[head];
+  key[x] = ((u64)(unsigned)head << 32) | (unsigned)t.depth_end[x];   // parked duplicates: a chain of their own
 }
 
 __global__ void rm_compact_len_kernel(RmTree t, int n, const unsigned* __restrict__ sval, i64* __restrict__ len_out) {
@@ -796,7 +832,8 @@ __global__ void rm_scan_i64_kernel(i64* __restrict__ data, int n, i64* __restric
 // its new place (only this group reads edge_off[x])
 template <int G>
 __global__ void rm_compact_copy_kernel(RmTree t, int n, const unsigned* __restrict__ sval, const i64* __restrict__ new_off,
-                                       int2* __restrict__ nts, i64* __restrict__ nval, int with_values) {
+                                       const u64* __restrict__ best, int2* __restrict__ nts, i64* __restrict__ nval,
+                                       int with_values) {
   RmGroup<G> g;
   const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
   if (i >= n) return;
@@ -804,8 +841,11 @@ __global__ void rm_compact_copy_kernel(RmTree t, int n, const unsigned* __restri
   if (!rm_node_has_run(t, x)) return;
   const i64 src = t.edge_off[x], dst = new_off[i];
   const int len = t.edge_len[x];
+  // owner words are rewritten: the node's id, flagged contiguous on the first position iff the node sits directly
+  // behind its parent in the new layout (heaviest child of a parent that has a run)
+  const int first = (rm_is_tree_node(t, x) && rm_is_heavy_child(t, best, x)) ? (x | RM_SEG_CONT) : x;
   for (int k = g.lane; k < len; k += G) {
-    nts[dst + k] = t.ts[src + k];
+    nts[dst + k] = make_int2(t.ts[src + k].x, k == 0 ? first : x);
     if (with_values) nval[dst + k] = t.val[src + k];
   }
   g.sync();
@@ -851,8 +891,15 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
   RM_CUDA(cudaStreamSynchronize(s));
   const int n = c.node_hwm;
   const bool with_values = idx->cfg.mode != RM_MODE_ROUTER;
-  // runs in arena order
-  RM_LAUNCH(rm_compact_keys_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, sc.ev_key[0], sc.ev_val[0]);
+  // runs in heavy-path order
+  int* weight = sc.ev_rem;
+  u64* best = sc.ev_eff;
+  const int grid_n = (n + RM_MT_TPB - 1) / RM_MT_TPB;
+  RM_CUDA(cudaMemsetAsync(weight, 0, sizeof(int) * (size_t)n, s));
+  RM_CUDA(cudaMemsetAsync(best, 0, sizeof(u64) * (size_t)n, s));
+  RM_LAUNCH(rm_compact_weight_kernel, grid_n, RM_MT_TPB, s, t, n, weight);
+  RM_LAUNCH(rm_compact_heavy_kernel, grid_n, RM_MT_TPB, s, t, n, weight, best);
+  RM_LAUNCH(rm_compact_keys_kernel, grid_n, RM_MT_TPB, s, t, n, best, sc.ev_key[0], sc.ev_val[0]);
   const int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, 62, sc.ev_hist, s);
   i64* new_off = reinterpret_cast<i64*>(sc.ev_key[w ^ 1]);   // the spare ping-pong buffer, n x 8 bytes
   i64* total_d = reinterpret_cast<i64*>(sc.sufmax);
@@ -875,7 +922,8 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
   auto kc = rm_compact_copy_kernel<32>;
   const long long cthreads = (long long)n * 32;
 #endif
-  RM_LAUNCH(kc, (int)((cthreads + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, n, sc.ev_val[w], new_off, nts, nval, with_values ? 1 : 0);
+  RM_LAUNCH(kc, (int)((cthreads + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, n, sc.ev_val[w], new_off, best, nts, nval,
+            with_values ? 1 : 0);
   RM_CUDA(cudaGetLastError());
   RM_CUDA(cudaStreamSynchronize(s));
   // swap the arenas in, drop the old ones

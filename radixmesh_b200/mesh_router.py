@@ -29,17 +29,47 @@ class ShardedMeshRouter:
     result arrays by one all-gather.  `shard_pick=False`: every rank gathers all lengths and picks for the
     whole batch (the first version; 2.3x slower at 8 GPUs on 2K-token requests)."""
 
-    def __init__(self, index: capi.DeviceIndex, rank: int, world: int, group=None, shard_pick: bool = True):
+    def __init__(self, index: capi.DeviceIndex, rank: int, world: int, group=None, shard_pick: bool = True,
+                 bcast_group=None):
         self.ix, self.rank, self.world, self.group = index, rank, world, group
         self.shard_pick = shard_pick and world > 1
+        # route_pipelined sends the request tokens on a communicator of their own, so that chunk k+1 travels while
+        # chunk k is walked, exchanged and picked (pass a second group; collectives of one group run in issue order)
+        self.bcast_group = bcast_group if bcast_group is not None else group
 
-    def route(self, tokens, offsets, B: int, src: int = 0):
+    def route_pipelined(self, tokens, offsets, B: int, src: int = 0, chunks: int = 8):
+        """route() with the batch cut into `chunks` pieces.  What limits the sharded form is the broadcast of the
+        request tokens (every GPU must see every request; NVLink carries 4 bytes per token per GPU), so all the
+        broadcasts are queued at once on their own communicator and each chunk is walked, its matched lengths
+        exchanged and its slice picked as soon as its tokens have landed - everything but the first chunk's compute
+        hides under the transfer.  Same results as route()."""
+        import torch
+        import torch.distributed as dist
+        if self.world == 1 or chunks <= 1 or B < chunks:
+            return self.route(tokens, offsets, B, src)
+        tok_t, offs_t = _as_torch(tokens), _as_torch(offsets)
+        dist.broadcast(offs_t, src=src, group=self.group)
+        offs_h = offs_t.cpu()                                           # chunk boundaries in tokens: one host read per batch
+        step = (B + chunks - 1) // chunks
+        cuts = [min(k * step, B) for k in range(chunks + 1)]
+        works = [dist.broadcast(tok_t[int(offs_h[cuts[k]]):int(offs_h[cuts[k + 1]])], src=src, group=self.bcast_group, async_op=True)
+                 for k in range(chunks) if cuts[k + 1] > cuts[k]]
+        outs = []
+        for k, w in enumerate(works):
+            a, b = cuts[k], cuts[k + 1]
+            w.wait()
+            base = int(offs_h[a])
+            sub_offs = offs_t[a:b + 1] - base
+            outs.append(self.route(tok_t[base:int(offs_h[b])], sub_offs, b - a, src, _skip_broadcast=True))
+        return tuple(torch.cat([_as_torch(o[i]) for o in outs]) for i in range(5))
+
+    def route(self, tokens, offsets, B: int, src: int = 0, _skip_broadcast: bool = False):
         """tokens / offsets are device arrays; valid on `src`, overwritten elsewhere by the broadcast.
         Returns (prefill_rank, decode_rank, prefill_addr_idx, decode_addr_idx, err) device arrays."""
         import torch.distributed as dist
         be = self.ix.be
         W = self.world
-        if W > 1:
+        if W > 1 and not _skip_broadcast:
             dist.broadcast(_as_torch(tokens), src=src, group=self.group)
             dist.broadcast(_as_torch(offsets), src=src, group=self.group)
         lens = be.empty(B, np.int32)

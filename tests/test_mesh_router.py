@@ -92,6 +92,13 @@ def _worker(rank, world, port, q):
     r = ShardedMeshRouter(ix, rank, world)
     pf, dc, pa, da, err = r.route(qt, qo, len(queries))
     sharded = (pf.tolist(), dc.tolist(), pa.tolist(), da.tolist(), err.tolist())
+    # the same batch in pieces, token broadcasts queued ahead on a communicator of their own
+    qt2, _ = pack(queries)
+    if rank != 0:
+        qt2[:] = 0
+    rp = ShardedMeshRouter(ix, rank, world, bcast_group=dist.new_group(list(range(world))))
+    piped = tuple(x.tolist() for x in rp.route_pipelined(qt2, qo.copy(), len(queries), chunks=3))
+    assert piped == sharded, (piped, sharded)
     # replicated router tree, query batch sharded
     rt = mk(mode=3, self_rank=2, n_prefill=1, n_decode=1, max_nodes=256, max_tokens=4096, max_batch=16, max_key_len=32)
     rt.set_rings(*_rings(addrs_p), *_rings(addrs_d))
