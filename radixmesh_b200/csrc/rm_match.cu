@@ -187,18 +187,16 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
 // its parent and edge start are loaded once, there.  (The ROUTER variant keeps the rank-pick state of
 // radix_mesh.py:219-238 per boundary it crosses.)
 //
-// STAGE (32 lanes per query, the product path): the query is not on the dependent chain at all.  Its tokens are
-// copied into shared memory with cp.async (16-byte pieces, L2 evict-first, 256-token chunks in a two-chunk ring,
-// the next chunk requested 64 tokens into the current one), so a step waits for its arena records only - L2 hits -
-// instead of a DRAM round trip for the 128 bytes of query it compares them with.
-#define RM_QCH 256   // tokens per staged query chunk; the ring holds two
-template <int G, bool SPLIT, bool ROUTER, int DEPTH, bool STAGE, int MINB = 8>
-__global__ void __launch_bounds__(STAGE ? 128 : RM_MATCH_TPB, STAGE ? MINB : 8)
+// (A variant that staged the query in shared memory with cp.async - 256-token chunks, two in flight - so that a step
+// waited for its arena records only was built and measured: 52 us against 45 on C2, 72 against 62 on the target
+// shape.  With 64 warps per SM the query loads are already hidden, and the ring bookkeeping cost issue slots the
+// kernel does not have; it was removed.  profiles/README.md, round 2.)
+template <int G, bool SPLIT, bool ROUTER, int DEPTH>
+__global__ void __launch_bounds__(RM_MATCH_TPB, 8)
 rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
                      int len_bits, int* __restrict__ out_len, int* __restrict__ out_node, u64* __restrict__ req_key,
                      unsigned* __restrict__ req_val, RmRouteOut ro, int flags) {
   static_assert(DEPTH * G <= RM_ARENA_PAD, "a walk reads DEPTH steps past a run position");
-  static_assert(!STAGE || G == 32, "query staging is per warp");
   RmGroup<G> g;
   rm_grid_dependency_trigger();        // the split kernel that follows may be scheduled now; it waits for this grid
   const int q = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
@@ -214,50 +212,6 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
   const u64 qpol = t.qpol;               // L2 evict-first descriptor, made once per index: a kernel parameter stays in uniform registers
   const int lane = g.lane;
 
-  // ---- query staging (STAGE only)
-#ifndef RM_EMU
-  extern __shared__ int rm_qstage[];
-  int* const qbuf = STAGE ? rm_qstage + (threadIdx.x >> 5) * (2 * RM_QCH) : nullptr;
-  const int qm = STAGE ? (int)((reinterpret_cast<size_t>(key) >> 2) & 3) : 0;   // tokens between the 16-byte boundary and key[0]
-  const int* const qbase = key - qm;
-  const int qend = L + qm;             // staged index of token i is i + qm
-  int q_issued = 0, q_ready = 0;
-  auto q_issue = [&](int k) {
-#pragma unroll
-    for (int h = 0; h < RM_QCH / 4 / 32; ++h) {
-      const int t0 = k * RM_QCH + 4 * (lane + 32 * h);
-      const int nb = min(16, (qend - t0) * 4);
-      if (nb > 0) {
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(qbuf + (t0 & (2 * RM_QCH - 1)));
-        asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2, %3;" ::"r"(dst), "l"(qbase + t0), "r"(nb), "l"(qpol)
-                     : "memory");
-      }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-  // make the tokens [i, i + look) usable; requests the chunks the walk is about to enter
-  auto q_ensure = [&](int i, int look) {
-    while (q_issued * RM_QCH < qend && q_issued <= ((i + qm + 192) >> 8)) q_issue(q_issued++);
-    const int kneed = min(i + qm + look - 1, qend - 1) >> 8;
-    if (kneed >= q_ready) {
-      if (kneed == q_issued - 1) {
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        q_ready = q_issued;
-      } else {
-        asm volatile("cp.async.wait_group 1;" ::: "memory");
-        q_ready = q_issued - 1;
-      }
-      __syncwarp();
-    }
-  };
-#endif
-  auto ldq = [&](int i) -> int {
-#ifndef RM_EMU
-    if (STAGE) return qbuf[(i + qm) & (2 * RM_QCH - 1)];
-#endif
-    return rm_ld_query(key + i, qpol);
-  };
-
   int node = 0, pos = 0;               // `node` is matched in full through `pos` (same in every lane)
   u64 req = RM_NO_REQ;
   int cnt = 0, deepest = -1, last_prefill = -1;
@@ -269,12 +223,7 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
   while (!done) {
     // ---- child of `node` that starts with key[pos]: child-table probe (same address in every lane)
     int tk = tk_next;
-    if (!have_tk) {
-#ifndef RM_EMU
-      if (STAGE) q_ensure(pos, 1);
-#endif
-      tk = ldq(pos);
-    }
+    if (!have_tk) tk = rm_ld_query(key + pos, qpol);
     have_tk = false;
     int cur = -1;
     i64 cs = 0;
@@ -308,11 +257,8 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       int kjv[DEPTH];
 #pragma unroll
       for (int u = 0; u < DEPTH; ++u) tv[u] = __ldg(tp + u * G);
-#ifndef RM_EMU
-      if (STAGE) q_ensure(qi, DEPTH * G);
-#endif
       const int lim = L - qi - lane;    // this lane's position u*G is inside the query iff u*G < lim
-      if (!STAGE) {
+      {
         const int* __restrict__ kp = key + qi + lane;
 #pragma unroll
         for (int u = 0; u < DEPTH; ++u) kjv[u] = u * G < lim ? rm_ld_query(kp + u * G, qpol) : 0;
@@ -322,7 +268,7 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       for (int u = 0; u < DEPTH; ++u) {
         const int tj = tv[u].x, sj = tv[u].y;
         const bool inq = u * G < lim;
-        const int kj = STAGE ? (inq ? ldq(qi + u * G + lane) : 0) : kjv[u];
+        const int kj = kjv[u];
         const int own = sj < 0 ? -1 : (sj & 0x3FFFFFFF);
         int prev = g.shfl_up(own, 1);
         if (lane == 0) prev = lastown;
@@ -404,9 +350,6 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
       }
     }
   }
-#ifndef RM_EMU
-  if (STAGE) asm volatile("cp.async.wait_group 0;" ::: "memory");   // nothing of this warp may still be landing at exit
-#endif
   if (lane == 0) {
     if (node > 0 && !(flags & 1)) atomicMax(stamp + node, seq);   // lazy stamps: the endpoint only
     out_len[q] = pos;
@@ -995,15 +938,6 @@ static int rm_match_group() {
 #endif
 }
 
-#ifndef RM_EMU
-// launch with dynamic shared memory (the staged query ring of the run-following walk)
-#define RM_LAUNCH_SMEM(kernel, grid, block, smem, stream, ...)      \
-  do {                                                              \
-    ++g_rm_launches;                                                \
-    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);     \
-  } while (0)
-#endif
-
 template <bool SPLIT, bool ROUTER>
 static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offsets, int B, u64 seq_base, int* out_len,
                               int* out_node, RmRouteOut ro, cudaStream_t s) {
@@ -1013,7 +947,7 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
   static const bool emu_group = getenv("RM_EMU_GROUP") != nullptr;
   const int grid = (B + RM_MATCH_TPB - 1) / RM_MATCH_TPB;
   if (!emu_group) {
-    auto kr = rm_match_rung_kernel<1, SPLIT, ROUTER, 2, false>;
+    auto kr = rm_match_rung_kernel<1, SPLIT, ROUTER, 2>;
     RM_LAUNCH(kr, grid, RM_MATCH_TPB, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
               idx->sc.key[0], idx->sc.val[0], ro, 0);
     return;
@@ -1022,58 +956,39 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
   RM_LAUNCH(k, grid, RM_MATCH_TPB, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,
             idx->sc.key[0], idx->sc.val[0], ro);
 #else
-  // RM_WALK selects the walk kernel: "run" (default) = run-following, RM_RUN_G lanes per query (default 32, with the
-  // query staged in shared memory; RM_RUN_STAGE=0 reads it from global memory instead; RM_RUN_DEPTH = steps in
-  // flight); "table" = hop by hop through the child table, RM_MATCH_G lanes per query.  The non-default forms are
-  // kept for A/B measurements and tests.
+  // RM_WALK selects the walk kernel: "run" (default) = run-following, RM_RUN_G lanes per query (default 32),
+  // RM_RUN_DEPTH steps in flight (default 3); "table" = hop by hop through the child table, RM_MATCH_G lanes per
+  // query.  The non-default forms are kept for A/B measurements and tests.
   static const char* walk = getenv("RM_WALK") ? getenv("RM_WALK") : "run";
   // RM_EXP_FLAGS: measurement experiments only (bit 0 = skip the stamp atomics; results then differ from the
   // reference in eviction order, never use it outside a profiling run)
   static const int run_flags = getenv("RM_EXP_FLAGS") ? (atoi(getenv("RM_EXP_FLAGS")) & 1) : 0;
   if (strcmp(walk, "table") != 0) {
     static const int rg = getenv("RM_RUN_G") ? atoi(getenv("RM_RUN_G")) : 32;
-    static const int stage_env = getenv("RM_RUN_STAGE") ? atoi(getenv("RM_RUN_STAGE")) : 1;
     static const int depth_env = getenv("RM_RUN_DEPTH") ? atoi(getenv("RM_RUN_DEPTH")) : 3;
     static const int rtpb_env = getenv("RM_RUN_TPB") ? atoi(getenv("RM_RUN_TPB")) : 0;
     const long long rthreads = (long long)B * rg;
     // 4 queries per block: a block's warps end at different times and its slots are only handed on when the last
     // one is done (128 threads: +2 % over 256 on both bench shapes)
-    const int rtpb = (rtpb_env && !(rg == 32 && stage_env && rtpb_env > 128)) ? rtpb_env : (rthreads >= 148LL * 8 * 128 ? 128 : 64);
+    const int rtpb = rtpb_env ? rtpb_env : (rthreads >= 148LL * 8 * 128 ? 128 : 64);
     const int rgrid = (int)((rthreads + rtpb - 1) / rtpb);
-    // staging needs 16-byte aligned pieces: the token buffer itself must be 16-byte aligned (cudaMalloc / torch are)
-    const bool stage = rg == 32 && stage_env && (reinterpret_cast<size_t>(tokens) & 15) == 0;
-#define RM_RLAUNCH(GG, DD, ST, ...)                                                                                \
-  do {                                                                                                             \
-    auto kr = rm_match_rung_kernel<GG, SPLIT, ROUTER, DD, ST, ##__VA_ARGS__>;                                      \
-    RM_LAUNCH_SMEM(kr, rgrid, rtpb, (ST) ? (size_t)(rtpb / 32) * 2 * RM_QCH * sizeof(int) : 0, s, idx->t, tokens,  \
-                   offsets, B, seq_base, idx->len_bits, out_len, out_node, idx->sc.key[0], idx->sc.val[0], ro,     \
-                   run_flags);                                                                                     \
+#define RM_RLAUNCH(GG, DD)                                                                                        \
+  do {                                                                                                            \
+    auto kr = rm_match_rung_kernel<GG, SPLIT, ROUTER, DD>;                                                        \
+    RM_LAUNCH(kr, rgrid, rtpb, s, idx->t, tokens, offsets, B, seq_base, idx->len_bits, out_len, out_node,        \
+              idx->sc.key[0], idx->sc.val[0], ro, run_flags);                                                     \
   } while (0)
-    static const int minb_env = getenv("RM_RUN_MINB") ? atoi(getenv("RM_RUN_MINB")) : 12;
-    if (stage && minb_env == 16) {
-      switch (depth_env) {
-        case 2: RM_RLAUNCH(32, 2, true, 16); break;
-        case 4: RM_RLAUNCH(32, 4, true, 16); break;
-        default: RM_RLAUNCH(32, 3, true, 16); break;
-      }
-    } else if (stage) {
-      switch (depth_env) {
-        case 2: RM_RLAUNCH(32, 2, true, 12); break;
-        case 4: RM_RLAUNCH(32, 4, true, 12); break;
-        default: RM_RLAUNCH(32, 3, true, 12); break;
-      }
-    } else {
-      switch (rg) {
-        case 4: RM_RLAUNCH(4, 2, false); break;
-        case 8: RM_RLAUNCH(8, 2, false); break;
-        case 16: RM_RLAUNCH(16, 2, false); break;
-        default:
-          if (depth_env == 3) RM_RLAUNCH(32, 3, false);
-          else if (depth_env == 4) RM_RLAUNCH(32, 4, false);
-          else RM_RLAUNCH(32, 2, false);
-          break;
-      }
+    switch (rg) {
+      case 4: RM_RLAUNCH(4, 2); break;
+      case 8: RM_RLAUNCH(8, 2); break;
+      case 16: RM_RLAUNCH(16, 2); break;
+      default:
+        if (depth_env == 2) RM_RLAUNCH(32, 2);
+        else if (depth_env == 4) RM_RLAUNCH(32, 4);
+        else RM_RLAUNCH(32, 3);
+        break;
     }
+#undef RM_RLAUNCH
     return;
   }
   const int G = rm_match_group();
@@ -1202,11 +1117,11 @@ static int rm_launch_walk_flags(rm_index* idx, const int* tokens, const i64* off
   RmRouteOut ro = {nullptr, nullptr, nullptr};
 #ifdef RM_EMU
   const int tpb = RM_MATCH_TPB;
-  auto k = rm_match_rung_kernel<1, true, false, 2, false>;
+  auto k = rm_match_rung_kernel<1, true, false, 2>;
   const long long wthreads = N;
 #else
   const int tpb = N >= 148 * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (N >= 148 * 8 * 128 ? 128 : 64);
-  auto k = rm_match_rung_kernel<8, true, false, 2, false>;
+  auto k = rm_match_rung_kernel<8, true, false, 2>;
   const long long wthreads = (long long)N * 8;
 #endif
   RM_LAUNCH(k, (int)((wthreads + tpb - 1) / tpb), tpb, s, idx->t, tokens, offsets, N, seq_base, idx->len_bits, out_len,

@@ -34,9 +34,8 @@ WALKS = [("run", 4), ("run", 8), ("run", 16), ("run", 32), ("table", 2), ("table
 @pytest.mark.parametrize("walk,group", WALKS, ids=[f"{w}{g}" for w, g in WALKS])
 def test_gpu_zipf_match_all_walk_kernels(walk, group):
     """Zipf shared-prefix workload at reduced size, device-pointer entry points, every form of the
-    walk kernel (run-following with 4..32 lanes per query - 32 is the product path, with the query staged in shared
-    memory - and hop-by-hop through the child table with 2..32 lanes per query): lengths, last nodes, values and
-    final tree."""
+    walk kernel (run-following with 4..32 lanes per query - 32 is the product path - and hop-by-hop through the
+    child table with 2..32 lanes per query): lengths, last nodes, values and final tree."""
     import os
     import subprocess
     import sys
@@ -48,13 +47,14 @@ def test_gpu_zipf_match_all_walk_kernels(walk, group):
                    cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-@pytest.mark.parametrize("env", [{"RM_RUN_STAGE": "0"}, {"RM_RUN_DEPTH": "2"}, {"RM_RUN_DEPTH": "4"}, {"RM_RUN_MINB": "16"},
+@pytest.mark.parametrize("env", [{"RM_RUN_DEPTH": "2"}, {"RM_RUN_DEPTH": "4"}, {"RM_SPLIT_ROLES": "0"}, {"RM_SPLIT_THREAD_MAX": "1"},
                                  {"RM_SPLIT_SMALL_MAX": "1"}, {"RM_SPLIT_SMALL_MAX": "3"}],
                          ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
 def test_gpu_zipf_match_kernel_options(env):
-    """The same check with the product walk's options (query read from global memory instead of staged, 2 or 4 steps
-    in flight, 16 blocks per SM) and with the split stage's in-register path cut down, so that edges with more than
-    1 or 3 requests go through its sorted path (run by the last block of the same launch)."""
+    """The same check with the product walk's options (2 or 4 steps in flight) and the split stage's: singles and
+    groups in the same blocks, handfuls of requests ordered by the warp instead of one thread, and the in-register
+    paths cut down so that edges with more than 1 or 3 requests go through the sorted path (run by the last block of
+    the same launch)."""
     import os
     import subprocess
     import sys

@@ -295,10 +295,13 @@ def c4_workload(world):
     ends = Lp + np.cumsum(tl, axis=1)                                   # ends[c, j] = length of the prefix through turn j
     pool = rng.integers(0, 32000, (w["n_conv"], Lmax), dtype=np.int32)
     pool[:, :Lp] = prompts[pid]
+    # KV indices: one per token of the workload, the same whoever inserts it (a prompt's are shared by its conversations)
+    vals = np.arange(w["n_conv"], dtype=np.int64)[:, None] * Lmax + np.arange(Lmax, dtype=np.int64)[None, :]
+    vals[:, :Lp] = (w["n_conv"] + pid.astype(np.int64))[:, None] * Lmax + np.arange(Lp, dtype=np.int64)[None, :]
     t_c = (rng.random(w["n_conv"]) * T).astype(np.int64)                # turn the conversation is at (0 = first turn)
     owner = rng.integers(0, world, size=(w["n_conv"], w["max_turns"]))  # rank that served (inserted) turn j
     req_len = ends[np.arange(w["n_conv"]), t_c]
-    return dict(pool=pool, pid=pid, ends=ends, t_c=t_c, owner=owner, req_len=req_len, Lmax=Lmax)
+    return dict(pool=pool, vals=vals, pid=pid, ends=ends, t_c=t_c, owner=owner, req_len=req_len, Lmax=Lmax)
 
 
 def c4_inserts(wk, only_rank=None, convs=None):
@@ -321,9 +324,11 @@ def c4_apply_inserts(ix, wk, recs, with_values, chunk=1024):
         offs = np.zeros(len(part) + 1, dtype=np.int64)
         np.cumsum(lens, out=offs[1:])
         tok = np.empty(int(offs[-1]), dtype=np.int32)
+        vals = np.empty(int(offs[-1]), dtype=np.int64) if with_values else None
         for i, (c, j, _) in enumerate(part):
             tok[offs[i]:offs[i + 1]] = pool[c, :lens[i]]
-        vals = np.arange(int(offs[-1]), dtype=np.int64) if with_values else None
+            if with_values:
+                vals[offs[i]:offs[i + 1]] = wk["vals"][c, :lens[i]]
         ranks = np.asarray([r for _, _, r in part], dtype=np.int32)
         ix.insert_host(tok, vals, offs, ranks)
     ix.check_device_error()
@@ -371,7 +376,7 @@ def mesh_route_block(torch, capi, rank, world, steps=4, warmup=2, check_requests
     sh = capi.DeviceIndex(mode=capi.MODE_DECODE, self_rank=rank, **kw)
     sh.set_rings(*rings)
     c4_apply_inserts(sh, wk, c4_inserts(wk, only_rank=rank), with_values=True)
-    rp = capi.DeviceIndex(mode=capi.MODE_ROUTER, self_rank=P + D, **kw)
+    rp = capi.DeviceIndex(mode=capi.MODE_ROUTER, self_rank=P + D, max_dups=1 << 20, **kw)   # ownership conflicts on shared prompts are booked as duplicates
     rp.set_rings(*rings)
     all_recs = c4_inserts(wk)
     c4_apply_inserts(rp, wk, all_recs, with_values=False)
