@@ -57,7 +57,11 @@ typedef struct {
   int32_t max_batch;     /* largest B / N any *_batch call will pass (scratch is sized from it) */
   int32_t max_dups;      /* capacity of the duplicate-node table (RadixMesh.dup_nodes) */
   int32_t max_key_len;   /* longest key (tokens) any insert / query will pass; bounds edge lengths */
-  int32_t reserved;
+  int32_t max_batch_tokens; /* token budget of one *_batch call (sum of key lengths), 0 = unknown.  When given, the
+                               device staging of the *_h entry points and the consistent-hash message scratch are
+                               sized from it once, at rm_create / rm_route_set_rings; with 0 the staging grows on
+                               demand (a cudaFree + cudaMalloc on the calling path the first time a larger batch
+                               arrives) and the hash scratch is capped at 1 GiB (RM_ROUTE_SCRATCH_MB) */
   int64_t max_nodes;     /* node pool capacity, including the root */
   int64_t max_tokens;    /* edge arena capacity in tokens (keys i32 + values i64 per token) */
 } rm_config;

@@ -22,7 +22,7 @@ MODE_BASE, MODE_PREFILL, MODE_DECODE, MODE_ROUTER = range(4)
 class RmConfig(C.Structure):
     _fields_ = [("struct_size", C.c_int32), ("device", C.c_int32), ("mode", C.c_int32), ("self_rank", C.c_int32),
                 ("n_prefill", C.c_int32), ("n_decode", C.c_int32), ("max_batch", C.c_int32), ("max_dups", C.c_int32),
-                ("max_key_len", C.c_int32), ("reserved", C.c_int32), ("max_nodes", C.c_int64),
+                ("max_key_len", C.c_int32), ("max_batch_tokens", C.c_int32), ("max_nodes", C.c_int64),
                 ("max_tokens", C.c_int64)]
 
 
@@ -146,11 +146,11 @@ class DeviceIndex:
 
     def __init__(self, *, mode=MODE_BASE, max_nodes=1 << 16, max_tokens=1 << 20, max_batch=1 << 12,
                  max_key_len=1 << 13, max_dups=1 << 10, self_rank=0, n_prefill=0, n_decode=0, device=0,
-                 backend=None, library=None):
+                 max_batch_tokens=0, backend=None, library=None):
         self.be = backend if backend is not None else TorchCuda(device)
         self.lib = library if library is not None else lib()
         self.cfg = RmConfig(C.sizeof(RmConfig), device, mode, self_rank, n_prefill, n_decode, max_batch, max_dups,
-                            max_key_len, 0, max_nodes, max_tokens)
+                            max_key_len, int(max_batch_tokens), max_nodes, max_tokens)
         self.mode = mode
         self._h = _P()
         self._mutex = threading.RLock()   # one host thread at a time per index (SURVEY 8b threading)

@@ -130,7 +130,7 @@ int rm_create(const rm_config* cfg, rm_index** out) {
     return RM_E_INVALID;
   }
   if (cfg->max_nodes < 2 || cfg->max_nodes > (1ll << 29) || cfg->max_tokens < 1 || cfg->max_batch < 1 ||
-      cfg->max_key_len < 1 || cfg->max_key_len > RM_MAX_EDGE_LEN || cfg->n_prefill < 0 || cfg->n_decode < 0 ||
+      cfg->max_key_len < 1 || cfg->max_key_len > RM_MAX_EDGE_LEN || cfg->max_batch_tokens < 0 || cfg->n_prefill < 0 || cfg->n_decode < 0 ||
       cfg->n_prefill + cfg->n_decode > 250 || cfg->self_rank > 253 || cfg->mode < RM_MODE_BASE || cfg->mode > RM_MODE_ROUTER) {
     rm_set_error("rm_create: max_nodes/max_tokens/max_batch/max_key_len/mode out of range");
     return RM_E_INVALID;
@@ -219,6 +219,11 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&sc.h_ranks, B));
   A(rm_dalloc(&sc.h_out_a, B));
   A(rm_dalloc(&sc.h_out_b, B));
+  if (cfg->max_batch_tokens > 0) {          // staging of the *_h entry points sized once, here (else it grows on demand)
+    A(rm_dalloc(&sc.h_tokens, (size_t)cfg->max_batch_tokens));
+    if (with_values) A(rm_dalloc(&sc.h_values, (size_t)cfg->max_batch_tokens));
+    sc.h_tokens_cap = cfg->max_batch_tokens;
+  }
 #undef A
   if (e != cudaSuccess) {
     rm_set_error("rm_create: device allocation failed: %s", cudaGetErrorString(e));

@@ -554,13 +554,16 @@ extern "C" int rm_route_set_rings(rm_index* idx, const uint32_t* p_points_h, con
   if (rc) return rc;
   rc = rm_set_ring(&idx->ring_d, &idx->ring_d_owner, &idx->ring_d_n, d_points_h, d_owner_h, n_d);
   if (rc) return rc;
-  // scratch of the rendered hash messages: 16 bytes per token + 128 per request of the largest batch, capped
-  // (RM_ROUTE_SCRATCH_MB, default 1024); requests that do not fit are hashed by the streamed form
+  // scratch of the rendered hash messages: 16 bytes per token + 128 per request of the largest batch
+  // (rm_config.max_batch_tokens; without it max_batch * max_key_len capped at RM_ROUTE_SCRATCH_MB, default 1024);
+  // requests that do not fit are hashed by the streamed form
   if (!idx->route_nblk) {
     size_t cap_mb = 1024;
     if (const char* e = getenv("RM_ROUTE_SCRATCH_MB")) cap_mb = (size_t)atoll(e);
     size_t want = (size_t)idx->cfg.max_batch * ((size_t)idx->cfg.max_key_len * 16 + 128) + 64;
-    if (want > (cap_mb << 20)) want = cap_mb << 20;
+    if (idx->cfg.max_batch_tokens > 0)      // the caller stated its largest batch: room for all of it, no cap
+      want = (size_t)idx->cfg.max_batch_tokens * 16 + (size_t)idx->cfg.max_batch * 128 + 256;
+    else if (want > (cap_mb << 20)) want = cap_mb << 20;
     RM_CUDA(cudaMalloc(reinterpret_cast<void**>(&idx->route_nblk), sizeof(int) * (size_t)idx->cfg.max_batch));
     idx->route_msg = nullptr;
     idx->route_msg_bytes = 0;

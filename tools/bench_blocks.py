@@ -371,7 +371,8 @@ def mesh_route_block(torch, capi, rank, world, steps=4, warmup=2, check_requests
     pa = [f"p{i}:1" for i in range(P)]
     da = [f"d{i}:1" for i in range(max(D, 1))]
     rings = (*ConsistentHash(pa).device_arrays(pa), *ConsistentHash(da).device_arrays(da))
-    kw = dict(device=dev.index, n_prefill=P, n_decode=D, max_nodes=1 << 19, max_tokens=1 << 25, max_batch=B, max_key_len=wk["Lmax"])
+    kw = dict(device=dev.index, n_prefill=P, n_decode=D, max_nodes=1 << 19, max_tokens=1 << 25, max_batch=B, max_key_len=wk["Lmax"],
+              max_batch_tokens=int(B * float(np.mean(wk["req_len"])) * 1.08))
     t0 = time.perf_counter()
     sh = capi.DeviceIndex(mode=capi.MODE_DECODE, self_rank=rank, **kw)
     sh.set_rings(*rings)
