@@ -330,9 +330,10 @@ def main():
     ix.close()
     del dev_batches, host_batches
     torch.cuda.empty_cache()
-    mesh = None
+    mesh = oplog = None
     if not args.no_blocks and args.workload == "c2":
         mesh = blocks.mesh_route_block(torch, capi, rank, world)
+        oplog = blocks.oplog_exchange_block(torch, capi, rank, world)
 
     if rank == 0:
         value = world * B * K / (ms * 1e-3)
@@ -398,6 +399,8 @@ def main():
             if mesh["parity_check"]["mismatches"]:
                 sys.stderr.write(json.dumps({"error": "mesh_route parity_check failed", "parity_check": mesh["parity_check"]}) + "\n")
                 raise SystemExit(3)
+        if oplog is not None:
+            line["oplog_exchange"] = oplog
         if world == 1 and not args.no_blocks and not args.no_cpu and args.workload == "c2":
             tb, tix, tstate = blocks.target_block(sys.modules[__name__], torch, capi, peak)
             line["target"] = tb

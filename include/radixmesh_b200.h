@@ -249,6 +249,29 @@ int rm_sizes(rm_index* idx, rm_sizes_t* out_h, void* stream);
 int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, int32_t* edge_len_h,
             int32_t* lock_ref_h, uint64_t* stamp_h, int32_t* rank_h, int32_t* depth_h, int32_t* nchild_h,
             int32_t* gen_h, int32_t* parked_h, int32_t* out_n_h, void* stream);
+/*
+ * TreeNode attribute reads for the handles a caller holds (radix_cache.py:35-64; test/test_util.py:10-13 reads
+ * .id .key .value .lock_ref .parent .children): rows for n node ids given in a HOST array, independent of the tree size.
+ * parent = -1 for the root and for a free id, -2 for an id outside the pool.  Synchronises.
+ */
+typedef struct {
+  int32_t parent, edge_len, lock_ref, rank, depth_end, nchild, gen, parked;
+  int64_t edge_off;      /* start of the node's key / value run in the arenas (rm_read_arena) */
+  uint64_t stamp;        /* raw last-access stamp of the node itself (its effective stamp is the subtree maximum) */
+} rm_node_info_t;
+int rm_node_info(rm_index* idx, const int32_t* ids_h, int32_t n, rm_node_info_t* out_h, void* stream);
+/* TreeNode.children of one node (radix_cache.py:39): child id, first token of its edge (the dict key), generation and
+ * dict-order key (ascending = the reference's dict insertion order) per child, to HOST arrays of `cap` entries;
+ * *out_n_h = number of children.  One pass over the node pool on the device, a few bytes back.  Synchronises. */
+int rm_node_children(rm_index* idx, int32_t node, int32_t cap, int32_t* ids_h, int32_t* first_tokens_h, int32_t* gens_h,
+                     uint64_t* order_h, int32_t* out_n_h, void* stream);
+/* RadixCache.total_size (radix_cache.py:239-241, 354-364): sum of len(value) over the tree, reduced on the device.
+ * Synchronises. */
+int rm_total_size(rm_index* idx, int64_t* out_h, void* stream);
+/* Dict-order keys of node ids [0, cap) to HOST (with rm_dump: all_values_flatten in the reference's pre-order,
+ * children in dict insertion order, radix_cache.py:239-248).  Synchronises. */
+int rm_dump_order(rm_index* idx, int32_t cap, uint64_t* order_h, void* stream);
+
 /* Read `n` tokens / values of the edge arenas starting at token offset `off` into HOST buffers. */
 int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream);
 

@@ -33,6 +33,12 @@ class RmSizes(C.Structure):
                 ("table_tombs", C.c_int32)]
 
 
+class RmNodeInfo(C.Structure):
+    _fields_ = [("parent", C.c_int32), ("edge_len", C.c_int32), ("lock_ref", C.c_int32), ("rank", C.c_int32),
+                ("depth_end", C.c_int32), ("nchild", C.c_int32), ("gen", C.c_int32), ("parked", C.c_int32),
+                ("edge_off", C.c_int64), ("stamp", C.c_uint64)]
+
+
 class RadixMeshError(RuntimeError):
     def __init__(self, status: int, text: str):
         super().__init__(f"radixmesh_b200 status {status}: {text}")
@@ -62,6 +68,10 @@ _PROTOS = {
     "rm_route_set_rings": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, C.c_int32]),
     "rm_sizes": (C.c_int, [_P, C.POINTER(RmSizes), _P]),
     "rm_dump": (C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "rm_node_info": (C.c_int, [_P, _P, C.c_int32, _P, _P]),
+    "rm_node_children": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P]),
+    "rm_total_size": (C.c_int, [_P, _P, _P]),
+    "rm_dump_order": (C.c_int, [_P, C.c_int32, _P, _P]),
     "rm_read_arena": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
     "rm_read_segments": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P]),
     "rm_launch_count": (C.c_uint64, []),
@@ -326,6 +336,44 @@ class DeviceIndex:
                                          ptr(a["nchild"]), ptr(a["gen"]), ptr(a["parked"]), C.addressof(out_n), self._s()))
         a["n"] = n
         return a
+
+    def node_info(self, ids):
+        """rm_node_info: one RmNodeInfo per node id (a few dozen bytes each, whatever the size of the tree)."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        n = len(ids)
+        out = (RmNodeInfo * max(n, 1))()
+        if n:
+            with self._mutex:
+                self._check(self.lib.rm_node_info(self._h, ptr(ids), n, C.addressof(out), self._s()))
+        return [out[i] for i in range(n)]
+
+    def node_children(self, node: int, cap: int = 1 << 16):
+        """rm_node_children: [(child id, first token, generation)] in the reference's dict order."""
+        while True:
+            ids, tok, gen = (np.zeros(cap, np.int32) for _ in range(3))
+            od = np.zeros(cap, np.uint64)
+            n = C.c_int32(0)
+            with self._mutex:
+                self._check(self.lib.rm_node_children(self._h, int(node), cap, ptr(ids), ptr(tok), ptr(gen), ptr(od),
+                                                      C.addressof(n), self._s()))
+            if n.value <= cap:
+                break
+            cap = n.value
+        k = n.value
+        order = np.lexsort((ids[:k], od[:k]))
+        return [(int(ids[i]), int(tok[i]), int(gen[i])) for i in order]
+
+    def total_size(self) -> int:
+        v = C.c_int64(0)
+        with self._mutex:
+            self._check(self.lib.rm_total_size(self._h, C.addressof(v), self._s()))
+        return int(v.value)
+
+    def dump_order(self, n: int) -> np.ndarray:
+        od = np.zeros(max(n, 1), np.uint64)
+        with self._mutex:
+            self._check(self.lib.rm_dump_order(self._h, int(n), ptr(od), self._s()))
+        return od[:n]
 
     def read_segments(self, off: int, n: int) -> np.ndarray:
         seg = np.zeros(n, np.int32)

@@ -113,10 +113,10 @@ int rm_destroy(rm_index* idx) {
   RmTree& t = idx->t;
   RmScratch& sc = idx->sc;
   void* ptrs[] = {t.table, t.parent, t.edge_off, t.edge_len, t.lock_ref, t.stamp, t.rank, t.depth_end, t.nchild,
-                  t.gen, t.parked, t.born, t.ts, t.val, t.req_cnt, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
+                  t.gen, t.parked, t.born, t.ord, t.ts, t.val, t.req_cnt, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
                   sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.link, t.req_head, sc.hist, sc.ev_key[0], sc.ev_key[1],
                   sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ins_mark, sc.lock_first, sc.lock_cnt, sc.lock_flag,
-                  sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b,
+                  sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b, sc.info_ids, sc.info_rows,
                   idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner, idx->route_msg, idx->route_nblk};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -181,6 +181,7 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&t.gen, N));
   A(rm_dalloc(&t.parked, N));
   A(rm_dalloc(&t.born, N));
+  A(rm_dalloc(&t.ord, N));
   A(rm_dalloc(&t.ts, (size_t)cfg->max_tokens + RM_ARENA_PAD));
   A(rm_dalloc(&t.val, with_values ? (size_t)cfg->max_tokens + RM_ARENA_PAD : 1));
   A(rm_dalloc(&t.free_ids, N));
@@ -219,6 +220,8 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&sc.h_ranks, B));
   A(rm_dalloc(&sc.h_out_a, B));
   A(rm_dalloc(&sc.h_out_b, B));
+  A(rm_dalloc(&sc.info_ids, 256));
+  A(rm_dalloc(&sc.info_rows, 256));
   if (cfg->max_batch_tokens > 0) {          // staging of the *_h entry points sized once, here (else it grows on demand)
     A(rm_dalloc(&sc.h_tokens, (size_t)cfg->max_batch_tokens));
     if (with_values) A(rm_dalloc(&sc.h_values, (size_t)cfg->max_batch_tokens));
@@ -510,6 +513,35 @@ int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void
   if (!idx || off < 0 || n < 0 || off + n > idx->t.max_tokens || !seg_h) return RM_E_INVALID;
   RM_CUDA(cudaSetDevice(idx->cfg.device));
   return rm_read_arena_component(idx, off, n, 1, seg_h, (cudaStream_t)stream);
+}
+
+int rm_node_info(rm_index* idx, const int32_t* ids_h, int32_t n, rm_node_info_t* out_h, void* stream) {
+  if (!idx || n < 0 || (n > 0 && (!ids_h || !out_h))) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_node_info(idx, ids_h, n, out_h, (cudaStream_t)stream);
+}
+
+int rm_node_children(rm_index* idx, int32_t node, int32_t cap, int32_t* ids_h, int32_t* first_tokens_h, int32_t* gens_h,
+                     uint64_t* order_h, int32_t* out_n_h, void* stream) {
+  if (!idx || !out_n_h || cap < 0 || (cap > 0 && (!ids_h || !first_tokens_h || !gens_h || !order_h))) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_node_children(idx, node, cap, ids_h, first_tokens_h, gens_h, (u64*)order_h, out_n_h, (cudaStream_t)stream);
+}
+
+int rm_total_size(rm_index* idx, int64_t* out_h, void* stream) {
+  if (!idx || !out_h) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  return rm_launch_total_size(idx, (i64*)out_h, (cudaStream_t)stream);
+}
+
+int rm_dump_order(rm_index* idx, int32_t cap, uint64_t* order_h, void* stream) {
+  if (!idx || cap < 0 || !order_h) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int n = cap < idx->t.max_nodes ? cap : idx->t.max_nodes;
+  RM_CUDA(cudaMemcpyAsync(order_h, idx->t.ord, sizeof(u64) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
 }
 
 int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream) {

@@ -97,6 +97,7 @@ struct RmCounters {
                       // (kept next to n_req: one memset clears both)
   int evict_n;        // scratch: nodes evicted by the current rm_evict
   unsigned split_done; // scratch: blocks of the split kernel that have finished (the last one runs the rare big groups)
+  int n_kids;         // scratch: children found by rm_node_children
   int n_tomb;         // tombstoned child-table slots (evicted nodes); empty slots = capacity - n_nodes - n_tomb
   int dbg_max_group;  // largest split-request group seen (diagnostics)
   int dbg_groups;     // split-request groups seen (diagnostics)
@@ -122,6 +123,8 @@ struct RmTree {
   int* gen;        // generation of the object a tree id stands for (bumped by a locked swap); parked: -(gen)-1
   int* parked;     // tree node: most recently parked predecessor (or -1); parked node: the one parked before it
   u64* born;       // op seq of the insert record that created the node (0 = older than any batch in flight)
+  u64* ord;        // place among the parent's children in the reference's dict order (radix_cache.py:39, 239-248):
+                   // op seq of the insert that added the child to its parent; a split's upper node inherits it
   int2* ts;        // per arena position: .x = token, .y = seg = id of the node whose edge covers it (-1 = free), see RM_SEG_CONT
   i64* val;
   int* req_head;   // per node: last split request of the current match batch on it (an index into the batch's request list; -1 between batches)

@@ -221,6 +221,8 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.gen[u] = 0;
           t.parked[u] = -1;
           t.born[u] = seq_base + (u64)r;
+          t.ord[u] = t.ord[c];       // u takes c's place in the parent's dict (radix_cache.py:292); c is u's first child
+          t.ord[c] = 0;
           t.stamp[u] = c_before > seq ? c_before : seq;   // later records that passed c in full pass u as well
           atomicMax(&t.ctr->node_hwm, u + 1);
           t.table[sidx].child = u;
@@ -338,6 +340,7 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
           t.gen[leaf] = 0;
           t.parked[leaf] = -1;
           t.born[leaf] = seq_base + (u64)r;
+          t.ord[leaf] = seq_base + (u64)r;   // appended to the parent's dict by this record (radix_cache.py:323)
           t.stamp[leaf] = seq;
           atomicMax(&t.ctr->node_hwm, leaf + 1);
           atomicAdd(&t.nchild[node], 1);

@@ -38,6 +38,9 @@ struct RmScratch {
   int* h_out_a;
   int* h_out_b;
   i64 h_tokens_cap;
+  // rm_node_info staging (fixed size)
+  int* info_ids;
+  rm_node_info_t* info_rows;
 };
 
 struct rm_index {
@@ -92,6 +95,10 @@ int rm_launch_lock(rm_index* idx, const int* nodes, int B, int dir, i64* out_del
 int rm_launch_lock_g(rm_index* idx, const int* nodes, const int* gens, int B, int dir, i64* out_delta, cudaStream_t s);
 int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
                     int* out_n_h, cudaStream_t s);
+int rm_launch_node_info(rm_index* idx, const int* ids_h, int n, rm_node_info_t* out_h, cudaStream_t s);
+int rm_launch_node_children(rm_index* idx, int node, int cap, int* ids_h, int* toks_h, int* gens_h, u64* ords_h, int* out_n_h,
+                            cudaStream_t s);
+int rm_launch_total_size(rm_index* idx, i64* out_h, cudaStream_t s);
 int rm_table_rebuild(rm_index* idx, int n_nodes_hwm, cudaStream_t s);
 int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int* out_n_h, cudaStream_t s);
 int rm_launch_gc_agree(rm_index* idx, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n,

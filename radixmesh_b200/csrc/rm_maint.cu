@@ -33,6 +33,7 @@ __global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
     t.gen[x] = 0;
     t.parked[x] = -1;
     t.born[x] = 0;
+    t.ord[x] = 0;
     lock_first[x] = RM_INT_MAX;
     lock_cnt[x] = 0;
   }
@@ -51,6 +52,7 @@ __global__ void rm_reset_kernel(RmTree t, int* lock_first, int* lock_cnt) {
     c.evict_n = 0;
     c.split_done = 0;
     c.n_tomb = 0;
+    c.n_kids = 0;
     c.n_big = 0;
     c.dbg_max_group = 0;
     c.dbg_groups = 0;
@@ -944,5 +946,124 @@ extern "C" int rm_compact(rm_index* idx, void* stream) {
   RM_CUDA(cudaStreamSynchronize(s));
   RM_CUDA(cudaGetLastError());
   (void)rm_bits_u64;
+  return RM_OK;
+}
+
+// ------------------------------------------------------------------ TreeNode proxy support (O(1) in the tree size)
+// The drop-in's single-key surface (RadixCache.match_prefix -> MatchResult.last_device_node, TreeNode.parent /
+// .lock_ref / .children / .key / .value; radix_cache.py:35-64) reads the handful of nodes it touches, not the pool.
+__global__ void rm_node_info_kernel(RmTree t, const int* __restrict__ ids, int n, rm_node_info_t* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int x = ids[i];
+  rm_node_info_t r;
+  if (x < 0 || x >= t.max_nodes) {
+    r.parent = -2;
+    r.edge_len = r.lock_ref = r.rank = r.depth_end = r.nchild = r.gen = 0;
+    r.parked = -1;
+    r.edge_off = 0;
+    r.stamp = 0;
+  } else {
+    r.parent = t.parent[x];
+    r.edge_len = t.edge_len[x];
+    r.lock_ref = t.lock_ref[x];
+    r.rank = t.rank[x];
+    r.depth_end = t.depth_end[x];
+    r.nchild = t.nchild[x];
+    r.gen = t.gen[x];
+    r.parked = t.parked[x];
+    r.edge_off = t.edge_off[x];
+    r.stamp = t.stamp[x];
+  }
+  out[i] = r;
+}
+
+// children of one node: (child id, first token of its edge, generation, dict-order key) per child, unordered
+__global__ void rm_node_children_kernel(RmTree t, int n, int node, int cap, int* __restrict__ out_id, int* __restrict__ out_tok,
+                                        int* __restrict__ out_gen, u64* __restrict__ out_ord) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || x == 0 || t.parent[x] != node || t.gen[x] < 0 || t.edge_len[x] <= 0) return;
+  const int k = atomicAdd(&t.ctr->n_kids, 1);
+  if (k >= cap) return;
+  out_id[k] = x;
+  out_tok[k] = rm_tok(t, t.edge_off[x]);
+  out_gen[k] = t.gen[x];
+  out_ord[k] = t.ord[x];
+}
+
+// RadixCache.total_size (radix_cache.py:354-364): sum of len(value) over the tree
+__global__ void rm_total_size_kernel(RmTree t, int n, u64* __restrict__ out) {
+  i64 local = 0;
+  for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < n; x += gridDim.x * blockDim.x)
+    if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0) local += t.mode == RM_MODE_ROUTER ? 1 : t.edge_len[x];
+#ifndef RM_EMU
+  for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
+  if ((threadIdx.x & 31) == 0 && local) atomicAdd(out, (u64)local);
+#else
+  if (local) atomicAdd(out, (u64)local);
+#endif
+}
+
+#define RM_INFO_CHUNK 256
+int rm_launch_node_info(rm_index* idx, const int* ids_h, int n, rm_node_info_t* out_h, cudaStream_t s) {
+  RmScratch& sc = idx->sc;
+  for (int a = 0; a < n; a += RM_INFO_CHUNK) {
+    const int m = n - a < RM_INFO_CHUNK ? n - a : RM_INFO_CHUNK;
+    RM_CUDA(cudaMemcpyAsync(sc.info_ids, ids_h + a, sizeof(int) * (size_t)m, cudaMemcpyHostToDevice, s));
+    RM_LAUNCH(rm_node_info_kernel, 1, RM_INFO_CHUNK, s, idx->t, sc.info_ids, m, sc.info_rows);
+    RM_CUDA(cudaMemcpyAsync(out_h + a, sc.info_rows, sizeof(rm_node_info_t) * (size_t)m, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaStreamSynchronize(s));
+  }
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
+int rm_launch_node_children(rm_index* idx, int node, int cap, int* ids_h, int* toks_h, int* gens_h, u64* ords_h, int* out_n_h,
+                            cudaStream_t s) {
+  RmTree& t = idx->t;
+  RmScratch& sc = idx->sc;
+  RmCounters c;
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  const int n = c.node_hwm;
+  RM_CUDA(cudaMemsetAsync(&t.ctr->n_kids, 0, sizeof(int), s));
+  // the eviction scratch is free between calls (one host thread at a time per index): ids / tokens / gens / order keys
+  int* d_id = reinterpret_cast<int*>(sc.ev_val[0]);
+  int* d_tok = reinterpret_cast<int*>(sc.ev_val[1]);
+  int* d_gen = sc.ev_lens;
+  u64* d_ord = sc.ev_key[0];
+  RM_LAUNCH(rm_node_children_kernel, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, node, t.max_nodes, d_id, d_tok, d_gen, d_ord);
+  RM_CUDA(cudaGetLastError());
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  int k = c.n_kids;
+  *out_n_h = k;
+  if (k > cap) k = cap;
+  if (k > 0) {
+    RM_CUDA(cudaMemcpyAsync(ids_h, d_id, sizeof(int) * (size_t)k, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(toks_h, d_tok, sizeof(int) * (size_t)k, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(gens_h, d_gen, sizeof(int) * (size_t)k, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(ords_h, d_ord, sizeof(u64) * (size_t)k, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaStreamSynchronize(s));
+  }
+  return RM_OK;
+}
+
+int rm_launch_total_size(rm_index* idx, i64* out_h, cudaStream_t s) {
+  RmTree& t = idx->t;
+  RmCounters c;
+  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  u64* acc = reinterpret_cast<u64*>(idx->sc.info_rows);
+  RM_CUDA(cudaMemsetAsync(acc, 0, sizeof(u64), s));
+  const int n = c.node_hwm;
+  int grid = (n + RM_MT_TPB - 1) / RM_MT_TPB;
+  if (grid > 1184) grid = 1184;
+  RM_LAUNCH(rm_total_size_kernel, grid, RM_MT_TPB, s, t, n, acc);
+  RM_CUDA(cudaGetLastError());
+  u64 v = 0;
+  RM_CUDA(cudaMemcpyAsync(&v, acc, sizeof(u64), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  *out_h = (i64)v;
   return RM_OK;
 }

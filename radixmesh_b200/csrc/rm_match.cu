@@ -470,6 +470,7 @@ __device__ __forceinline__ void rm_split_apply_body(const RmTree& t, const u64* 
   const int lk = t.lock_ref[c];
   const int rk = t.rank[c];
   const u64 st_c = t.stamp[c];
+  const u64 ord_c = t.ord[c];
   g.sync();
   // pass 3: one upper node per distinct split point, chained parent -> u_0 -> ... -> u_{U-1} -> c
   for (int kk0 = 0; kk0 < U; kk0 += G) {
@@ -501,6 +502,8 @@ __device__ __forceinline__ void rm_split_apply_body(const RmTree& t, const u64* 
     t.gen[u] = 0;
     t.parked[u] = -1;
     t.stamp[u] = st;
+    t.ord[u] = kk == 0 ? ord_c : 0;    // the first upper node takes c's place in the parent's dict; the rest are only children
+    if (kk == U - 1) t.ord[c] = 0;
     atomicMax(&t.ctr->node_hwm, u + 1);
     // owner map of segment [a, p): the first position keeps the edge's own flag (kk == 0) or marks u as the
     // contiguous child of the previous segment
@@ -610,6 +613,7 @@ __device__ __forceinline__ void rm_split_small_group(const RmTree& t, const u64*
   const int lk = t.lock_ref[c];
   const int rk = t.rank[c];
   const u64 st_c = t.stamp[c];
+  const u64 ord_c = t.ord[c];
   const int seg0 = rm_seg(t, off);
   g.sync();
   for (int j0 = 0; j0 < n; j0 += G) {
@@ -657,6 +661,8 @@ __device__ __forceinline__ void rm_split_small_group(const RmTree& t, const u64*
         t.gen[u] = 0;
         t.parked[u] = -1;
         t.stamp[u] = st;
+        t.ord[u] = kk == 0 ? ord_c : 0;
+        if (kk == U - 1) t.ord[c] = 0;
         atomicMax(&t.ctr->node_hwm, u + 1);
         rm_set_seg(t, off + a, kk == 0 ? ((seg0 & RM_SEG_CONT) | u) : (u | RM_SEG_CONT));
         fill_off = off + a;
@@ -744,7 +750,7 @@ rm_split_kernel(RmTree t, u64* rkey, unsigned* rval, int Bmax, int len_bits, int
     int c = 0, par = 0, len = 0, dend = 0, lk = 0, rk = 0;
     unsigned q = 0;
     i64 off = 0;
-    u64 st_c = 0;
+    u64 st_c = 0, ord_c = 0;
     if (i < B) {
       ki = rkey[i];
       c = (int)(ki >> len_bits);
@@ -759,6 +765,7 @@ rm_split_kernel(RmTree t, u64* rkey, unsigned* rval, int Bmax, int len_bits, int
       lk = t.lock_ref[c];
       rk = t.rank[c];
       st_c = t.stamp[c];
+      ord_c = t.ord[c];
       const bool is_head = head == i;
       if (n > small_max && n > 1) {                                         // many: sorted, then a warp per edge
         if (role != 1) {                                                    // (that path re-arms head and count itself)
@@ -812,6 +819,8 @@ rm_split_kernel(RmTree t, u64* rkey, unsigned* rval, int Bmax, int len_bits, int
         t.gen[u] = 0;
         t.parked[u] = -1;
         t.stamp[u] = st;
+        t.ord[u] = ord_c;           // u takes c's place in the parent's dict; c is u's only child
+        t.ord[c] = 0;
         made_hwm = u + 1;
         rm_set_seg(t, off, (r0.y & RM_SEG_CONT) | u);          // owner map: [off, off+p) is u's, c starts at off+p
         rm_set_seg(t, off + p, c | RM_SEG_CONT);

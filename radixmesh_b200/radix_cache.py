@@ -17,7 +17,8 @@ from . import capi
 
 class TreeNode:
     """Handle to a node of the device tree (reference: radix_cache.py:35-64).  Attributes are read from
-    the device on access.  `id` is the node's pool id; like the reference's creation counter it is not
+    the device on access, a few dozen bytes per node through rm_node_info / rm_node_children whatever the
+    size of the tree.  `id` is the node's pool id; like the reference's creation counter it is not
     comparable across replicas — identity for parity is the full key."""
 
     __slots__ = ("_cache", "id", "_gen")
@@ -40,7 +41,7 @@ class TreeNode:
 
     @property
     def lock_ref(self) -> int:
-        return int(self._cache._dump()["lock_ref"][self._resolved()])
+        return int(self._cache._info(self._resolved()).lock_ref)
 
     @property
     def last_access_time(self) -> int:
@@ -51,17 +52,12 @@ class TreeNode:
         x = self._resolved()
         if x == 0:
             return None
-        return self._cache._handle(int(self._cache._dump()["parent"][x]))
+        return self._cache._handle(int(self._cache._info(x).parent))
 
     @property
     def children(self) -> dict:
-        d = self._cache._dump()
-        x = self._resolved()
-        out = {}
-        for c in np.nonzero((d["parent"][:d["n"]] == x) & (d["gen"][:d["n"]] >= 0))[0]:
-            if c != 0:
-                out[self._cache._node_tokens(int(c))[0]] = self._cache._handle(int(c))
-        return out
+        """{child key: TreeNode} in the reference's dict order (one scan of the pool on the device, the children back)."""
+        return self._cache._children(self._resolved())
 
     hit_count = 0          # never incremented in the reference either (SURVEY.md 5)
     loading = False
@@ -130,11 +126,29 @@ class RadixCache:
         self._be = self._ix.be
         self.device = getattr(self._be, "device", "cpu")
         self._dump_cache = None
+        self._info_cache = {}
         self.root_node = TreeNode(self, 0, 0)
 
     # ------------------------------------------------------------------ helpers
     def _invalidate(self) -> None:
         self._dump_cache = None
+        self._info_cache = {}
+
+    def _info(self, x: int):
+        """rm_node_info row of node x (cached until the next mutation)."""
+        self._flush()
+        r = self._info_cache.get(x)
+        if r is None:
+            r = self._info_cache[x] = self._ix.node_info([x])[0]
+        return r
+
+    def _children(self, x: int) -> dict:
+        self._flush()
+        out = {}
+        for cid, tok, gen in self._ix.node_children(x):
+            key = tok if self._P == 1 else tuple(self._page_tok[tok])
+            out[key] = self.root_node if cid == 0 else TreeNode(self, cid, gen)
+        return out
 
     def _dump(self) -> dict:
         self._flush()          # staged remote inserts (RadixMesh) must be visible to every read
@@ -163,26 +177,27 @@ class RadixCache:
     def _handle(self, node_id: int) -> TreeNode:
         if node_id == 0:
             return self.root_node
-        return TreeNode(self, node_id, int(self._dump()["gen"][node_id]))
+        return TreeNode(self, node_id, int(self._info(node_id).gen))
 
     def _resolve(self, node_id: int, gen: int) -> int:
         if gen < 0 or node_id == 0:
             return node_id
-        d = self._dump()
-        if int(d["gen"][node_id]) == gen:
+        r = self._info(node_id)
+        if int(r.gen) == gen:
             return node_id
-        x = int(d["parked"][node_id])
+        x = int(r.parked)
         while x >= 0:
-            if int(d["gen"][x]) == -(gen + 1):
+            r = self._info(x)
+            if int(r.gen) == -(gen + 1):
                 return x
-            x = int(d["parked"][x])
+            x = int(r.parked)
         return node_id
 
     def _node_tokens(self, x: int) -> List[int]:
         if x == 0:
             return []
-        d = self._dump()
-        tok, _ = self._ix.read_arena(int(d["edge_off"][x]), int(d["edge_len"][x]), values=False)
+        r = self._info(x)
+        tok, _ = self._ix.read_arena(int(r.edge_off), int(r.edge_len), values=False)
         if self._P > 1:
             return [t for sid in tok.tolist() for t in self._page_tok[sid]]
         return tok.tolist()
@@ -191,8 +206,8 @@ class RadixCache:
         import torch
         if x == 0:
             return []
-        d = self._dump()
-        _, val = self._ix.read_arena(int(d["edge_off"][x]), int(d["edge_len"][x]))
+        r = self._info(x)
+        _, val = self._ix.read_arena(int(r.edge_off), int(r.edge_len))
         if self._P > 1:
             val = self._rows_values(val)
         return torch.from_numpy(val)
@@ -384,17 +399,40 @@ class RadixCache:
         return int(self._ix.sizes().protected_) * self._P
 
     def total_size(self) -> int:
-        d = self._dump()
-        live = (d["parent"][:d["n"]] >= 0) & (d["gen"][:d["n"]] >= 0)
-        live[0] = False
-        return int(d["edge_len"][:d["n"]][live].sum()) * self._P
+        """radix_cache.py:239-241, 354-364: reduced on the device (rm_total_size), eight bytes back."""
+        self._flush()
+        return self._ix.total_size() * self._P
 
     def all_values_flatten(self):
-        """All values of the tree; node order is by pool id, not the reference's dict order."""
+        """radix_cache.py:243-248: the values of the tree in the reference's order - pre-order, the children of a node
+        in dict insertion order.  The device keeps that order as a key per node (the op that added the child to its
+        parent; a split's upper node inherits the place of the node it splits, radix_cache.py:292)."""
         import torch
         d = self._dump()
-        out = [self._node_value(int(x)) for x in range(1, d["n"]) if d["parent"][x] >= 0 and d["gen"][x] >= 0]
-        return torch.cat(out) if out else torch.empty((0,), dtype=torch.int64)
+        n = d["n"]
+        order = self._ix.dump_order(n)
+        live = np.nonzero((d["parent"][:n] >= 0) & (d["gen"][:n] >= 0))[0]
+        live = live[live != 0]
+        if len(live) == 0:
+            return torch.empty((0,), dtype=torch.int64)
+        # children lists in dict order: sort by (parent, order key), then cut at parent changes
+        srt = live[np.lexsort((live, order[live], d["parent"][live]))]
+        par = d["parent"][srt]
+        starts = np.nonzero(np.r_[True, par[1:] != par[:-1]])[0]
+        kids = {int(par[a]): srt[a:b] for a, b in zip(starts, np.r_[starts[1:], len(srt)])}
+        used = int(self._ix.sizes().arena_used)
+        _, val = self._ix.read_arena(0, used)
+        out, stack = [], [iter(kids.get(0, ()))]
+        while stack:
+            x = next(stack[-1], None)
+            if x is None:
+                stack.pop()
+                continue
+            x = int(x)
+            o, ln = int(d["edge_off"][x]), int(d["edge_len"][x])
+            out.append(self._rows_values(val[o:o + ln]) if self._P > 1 else val[o:o + ln])
+            stack.append(iter(kids.get(x, ())))
+        return torch.from_numpy(np.concatenate(out))
 
     def pretty_print(self) -> None:
         d = self._dump()
@@ -415,10 +453,9 @@ class RadixCache:
 
     # parity helper shared with the oracle's canonical()
     def full_key(self, node: TreeNode) -> List[int]:
-        d = self._dump()
         x = node._resolved()
         parts = []
         while x != 0:
             parts.append(self._node_tokens(x))
-            x = int(d["parent"][x])
+            x = int(self._info(x).parent)
         return [t for p in reversed(parts) for t in p]

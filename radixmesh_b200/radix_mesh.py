@@ -212,8 +212,7 @@ class RadixMesh(RadixCache):
         return None
 
     def _node_value(self, x: int):
-        d = self._dump()
-        rank = int(d["rank"][x])
+        rank = int(self._info(x).rank)
         if self.mode == RadixMode.ROUTER:
             return RankValue(rank)
         return OwnedValue(super()._node_value(x) if x else None, rank)

@@ -270,3 +270,63 @@ def run_insert_returns_own_prefix(kw):
     n1.oplog_received(CacheOplog(oplog_type=CacheOplogType.INSERT, node_rank=0, key=[9], value=[9], ttl=5))
     assert n1.insert([1, 2, 3, 4, 5, 6], torch.tensor([1, 2, 3, 4, 55, 66])) == 4
     assert n1.insert([7, 7], torch.tensor([5, 6])) == 0
+
+
+def run_flatten_order(kw, seed, page=1):
+    """all_values_flatten in the reference's order (pre-order, children in dict insertion order, radix_cache.py:239-248),
+    total_size on the device, and TreeNode.children / .parent / .lock_ref through rm_node_info / rm_node_children,
+    against the oracle under random insert / match (splitting) / lock / evict streams."""
+    import random
+    from oracle.radix_port import PortRadixCache
+    rnd = random.Random(7000 + seed)
+    alloc = FakeAllocator()
+    small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64)
+    small.update(kw)
+    t = RadixCache(None, alloc, page, **small)
+    orc = PortRadixCache(page)
+    vc = 0
+    held = []
+    for step in range(70):
+        kind = rnd.choice(["ins", "ins", "ins", "match", "match", "evict", "lock"])
+        key = [rnd.randrange(4) for _ in range(rnd.randrange(0, 16))]
+        if kind == "ins":
+            key = key[:len(key) // page * page]
+            val = list(range(vc, vc + len(key)))
+            vc += len(key)
+            assert t.insert(key, torch.tensor(val, dtype=torch.int64)) == orc.insert(list(key), np.asarray(val, dtype=np.int64))
+        elif kind == "match":
+            a, b = t.match_prefix(key), orc.match_prefix(list(key))
+            assert a.device_indices.tolist() == b.indices.tolist()
+            held.append((a.last_device_node, b.last_node))
+        elif kind == "lock" and held:
+            a, b = rnd.choice(held)
+            if b is not orc.root and b.parent is not None and (b.key is not None):
+                assert t.inc_lock_ref(a) == orc.inc_lock_ref(b)
+                assert a.lock_ref == b.lock_ref
+                assert t.dec_lock_ref(a) == orc.dec_lock_ref(b)
+        elif kind == "evict":
+            n = rnd.randrange(0, 12)
+            t.evict(n)
+            orc.evict(n)
+            held = [(a, b) for a, b in held if b is orc.root or _alive(orc, b)]
+        assert t.total_size() == orc.total_size()
+        assert t.all_values_flatten().tolist() == orc.all_values_flatten().tolist(), f"step {step} ({kind})"
+        # children of the root and of one random node on each side, in dict order
+        assert [k if page == 1 else tuple(k) for k in t.root_node.children.keys()] == list(orc.root.children.keys())
+        if held:
+            a, b = held[-1]
+            if b is orc.root or b.parent is not None:
+                live = b is orc.root or _alive(orc, b)
+                if live:
+                    assert list(a.children.keys()) == list(b.children.keys())
+                    if b is not orc.root:
+                        assert t.full_key(a.parent) == orc.full_key(b.parent)
+
+
+def _alive(orc, node):
+    while node is not orc.root:
+        p = node.parent
+        if p is None or all(c is not node for c in p.children.values()):
+            return False
+        node = p
+    return True

@@ -97,3 +97,13 @@ def test_paged_random_against_oracle(seed):
             orc.evict(n)
             assert alloc.freed[before_d:] == orc.freed[before_o:]
         assert (t.evictable_size(), t.total_size()) == (orc.evictable, orc.total_size())
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_flatten_order_children_and_total_size(seed):
+    dc.run_flatten_order(kw(), seed)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_flatten_order_paged(seed):
+    dc.run_flatten_order(kw(), 50 + seed, page=2)

@@ -1,5 +1,6 @@
 """GPU parity: mesh kernels (conflict rule, duplicate table, locked swap, router pick, device MD5
 fallback) and the drop-in classes against the oracle / the reference's recorded results."""
+import numpy as np
 import pytest
 
 from tests import cases_mesh
@@ -152,3 +153,58 @@ def test_paged_sequences(case):
     """RadixCache(page_size > 1) recorded from the reference: the drop-in runs the device index on page symbols."""
     dc.replay_base_sequence(case, {})
 
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_gpu_oplog_wire_ingest(seed):
+    """SURVEY.md 8f-1 on the GPU: packed and JSON wire bytes through RadixMesh.oplog_received_wire into a CUDA index
+    (staged, gated on the header fields, applied as ordered rm_insert_batch_h calls) against the object path and the
+    oracle's node."""
+    from tests.test_oplog_codec import run_wire_case
+    run_wire_case(seed, dict)
+
+
+def test_gpu_oplog_exchange_on_one_rank():
+    """SURVEY.md 8f-2, the apply half on the GPU (the all-gather needs one GPU per rank: bench.py --gpus N runs it over
+    NCCL and compares the replicas): staged local inserts, packed, applied through rm_insert_batch on device pointers in
+    max_batch chunks to a P/D tree and a ROUTER replica, against the oracle's nodes fed the same records."""
+    import random
+    from oracle.radix_port import MODE_PREFILL, MODE_ROUTER, PortRadixMesh
+    from radixmesh_b200.mesh_oplog import NvlinkOplogExchange
+    from tests.test_mesh_oplog import _canon
+    kw = dict(n_prefill=1, n_decode=1, max_nodes=4096, max_tokens=1 << 16, max_batch=8, max_key_len=32, max_dups=512)
+    tree = make_index(mode=1, self_rank=0, **kw)
+    router = make_index(mode=3, self_rank=2, **kw)
+    ex = NvlinkOplogExchange([tree, router], 0, 1)
+    ports = [PortRadixMesh(MODE_PREFILL, 0, 1, 1), PortRadixMesh(MODE_ROUTER, 2, 1, 1)]
+    rnd = random.Random(9)
+    for rd in range(5):
+        n = rnd.randrange(0, 30)
+        for _ in range(n):
+            key = [rnd.randrange(3) for _ in range(rnd.randrange(1, 9))]
+            val = [10 * i + t for i, t in enumerate(key)]
+            ex.stage(key, np.asarray(val, dtype=np.int64))
+            for p in ports:
+                p.apply_insert(list(key), np.asarray(val, dtype=np.int64), 0)
+        assert ex.exchange_and_apply() == n
+
+    def port_canon(t):
+        rows = []
+        for nd in t.iter_nodes():
+            raw = t._raw(nd.value)
+            rows.append((tuple(t.full_key(nd)), len(nd.key), tuple(int(x) for x in raw) if raw is not None else (), nd.value.rank, nd.lock_ref))
+        rows.sort()
+        dup = sorted((tuple(k[0]), k[1], v is not None) for k, v in t.dup_canonical().items())
+        return {"nodes": rows, "evictable": t.evictable, "protected": t.protected, "dup": dup}
+
+    assert _canon(tree) == port_canon(ports[0])
+    assert _canon(router) == port_canon(ports[1])
+    tree.close()
+    router.close()
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_gpu_flatten_order_children_and_total_size(seed):
+    """a12 on the GPU: all_values_flatten in the reference's pre-order / dict order, total_size reduced on the device,
+    TreeNode attributes through rm_node_info / rm_node_children."""
+    dc.run_flatten_order({}, seed)

@@ -101,15 +101,19 @@ def _decode_node(kw):
 
 @pytest.mark.parametrize("seed", range(6))
 def test_mesh_node_fed_from_the_wire_matches_object_path_and_oracle(seed):
+    from tests.emu.emu_backend import NumpyBackend, emu_lib
+    run_wire_case(seed, lambda: dict(_backend=NumpyBackend(), _library=emu_lib()))
+
+
+def run_wire_case(seed, make_kw):
     """A decode node receives the INSERT stream of its peers as packed bytes, JSON bytes and objects, interleaved;
     its tree must equal that of a node fed the same records as objects (the path the reference goldens pin) and
-    its matches those of the oracle's node."""
+    its matches those of the oracle's node.  (Host emulation here; tests/test_gpu_mesh.py runs it on CUDA indexes.)"""
     from oracle.radix_port import MODE_DECODE, PortRadixMesh
     from tests import dropin_cases as dc
-    from tests.emu.emu_backend import NumpyBackend, emu_lib
     rnd = random.Random(seed)
-    wire_node = _decode_node(dict(_backend=NumpyBackend(), _library=emu_lib()))
-    obj_node = _decode_node(dict(_backend=NumpyBackend(), _library=emu_lib()))
+    wire_node = _decode_node(make_kw())
+    obj_node = _decode_node(make_kw())
     port = PortRadixMesh(MODE_DECODE, 3, 3, 2)
     packed, js = PackedSerializer(), JsonSerializer()
     for step in range(60):                                  # > max_batch records between flushes: chunked apply

@@ -505,3 +505,73 @@ def mesh_route_block(torch, capi, rank, world, steps=4, warmup=2, check_requests
                          "oracle": "PortRadixMesh (ROUTER mode) fed every insert under the 6 rarest prompts; replicated form",
                          "sharded_equals_replicated_frac": agree, "error_rows": int((~ok_rows).sum())},
     }
+
+
+def oplog_exchange_block(torch, capi, rank, world, records=1024, L=512, rounds=4, warmup=1):
+    """every rank stages `records` local inserts per round (Zipf-shared prefixes, half of them carrying
+    rank-specific values: conflicts for the lower-rank-wins rule), all ranks all-gather the packed records over NCCL
+    and apply rank 0's, rank 1's, ... in that order.  Replicas are compared by a digest of their canonical trees."""
+    import hashlib
+    import torch.distributed as dist
+    from radixmesh_b200.mesh_oplog import NvlinkOplogExchange
+    from tests.parity import device_digest
+    dev = torch.device("cuda", torch.cuda.current_device())
+    P = max(1, world // 2)
+    D = world - P
+    docs = np.random.default_rng(3).integers(0, 32000, (256, L), dtype=np.int32)
+    mode = capi.MODE_PREFILL if rank < P else capi.MODE_DECODE
+    tot = world * records * (rounds + warmup)
+    ix = capi.DeviceIndex(mode=mode, device=dev.index, self_rank=rank, n_prefill=P, n_decode=max(D, 1), max_nodes=4 * tot + (1 << 16),
+                          max_tokens=tot * L + (1 << 22), max_batch=4096, max_key_len=max(L, 64), max_dups=2 * tot + 1024)
+    ex = NvlinkOplogExchange([ix], rank, world)
+    rng = np.random.default_rng(100 + rank)
+    w = 1.0 / np.arange(1, 257) ** 1.1
+    w /= w.sum()
+    times = []
+    for rd in range(rounds + warmup):
+        d = rng.choice(256, size=records, p=w)
+        cut = rng.integers(L // 8, L + 1, size=records)
+        keys = rng.integers(0, 32000, (records, L), dtype=np.int32)
+        mask = np.arange(L)[None, :] < cut[:, None]
+        keys[mask] = docs[d][mask]
+        base = (rd * world + rank) * records * L
+        for i in range(records):
+            v = np.arange(base + i * L, base + (i + 1) * L, dtype=np.int64) if i % 2 else np.arange(L, dtype=np.int64) + int(d[i]) * L
+            ex.stage(keys[i], v)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        ex.exchange_and_apply()
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        if rd >= warmup:
+            times.append(float(dt.item()))
+    ix.check_device_error()
+    dd = device_digest(ix)
+    rk = dd["dump"]["rank"]
+    h = hashlib.blake2b(digest_size=16)
+    d = dd["dump"]
+    for dg, ln, lk, r in sorted((dd["by_id"][x], int(d["edge_len"][x]), int(d["lock_ref"][x]), int(rk[x])) for x in dd["by_id"] if x):
+        h.update(dg)
+        h.update(np.asarray([ln, lk, r], dtype=np.int64).tobytes())
+    s = ix.sizes()
+    sig = torch.tensor(list(h.digest()) + [int(s.n_nodes) & 0xFF, int(s.n_dups) & 0xFF], dtype=torch.uint8, device=dev)
+    allsig = [torch.zeros_like(sig) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(allsig, sig)
+    else:
+        allsig = [sig]
+    same = all(bool((a == allsig[0]).all()) for a in allsig)
+    ix.close()
+    if rank != 0:
+        return None
+    per = sum(times) / len(times)
+    return {"what": "all-gather of packed INSERT records over NCCL + one ordered apply on every replica (mesh_oplog.py)",
+            "n_gpus": world, "records_per_round_per_rank": records, "tokens_per_record": L, "rounds": rounds,
+            "ms_per_round": 1e3 * per, "records_per_s_applied_per_replica": world * records / per,
+            "bytes_gathered_per_round_per_gpu": world * records * L * 12,
+            "replicas_identical": same, "nodes": int(s.n_nodes), "dups": int(s.n_dups),
+            "check": "digest over every replica's canonical tree (keys, values, boundaries, owner ranks, locks) + node and duplicate counts"}
