@@ -214,6 +214,7 @@ def main():
     ap.add_argument("--stages", action="store_true", help="also time the split stage (one more CUDA event per step)")
     ap.add_argument("--no-compact", action="store_true", help="skip rm_compact after the build (A/B of the arena layout)")
     ap.add_argument("--no-blocks", action="store_true", help="headline only: no target / c3 / mesh_route blocks")
+    ap.add_argument("--with-c5", action="store_true", help="also run the 10 M-node / 4K-token block (tools/bench_c5.py; ~1 min more)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
@@ -410,6 +411,12 @@ def main():
             hpt = tb["roofline"]["mean_hops"] / max(tb["mean_matched_len"], 1.0)
             line["c3"] = blocks.c3_block(sys.modules[__name__], torch, capi, peak, tix, tstate, hpt)
             tix.close()
+        if world == 1 and args.with_c5:
+            import bench_c5
+            line["c5"] = bench_c5.run(peak=peak)
+            if line["c5"]["parity_check"]["mismatches"]:
+                sys.stderr.write(json.dumps({"error": "c5 parity_check failed", "parity_check": line["c5"]["parity_check"]}) + "\n")
+                raise SystemExit(3)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

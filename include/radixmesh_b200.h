@@ -280,6 +280,41 @@ int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int6
 int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void* stream);
 
 /*
+ * Paged keys: RadixCache(page_size > 1) (radix_cache.py:23-32 _key_match_paged, :109-114 child key = first page,
+ * :148-150 page-aligned match).  A paged radix tree over tokens is a radix tree over page symbols, so an rm_index in
+ * BASE mode runs unchanged on symbols; an rm_pages object beside it turns tokens into symbols on the device and keeps
+ * the KV indices of a page as one row (the index's value of a symbol position is the row id).  All pointers are
+ * DEVICE pointers; keys are taken in whole pages (len / page_size, the reference's callers align).
+ *   rm_pages_intern    key q = tokens[offsets[q] .. offsets[q+1]); its symbols go to out_syms[sym_offsets[q] ..
+ *                      sym_offsets[q+1]) (sym_offsets[q+1] - sym_offsets[q] = whole pages of key q; total_pages =
+ *                      sym_offsets[B]).  create != 0 (insert): unseen pages get new symbols.  create == 0 (match): the
+ *                      first unseen page of a key and everything after it become a symbol no edge holds, so the walk
+ *                      ends there as the reference's dict lookup would; out_npages[q] (may be NULL) = pages resolved.
+ *                      scratch: total_pages int32.  Every table hit is verified against the stored page tokens.
+ *   rm_pages_rows_put  n_rows rows of page_size KV indices each (values, row-major) -> out_rows[n_rows] row ids: the
+ *                      `values` array of rm_insert_batch on the symbols.
+ *   rm_pages_rows_free hand rows back: those of evicted runs, and those of the pages an insert found already present
+ *                      (the first out_prefix_len[r] rows of record r).
+ *   rm_pages_rows_get  row ids (rm_gather_values / rm_read_arena output) -> KV indices, page_size per row.
+ *   rm_pages_tokens    symbols -> page tokens (TreeNode.key).
+ *   rm_pages_status    HOST out: symbols in use, free rows, sticky device error (RM_E_NOSPACE: table or rows exhausted;
+ *                      RM_E_INVALID: two different new pages of one batch with the same 64-bit hash), page_size.
+ *                      Synchronises.
+ */
+typedef struct rm_pages rm_pages;
+int rm_pages_create(int32_t device, int32_t page_size, int64_t max_pages, int64_t max_rows, rm_pages** out);
+int rm_pages_destroy(rm_pages* p);
+int rm_pages_reset(rm_pages* p, void* stream);
+int rm_pages_intern(rm_pages* p, const int32_t* tokens, const int64_t* offsets, int32_t B, int32_t create,
+                    const int64_t* sym_offsets, int64_t total_pages, int32_t* out_syms, int32_t* out_npages, int32_t* scratch,
+                    void* stream);
+int rm_pages_rows_put(rm_pages* p, const int64_t* values, int64_t n_rows, int64_t* out_rows, void* stream);
+int rm_pages_rows_free(rm_pages* p, const int64_t* rows, int64_t n, void* stream);
+int rm_pages_rows_get(rm_pages* p, const int64_t* rows, int64_t n, int64_t* out_values, void* stream);
+int rm_pages_tokens(rm_pages* p, const int32_t* syms, int64_t n, int32_t* out_tokens, void* stream);
+int rm_pages_status(rm_pages* p, int64_t* out4_h, void* stream);
+
+/*
  * Measurement aids (no counterpart in the reference, which has no instrumentation).
  * rm_launch_count: kernels this library has launched in this process.
  * rm_profile(idx, 1): record a CUDA-event pair around the walk kernel (K1) of every following

@@ -12,7 +12,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 OUT_DIR = os.path.join(PKG, "_lib")
 OUT = os.path.join(OUT_DIR, "libradixmesh_b200.so")
-SOURCES = ["rm_api.cu", "rm_match.cu", "rm_insert.cu", "rm_maint.cu", "rm_route.cu", "rm_noalloc.cu"]
+SOURCES = ["rm_api.cu", "rm_match.cu", "rm_insert.cu", "rm_maint.cu", "rm_route.cu", "rm_noalloc.cu", "rm_pages.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
 

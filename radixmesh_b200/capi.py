@@ -72,6 +72,15 @@ _PROTOS = {
     "rm_node_children": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P]),
     "rm_total_size": (C.c_int, [_P, _P, _P]),
     "rm_dump_order": (C.c_int, [_P, C.c_int32, _P, _P]),
+    "rm_pages_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.POINTER(_P)]),
+    "rm_pages_destroy": (C.c_int, [_P]),
+    "rm_pages_reset": (C.c_int, [_P, _P]),
+    "rm_pages_intern": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, _P, C.c_int64, _P, _P, _P, _P]),
+    "rm_pages_rows_put": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "rm_pages_rows_free": (C.c_int, [_P, _P, C.c_int64, _P]),
+    "rm_pages_rows_get": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "rm_pages_tokens": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "rm_pages_status": (C.c_int, [_P, _P, _P]),
     "rm_read_arena": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
     "rm_read_segments": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P]),
     "rm_launch_count": (C.c_uint64, []),
@@ -402,3 +411,69 @@ class DeviceIndex:
         with self._mutex:
             self._check(self.lib.rm_read_arena(self._h, int(off), int(n), ptr(tok), ptr(val), self._s()))
         return tok, val
+
+
+class DevicePages:
+    """rm_pages: page interning table + value rows for RadixCache(page_size > 1), beside a BASE-mode DeviceIndex that
+    runs on page symbols.  Arrays are the backend's (torch CUDA tensors in the product)."""
+
+    def __init__(self, page_size: int, max_pages: int, max_rows: int, *, device=0, backend=None, library=None):
+        self.be = backend if backend is not None else TorchCuda(device)
+        self.lib = library if library is not None else lib()
+        self.P = int(page_size)
+        self._h = _P()
+        self._mutex = threading.RLock()
+        self._check(self.lib.rm_pages_create(int(device), self.P, int(max_pages), int(max_rows), C.byref(self._h)))
+
+    def _check(self, st: int) -> None:
+        if st != RM_OK:
+            raise RadixMeshError(st, (self.lib.rm_last_error() or b"").decode())
+
+    def _s(self):
+        return self.be.stream()
+
+    def close(self) -> None:
+        if self._h:
+            self.lib.rm_pages_destroy(self._h)
+            self._h = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_pages_reset(self._h, self._s()))
+
+    def intern(self, tokens, offsets, B, create, sym_offsets, total_pages, out_syms, out_npages, scratch) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_pages_intern(self._h, ptr(tokens), ptr(offsets), B, 1 if create else 0, ptr(sym_offsets),
+                                                 int(total_pages), ptr(out_syms), ptr(out_npages), ptr(scratch), self._s()))
+
+    def rows_put(self, values, n_rows, out_rows) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_pages_rows_put(self._h, ptr(values), int(n_rows), ptr(out_rows), self._s()))
+
+    def rows_free(self, rows, n) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_pages_rows_free(self._h, ptr(rows), int(n), self._s()))
+
+    def rows_get(self, rows, n, out_values) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_pages_rows_get(self._h, ptr(rows), int(n), ptr(out_values), self._s()))
+
+    def tokens(self, syms, n, out_tokens) -> None:
+        with self._mutex:
+            self._check(self.lib.rm_pages_tokens(self._h, ptr(syms), int(n), ptr(out_tokens), self._s()))
+
+    def status(self):
+        """(symbols in use, free rows, sticky device error, page_size); raises on a device error."""
+        out = (C.c_int64 * 4)()
+        with self._mutex:
+            self._check(self.lib.rm_pages_status(self._h, out, self._s()))
+        if out[2]:
+            raise RadixMeshError(int(out[2]), "raised inside a page kernel (page table / value rows exhausted, or two new "
+                                              "pages of one batch with the same 64-bit hash)")
+        return int(out[0]), int(out[1]), int(out[2]), int(out[3])

@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "radixmesh_b200", "csrc")
 OUT = os.path.join(HERE, "_rm_emu.so")
-SOURCES = ["rm_api.cu", "rm_match.cu", "rm_insert.cu", "rm_maint.cu", "rm_route.cu", "rm_noalloc.cu"]
+SOURCES = ["rm_api.cu", "rm_match.cu", "rm_insert.cu", "rm_maint.cu", "rm_route.cu", "rm_noalloc.cu", "rm_pages.cu"]
 
 
 def build(force=False):

@@ -20,19 +20,18 @@ def _events(torch, n):
     return [torch.cuda.Event(enable_timing=True) for _ in range(n)]
 
 
-def node_hops(ix):
-    """Per node id: how many nodes lie on its root path (= the hops a walk that ends there makes), from the device
-    tree.  Used for the 8d byte model where the Python port cannot hold the tree (1 M nodes)."""
-    d = ix.dump()
-    n = d["n"]
-    parent = d["parent"][:n].astype(np.int64)
-    order = np.argsort(d["depth"][:n], kind="stable")
-    hops = np.zeros(n, dtype=np.int32)
-    for x in order.tolist():
-        p = parent[x]
-        if x != 0 and p >= 0:
-            hops[x] = hops[p] + 1
-    return hops
+def node_hops(ix, nodes):
+    """How many nodes lie on the root path of each node id in `nodes` (= the hops a walk that ends there makes), by
+    climbing the device tree's parent array.  Used for the 8d byte model where the Python port cannot hold the tree."""
+    parent = ix.dump()["parent"].astype(np.int64)
+    cur = np.asarray(nodes, dtype=np.int64).copy()
+    hops = np.zeros(len(cur), dtype=np.int64)
+    while True:
+        live = cur > 0
+        if not live.any():
+            return hops
+        hops += live
+        cur = np.where(live, parent[np.maximum(cur, 0)], 0)
 
 
 def build_tree(bench, wl, docs, ix, dev, torch, keep_rows):
@@ -117,7 +116,7 @@ def target_block(bench, torch, capi, peak, steps=6, warmup=3, cpu_queries=2048, 
     exp = longest_prefix_lengths(ins, host_q[s_chk][:check_queries])
     mism = int((got[:check_queries] != exp).sum())
     # 8d byte model: m from the oracle, hops from the device tree (the Python port cannot hold 1 M nodes)
-    hops = node_hops(ix)[out_node[s_chk].cpu().numpy()]
+    hops = node_hops(ix, out_node[s_chk].cpu().numpy())
     m = got.astype(np.int64)
     bpl = float((8 * np.minimum(L, m + 1) + 40 * hops + 8).mean())
     achieved = bpl * B / (walk_ms * 1e-3) / 1e9
