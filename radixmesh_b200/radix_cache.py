@@ -104,26 +104,28 @@ class RadixCache:
             raise ValueError("page_size > 1 is a RadixCache feature; RadixMesh hard-codes 1 (radix_mesh.py:87)")
         # Paged keys (radix_cache.py:23-32, 109-114: child key = first page, keys compared a page at a time, splits at
         # page multiples).  A paged radix tree over tokens IS a radix tree over page symbols, so the device index runs
-        # unchanged on symbols: this class keeps the exact dictionary page -> symbol on the host, stores one row of
-        # page_size KV indices per symbol in a host value store (the device value is the row id) and scales every
-        # length by page_size.  Host-side adapter: correct, Python-paced; the page_size == 1 path is untouched.
+        # unchanged on symbols; pages are interned on the device (rm_pages_intern: hash table, every hit verified
+        # against the stored page) and the KV indices of a page live in a device row store, the index's value of a
+        # symbol position being the row id (capi.DevicePages, csrc/rm_pages.cu).  Lengths, sizes, lock deltas and the
+        # eviction budget scale by page_size.  max_tokens stays a capacity in TOKENS.
         self._P = int(page_size)
-        self._page_id: dict = {}
-        self._page_tok: list = []
-        self._vs = np.zeros((1024, self._P), dtype=np.int64) if self._P > 1 else None
-        self._vs_free: list = []
-        self._vs_top = 0
+        self._pg = None
         self.req_to_token_pool = req_to_token_pool
         self.token_to_kv_pool_allocator = token_to_kv_pool_allocator
         self.page_size = page_size
         self.disable = disable
         self.enable_kv_cache_events = enable_kv_cache_events   # events are not produced (reference: NameError if on)
         self.kv_event_queue = []
-        kw = dict(mode=self.MODE, max_nodes=max_nodes, max_tokens=max_tokens, max_batch=max_batch,
-                  max_key_len=max_key_len, max_dups=max_dups, device=device, backend=_backend, library=_library)
+        P = self._P
+        kw = dict(mode=self.MODE, max_nodes=max_nodes, max_tokens=max(max_tokens // P, 1), max_batch=max_batch,
+                  max_key_len=max(max_key_len // P, 1), max_dups=max_dups, device=device, backend=_backend, library=_library)
         kw.update(_index_kwargs or {})
         self._ix = capi.DeviceIndex(**kw)
         self._be = self._ix.be
+        if P > 1:
+            n_sym = max(max_tokens // P, 1) + (1 << 12)
+            self._pg_rows_total = n_sym + max_batch * max(max_key_len // P, 1)
+            self._pg = capi.DevicePages(P, n_sym, self._pg_rows_total, device=device, backend=self._be, library=self._ix.lib)
         self.device = getattr(self._be, "device", "cpu")
         self._dump_cache = None
         self._info_cache = {}
@@ -146,7 +148,7 @@ class RadixCache:
         self._flush()
         out = {}
         for cid, tok, gen in self._ix.node_children(x):
-            key = tok if self._P == 1 else tuple(self._page_tok[tok])
+            key = tok if self._P == 1 else tuple(self._pages_of([tok]))
             out[key] = self.root_node if cid == 0 else TreeNode(self, cid, gen)
         return out
 
@@ -199,7 +201,7 @@ class RadixCache:
         r = self._info(x)
         tok, _ = self._ix.read_arena(int(r.edge_off), int(r.edge_len), values=False)
         if self._P > 1:
-            return [t for sid in tok.tolist() for t in self._page_tok[sid]]
+            return self._pages_of(tok)
         return tok.tolist()
 
     def _node_value(self, x: int):
@@ -216,64 +218,103 @@ class RadixCache:
         import torch
         return a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
 
-    # ------------------------------------------------------------------ paged keys: symbols and the value store
-    def _symbols(self, key, create: bool) -> List[int]:
-        P = self._P
-        out = []
-        for i in range(0, len(key) // P * P, P):
-            page = tuple(int(t) for t in key[i:i + P])
-            sid = self._page_id.get(page)
-            if sid is None:
-                if not create:
-                    break                      # a page the tree has never seen: nothing can match from here on
-                sid = len(self._page_tok)
-                self._page_id[page] = sid
-                self._page_tok.append(page)
-            out.append(sid)
-        return out
+    # ------------------------------------------------------------------ paged keys: symbols and value rows on the device
+    def _xp(self, x):
+        """torch for device tensors, numpy for the host-emulation backend."""
+        if hasattr(x, "data_ptr"):
+            import torch
+            return torch
+        return np
 
-    def _rows_alloc(self, n: int) -> np.ndarray:
-        rows = np.empty(n, dtype=np.int64)
-        k = min(n, len(self._vs_free))
-        for i in range(k):
-            rows[i] = self._vs_free.pop()
-        if n > k:
-            need = self._vs_top + (n - k)
-            if need > self._vs.shape[0]:
-                grown = np.zeros((max(need, 2 * self._vs.shape[0]), self._P), dtype=np.int64)
-                grown[:self._vs.shape[0]] = self._vs
-                self._vs = grown
-            rows[k:] = np.arange(self._vs_top, need)
-            self._vs_top = need
-        return rows
+    def _pages_of(self, syms) -> List[int]:
+        """Page tokens of a list of symbols (TreeNode.key, child keys)."""
+        syms = np.ascontiguousarray(syms, dtype=np.int32)
+        n = len(syms)
+        if n == 0:
+            return []
+        out = self._be.empty(n * self._P, np.int32)
+        self._pg.tokens(self._be.to_device(syms), n, out)
+        return self._be.to_host(out).tolist()
 
     def _rows_values(self, rows) -> np.ndarray:
-        rows = np.asarray(rows, dtype=np.int64)
-        return self._vs[rows].reshape(-1) if len(rows) else np.zeros(0, dtype=np.int64)
+        """KV indices of value rows (host array of row ids in, host array out)."""
+        rows = np.ascontiguousarray(rows, dtype=np.int64)
+        n = len(rows)
+        if n == 0:
+            return np.zeros(0, dtype=np.int64)
+        out = self._be.empty(n * self._P, np.int64)
+        self._pg.rows_get(self._be.to_device(rows), n, out)
+        return self._be.to_host(out)
 
-    def _no_paged_batch(self) -> None:
-        if self._P > 1:
-            raise NotImplementedError("the *_batch additions take tokens as they are: page_size 1 only")
+    def _intern(self, tokens, offsets, B: int, create: bool):
+        """Device tokens / offsets -> (symbols, symbol offsets [B+1], pages resolved per key), all on the device."""
+        xp = self._xp(offsets)
+        lens = offsets[1:] - offsets[:-1]
+        npg = lens // self._P if xp is np else xp.div(lens, self._P, rounding_mode="floor")
+        soffs = xp.zeros(B + 1, dtype=xp.int64) if xp is np else xp.zeros(B + 1, dtype=xp.int64, device=offsets.device)
+        soffs[1:] = xp.cumsum(npg, 0)
+        total = int(soffs[-1])
+        syms = self._be.empty(total + 1, np.int32)
+        npages = self._be.empty(B, np.int32)
+        if total:
+            self._pg.intern(tokens, offsets, B, create, soffs, total, syms, npages, self._be.empty(total + 1, np.int32))
+        return syms, soffs, npages, total
+
+    def _rows_of_prefixes(self, rows, soffs, prefix, B: int, total: int):
+        """Rows of the first prefix[r] pages of every record r (the pages an insert found already present)."""
+        xp = self._xp(rows)
+        if xp is np:
+            rec = np.repeat(np.arange(B), np.diff(soffs))
+            pos = np.arange(total) - soffs[:-1][rec]
+            return rows[:total][pos < prefix[rec]]
+        rec = xp.repeat_interleave(xp.arange(B, device=rows.device), soffs[1:] - soffs[:-1])
+        pos = xp.arange(total, device=rows.device) - soffs[:-1][rec]
+        return rows[:total][pos < prefix.to(xp.int64)[rec]].contiguous()
+
+    def _paged_insert(self, tokens, values, offsets, B: int):
+        """Ordered batch of paged inserts on device arrays; returns matched prefix lengths in PAGES (device int32)."""
+        syms, soffs, _, total = self._intern(tokens, offsets, B, create=True)
+        out = self._be.empty(B, np.int32)
+        if total == 0:
+            return out
+        rows = self._be.empty(total + 1, np.int64)
+        self._pg.rows_put(values, total, rows)        # values are page aligned: row i = values[i*P : (i+1)*P]
+        self._ix.insert(syms, rows, soffs, None, B, out)
+        dead = self._rows_of_prefixes(rows, soffs, out, B, total)
+        if len(dead):
+            self._pg.rows_free(dead, len(dead))
+        self._invalidate()
+        self._ix.check_device_error()
+        self._pg.status()
+        return out
 
     # ------------------------------------------------------------------ public API (radix_cache.py:117-248)
     def reset(self) -> None:
         self._ix.reset()
         self._invalidate()
-        self._page_id, self._page_tok, self._vs_free, self._vs_top = {}, [], [], 0
+        if self._pg is not None:
+            self._pg.reset()
 
     def match_prefix(self, key: List[int], **kwargs) -> MatchResult:
         import torch
         if self.disable or len(key) == 0:
             return MatchResult(torch.empty((0,), dtype=torch.int64), self.root_node, self.root_node)
         if self._P > 1:
-            key = self._symbols(key, create=False)       # page aligned (radix_cache.py:148-150), in symbols
-            if not key:
+            # page aligned (radix_cache.py:148-150); the pages become symbols on the device, an unseen page ends the key
+            be = self._be
+            n = len(key) // self._P * self._P
+            if n == 0:
                 return MatchResult(torch.empty((0,), dtype=torch.int64), self.root_node, self.root_node)
+            lens, nodes = self.match_prefix_batch(be.to_device(np.asarray(key[:n], dtype=np.int32)),
+                                                  be.to_device(np.asarray([0, n], dtype=np.int64)))
+            m = int(be.to_host(lens)[0])
+            vals = be.empty(m + 1, np.int64)
+            self.gather_values_batch(nodes, lens, be.to_device(np.asarray([0, m], dtype=np.int64)), vals)
+            node = self._handle(int(be.to_host(nodes)[0]))
+            return MatchResult(self._tensor(be.to_host(vals)[:m].copy()), node, node)
         lens, nodes, vals, offs = self._match_keys([key])
         node = self._handle(int(nodes[0]))
         got = vals[:int(lens[0])]
-        if self._P > 1:
-            got = self._rows_values(self._be.to_host(got))
         return MatchResult(self._tensor(got), node, node)
 
     def _match_keys(self, keys):
@@ -294,21 +335,37 @@ class RadixCache:
         return lens, nodes, d_out[:int(voffs[-1])], voffs
 
     def match_prefix_batch(self, tokens, offsets, out_len=None, out_node=None):
-        """Addition: device tensors in, device tensors out (int32 lengths, int32 last-node ids), equal to
-        match_prefix on each query in order."""
-        self._no_paged_batch()
+        """Addition: device tensors in, device tensors out (int32 matched lengths in tokens, int32 last-node ids), equal
+        to match_prefix on each query in order.  With page_size > 1 every query is matched in whole pages."""
         self._flush()
         B = int(offsets.shape[0]) - 1
         out_len = out_len if out_len is not None else self._be.empty(B, np.int32)
         out_node = out_node if out_node is not None else self._be.empty(B, np.int32)
-        self._ix.match(tokens, offsets, B, out_len, out_node)
+        if self._P > 1:
+            syms, soffs, _, total = self._intern(tokens, offsets, B, create=False)
+            self._ix.match(syms, soffs, B, out_len, out_node)
+            out_len *= self._P
+        else:
+            self._ix.match(tokens, offsets, B, out_len, out_node)
         self._invalidate()
         return out_len, out_node
 
     def gather_values_batch(self, nodes, lens, out_offsets, out_values):
-        """Addition: the torch.cat of match_prefix for a whole batch (ragged, caller-provided offsets)."""
-        self._no_paged_batch()
-        self._ix.gather(nodes, lens, out_offsets, int(nodes.shape[0]), out_values)
+        """Addition: the torch.cat of match_prefix for a whole batch (ragged, caller-provided offsets; lens and
+        out_offsets in tokens, as match_prefix_batch returns them)."""
+        B = int(nodes.shape[0])
+        if self._P > 1:
+            P = self._P
+            xp = self._xp(lens)
+            plens = lens // P if xp is np else xp.div(lens, P, rounding_mode="floor")
+            poffs = out_offsets // P if xp is np else xp.div(out_offsets, P, rounding_mode="floor")
+            n_rows = int(out_values.shape[0]) // P
+            rows = self._be.empty(n_rows + 1, np.int64)
+            rows[:] = -1
+            self._ix.gather(nodes, plens, poffs, B, rows)
+            self._pg.rows_get(rows, n_rows, out_values)
+            return out_values
+        self._ix.gather(nodes, lens, out_offsets, B, out_values)
         return out_values
 
     def insert(self, key: List, value=None) -> int:
@@ -322,15 +379,13 @@ class RadixCache:
                 # the reference would store a ragged last page in the leaf (radix_cache.py:296-326 never aligns);
                 # its callers insert page-aligned keys, and so must the callers of this class
                 raise ValueError(f"paged insert: key of {len(key)} tokens is not a multiple of page_size {P}")
-            sym = self._symbols(key, create=True)
-            if not sym:
+            if len(key) == 0:
                 return 0
+            be = self._be
             v = value.cpu().numpy() if hasattr(value, "cpu") else np.asarray(value)
-            rows = self._rows_alloc(len(sym))
-            self._vs[rows] = v.astype(np.int64, copy=False).reshape(len(sym), P)
-            m = int(self._insert_records([(sym, rows, -1)])[0])
-            self._vs_free.extend(int(r) for r in rows[:m])      # pages the tree already held: their rows stay unused
-            return m * P
+            out = self._paged_insert(be.to_device(np.asarray(key, dtype=np.int32)), be.to_device(v.astype(np.int64, copy=False)),
+                                     be.to_device(np.asarray([0, len(key)], dtype=np.int64)), 1)
+            return int(be.to_host(out)[0]) * P
         return int(self._insert_records([(list(key), value, -1)])[0])
 
     def _insert_records(self, recs) -> np.ndarray:
@@ -350,10 +405,17 @@ class RadixCache:
         return out
 
     def insert_batch(self, tokens, values, offsets, ranks=None, out_prefix_len=None):
-        """Addition: ordered batch of inserts on device tensors (rm_insert_batch)."""
-        self._no_paged_batch()
+        """Addition: ordered batch of inserts on device tensors (rm_insert_batch); returns the matched prefix lengths in
+        tokens.  With page_size > 1 every key (and its values) must be a whole number of pages."""
         self._flush()
         N = int(offsets.shape[0]) - 1
+        if self._P > 1:
+            out = self._paged_insert(tokens, values, offsets, N)
+            out *= self._P
+            if out_prefix_len is not None:
+                out_prefix_len[:] = out
+                return out_prefix_len
+            return out
         out = out_prefix_len if out_prefix_len is not None else self._be.empty(N, np.int32)
         self._ix.insert(tokens, values, offsets, ranks, N, out)
         self._invalidate()
@@ -366,12 +428,20 @@ class RadixCache:
         P = self._P
         nodes, offs, lens = self._ix.evict((int(num_tokens) + P - 1) // P)   # sum(len * P) >= n  <=>  sum(len) >= ceil(n / P)
         self._invalidate()
+        if P > 1:
+            runs = [self._ix.read_arena(o, n)[1] for o, n in zip(offs.tolist(), lens.tolist())]
+            if runs:
+                rows = np.concatenate(runs)
+                vals = self._rows_values(rows)
+                self._pg.rows_free(self._be.to_device(rows), len(rows))
+                at = 0
+                for r in runs:
+                    if self.token_to_kv_pool_allocator is not None:
+                        self.token_to_kv_pool_allocator.free(self._tensor(vals[at * P:(at + len(r)) * P].copy()))
+                    at += len(r)
+            return
         for o, n in zip(offs.tolist(), lens.tolist()):
             _, val = self._ix.read_arena(o, n)
-            if P > 1:
-                rows = val
-                val = self._rows_values(rows)
-                self._vs_free.extend(int(r) for r in rows)
             if self.token_to_kv_pool_allocator is not None:
                 self.token_to_kv_pool_allocator.free(self._tensor(val))      # radix_cache.py:195
 

@@ -330,3 +330,61 @@ def _alive(orc, node):
             return False
         node = p
     return True
+
+
+def run_paged_batch(kw, seed):
+    """The *_batch additions with page_size > 1: pages interned on the device (rm_pages_intern), values as rows of a
+    device row store, the index running on page symbols - against the oracle's paged RadixCache, record by record."""
+    import random
+    from oracle.radix_port import PortRadixCache
+    rnd = random.Random(8100 + seed)
+    page = rnd.choice([2, 3, 4])
+    alloc = FakeAllocator()
+    small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64)
+    small.update(kw)
+    t = RadixCache(None, alloc, page, **small)
+    be = t._be
+    orc = PortRadixCache(page)
+    vc = 0
+    for rd in range(12):
+        keys = []
+        for _ in range(rnd.randrange(1, 12)):
+            k = [rnd.randrange(3) for _ in range(rnd.randrange(0, 24))]
+            keys.append(k[:len(k) // page * page])
+        vals = []
+        for k in keys:
+            vals.append(list(range(vc, vc + len(k))))
+            vc += len(k)
+        offs = np.zeros(len(keys) + 1, dtype=np.int64)
+        np.cumsum([len(k) for k in keys], out=offs[1:])
+        flat = np.asarray([x for k in keys for x in k] or [0], dtype=np.int32)
+        fv = np.asarray([x for v in vals for x in v] or [0], dtype=np.int64)
+        got = be.to_host(t.insert_batch(be.to_device(flat), be.to_device(fv), be.to_device(offs))).tolist()
+        assert got == [orc.insert(list(k), np.asarray(v, dtype=np.int64)) for k, v in zip(keys, vals)]
+        qs = [[rnd.randrange(3) for _ in range(rnd.randrange(1, 26))] for _ in range(rnd.randrange(1, 16))]
+        qo = np.zeros(len(qs) + 1, dtype=np.int64)
+        np.cumsum([len(q) for q in qs], out=qo[1:])
+        qf = np.asarray([x for q in qs for x in q], dtype=np.int32)
+        lens, nodes = t.match_prefix_batch(be.to_device(qf), be.to_device(qo))
+        exp = [orc.match_prefix(list(q)) for q in qs]
+        hl = be.to_host(lens)
+        assert hl.tolist() == [len(m.indices) for m in exp]
+        vo = np.zeros(len(qs) + 1, dtype=np.int64)
+        np.cumsum(hl, out=vo[1:])
+        out = be.empty(int(vo[-1]) + 1, np.int64)
+        t.gather_values_batch(nodes, lens, be.to_device(vo), out)
+        hv = be.to_host(out)
+        hn = be.to_host(nodes)
+        for i, m in enumerate(exp):
+            assert hv[vo[i]:vo[i + 1]].tolist() == m.indices.tolist()
+            assert t.full_key(t._handle(int(hn[i]))) == orc.full_key(m.last_node)
+        if rd % 3 == 2:
+            n = rnd.randrange(0, 20)
+            b0, b1 = len(alloc.freed), len(orc.freed)
+            t.evict(n)
+            orc.evict(n)
+            assert alloc.freed[b0:] == orc.freed[b1:]
+        assert (t.evictable_size(), t.total_size()) == (orc.evictable, orc.total_size())
+    # every row the tree does not hold is back in the ring: rows in use = pages in the tree
+    syms, free_rows, _, _ = t._pg.status()
+    assert free_rows + t.total_size() // page == t._pg_rows_total

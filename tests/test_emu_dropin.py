@@ -58,8 +58,6 @@ def test_paged_restrictions():
     assert t.match_prefix([1, 2, 3, 4, 5, 6, 7]).device_indices.tolist() == [0, 1, 2, 3]   # page aligned (radix_cache.py:148-150)
     assert t.match_prefix([1, 2, 3]).device_indices.tolist() == []
     assert (t.evictable_size(), t.total_size()) == (8, 8)
-    with pytest.raises(NotImplementedError):
-        t.match_prefix_batch(None, None)
     t.reset()
     assert t.total_size() == 0 and t.match_prefix([1, 2, 3, 4]).device_indices.tolist() == []
 
@@ -107,3 +105,8 @@ def test_flatten_order_children_and_total_size(seed):
 @pytest.mark.parametrize("seed", range(4))
 def test_flatten_order_paged(seed):
     dc.run_flatten_order(kw(), 50 + seed, page=2)
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_paged_batch_entry_points(seed):
+    dc.run_paged_batch(kw(), seed)

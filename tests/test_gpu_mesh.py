@@ -208,3 +208,14 @@ def test_gpu_flatten_order_children_and_total_size(seed):
     """a12 on the GPU: all_values_flatten in the reference's pre-order / dict order, total_size reduced on the device,
     TreeNode attributes through rm_node_info / rm_node_children."""
     dc.run_flatten_order({}, seed)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_gpu_paged_batch_entry_points(seed):
+    """a2 on the GPU: page interning, value rows and the *_batch entry points with page_size 2..4 against the oracle."""
+    dc.run_paged_batch({}, seed)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_gpu_paged_random_against_oracle(seed):
+    dc.run_flatten_order({}, 50 + seed, page=2)
