@@ -49,7 +49,7 @@ def run(nodes=10_000_000, steps=6, warmup=3, B=16384, peak=None, seed=3):
     docs = torch.randint(0, V_DOC, (N_DOCS, L), dtype=torch.int32, device=dev, generator=g)
     cdf = zipf_sampler(N_DOCS, 1.1, dev)
     ix = capi.DeviceIndex(mode=capi.MODE_BASE, device=dev.index, max_nodes=int(nodes * 1.15) + (steps + warmup + 1) * B + (1 << 16),
-                          max_tokens=int(N_DOCS * L * 1.05) + int(nodes * 0.55 * 165) + (1 << 24), max_batch=B, max_key_len=L + 256)
+                          max_tokens=int(nodes * 152) + (1 << 24), max_batch=B, max_key_len=L + 256)   # measured: ~142 arena tokens per node
     maxcut = torch.zeros(N_DOCS, dtype=torch.int64, device=dev)
     out = torch.empty(NB, dtype=torch.int32, device=dev)
     t0 = time.perf_counter()
@@ -72,9 +72,12 @@ def run(nodes=10_000_000, steps=6, warmup=3, B=16384, peak=None, seed=3):
         ins_s += time.perf_counter() - t1
         maxcut.scatter_reduce_(0, d, cut, reduce="amax")
         n_ins += NB
-        if n_ins % (64 * NB) == 0 or n_ins == NB:
-            ix.check_device_error()
-            if ix.sizes().n_nodes >= nodes:
+        if n_ins % (16 * NB) == 0 or n_ins == NB:
+            sz = ix.sizes()
+            if sz.device_error:
+                raise RuntimeError(f"device error {sz.device_error} after {n_ins} inserts: nodes {sz.n_nodes} (hwm {sz.node_hwm}, pool "
+                                   f"{ix.cfg.max_nodes}), arena {sz.arena_used} of {ix.cfg.max_tokens}")
+            if sz.n_nodes >= nodes:
                 break
     ix.compact()
     torch.cuda.synchronize()
