@@ -238,7 +238,8 @@ def main():
     n_batches = 2 * (K + W)
     max_nodes = int(wl["tree_nodes"] * 1.3) + n_batches * (B // 2) + (1 << 16)   # ~15 % of first-sight queries add a node
     ix = capi.DeviceIndex(mode=capi.MODE_BASE, device=local, max_nodes=max_nodes,
-                          max_tokens=int(wl["tree_nodes"] * L * 0.9) + (1 << 22), max_batch=B, max_key_len=max(L, 1024))
+                          max_tokens=int(wl["tree_nodes"] * L * 0.9) + (1 << 22), max_batch=B, max_key_len=max(L, 1024),
+                          max_batch_tokens=B * L)      # staging of the host-buffer entry point sized once, at rm_create
     docs = gen_docs(wl)
 
     # ---- build the tree on the device (untimed) -----------------------------------------------
