@@ -225,17 +225,6 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
     int tk = tk_next;
     if (!have_tk) tk = rm_ld_query(key + pos, qpol);
     have_tk = false;
-    // The query tokens of the run's first round are requested BEFORE the probe: the run starts at pos + 1 whatever
-    // child the probe finds, so the DRAM round trip of the query (the batch streams through HBM once) overlaps the
-    // probe's L2 round trip instead of following it.  Wasted only when the probe misses, i.e. once per query at most.
-    int kjv[DEPTH];
-    if (!(flags & 8)) {
-      const int lim0 = L - (pos + 1) - lane;
-      const int* __restrict__ kp0 = key + (pos + 1) + lane;
-#pragma unroll
-      for (int u = 0; u < DEPTH; ++u) kjv[u] = u * G < lim0 ? rm_ld_query(kp0 + u * G, qpol) : 0;
-    }
-    bool first = !(flags & 8);
     int cur = -1;
     i64 cs = 0;
     {
@@ -268,12 +257,12 @@ rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restri
 #pragma unroll
       for (int u = 0; u < DEPTH; ++u) tv[u] = __ldg(tp + u * G);
       const int lim = L - qi - lane;    // this lane's position u*G is inside the query iff u*G < lim
-      if (!first) {
+      int kjv[DEPTH];
+      {
         const int* __restrict__ kp = key + qi + lane;
 #pragma unroll
         for (int u = 0; u < DEPTH; ++u) kjv[u] = u * G < lim ? rm_ld_query(kp + u * G, qpol) : 0;
       }
-      first = false;
       bool all = true;
 #pragma unroll
       for (int u = 0; u < DEPTH; ++u) {
@@ -982,8 +971,7 @@ static void rm_match_dispatch(rm_index* idx, const int* tokens, const i64* offse
   static const char* walk = getenv("RM_WALK") ? getenv("RM_WALK") : "run";
   // RM_EXP_FLAGS: measurement experiments only (bit 0 = skip the stamp atomics; results then differ from the
   // reference in eviction order, never use it outside a profiling run)
-  // (bit 3 = request a run's first query tokens after the probe instead of before it: A/B of the early request)
-  static const int run_flags = getenv("RM_EXP_FLAGS") ? (atoi(getenv("RM_EXP_FLAGS")) & 9) : 0;
+  static const int run_flags = getenv("RM_EXP_FLAGS") ? (atoi(getenv("RM_EXP_FLAGS")) & 1) : 0;
   if (strcmp(walk, "table") != 0) {
     static const int rg = getenv("RM_RUN_G") ? atoi(getenv("RM_RUN_G")) : 32;
     static const int depth_env = getenv("RM_RUN_DEPTH") ? atoi(getenv("RM_RUN_DEPTH")) : 3;

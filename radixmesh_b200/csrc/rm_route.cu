@@ -131,6 +131,33 @@ struct RmMd5Words {
 // Text of one list item, first character in the lowest byte of (lo, hi): the decimal digits of v ('-' in front
 // of a negative one), preceded by ", " (lead 1) or "[" (lead 2) or nothing (lead 0).  At most 13 bytes.
 __device__ __forceinline__ int rm_render_token(int v, int lead, u64& tlo, u64& thi) {
+  if ((unsigned)v < 100000u) {
+    // every token id of a real vocabulary: five digits by constant division (multiply-high), leading zeros shifted
+    // out, no loop (the general path below is ~3x the instructions, and rendering is issue bound)
+    unsigned x = (unsigned)v;
+    const unsigned d4 = x / 10000u;
+    x -= d4 * 10000u;
+    const unsigned d3 = x / 1000u;
+    x -= d3 * 1000u;
+    const unsigned d2 = x / 100u;
+    x -= d2 * 100u;
+    const unsigned d1 = x / 10u;
+    const unsigned d0 = x - d1 * 10u;
+    u64 s = (u64)(0x30303030u + (d4 | (d3 << 8) | (d2 << 16) | (d1 << 24))) | ((u64)(0x30u + d0) << 32);
+    const int nd = 1 + (v >= 10) + (v >= 100) + (v >= 1000) + (v >= 10000);
+    s >>= 8 * (5 - nd);
+    int len = nd;
+    if (lead == 1) {
+      s = (s << 16) | ((u64)' ' << 8) | (u64)',';
+      len += 2;
+    } else if (lead == 2) {
+      s = (s << 8) | (u64)'[';
+      ++len;
+    }
+    tlo = s;
+    thi = 0;
+    return len;
+  }
   // decimal digits, least significant first; shifting what is there up by a byte puts the most
   // significant digit in the lowest byte, i.e. first in the text
   int len = 0;
@@ -247,7 +274,10 @@ __device__ unsigned rm_hash_token_list(const int* __restrict__ key, int n, const
 __device__ __forceinline__ u64 rm_msg_off(i64 rel_tok, int q) { return 64ull * ((u64)((rel_tok + 3) >> 2) + 2ull * (u64)q); }
 
 __device__ __forceinline__ void rm_put_bytes(unsigned char* dst, u64 lo, u64 hi, int len) {
-  for (int b = 0; b < len; ++b) dst[b] = (unsigned char)((b < 8 ? lo >> (8 * b) : hi >> (8 * (b - 8))) & 0xffu);
+#pragma unroll
+  for (int b = 0; b < 8; ++b)
+    if (b < len) dst[b] = (unsigned char)(lo >> (8 * b));
+  for (int b = 8; b < len; ++b) dst[b] = (unsigned char)(hi >> (8 * (b - 8)));
 }
 
 // closing bracket, 0x80, zeros to 56 mod 64, bit length; returns the number of 64-byte blocks
