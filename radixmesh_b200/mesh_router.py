@@ -38,12 +38,12 @@ class ShardedMeshRouter:
         self.bcast_group = bcast_group if bcast_group is not None else group
 
     def route_pipelined(self, tokens, offsets, B: int, src: int = 0, chunks: int = 8):
-        """route() with the batch cut into `chunks` pieces.  What limits the sharded form is the broadcast of the
-        request tokens (every GPU must see every request; NVLink carries 4 bytes per token per GPU), so all the
-        broadcasts are queued at once on their own communicator and each chunk is walked, its matched lengths
-        exchanged and its slice picked as soon as its tokens have landed - everything but the first chunk's compute
-        hides under the transfer.  Same results as route()."""
-        import torch
+        """route() with the token broadcast cut into `chunks` pieces.  What limits the sharded form is the broadcast of
+        the request tokens (every GPU must see every request; NVLink carries 4 bytes per token per GPU), so all the
+        broadcasts are queued at once on their own communicator and each chunk is WALKED as soon as its tokens have
+        landed - the walk hides under the transfer.  The exchange of the matched lengths, the pick and the result gather
+        then run once for the whole batch: the pick's consistent-hash fallback is a dependent chain per request
+        (MD5), whose latency a small chunk pays in full, so it is not chunked.  Same results as route()."""
         import torch.distributed as dist
         if self.world == 1 or chunks <= 1 or B < chunks:
             return self.route(tokens, offsets, B, src)
@@ -54,27 +54,35 @@ class ShardedMeshRouter:
         cuts = [min(k * step, B) for k in range(chunks + 1)]
         works = [dist.broadcast(tok_t[int(offs_h[cuts[k]]):int(offs_h[cuts[k + 1]])], src=src, group=self.bcast_group, async_op=True)
                  for k in range(chunks) if cuts[k + 1] > cuts[k]]
-        outs = []
+        lens = self.ix.be.empty(B, np.int32)
+        nodes = self.ix.be.empty(B, np.int32)
         for k, w in enumerate(works):
             a, b = cuts[k], cuts[k + 1]
             w.wait()
             base = int(offs_h[a])
             sub_offs = offs_t[a:b + 1] - base
-            outs.append(self.route(tok_t[base:int(offs_h[b])], sub_offs, b - a, src, _skip_broadcast=True))
-        return tuple(torch.cat([_as_torch(o[i]) for o in outs]) for i in range(5))
+            self.ix.match(self._arr(tok_t[base:int(offs_h[b])]), self._arr(sub_offs), b - a, lens[a:b], nodes[a:b])
+        return self.route(tokens, offsets, B, src, _lens=lens)
 
-    def route(self, tokens, offsets, B: int, src: int = 0, _skip_broadcast: bool = False):
+    def _arr(self, t):
+        """torch tensor -> what the index's backend takes (numpy view for the host-emulation backend)."""
+        return t if getattr(self.ix.be, "name", "") == "cuda" else t.numpy()
+
+    def route(self, tokens, offsets, B: int, src: int = 0, _lens=None):
         """tokens / offsets are device arrays; valid on `src`, overwritten elsewhere by the broadcast.
         Returns (prefill_rank, decode_rank, prefill_addr_idx, decode_addr_idx, err) device arrays."""
         import torch.distributed as dist
         be = self.ix.be
         W = self.world
-        if W > 1 and not _skip_broadcast:
-            dist.broadcast(_as_torch(tokens), src=src, group=self.group)
-            dist.broadcast(_as_torch(offsets), src=src, group=self.group)
-        lens = be.empty(B, np.int32)
-        nodes = be.empty(B, np.int32)
-        self.ix.match(tokens, offsets, B, lens, nodes)              # K1, non-splitting (DECODE-mode index)
+        if _lens is not None:                                        # route_pipelined: broadcast and walk already done
+            lens = _lens
+        else:
+            if W > 1:
+                dist.broadcast(_as_torch(tokens), src=src, group=self.group)
+                dist.broadcast(_as_torch(offsets), src=src, group=self.group)
+            lens = be.empty(B, np.int32)
+            nodes = be.empty(B, np.int32)
+            self.ix.match(tokens, offsets, B, lens, nodes)          # K1, non-splitting (DECODE-mode index)
         if not self.shard_pick:
             depths = be.empty(W * B, np.int32)
             if W > 1:
@@ -110,20 +118,21 @@ class ReplicatedMeshRouter:
         self.ix, self.rank, self.world, self.group = index, rank, world, group
 
     def route_shard(self, tokens, offsets, B_local: int, warm: bool = True):
-        """Route this rank's shard; returns the all-gathered (world*B_local) result arrays."""
+        """Route this rank's shard; returns the all-gathered (world*B_local) result arrays (prefill rank, decode rank,
+        prefill address index, decode address index, error), gathered in ONE collective."""
+        import torch
         import torch.distributed as dist
         be = self.ix.be
-        local = [be.empty(B_local, np.int32) for _ in range(4)]
-        err = be.empty(B_local, np.int32)
+        W = self.world
+        loc = be.empty(5 * B_local, np.int32)
         err8 = be.empty(B_local, np.uint8)
-        self.ix.route(tokens, offsets, B_local, warm, local[0], local[1], local[2], local[3], err8)
-        _as_torch(err).copy_(_as_torch(err8))
-        outs = []
-        for a in local + [err]:
-            g = be.empty(self.world * B_local, np.int32)
-            if self.world > 1:
-                dist.all_gather_into_tensor(_as_torch(g), _as_torch(a), group=self.group)
-            else:
-                _as_torch(g).copy_(_as_torch(a))
-            outs.append(g)
-        return outs
+        self.ix.route(tokens, offsets, B_local, warm, loc[0:B_local], loc[B_local:2 * B_local], loc[2 * B_local:3 * B_local],
+                      loc[3 * B_local:4 * B_local], err8)
+        _as_torch(loc)[4 * B_local:].copy_(_as_torch(err8))
+        if W == 1:
+            t = _as_torch(loc)
+            return [t[i * B_local:(i + 1) * B_local] for i in range(5)]
+        g = be.empty(W * 5 * B_local, np.int32)
+        dist.all_gather_into_tensor(_as_torch(g), _as_torch(loc), group=self.group)
+        r = _as_torch(g).view(W, 5, B_local).permute(1, 0, 2).reshape(5, W * B_local)
+        return [r[i] for i in range(5)]

@@ -404,19 +404,26 @@ def mesh_route_block(torch, capi, rank, world, steps=4, warmup=2, check_requests
 
     # ---- sharded form: only rank 0 holds the batch before the call
     work = [(b[0].clone() if rank == 0 else torch.zeros_like(b[0]), b[1].clone() if rank == 0 else torch.zeros_like(b[1])) for b in batches]
-    res_sh = None
-    for s in range(warmup):
-        res_sh = sharded.route_pipelined(work[s][0], work[s][1], B)
-    barrier()
-    e0, e1 = _events(torch, 2)
-    e0.record()
-    for s in range(warmup, warmup + steps):
-        out = sharded.route_pipelined(work[s][0], work[s][1], B)
-        if s == warmup:
-            res_first_sh = out
-    e1.record()
-    barrier()
-    ms_sh = max_ms(e0.elapsed_time(e1)) / steps
+    def time_sharded(fn):
+        first = None
+        for s in range(warmup):
+            fn(work[s][0], work[s][1], B)
+        barrier()
+        e0, e1 = _events(torch, 2)
+        e0.record()
+        for s in range(warmup, warmup + steps):
+            out = fn(work[s][0], work[s][1], B)
+            if s == warmup:
+                first = out
+        e1.record()
+        barrier()
+        return max_ms(e0.elapsed_time(e1)) / steps, first
+
+    ms_sh, res_first_sh = time_sharded(sharded.route_pipelined)
+    if world > 1:                     # the same batches again (every rank holds them now; the broadcast still runs)
+        ms_sh_plain, _ = time_sharded(sharded.route)
+    else:
+        ms_sh_plain = ms_sh
     # phases of the unpipelined sequence, one extra batch (rank 0's view)
     ph = {}
     if world > 1:
@@ -496,8 +503,10 @@ def mesh_route_block(torch, capi, rank, world, steps=4, warmup=2, check_requests
         "replicated": {"requests_per_s": n_rp / (ms_rp * 1e-3), "ms_per_batch": ms_rp,
                        "what": "ROUTER tree on every GPU, batch sharded, one all-gather of the results (throughput form)"},
         "sharded": {"requests_per_s": B / (ms_sh * 1e-3), "tree_lookups_per_s": world * B / (ms_sh * 1e-3), "ms_per_batch": ms_sh,
+                    "ms_per_batch_unpipelined": ms_sh_plain,
                     "what": "tree of rank g's own keys on GPU g, request tokens broadcast in 8 chunks on their own communicator "
-                            "while earlier chunks are walked / exchanged / picked (memory-saving form: 1/N of the index per GPU)",
+                            "and walked chunk by chunk as they land; one all-to-all of the matched lengths, pick by slice, one "
+                            "gather (memory-saving form: 1/N of the index per GPU)",
                     "phases_unpipelined": ph,
                     "cap": "the broadcast of the request tokens (4 B per token to every GPU over NVLink)" if world > 1 else "none (one GPU)"},
         "parity_check": {"requests": len(idxs), "mismatches": int(mism),
