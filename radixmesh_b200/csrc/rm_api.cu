@@ -115,7 +115,7 @@ int rm_destroy(rm_index* idx) {
   void* ptrs[] = {t.table, t.parent, t.edge_off, t.edge_len, t.lock_ref, t.stamp, t.rank, t.depth_end, t.nchild,
                   t.gen, t.parked, t.born, t.ord, t.ts, t.val, t.req_cnt, t.free_ids, t.ctr, t.dup_key, t.dup_parked, sc.key[0], sc.key[1],
                   sc.val[0], sc.val[1], sc.sufmax, sc.krank, sc.uniq_pos, sc.uniq_min, sc.link, t.req_head, sc.hist, sc.ev_key[0], sc.ev_key[1],
-                  sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ins_mark, sc.lock_first, sc.lock_cnt, sc.lock_flag,
+                  sc.ev_val[0], sc.ev_val[1], sc.ev_hist, sc.ev_lens, sc.ev_eff, sc.ev_rem, sc.ev_selw, sc.ev_selc, sc.ins_mark, sc.lock_first, sc.lock_cnt, sc.lock_flag,
                   sc.dup_out, sc.dup_out_n, sc.h_tokens, sc.h_values, sc.h_offsets, sc.h_ranks, sc.h_out_a, sc.h_out_b, sc.info_ids, sc.info_rows,
                   idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner, idx->route_msg, idx->route_nblk};
   for (void* p : ptrs)
@@ -210,6 +210,8 @@ int rm_create(const rm_config* cfg, rm_index** out) {
   A(rm_dalloc(&sc.ev_lens, N));
   A(rm_dalloc(&sc.ev_eff, N));
   A(rm_dalloc(&sc.ev_rem, N));
+  A(rm_dalloc(&sc.ev_selw, 4096 + 8));
+  A(rm_dalloc(&sc.ev_selc, 4096));
   A(rm_dalloc(&sc.ins_mark, N));
   A(rm_dalloc(&sc.lock_first, N));
   A(rm_dalloc(&sc.lock_cnt, N));

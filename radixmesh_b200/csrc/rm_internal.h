@@ -22,6 +22,8 @@ struct RmScratch {
   int* ev_lens;       // value-run lengths of the evicted nodes, in eviction order
   u64* ev_eff;        // effective (subtree-max) stamps
   int* ev_rem;        // children still to report, per node
+  u64* ev_selw;       // radix select of the eviction frontier: token weight per digit (4096) + its state behind them
+  unsigned* ev_selc;  // ... and key count per digit
   int* ins_mark;      // per node, zero between insert batches: root child whose first-token group stays on the ordered path
   // lock batches (sized by max_nodes)
   int* lock_first;

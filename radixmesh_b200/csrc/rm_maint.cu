@@ -243,8 +243,8 @@ __global__ void rm_evict_pin_kernel(RmTree t, int n, int* __restrict__ pinned) {
 //
 // Computing eff for the whole tree bottom-up is a chain of dependent atomics as long as the tree is deep
 // (0.5 ms on a 1 M-node tree).  Only the nodes that CAN be evicted by this call need it:
-//   1. order the evictable LEAVES alone by (raw stamp, deeper first) - a leaf's eff is its raw stamp - and
-//      find the frontier key K0 where their lengths reach num_tokens;
+//   1. take the evictable LEAVES alone, keyed (raw stamp, deeper first) - a leaf's eff is its raw stamp - and
+//      find the frontier key K0 where their lengths, in key order, reach num_tokens (a radix select, below);
 //   2. the true cut lies at or before K0 (inner nodes only add tokens earlier), and a node's key is never
 //      below a descendant's, so every node the call can evict has its whole subtree at keys <= K0;
 //   3. so: the leaves up to K0 climb; a parent joins the candidates when ALL its children have reported
@@ -275,27 +275,105 @@ __global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int*
   val[x] = (unsigned)x;
 }
 
-// after the cut over the leaves: frontier key, number of leaves at or below it (ties included)
-__global__ void rm_evict_frontier_kernel(RmTree t, const u64* __restrict__ skey, int n) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  int m = t.ctr->evict_n;
-  u64 k0 = 0;
-  if (m > 0) {
-    if (m >= n || skey[m] == RM_NO_REQ) {
-      k0 = RM_NO_REQ - 1;            // every evictable leaf is taken: nothing bounds the climb
+// Step 1 without sorting a million keys to use a few thousand of them: a weighted radix SELECT.  The frontier key K0 is
+// the smallest key such that the value lengths of the evictable leaves at or below it reach num_tokens.  Twelve bits at
+// a time from the top: a histogram of token weight per digit over the keys that share the prefix chosen so far, then
+// one block picks the digit where the running weight crosses what is still needed.  ceil(bits / 12) passes over the
+// key array (each a few microseconds at 1 M nodes) instead of 5 sort passes of three kernels each; the leaves at or
+// below K0 are then compacted, unordered, for the climb (the candidates are sorted afterwards anyway).
+#define RM_SEL_BITS 12
+#define RM_SEL_BINS (1 << RM_SEL_BITS)
+struct RmEvictSel {
+  u64 prefix;      // digits chosen so far (high bits of K0)
+  i64 need;        // tokens still to be covered inside the prefix
+  int all;         // the evictable leaves do not hold num_tokens: take every one of them
+  int pad;
+};
+
+__global__ void rm_evict_sel_init_kernel(RmEvictSel* st, i64 num_tokens, u64* __restrict__ hw, unsigned* __restrict__ hc) {
+  for (int b = threadIdx.x; b < RM_SEL_BINS; b += blockDim.x) {
+    hw[b] = 0;
+    hc[b] = 0;
+  }
+  if (threadIdx.x == 0) {
+    st->prefix = 0;
+    st->need = num_tokens;
+    st->all = 0;
+  }
+}
+
+__global__ void rm_evict_sel_hist_kernel(RmTree t, const u64* __restrict__ key, int n, int shift, const RmEvictSel* st,
+                                         u64* __restrict__ hw, unsigned* __restrict__ hc) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n) return;
+  const u64 k = key[x];
+  if (k == RM_NO_REQ || st->all) return;
+  if ((k >> shift >> RM_SEL_BITS) != st->prefix) return;
+  const unsigned b = (unsigned)(k >> shift) & (RM_SEL_BINS - 1);
+  atomicAdd(&hw[b], (u64)t.edge_len[x]);
+  atomicAdd(&hc[b], 1u);
+}
+
+// last level when bits is not a multiple of 12: the remaining low bits are shifted UP into the digit
+__global__ void rm_evict_sel_histup_kernel(RmTree t, const u64* __restrict__ key, int n, int up, const RmEvictSel* st,
+                                           u64* __restrict__ hw, unsigned* __restrict__ hc) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n) return;
+  const u64 k = key[x];
+  if (k == RM_NO_REQ || st->all) return;
+  const u64 kk = k << up;
+  if ((kk >> RM_SEL_BITS) != st->prefix) return;
+  const unsigned b = (unsigned)kk & (RM_SEL_BINS - 1);
+  atomicAdd(&hw[b], (u64)t.edge_len[x]);
+  atomicAdd(&hc[b], 1u);
+}
+
+// one block: the digit where the running weight reaches `need`; clears the histogram for the next level
+__global__ void rm_evict_sel_pick_kernel(RmEvictSel* st, u64* __restrict__ hw, unsigned* __restrict__ hc) {
+  if (threadIdx.x == 0 && !st->all) {
+    i64 run = 0;
+    int b = 0;
+    for (; b < RM_SEL_BINS; ++b) {
+      if (run + (i64)hw[b] >= st->need) break;
+      run += (i64)hw[b];
+    }
+    if (b == RM_SEL_BINS) {
+      st->all = 1;
     } else {
-      k0 = skey[m - 1];
-      while (m < n && skey[m] == k0) ++m;
+      st->need -= run;
+      st->prefix = (st->prefix << RM_SEL_BITS) | (u64)b;
     }
   }
-  t.ctr->ev_total = m;
-  t.ctr->ev_k0 = k0;
+  __syncthreads();
+  for (int b = threadIdx.x; b < RM_SEL_BINS; b += blockDim.x) {
+    hw[b] = 0;
+    hc[b] = 0;
+  }
+}
+
+// the leaves at or below K0 (K0 = the full prefix after the last level; shift_out drops padding bits of the last digit)
+__global__ void rm_evict_sel_compact_kernel(RmTree t, const u64* __restrict__ key, int n, const RmEvictSel* st, int pad_bits,
+                                            u64* __restrict__ skey, unsigned* __restrict__ sval) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x == 0 && blockIdx.x == 0) t.ctr->ev_k0 = st->all ? RM_NO_REQ - 1 : (st->prefix >> pad_bits);
+  if (x >= n) return;
+  const u64 k = key[x];
+  if (k == RM_NO_REQ) return;
+  if (!st->all && k > (st->prefix >> pad_bits)) return;
+  const int slot = atomicAdd(&t.ctr->ev_total, 1);
+  skey[slot] = k;
+  sval[slot] = (unsigned)x;
+}
+
+__global__ void rm_evict_sel_seal_kernel(RmTree t) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) t.ctr->evict_n = t.ctr->ev_total;   // evict_n doubles as "leaves among the candidates" until the cut
 }
 
 // step 3: parents exposed by the candidate leaves are appended behind them
 __global__ void rm_evict_climb_kernel(RmTree t, int n, int depth_bits, const int* __restrict__ pinned, u64* __restrict__ eff,
-                                      int* __restrict__ rem, u64* skey, unsigned* sval, int m_leaves) {
+                                      int* __restrict__ rem, u64* skey, unsigned* sval, int m_leaves_bound) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m_leaves = min(t.ctr->evict_n, m_leaves_bound);       // sealed before this launch (rm_evict_sel_seal_kernel)
   if (i >= m_leaves) return;
   const u64 k0 = t.ctr->ev_k0;
   int y = (int)sval[i];
@@ -450,21 +528,31 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
   RM_CUDA(cudaMemsetAsync(sc.ev_rem, 0, sizeof(int) * (size_t)n, s));
   RM_LAUNCH(rm_evict_count_kernel, grid_n, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem);
   RM_LAUNCH(rm_evict_keys_kernel, grid_n, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_rem, sc.ev_key[0], sc.ev_val[0]);
-  // 1. leaves alone, frontier
-  int w = rm_sort_pairs(sc.ev_key[0], sc.ev_val[0], sc.ev_key[1], sc.ev_val[1], n, bits, sc.ev_hist, s);
-  RM_LAUNCH(rm_evict_cut_kernel, 1, cut_tpb, s, t, sc.ev_key[w], sc.ev_val[w], n, num_tokens, n);
-  RM_LAUNCH(rm_evict_frontier_kernel, 1, 1, s, t, sc.ev_key[w], n);
-  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
-  RM_CUDA(cudaStreamSynchronize(s));
-  const int m_leaves = c.ev_total;
-  if (m_leaves <= 0) return RM_OK;
-  // 3. climb, 4. exact order and cut over the candidates
-  RM_LAUNCH(rm_evict_climb_kernel, (m_leaves + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_eff,
-            sc.ev_rem, sc.ev_key[w], sc.ev_val[w], m_leaves);
+  // 1. frontier key by weighted radix select over the leaves' keys, 2. the leaves at or below it, compacted
+  RmEvictSel* st = reinterpret_cast<RmEvictSel*>(sc.ev_selw + RM_SEL_BINS);
+  const int levels = (bits + RM_SEL_BITS - 1) / RM_SEL_BITS;
+  const int pad_bits = levels * RM_SEL_BITS - bits;                 // the key is padded at the LOW end of the last digit
+  RM_LAUNCH(rm_evict_sel_init_kernel, 1, RM_MT_TPB, s, st, num_tokens, sc.ev_selw, sc.ev_selc);
+  for (int l = 0; l < levels; ++l) {
+    const int shift = (levels - 1 - l) * RM_SEL_BITS - pad_bits;    // may be negative on the last level: keys are shifted up instead
+    if (shift >= 0) {
+      RM_LAUNCH(rm_evict_sel_hist_kernel, grid_n, RM_MT_TPB, s, t, sc.ev_key[0], n, shift, st, sc.ev_selw, sc.ev_selc);
+    } else {
+      RM_LAUNCH(rm_evict_sel_histup_kernel, grid_n, RM_MT_TPB, s, t, sc.ev_key[0], n, -shift, st, sc.ev_selw, sc.ev_selc);
+    }
+    RM_LAUNCH(rm_evict_sel_pick_kernel, 1, RM_MT_TPB, s, st, sc.ev_selw, sc.ev_selc);
+  }
+  RM_CUDA(cudaMemsetAsync(&t.ctr->ev_total, 0, sizeof(int), s));
+  int w = 1;
+  RM_LAUNCH(rm_evict_sel_compact_kernel, grid_n, RM_MT_TPB, s, t, sc.ev_key[0], n, st, pad_bits, sc.ev_key[w], sc.ev_val[w]);
+  RM_LAUNCH(rm_evict_sel_seal_kernel, 1, 1, s, t);
+  // 3. climb (the leaf count stays on the device), 4. exact order and cut over the candidates
+  RM_LAUNCH(rm_evict_climb_kernel, grid_n, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_eff, sc.ev_rem, sc.ev_key[w], sc.ev_val[w], n);
   RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));
   const int m_all = c.ev_total < n ? c.ev_total : n;
-  if (m_all > m_leaves) {
+  if (m_all <= 0) return RM_OK;
+  {
     const int w2 = rm_sort_pairs(sc.ev_key[w], sc.ev_val[w], sc.ev_key[w ^ 1], sc.ev_val[w ^ 1], m_all, bits, sc.ev_hist, s);
     w ^= w2;
   }

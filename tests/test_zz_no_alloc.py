@@ -1,12 +1,13 @@
 """rm_match_batch_static: the prefix match for callers that must not allocate device memory.
 
-Engines that pre-commit HBM to their KV pool, request-path threads that cannot absorb cudaMalloc's
-device-wide synchronisation, and code running under stream capture send their match batches through
-this entry point; its scratch is a fixed array inside the library.  The test builds the same tree in
-two indexes, sends the same two query batches through the regular entry point on one and through the
-static-scratch entry point on the other (whose own scratch is far too small for these batches), and
-requires identical results: matched lengths bit-exact, the same last nodes (compared by full key,
-since node ids are handed out in parallel) and the same final tree.  Collected last on purpose.
+Engines that pre-commit HBM to their KV pool and request-path threads that cannot absorb cudaMalloc's
+device-wide synchronisation send their match batches through this entry point; its scratch is a fixed
+array inside the library.  The test builds the same tree in two indexes and in the CPU oracle, sends
+the same two query batches through the regular entry point on one index and through the static-scratch
+entry point on the other (whose own scratch is far too small for these batches), and requires
+identical results: matched lengths bit-exact against each other and against the oracle, the same last
+nodes (compared by full key, since node ids are handed out in parallel) and the same final tree as the
+oracle's.  Collected last on purpose.
 """
 import numpy as np
 import pytest
@@ -40,6 +41,10 @@ def test_static_scratch_match_equals_regular_match_twice():
     frugal = capi.DeviceIndex(mode=capi.MODE_BASE, max_nodes=1 << 16, max_tokens=1 << 20, max_batch=128, max_key_len=256)
     _build(regular, ins, L)
     _build(frugal, ins, L)
+    from oracle.radix_port import PortRadixCache
+    orc = PortRadixCache(1)
+    for i, row in enumerate(ins):
+        orc.insert(row.tolist(), np.arange(i * L, (i + 1) * L, dtype=np.int64))
     dev = torch.device("cuda")
     offs = torch.arange(0, (n_q + 1) * L, L, dtype=torch.int64, device=dev)
     for call in range(2):   # two calls in a row: the second reuses whatever the first left in the array
@@ -51,12 +56,16 @@ def test_static_scratch_match_equals_regular_match_twice():
         frugal.match_static(tok, offs, n_q, lb, nb)
         torch.cuda.synchronize()
         assert torch.equal(la, lb), f"matched lengths differ on call {call}"
+        exp = [orc.match_prefix(r.tolist()) for r in qs]
+        assert lb.cpu().tolist() == [len(m.indices) for m in exp], f"static entry point differs from the oracle on call {call}"
         ca, cb = device_canonical(regular), device_canonical(frugal)
         ka = {v: k for k, v in ca["_ids"].items()}
         kb = {v: k for k, v in cb["_ids"].items()}
         ka[0] = kb[0] = ()
         assert [ka[x] for x in na.cpu().tolist()] == [kb[x] for x in nb.cpu().tolist()], f"last nodes differ on call {call}"
         assert_same_tree(cb, {"nodes": ca["nodes"], "evictable": ca["evictable"], "protected": ca["protected"]})
+        assert [kb[x] for x in nb.cpu().tolist()] == [tuple(orc.full_key(m.last_node)) for m in exp], f"last nodes differ from the oracle on call {call}"
+        assert_same_tree(cb, orc.canonical())
     regular.check_device_error()
     frugal.check_device_error()
     regular.close()
