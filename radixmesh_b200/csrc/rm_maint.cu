@@ -283,6 +283,11 @@ __global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int*
 // below K0 are then compacted, unordered, for the climb (the candidates are sorted afterwards anyway).
 #define RM_SEL_BITS 12
 #define RM_SEL_BINS (1 << RM_SEL_BITS)
+#ifdef RM_EMU
+#define RM_SEL_PICK_TPB 64
+#else
+#define RM_SEL_PICK_TPB 1024     // x 4 bins per thread = RM_SEL_BINS
+#endif
 struct RmEvictSel {
   u64 prefix;      // digits chosen so far (high bits of K0)
   i64 need;        // tokens still to be covered inside the prefix
@@ -330,6 +335,7 @@ __global__ void rm_evict_sel_histup_kernel(RmTree t, const u64* __restrict__ key
 
 // one block: the digit where the running weight reaches `need`; clears the histogram for the next level
 __global__ void rm_evict_sel_pick_kernel(RmEvictSel* st, u64* __restrict__ hw, unsigned* __restrict__ hc) {
+#ifdef RM_EMU
   if (threadIdx.x == 0 && !st->all) {
     i64 run = 0;
     int b = 0;
@@ -344,11 +350,55 @@ __global__ void rm_evict_sel_pick_kernel(RmEvictSel* st, u64* __restrict__ hw, u
       st->prefix = (st->prefix << RM_SEL_BITS) | (u64)b;
     }
   }
-  __syncthreads();
   for (int b = threadIdx.x; b < RM_SEL_BINS; b += blockDim.x) {
     hw[b] = 0;
     hc[b] = 0;
   }
+#else
+  // 1024 threads x 4 consecutive bins: block-wide exclusive scan of the weights, then the one thread whose four bins
+  // contain the crossing names the digit (a single thread reading 4096 bins one after another took 0.1-1 ms per level)
+  __shared__ i64 wtot[32];
+  __shared__ int found_s;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) found_s = 0;
+  const bool all = st->all != 0;
+  const i64 need = st->need;
+  i64 w4[4];
+  i64 mine = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    w4[j] = (i64)hw[4 * threadIdx.x + j];
+    mine += w4[j];
+  }
+  i64 inc = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const i64 o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) wtot[wid] = inc;
+  __syncthreads();
+  i64 before = inc - mine;
+  for (int w = 0; w < wid; ++w) before += wtot[w];
+  if (!all && before < need && before + mine >= need) {     // the crossing is inside my four bins
+    i64 run = before;
+    int j = 0;
+    for (; j < 4; ++j) {
+      if (run + w4[j] >= need) break;
+      run += w4[j];
+    }
+    st->need = need - run;
+    st->prefix = (st->prefix << RM_SEL_BITS) | (u64)(4 * threadIdx.x + j);
+    found_s = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && !all && !found_s) st->all = 1;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    hw[4 * threadIdx.x + j] = 0;
+    hc[4 * threadIdx.x + j] = 0;
+  }
+#endif
 }
 
 // the leaves at or below K0 (K0 = the full prefix after the last level; shift_out drops padding bits of the last digit)
@@ -540,7 +590,7 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
     } else {
       RM_LAUNCH(rm_evict_sel_histup_kernel, grid_n, RM_MT_TPB, s, t, sc.ev_key[0], n, -shift, st, sc.ev_selw, sc.ev_selc);
     }
-    RM_LAUNCH(rm_evict_sel_pick_kernel, 1, RM_MT_TPB, s, st, sc.ev_selw, sc.ev_selc);
+    RM_LAUNCH(rm_evict_sel_pick_kernel, 1, RM_SEL_PICK_TPB, s, st, sc.ev_selw, sc.ev_selc);
   }
   RM_CUDA(cudaMemsetAsync(&t.ctr->ev_total, 0, sizeof(int), s));
   int w = 1;
