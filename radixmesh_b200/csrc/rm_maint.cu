@@ -620,13 +620,20 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
             sc.ev_eff, d_nodes, d_offs, d_lens);
 #endif
   RM_CUDA(cudaGetLastError());
+  // the count and the first results travel together: one synchronisation for the usual call (a few thousand nodes)
+  const int first = lim < 8192 ? lim : 8192;
   RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  if (first > 0) {
+    RM_CUDA(cudaMemcpyAsync(out_nodes_h, d_nodes, sizeof(int) * first, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(out_offs_h, d_offs, sizeof(i64) * first, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(out_lens_h, d_lens, sizeof(int) * first, cudaMemcpyDeviceToHost, s));
+  }
   RM_CUDA(cudaStreamSynchronize(s));
   const int k = c.evict_n;
-  if (k > 0) {
-    RM_CUDA(cudaMemcpyAsync(out_nodes_h, d_nodes, sizeof(int) * k, cudaMemcpyDeviceToHost, s));
-    RM_CUDA(cudaMemcpyAsync(out_offs_h, d_offs, sizeof(i64) * k, cudaMemcpyDeviceToHost, s));
-    RM_CUDA(cudaMemcpyAsync(out_lens_h, d_lens, sizeof(int) * k, cudaMemcpyDeviceToHost, s));
+  if (k > first) {
+    RM_CUDA(cudaMemcpyAsync(out_nodes_h + first, d_nodes + first, sizeof(int) * (k - first), cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(out_offs_h + first, d_offs + first, sizeof(i64) * (k - first), cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(out_lens_h + first, d_lens + first, sizeof(int) * (k - first), cudaMemcpyDeviceToHost, s));
     RM_CUDA(cudaStreamSynchronize(s));
   }
   *out_n_h = k;
