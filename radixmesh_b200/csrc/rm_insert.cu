@@ -518,8 +518,33 @@ rm_insert_lost_kernel(RmTree t, const i64* __restrict__ rval, const i64* __restr
 int rm_launch_walk_records(rm_index* idx, const int* tokens, const i64* offsets, int N, u64 seq_base, int* out_len,
                            int* out_node, cudaStream_t s);
 
+static int rm_launch_insert_one(rm_index* idx, const int* tokens, const i64* values, const i64* offsets, const int* ranks, int N,
+                                int* out_prefix_len, cudaStream_t s);
+
+// A batch is applied in arrival order inside every group of records that leave the tree at the same node through the
+// same token.  Into a nearly EMPTY tree that is the whole batch per hot document: every record of the document lands in
+// one group and re-walks what the records before it built (34.8 ms for the first 4,096-record batch, against 0.18 ms
+// in steady state).  While the index has seen fewer records than two such batches, a batch is therefore applied as
+// consecutive chunks of 256 records - same order, same result: a chunk's groups are short, and the chunks after it
+// find the documents' paths in the tree and spread over many groups.
+#define RM_COLD_CHUNK 256
 int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const i64* offsets, const int* ranks, int N,
                      int* out_prefix_len, cudaStream_t s) {
+  if (N <= 0) return RM_OK;
+  const bool cold = N > RM_COLD_CHUNK && idx->ins_records < 2ull * (u64)N;
+  idx->ins_records += (u64)N;
+  if (!cold) return rm_launch_insert_one(idx, tokens, values, offsets, ranks, N, out_prefix_len, s);
+  for (int a = 0; a < N; a += RM_COLD_CHUNK) {
+    const int n = N - a < RM_COLD_CHUNK ? N - a : RM_COLD_CHUNK;
+    // offsets are absolute positions in tokens / values: a chunk is a window of the offsets, ranks and outputs
+    int rc = rm_launch_insert_one(idx, tokens, values, offsets + a, ranks ? ranks + a : nullptr, n, out_prefix_len + a, s);
+    if (rc) return rc;
+  }
+  return RM_OK;
+}
+
+static int rm_launch_insert_one(rm_index* idx, const int* tokens, const i64* values, const i64* offsets, const int* ranks, int N,
+                                int* out_prefix_len, cudaStream_t s) {
   if (N <= 0) return RM_OK;
   RmScratch& sc = idx->sc;
   const u64 seq_base = idx->op_seq + 1;

@@ -50,6 +50,7 @@ struct rm_index {
   RmTree t;           // device pointers, passed by value to kernels
   RmScratch sc;
   u64 op_seq;         // logical clock: operations applied so far
+  u64 ins_records;    // insert records applied since the last reset (a cold index applies its first batches in chunks)
   int node_bits;      // bits of a node id
   int len_bits;       // bits of an edge length / split point
   unsigned* ring_p;   // consistent-hash rings (device)

@@ -88,6 +88,7 @@ int rm_launch_reset(rm_index* idx, cudaStream_t s) {
   RM_LAUNCH(rm_reset_kernel, grid, RM_MT_TPB, s, t, ls.first, ls.cnt);
   RM_CUDA(cudaGetLastError());
   idx->op_seq = 1;   // reset itself is operation 1 of the logical clock
+  idx->ins_records = 0;
   return RM_OK;
 }
 

@@ -239,3 +239,29 @@ def run_tombstone_pressure(make_index, seed, rounds=60):
     assert max_tombs > 0                       # ... and tombstones were seen and kept in check
     assert_same_tree(device_canonical(ix), orc.canonical())
     ix.close()
+
+
+def run_cold_batch(make_index, seed, n=900, L=24, n_docs=6):
+    """The first batches into an empty index are applied as consecutive chunks of 256 records (rm_insert.cu: every record
+    of a hot document would otherwise queue in one in-order group).  Same order, so the same prefix lengths, tree and
+    eviction order as the oracle applying the records one by one; a third batch goes through the unchunked path."""
+    from tests.parity import zipf_prefix
+    ix = make_index(mode=0, max_nodes=1 << 14, max_tokens=1 << 18, max_batch=1024, max_key_len=4 * L)
+    orc = PortRadixCache(1)
+    docs = None
+    vc = 0
+    for b in range(3):
+        seqs, docs = zipf_prefix(seed * 10 + b, n_docs, n, L, vocab=40, docs=docs)
+        vals = np.arange(vc, vc + n * L, dtype=np.int64)
+        vc += n * L
+        offs = np.arange(0, (n + 1) * L, L, dtype=np.int64)
+        got = ix.insert_host(seqs.reshape(-1).copy(), vals, offs)
+        exp = [orc.insert(r.tolist(), vals[i * L:(i + 1) * L]) for i, r in enumerate(seqs)]
+        assert got.tolist() == exp, f"batch {b}"
+        ix.check_device_error()
+        assert_same_tree(device_canonical(ix), orc.canonical())
+    before = len(orc.freed)
+    orc.evict(1 << 30)
+    _, eo, el = ix.evict(1 << 30)
+    assert el.tolist() == [len(r) for r in orc.freed[before:]]
+    ix.close()

@@ -30,6 +30,11 @@ def test_emu_streaming_insert_evict_compact(seed):
     cases.run_stream_evict(make_index, seed)
 
 
+@pytest.mark.parametrize("seed", range(2))
+def test_emu_cold_batches_are_applied_in_chunks(seed):
+    cases.run_cold_batch(make_index, seed)
+
+
 @pytest.mark.parametrize("seed", range(3))
 def test_emu_tombstone_pressure_rebuilds_the_table(seed):
     cases.run_tombstone_pressure(make_index, seed)

@@ -224,7 +224,22 @@ def c3_block(bench, torch, capi, peak, ix, state, mean_hops_per_token, batches=8
     cpu_ev_s = time.perf_counter() - t0
     cpu_ev_nodes = len(t.freed) - before
     s1 = ix.sizes()
+    # the first batch into an EMPTY index (applied in chunks of 256 records: csrc/rm_insert.cu)
+    cold = capi.DeviceIndex(mode=capi.MODE_BASE, device=dev.index, max_nodes=1 << 16, max_tokens=NB * L + (1 << 16), max_batch=NB, max_key_len=1024)
+    first = next(bench.insert_stream(wl, docs))
+    tok0 = torch.from_numpy(first.reshape(-1)).to(dev)
+    val0 = torch.arange(NB * L, dtype=torch.int64, device=dev)
+    e0, e1 = _events(torch, 2)
+    torch.cuda.synchronize()
+    e0.record()
+    cold.insert(tok0, val0, offs, None, NB, outs[0])
+    e1.record()
+    torch.cuda.synchronize()
+    cold_ms = e0.elapsed_time(e1)
+    cold.check_device_error()
+    cold.close()
     return {
+        "cold_first_batch_ms": cold_ms,
         "workload": f"C3 streaming insert + LRU evict at 90% occupancy: 1M-node tree, {NB}-record batches of {L}-token keys",
         "value": NB * batches / total_s, "unit": "inserts/s (insert + evict time)", "batches": batches, "warmup": warmup,
         "inserts_per_s_insert_only": NB / (ms_ins * 1e-3), "ms_per_insert_batch": ms_ins,
