@@ -246,7 +246,7 @@ def run_cold_batch(make_index, seed, n=900, L=24, n_docs=6):
     of a hot document would otherwise queue in one in-order group).  Same order, so the same prefix lengths, tree and
     eviction order as the oracle applying the records one by one; a third batch goes through the unchunked path."""
     from tests.parity import zipf_prefix
-    ix = make_index(mode=0, max_nodes=1 << 14, max_tokens=1 << 18, max_batch=1024, max_key_len=4 * L)
+    ix = make_index(mode=0, max_nodes=1 << 16, max_tokens=max(1 << 18, 3 * n * L), max_batch=max(1024, n), max_key_len=4 * L)
     orc = PortRadixCache(1)
     docs = None
     vc = 0
