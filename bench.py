@@ -1,9 +1,9 @@
 """Headline benchmark: batched prefix-match lookups/s on the device-resident radix index.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|target] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--with-c5] [--no-blocks]
 
-One "step" = one pass of the hot path (rm_match_batch: walk kernel + split-request sort + split
-apply) over one batch of synthetic Zipf shared-prefix queries (SURVEY.md 8d generator).  Every step
+One "step" = one pass of the hot path (rm_match_batch: walk kernel + split stage, two launches)
+over one batch of synthetic Zipf shared-prefix queries (SURVEY.md 8d generator).  Every step
 gets a batch the tree has not seen before, so the splitting work the reference does on first sight
 of a prefix (radix_cache.py:262-266) is inside the timed region.
 
@@ -16,6 +16,12 @@ of a prefix (radix_cache.py:262-266) is inside the timed region.
 
 N > 1 (torchrun): every rank hosts a replica of the tree and its own shard of query batches; no
 data-path collective (weak scaling); time = max over ranks.
+
+The same line carries secondary blocks (tools/bench_blocks.py), each with its own parity check - the line is not
+printed if one fails: `parity_check` (first timed batch against the CPU port), `target` (1 M-node tree, 64 K x 512
+tokens), `c3` (streaming insert + LRU evict at 90 % occupancy), `mesh_route` (the C4 routing path on N GPUs, replicated
+and sharded forms), `oplog_exchange` (packed INSERT records all-gathered and applied on every replica), and with
+--with-c5 `c5` (10 M-node tree, 4,096-token queries).
 """
 import argparse
 import json
@@ -217,6 +223,9 @@ def main():
     ap.add_argument("--with-c5", action="store_true", help="also run the 10 M-node / 4K-token block (tools/bench_c5.py; ~1 min more)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    if args.workload != "c2":
+        args.no_cpu = True     # the port cannot hold these trees (minutes to hours): the default run's `target` block and
+                               # tools/bench_c5.py carry the parity checks and CPU samples for these shapes
     if args.impl == "reference":
         run_reference(args, wl)
         return
