@@ -29,6 +29,7 @@ extern "C" {
 #endif
 
 typedef struct rm_index rm_index;
+typedef struct rm_node_info_t rm_node_info_t;   /* defined with rm_node_info below */
 
 typedef enum {
   RM_OK = 0,
@@ -106,6 +107,16 @@ int rm_match_batch(rm_index* idx, const int32_t* tokens, const int64_t* offsets,
  * host memory makes the copies asynchronous with respect to each other. */
 int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offsets_h, int32_t B,
                      int32_t* out_len_h, int32_t* out_node_h, void* stream);
+
+/*
+ * RadixCache.match_prefix / RadixMesh.match_prefix (P/D) for ONE key in HOST memory, end to end with one synchronisation:
+ * H2D of the key, walk (+ split), gather of the values along the matched path (radix_cache.py:154-157), the record of
+ * last_device_node (rm_node_info), D2H.  out_values_h must hold n entries (the first *out_len_h are written);
+ * out_info_h may be NULL.  The single-key surface of the drop-in classes goes through this call: ~10 separate copies and
+ * launches otherwise.
+ */
+int rm_match_prefix_h(rm_index* idx, const int32_t* key_h, int32_t n, int32_t* out_len_h, int32_t* out_node_h,
+                      int64_t* out_values_h, rm_node_info_t* out_info_h, void* stream);
 
 /*
  * rm_match_batch for callers that must not allocate device memory.  No counterpart in the reference
@@ -254,11 +265,11 @@ int rm_dump(rm_index* idx, int32_t cap, int32_t* parent_h, int64_t* edge_off_h, 
  * .id .key .value .lock_ref .parent .children): rows for n node ids given in a HOST array, independent of the tree size.
  * parent = -1 for the root and for a free id, -2 for an id outside the pool.  Synchronises.
  */
-typedef struct {
+struct rm_node_info_t {
   int32_t parent, edge_len, lock_ref, rank, depth_end, nchild, gen, parked;
   int64_t edge_off;      /* start of the node's key / value run in the arenas (rm_read_arena) */
   uint64_t stamp;        /* raw last-access stamp of the node itself (its effective stamp is the subtree maximum) */
-} rm_node_info_t;
+};
 int rm_node_info(rm_index* idx, const int32_t* ids_h, int32_t n, rm_node_info_t* out_h, void* stream);
 /* TreeNode.children of one node (radix_cache.py:39): child id, first token of its edge (the dict key), generation and
  * dict-order key (ascending = the reference's dict insertion order) per child, to HOST arrays of `cap` entries;

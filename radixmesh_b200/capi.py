@@ -55,6 +55,7 @@ _PROTOS = {
     "rm_match_batch": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P]),
     "rm_match_batch_h": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P]),
     "rm_match_batch_static": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P]),
+    "rm_match_prefix_h": (C.c_int, [_P, _P, C.c_int32, _P, _P, _P, _P, _P]),
     "rm_gather_values": (C.c_int, [_P, _P, _P, _P, C.c_int32, _P, _P]),
     "rm_insert_batch": (C.c_int, [_P, _P, _P, _P, _P, C.c_int32, _P, _P]),
     "rm_insert_batch_h": (C.c_int, [_P, _P, _P, _P, _P, C.c_int32, _P, _P]),
@@ -212,6 +213,17 @@ class DeviceIndex:
         B = len(offsets_h) - 1
         with self._mutex:
             self._check(self.lib.rm_match_batch_h(self._h, ptr(tokens_h), ptr(offsets_h), B, ptr(out_len_h), ptr(out_node_h), self._s()))
+
+    def match_prefix_host(self, key_h: np.ndarray):
+        """rm_match_prefix_h: one key end to end -> (matched length, last node id, values[:length], RmNodeInfo of the node)."""
+        n = len(key_h)
+        ln, nd = C.c_int32(0), C.c_int32(0)
+        vals = np.empty(max(n, 1), dtype=np.int64)
+        info = RmNodeInfo()
+        with self._mutex:
+            self._check(self.lib.rm_match_prefix_h(self._h, ptr(key_h), n, C.addressof(ln), C.addressof(nd), ptr(vals),
+                                                   C.addressof(info), self._s()))
+        return ln.value, nd.value, vals[:ln.value], info
 
     def gather(self, nodes, lens, out_offsets, B, out_values) -> None:
         with self._mutex:

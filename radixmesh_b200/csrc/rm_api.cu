@@ -336,6 +336,33 @@ int rm_match_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* offs
   return RM_OK;
 }
 
+int rm_match_prefix_h(rm_index* idx, const int32_t* key_h, int32_t n, int32_t* out_len_h, int32_t* out_node_h,
+                      int64_t* out_values_h, rm_node_info_t* out_info_h, void* stream) {
+  if (!idx || n < 0 || !out_len_h || !out_node_h || (n > 0 && (!key_h || !out_values_h))) return RM_E_INVALID;
+  if (idx->cfg.mode == RM_MODE_ROUTER) return RM_E_MODE;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RmScratch& sc = idx->sc;
+  int rc = rm_stage_reserve(idx, n > 0 ? n : 1, true);
+  if (rc) return rc;
+  const i64 offs[2] = {0, (i64)n};
+  RM_CUDA(cudaMemcpyAsync(sc.h_offsets, offs, sizeof(offs), cudaMemcpyHostToDevice, s));
+  if (n > 0) RM_CUDA(cudaMemcpyAsync(sc.h_tokens, key_h, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
+  rc = rm_launch_match(idx, sc.h_tokens, sc.h_offsets, 1, sc.h_out_a, sc.h_out_b, s);
+  if (rc) return rc;
+  // values of the matched path into the staging array (written from position h_offsets[0] = 0), node record of the last node
+  rc = rm_launch_gather(idx, sc.h_out_b, sc.h_out_a, sc.h_offsets, 1, sc.h_values, s);
+  if (rc) return rc;
+  rc = rm_launch_node_info_dev(idx, sc.h_out_b, 1, s);
+  if (rc) return rc;
+  RM_CUDA(cudaMemcpyAsync(out_len_h, sc.h_out_a, sizeof(int), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaMemcpyAsync(out_node_h, sc.h_out_b, sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (n > 0) RM_CUDA(cudaMemcpyAsync(out_values_h, sc.h_values, sizeof(i64) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  if (out_info_h) RM_CUDA(cudaMemcpyAsync(out_info_h, sc.info_rows, sizeof(rm_node_info_t), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaStreamSynchronize(s));
+  return RM_OK;
+}
+
 int rm_gather_values(rm_index* idx, const int32_t* nodes, const int32_t* lens, const int64_t* out_offsets, int32_t B,
                      int64_t* out_values, void* stream) {
   int rc = rm_check_batch(idx, B, "rm_gather_values");

@@ -102,6 +102,7 @@ int rm_launch_node_info(rm_index* idx, const int* ids_h, int n, rm_node_info_t* 
 int rm_launch_node_children(rm_index* idx, int node, int cap, int* ids_h, int* toks_h, int* gens_h, u64* ords_h, int* out_n_h,
                             cudaStream_t s);
 int rm_launch_total_size(rm_index* idx, i64* out_h, cudaStream_t s);
+int rm_launch_node_info_dev(rm_index* idx, const int* ids_d, int n, cudaStream_t s);   // rows into sc.info_rows (n <= 256)
 int rm_table_rebuild(rm_index* idx, int n_nodes_hwm, cudaStream_t s);
 int rm_launch_dups(rm_index* idx, int only_candidates, int cap, int* out_h, int* out_n_h, cudaStream_t s);
 int rm_launch_gc_agree(rm_index* idx, const int* tokens_h, const i64* offsets_h, const int* ranks_h, int n,

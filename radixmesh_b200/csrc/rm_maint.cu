@@ -1176,6 +1176,12 @@ int rm_launch_node_info(rm_index* idx, const int* ids_h, int n, rm_node_info_t* 
   return RM_OK;
 }
 
+int rm_launch_node_info_dev(rm_index* idx, const int* ids_d, int n, cudaStream_t s) {
+  RM_LAUNCH(rm_node_info_kernel, 1, RM_INFO_CHUNK, s, idx->t, ids_d, n, idx->sc.info_rows);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
 int rm_launch_node_children(rm_index* idx, int node, int cap, int* ids_h, int* toks_h, int* gens_h, u64* ords_h, int* out_n_h,
                             cudaStream_t s) {
   RmTree& t = idx->t;

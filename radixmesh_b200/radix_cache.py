@@ -312,10 +312,18 @@ class RadixCache:
             self.gather_values_batch(nodes, lens, be.to_device(np.asarray([0, m], dtype=np.int64)), vals)
             node = self._handle(int(be.to_host(nodes)[0]))
             return MatchResult(self._tensor(be.to_host(vals)[:m].copy()), node, node)
-        lens, nodes, vals, offs = self._match_keys([key])
-        node = self._handle(int(nodes[0]))
-        got = vals[:int(lens[0])]
-        return MatchResult(self._tensor(got), node, node)
+        vals, node = self._match_one(key)
+        return MatchResult(self._tensor(vals), node, node)
+
+    def _match_one(self, key):
+        """One key end to end through rm_match_prefix_h (one synchronisation): (values of the matched prefix, last node)."""
+        self._flush()
+        ln, nd, vals, info = self._ix.match_prefix_host(np.asarray(key, dtype=np.int32))
+        self._invalidate()
+        if nd == 0:
+            return vals, self.root_node
+        self._info_cache[nd] = info
+        return vals, TreeNode(self, nd, int(info.gen))
 
     def _match_keys(self, keys):
         """Host lists -> (lens, nodes, values, value offsets) as host arrays."""

@@ -100,9 +100,8 @@ class RadixMesh(RadixCache):
             if err[0] == 1:
                 raise AssertionError("[RadixMesh] Prefix match node_rank is invalid")   # radix_mesh.py:233-237
             return RouterMatchResult(int(pf[0]), int(dc[0]))
-        lens, nodes, vals, _ = self._match_keys([key])
-        node = self._handle(int(nodes[0]))
-        return MatchResult(self._tensor(vals[:int(lens[0])]), node, node)
+        vals, node = self._match_one(key)
+        return MatchResult(self._tensor(vals), node, node)
 
     def insert(self, key: List, value=None) -> int:
         assert self.mode in (RadixMode.PREFILL, RadixMode.DECODE), "only support prefill/decode node to insert"
