@@ -401,6 +401,7 @@ int rm_insert_batch_h(rm_index* idx, const int32_t* tokens_h, const int64_t* val
   RM_CUDA(cudaMemcpyAsync(sc.h_tokens, tokens_h, sizeof(int) * (size_t)nt, cudaMemcpyHostToDevice, s));
   if (with_values) RM_CUDA(cudaMemcpyAsync(sc.h_values, values_h, sizeof(i64) * (size_t)nt, cudaMemcpyHostToDevice, s));
   if (ranks_h) RM_CUDA(cudaMemcpyAsync(sc.h_ranks, ranks_h, sizeof(int) * (size_t)N, cudaMemcpyHostToDevice, s));
+  idx->hint_tokens = nt;
   rc = rm_launch_insert(idx, sc.h_tokens, sc.h_values, sc.h_offsets, ranks_h ? sc.h_ranks : nullptr, N, sc.h_out_a, s);
   if (rc) return rc;
   if (out_prefix_len_h)

@@ -531,7 +531,10 @@ static int rm_launch_insert_one(rm_index* idx, const int* tokens, const i64* val
 int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const i64* offsets, const int* ranks, int N,
                      int* out_prefix_len, cudaStream_t s) {
   if (N <= 0) return RM_OK;
-  const bool cold = N > RM_COLD_CHUNK && idx->ins_records < 2ull * (u64)N;
+  // (short keys have nothing long to re-walk: a batch known to average under 64 tokens per record is applied whole)
+  const bool short_keys = idx->hint_tokens > 0 && idx->hint_tokens < 64ll * N;
+  idx->hint_tokens = 0;
+  const bool cold = N > RM_COLD_CHUNK && idx->ins_records < 2ull * (u64)N && !short_keys;
   idx->ins_records += (u64)N;
   if (!cold) return rm_launch_insert_one(idx, tokens, values, offsets, ranks, N, out_prefix_len, s);
   for (int a = 0; a < N; a += RM_COLD_CHUNK) {

@@ -51,6 +51,7 @@ struct rm_index {
   RmScratch sc;
   u64 op_seq;         // logical clock: operations applied so far
   u64 ins_records;    // insert records applied since the last reset (a cold index applies its first batches in chunks)
+  i64 hint_tokens;    // tokens of the batch being inserted when the caller knows them (the *_h entry points), else 0
   int node_bits;      // bits of a node id
   int len_bits;       // bits of an edge length / split point
   unsigned* ring_p;   // consistent-hash rings (device)

@@ -241,7 +241,7 @@ def run_tombstone_pressure(make_index, seed, rounds=60):
     ix.close()
 
 
-def run_cold_batch(make_index, seed, n=900, L=24, n_docs=6):
+def run_cold_batch(make_index, seed, n=700, L=72, n_docs=6):
     """The first batches into an empty index are applied as consecutive chunks of 256 records (rm_insert.cu: every record
     of a hot document would otherwise queue in one in-order group).  Same order, so the same prefix lengths, tree and
     eviction order as the oracle applying the records one by one; a third batch goes through the unchunked path."""

@@ -187,7 +187,7 @@ def test_gpu_streaming_insert_evict_compact(seed):
 
 @pytest.mark.parametrize("seed", range(2))
 def test_gpu_cold_batches_are_applied_in_chunks(seed):
-    cases.run_cold_batch(make_index, seed, n=2500, L=48, n_docs=12)
+    cases.run_cold_batch(make_index, seed, n=2500, L=96, n_docs=12)
 
 
 @pytest.mark.parametrize("seed", range(2))
