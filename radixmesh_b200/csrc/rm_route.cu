@@ -29,8 +29,22 @@ struct RmMd5 {
 
 __device__ __forceinline__ unsigned rm_rotl(unsigned x, int s) { return (x << s) | (x >> (32 - s)); }
 
+// message word + round constant.  An MD5 step is a chain through the word computed by the step before; written
+// as one sum the compiler emits LOP3 -> IADD3(f, a, x) -> IADD(k) -> LEA.HI(rotate, + b), four dependent
+// instructions.  x + k does not depend on the chain: kept apart (the asm hides it from reassociation) the chain
+// is LOP3 -> IADD3(f, a, x + k) -> LEA.HI.
+__device__ __forceinline__ unsigned rm_md5_xk(unsigned x, unsigned k) {
+#ifdef RM_EMU
+  return x + k;
+#else
+  unsigned r;
+  asm("add.u32 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(k));
+  return r;
+#endif
+}
+
 #define RM_MD5_STEP(f, a, b, c, d, x, k, s) \
-  a = b + rm_rotl(a + (f) + (x) + (k), s)
+  a = b + rm_rotl(a + (f) + rm_md5_xk(x, k), s)
 
 template <class W>
 __device__ __forceinline__ void rm_md5_block(RmMd5& m, const W& w) {
@@ -128,35 +142,39 @@ struct RmMd5Words {
   __device__ __forceinline__ void set(int i, unsigned v) const { col[i * stride] = v; }
 };
 
+// The common case, 0 <= v < 100000 (every token id of a real vocabulary), without a loop: the top digit by a
+// constant division, the other four as two two-digit halves in one register (n / 10 == n * 103 >> 10 for n < 100,
+// and neither the products nor the differences carry from one half into the other), leading zeros shifted out.
+// Returns the length; text in s, first character lowest (at most 7 bytes with the separator).
+__device__ __forceinline__ int rm_render_small(unsigned v, int lead, u64& s) {
+  const unsigned d4 = v / 10000u;
+  const unsigned r = v - d4 * 10000u;
+  const unsigned h = r / 100u;
+  const unsigned p = h | ((r - h * 100u) << 16);
+  const unsigned t = ((p * 103u) >> 10) & 0x000f000fu;      // tens of both halves
+  const unsigned o = p - t * 10u;                           // ones of both halves
+  const unsigned w = (t | (o << 8)) + 0x30303030u;          // d3 d2 d1 d0
+  u64 t5 = (u64)(d4 + 0x30u) | ((u64)w << 8);
+  const int nd = 1 + (v >= 10u) + (v >= 100u) + (v >= 1000u) + (v >= 10000u);
+  t5 >>= 8 * (5 - nd);
+  if (lead == 1) {
+    s = (t5 << 16) | ((u64)' ' << 8) | (u64)',';
+    return nd + 2;
+  }
+  if (lead == 2) {
+    s = (t5 << 8) | (u64)'[';
+    return nd + 1;
+  }
+  s = t5;
+  return nd;
+}
+
 // Text of one list item, first character in the lowest byte of (lo, hi): the decimal digits of v ('-' in front
 // of a negative one), preceded by ", " (lead 1) or "[" (lead 2) or nothing (lead 0).  At most 13 bytes.
 __device__ __forceinline__ int rm_render_token(int v, int lead, u64& tlo, u64& thi) {
   if ((unsigned)v < 100000u) {
-    // every token id of a real vocabulary: five digits by constant division (multiply-high), leading zeros shifted
-    // out, no loop (the general path below is ~3x the instructions, and rendering is issue bound)
-    unsigned x = (unsigned)v;
-    const unsigned d4 = x / 10000u;
-    x -= d4 * 10000u;
-    const unsigned d3 = x / 1000u;
-    x -= d3 * 1000u;
-    const unsigned d2 = x / 100u;
-    x -= d2 * 100u;
-    const unsigned d1 = x / 10u;
-    const unsigned d0 = x - d1 * 10u;
-    u64 s = (u64)(0x30303030u + (d4 | (d3 << 8) | (d2 << 16) | (d1 << 24))) | ((u64)(0x30u + d0) << 32);
-    const int nd = 1 + (v >= 10) + (v >= 100) + (v >= 1000) + (v >= 10000);
-    s >>= 8 * (5 - nd);
-    int len = nd;
-    if (lead == 1) {
-      s = (s << 16) | ((u64)' ' << 8) | (u64)',';
-      len += 2;
-    } else if (lead == 2) {
-      s = (s << 8) | (u64)'[';
-      ++len;
-    }
-    tlo = s;
     thi = 0;
-    return len;
+    return rm_render_small((unsigned)v, lead, tlo);
   }
   // decimal digits, least significant first; shifting what is there up by a byte puts the most
   // significant digit in the lowest byte, i.e. first in the text
@@ -269,7 +287,9 @@ __device__ unsigned rm_hash_token_list(const int* __restrict__ key, int n, const
 // Place of request q's message: 64 * ((qoff[q] - qoff[0] + 3) / 4 + 2 q) bytes, which leaves room for 13 bytes
 // per token + brackets + padding without a prefix sum over the requests.  A request that does not fit the
 // scratch keeps nblk = 0 and is hashed by the streamed form above.
-#define RM_RENDER_TPB 128
+#define RM_RENDER_TPB 256
+#define RM_RENDER_WPB (RM_RENDER_TPB / 32)
+#define RM_RENDER_BUF (128 * 7 + 16)
 
 __device__ __forceinline__ u64 rm_msg_off(i64 rel_tok, int q) { return 64ull * ((u64)((rel_tok + 3) >> 2) + 2ull * (u64)q); }
 
@@ -290,11 +310,56 @@ __device__ __forceinline__ int rm_msg_finish(unsigned char* dst, u64 total) {
   return (int)(total >> 6);
 }
 
+// ---- four items per lane (rm_route_render_kernel's usual chunk) ---------------------------------------------
+// A lane's text starts sh = (its first byte's place) & 3 bytes into a word; those sh bytes are the end of the text
+// of the lane before it.  rm_quad_rest: the last `rest` (0..3) bytes of a lane's text, which are the tail of its
+// last item because an item with its separator is at least 3 bytes long.
+__device__ __forceinline__ unsigned rm_quad_rest(u64 s3, int l3, unsigned rest) {
+  return (unsigned)(s3 >> (8 * ((unsigned)l3 - rest)));
+}
+
+// cin (low sh bytes) ++ s0 ++ s1 ++ s2 ++ s3 in q0..q3, first byte lowest: at most 3 + 4 * 7 = 31 bytes.  An item
+// lands in the 64-bit word its first byte falls in and spills into the next (the split shift is written so that a
+// byte offset of 0 shifts by 56 + 8, never by 64).
+__device__ __forceinline__ void rm_quad_pack(unsigned cin, unsigned sh, u64 s0, int l0, u64 s1, int l1, u64 s2, int l2, u64 s3,
+                                             int l3, u64& q0, u64& q1, u64& q2, u64& q3) {
+  (void)l3;
+  cin &= (1u << (8 * sh)) - 1u;
+  const unsigned r0 = sh, r1 = r0 + (unsigned)l0, r2 = r1 + (unsigned)l1, r3 = r2 + (unsigned)l2;
+  q0 = (u64)cin | (s0 << (8 * r0));
+  q1 = (s0 >> 8) >> (56 - 8 * r0);
+  q2 = 0;
+  q3 = 0;
+  {
+    const unsigned rr = 8 * (r1 & 7u);
+    const u64 lo = s1 << rr, hi = (s1 >> 8) >> (56 - rr);
+    if (r1 < 8) { q0 |= lo; q1 |= hi; } else { q1 |= lo; q2 |= hi; }
+  }
+  {
+    const unsigned rr = 8 * (r2 & 7u), ix = r2 >> 3;
+    const u64 lo = s2 << rr, hi = (s2 >> 8) >> (56 - rr);
+    if (ix == 0) { q0 |= lo; q1 |= hi; } else if (ix == 1) { q1 |= lo; q2 |= hi; } else { q2 |= lo; q3 |= hi; }
+  }
+  {
+    const unsigned rr = 8 * (r3 & 7u), ix = r3 >> 3;
+    const u64 lo = s3 << rr, hi = (s3 >> 8) >> (56 - rr);
+    if (ix == 0) { q0 |= lo; q1 |= hi; } else if (ix == 1) { q1 |= lo; q2 |= hi; }
+    else if (ix == 2) { q2 |= lo; q3 |= hi; } else { q3 |= lo; }
+  }
+}
+
+// A WARP per request (a block per request with four block barriers per 128-token chunk was 1.4 ms for 64K
+// 2K-token requests, six times its instruction count: the barriers, not the issue slots, set the pace).
 __global__ void __launch_bounds__(RM_RENDER_TPB)
 rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, int warm,
                        const int* __restrict__ prefill, const int* __restrict__ decode, const unsigned char* __restrict__ err,
                        unsigned char* __restrict__ msg, u64 msg_bytes, int* __restrict__ nblk) {
-  const int q = blockIdx.x;
+#ifdef RM_EMU
+  const int lane = 0, q = blockIdx.x;           // one thread per request
+#else
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int q = blockIdx.x * RM_RENDER_WPB + wid;
+#endif
   if (q >= B) return;
   const bool need = warm ? ((prefill[q] == -1 || decode[q] == -1) && err[q] == 0) : true;
   const i64 o0 = qoff[q];
@@ -302,73 +367,177 @@ rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qof
   const u64 base = rm_msg_off(o0 - qoff[0], q);
   const bool fits = msg != nullptr && rm_msg_off(qoff[q + 1] - qoff[0], q + 1) <= msg_bytes;
   if (!need || !fits) {
-    if (threadIdx.x == 0) nblk[q] = 0;
+    if (lane == 0) nblk[q] = 0;
     return;
   }
   const int* __restrict__ key = qtok + o0;
   unsigned char* dst = msg + base;
 #ifdef RM_EMU
-  {
+  if (lane == 0) {
+    // the device's chunking, lanes visited in order: full chunks of 128 small ids through rm_quad_pack (whole words
+    // out, the rest handed to the next lane), anything else 32 items at a time byte by byte
     u64 total = 0;
     if (n == 0) dst[total++] = (unsigned char)'[';
-    for (int i = 0; i < n; ++i) {
-      u64 lo, hi;
-      const int len = rm_render_token(key[i], i ? 1 : 2, lo, hi);
-      rm_put_bytes(dst + total, lo, hi, len);
-      total += (u64)len;
+    int c0 = 0;
+    while (c0 < n) {
+      bool quad = c0 + 128 <= n;
+      for (int i = c0; quad && i < c0 + 128; ++i) quad = (unsigned)key[i] < 100000u;
+      if (quad) {
+        unsigned cout = 0;
+        const unsigned left = (unsigned)(total & 3ull);
+        for (unsigned b2 = 0; b2 < left; ++b2) cout |= (unsigned)dst[total - left + b2] << (8 * b2);
+        for (int l = 0; l < 32; ++l) {
+          u64 s0, s1, s2, s3, qq[4];
+          const int* kp = key + c0 + 4 * l;
+          const int l0 = rm_render_small((unsigned)kp[0], (c0 | l) ? 1 : 2, s0);
+          const int l1 = rm_render_small((unsigned)kp[1], 1, s1);
+          const int l2 = rm_render_small((unsigned)kp[2], 1, s2);
+          const int l3 = rm_render_small((unsigned)kp[3], 1, s3);
+          const unsigned tot = (unsigned)(l0 + l1 + l2 + l3);
+          const unsigned sh = (unsigned)(total & 3ull);
+          const unsigned cin = cout;
+          cout = rm_quad_rest(s3, l3, (unsigned)((total + tot) & 3ull));
+          rm_quad_pack(cin, sh, s0, l0, s1, l1, s2, l2, s3, l3, qq[0], qq[1], qq[2], qq[3]);
+          const unsigned nw = (sh + tot) >> 2;
+          unsigned char* o = dst + (total - sh);
+          for (unsigned w = 0; w < nw; ++w)
+            for (int b2 = 0; b2 < 4; ++b2) o[4 * w + b2] = (unsigned char)(qq[w >> 1] >> (32 * (w & 1) + 8 * b2));
+          total += tot;
+        }
+        const unsigned rest = (unsigned)(total & 3ull);
+        for (unsigned b2 = 0; b2 < rest; ++b2) dst[total - rest + b2] = (unsigned char)(cout >> (8 * b2));
+        c0 += 128;
+        continue;
+      }
+      for (int i = c0; i < n && i < c0 + 32; ++i) {
+        u64 lo, hi;
+        const int len = rm_render_token(key[i], i ? 1 : 2, lo, hi);
+        rm_put_bytes(dst + total, lo, hi, len);
+        total += (u64)len;
+      }
+      c0 += 32;
     }
     nblk[q] = rm_msg_finish(dst, total);
   }
 #else
-  // a chunk of RM_RENDER_TPB tokens is rendered into shared memory and leaves as whole 32-bit words (byte
-  // stores straight to global memory: 250 M partial-sector writes per batch, 0.37 ms); the 0-3 bytes that do
-  // not fill a word wait at the front of the buffer for the next chunk
-  __shared__ unsigned wsum[RM_RENDER_TPB / 32];
-  __shared__ unsigned chunk_total;
-  __shared__ __align__(16) unsigned char buf[RM_RENDER_TPB * 13 + 8];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // Text leaves the warp's shared buffer as whole 32-bit words (byte stores straight to global memory: 250 M
+  // partial-sector writes per batch, 0.37 ms); the 0-3 bytes that do not fill a word wait at the front of the
+  // buffer for the next chunk.
+  //
+  // Full chunks of 128 small tokens, four per lane (the usual case): a lane strings its four items together in
+  // registers behind the 0-3 bytes that the lane before it could not fit into a whole word (those are the tail
+  // of that lane's last item, at least 3 bytes long: one shuffle), stores its whole words, and hands its own
+  // remainder on.  No byte stores, one prefix sum and one flush per 128 tokens: ~55 instructions per token
+  // against ~240 for the 32-token form below, which remains for the last chunk and for ids outside [0, 100000).
+  __shared__ __align__(16) unsigned char bufs[RM_RENDER_WPB][RM_RENDER_BUF];
+  unsigned char* buf = bufs[wid];
+  unsigned* bw = reinterpret_cast<unsigned*>(buf);
   u64 flushed = 0;       // bytes already in global memory (multiple of 4)
   unsigned left = 0;     // bytes waiting in buf[0..left)
   if (n == 0) {
-    if (threadIdx.x == 0) buf[0] = (unsigned char)'[';
+    if (lane == 0) buf[0] = (unsigned char)'[';
     left = 1;
   }
-  for (int c0 = 0; c0 < n; c0 += RM_RENDER_TPB) {
-    const int i = c0 + (int)threadIdx.x;
+  int c0 = 0;
+  while (c0 < n) {
+    bool quad = false;
+    int v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+    if (c0 + 128 <= n) {
+      const int* kp = key + c0 + 4 * lane;
+      v0 = __ldg(kp);
+      v1 = __ldg(kp + 1);
+      v2 = __ldg(kp + 2);
+      v3 = __ldg(kp + 3);
+      quad = __all_sync(0xffffffffu, ((unsigned)v0 < 100000u) & ((unsigned)v1 < 100000u) & ((unsigned)v2 < 100000u) &
+                                         ((unsigned)v3 < 100000u));
+    }
+    if (quad) {
+      u64 s0, s1, s2, s3;
+      const int l0 = rm_render_small((unsigned)v0, (c0 | lane) ? 1 : 2, s0);
+      const int l1 = rm_render_small((unsigned)v1, 1, s1);
+      const int l2 = rm_render_small((unsigned)v2, 1, s2);
+      const int l3 = rm_render_small((unsigned)v3, 1, s3);
+      const unsigned tot = (unsigned)(l0 + l1 + l2 + l3);
+      unsigned inc = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += x;
+      }
+      const unsigned chunk_total = __shfl_sync(0xffffffffu, inc, 31);
+      const unsigned p0 = left + inc - tot;                  // this lane's first byte in the buffer
+      const unsigned sh = p0 & 3u;                           // bytes of the word it starts in that come from before
+      const unsigned sh_out = (p0 + tot) & 3u;               // bytes this lane leaves to the next
+      const unsigned cout = rm_quad_rest(s3, l3, sh_out);
+      unsigned cin = __shfl_up_sync(0xffffffffu, cout, 1);
+      if (lane == 0) cin = bw[0];                            // carried over from the chunk before
+      u64 q0, q1, q2, q3;
+      rm_quad_pack(cin, sh, s0, l0, s1, l1, s2, l2, s3, l3, q0, q1, q2, q3);
+      const unsigned nw = (sh + tot) >> 2;                   // whole words: 2..7
+      unsigned* o = bw + (p0 >> 2);                          // word 0 is lane 0's alone: read above, written here
+      o[0] = (unsigned)q0;
+      o[1] = (unsigned)(q0 >> 32);
+      if (nw > 2) o[2] = (unsigned)q1;
+      if (nw > 3) o[3] = (unsigned)(q1 >> 32);
+      if (nw > 4) o[4] = (unsigned)q2;
+      if (nw > 5) o[5] = (unsigned)(q2 >> 32);
+      if (nw > 6) o[6] = (unsigned)q3;
+      __syncwarp();
+      const unsigned avail = left + chunk_total;
+      const unsigned words = avail >> 2;
+      unsigned* __restrict__ gw = reinterpret_cast<unsigned*>(dst + flushed);
+      for (unsigned w = lane; w < words; w += 32) gw[w] = bw[w];
+      __syncwarp();
+      if (lane == 31) bw[0] = cout;                          // avail & 3 bytes, the low ones
+      flushed += 4ull * words;
+      left = avail & 3u;
+      __syncwarp();
+      c0 += 128;
+      continue;
+    }
+    const int i = c0 + lane;
     u64 lo = 0, hi = 0;
     int len = 0;
-    if (i < n) len = rm_render_token(key[i], i ? 1 : 2, lo, hi);
+    if (i < n) len = rm_render_token(__ldg(key + i), i ? 1 : 2, lo, hi);
     unsigned inc = (unsigned)len;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= o) inc += x;
     }
-    if (lane == 31) wsum[wid] = inc;
-    __syncthreads();
-    unsigned before = 0;
-    for (int w = 0; w < wid; ++w) before += wsum[w];
-    if (threadIdx.x == RM_RENDER_TPB - 1) chunk_total = before + inc;
-    rm_put_bytes(buf + left + before + inc - (unsigned)len, lo, hi, len);
-    __syncthreads();
+    const unsigned chunk_total = __shfl_sync(0xffffffffu, inc, 31);
+    rm_put_bytes(buf + left + inc - (unsigned)len, lo, hi, len);
+    __syncwarp();
     const unsigned avail = left + chunk_total;
     const unsigned words = avail >> 2;
     unsigned* __restrict__ gw = reinterpret_cast<unsigned*>(dst + flushed);
-    const unsigned* bw = reinterpret_cast<const unsigned*>(buf);
-    for (unsigned w = threadIdx.x; w < words; w += RM_RENDER_TPB) gw[w] = bw[w];
-    unsigned char carry = 0;
+    for (unsigned w = lane; w < words; w += 32) gw[w] = bw[w];
     const unsigned rest = avail & 3u;
-    if (threadIdx.x < rest) carry = buf[4 * words + threadIdx.x];
-    __syncthreads();
-    if (threadIdx.x < rest) buf[threadIdx.x] = carry;
+    unsigned char carry = 0;
+    if ((unsigned)lane < rest) carry = buf[4 * words + lane];
+    __syncwarp();
+    if ((unsigned)lane < rest) buf[lane] = carry;
     flushed += 4ull * words;
     left = rest;
-    __syncthreads();
+    __syncwarp();
+    c0 += 32;
   }
-  if (threadIdx.x == 0) {
-    for (unsigned b2 = 0; b2 < left; ++b2) dst[flushed + b2] = buf[b2];
-    nblk[q] = rm_msg_finish(dst, flushed + left);
+  // closing bracket, 0x80, zeros to 56 mod 64, bit length (RFC 1321): at most 3 + 73 bytes, built in the buffer
+  const u64 text = flushed + left + 1;                           // with the closing bracket
+  const u64 padded = (text + 1 + 8 + 63) & ~63ull;
+  const unsigned tail = (unsigned)(padded - flushed);            // bytes of the buffer to flush, multiple of 4
+  const u64 bits = text * 8ull;
+  for (unsigned j = left + lane; j < tail; j += 32) {
+    unsigned char v = 0;
+    if (j == left) v = (unsigned char)']';
+    else if (j == left + 1) v = 0x80;
+    else if (j >= tail - 8) v = (unsigned char)(bits >> (8 * (j - (tail - 8))));
+    buf[j] = v;
   }
+  __syncwarp();
+  unsigned* __restrict__ gw = reinterpret_cast<unsigned*>(dst + flushed);
+  for (unsigned w = lane; w < (tail >> 2); w += 32) gw[w] = bw[w];
+  if (lane == 0) nblk[q] = (int)(padded >> 6);
 #endif
 }
 
@@ -377,30 +546,71 @@ struct RmMd5Regs {
   __device__ __forceinline__ unsigned operator()(int i) const { return m[i]; }
 };
 
-// MD5 of a rendered, padded message of nb 64-byte blocks (64-byte aligned); next block loaded while this one
-// is compressed
-__device__ unsigned rm_hash_rendered(const unsigned char* __restrict__ msg, int nb) {
+// MD5 of a rendered, padded message of nb 64-byte blocks (64-byte aligned).  One thread per request and 50-250
+// blocks per request: a chain of ~3 dependent instructions per step with one or two warps per scheduler, so a
+// block that waits for its 64 bytes waits in full.  Loads written as "next block into registers while this one
+// is compressed" were scheduled two thirds of the way through the compression (the words of a block stay live
+// until its last round), ~350 cycles ahead of their use against ~800 of DRAM latency.  The blocks therefore
+// come through a ring of RM_MD5_STAGES asynchronous 64-byte copies per thread in shared memory
+// (ring[stage][quarter][thread], 16 bytes each: conflict free), RM_MD5_STAGES - 1 compressions ahead.
+#define RM_MD5_STAGES 4
+
+__device__ __forceinline__ unsigned rm_digest_word(const RmMd5& m) {
+  const unsigned a = m.a;
+  return ((a & 0xffu) << 24) | ((a & 0xff00u) << 8) | ((a >> 8) & 0xff00u) | (a >> 24);
+}
+
+#ifdef RM_EMU
+__device__ unsigned rm_hash_rendered(const unsigned char* __restrict__ msg, int nb, uint4* ring) {
+  (void)ring;
   RmMd5 m;
   rm_md5_init(m);
-  const uint4* __restrict__ p = reinterpret_cast<const uint4*>(msg);
-  uint4 x0 = p[0], x1 = p[1], x2 = p[2], x3 = p[3];
+  const unsigned* p = reinterpret_cast<const unsigned*>(msg);
   for (int b = 0; b < nb; ++b) {
+    RmMd5Regs w;
+    for (int i = 0; i < 16; ++i) w.m[i] = p[16 * b + i];
+    rm_md5_block(m, w);
+  }
+  return rm_digest_word(m);
+}
+#else
+__device__ __forceinline__ void rm_md5_fetch(uint4* ring, int stage, const unsigned char* src) {
+  const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (size_t)stage * 4 * RM_RT_TPB);
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (unsigned)(j * RM_RT_TPB * 16)), "l"(src + 16 * j)
+                 : "memory");
+}
+
+// ring: &ring[0][0][threadIdx.x]
+__device__ unsigned rm_hash_rendered(const unsigned char* __restrict__ msg, int nb, uint4* ring) {
+  RmMd5 m;
+  rm_md5_init(m);
+#pragma unroll
+  for (int s = 0; s < RM_MD5_STAGES - 1; ++s) {
+    if (s < nb) rm_md5_fetch(ring, s, msg + 64 * s);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  int stage = 0, ahead = RM_MD5_STAGES - 1;
+  for (int b = 0; b < nb; ++b) {
+    if (b + RM_MD5_STAGES - 1 < nb) rm_md5_fetch(ring, ahead, msg + 64 * (size_t)(b + RM_MD5_STAGES - 1));
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group %0;" ::"n"(RM_MD5_STAGES - 1) : "memory");
+    const uint4* r = ring + (size_t)stage * 4 * RM_RT_TPB;
+    const uint4 x0 = r[0], x1 = r[RM_RT_TPB], x2 = r[2 * RM_RT_TPB], x3 = r[3 * RM_RT_TPB];
     RmMd5Regs w;
     w.m[0] = x0.x; w.m[1] = x0.y; w.m[2] = x0.z; w.m[3] = x0.w;
     w.m[4] = x1.x; w.m[5] = x1.y; w.m[6] = x1.z; w.m[7] = x1.w;
     w.m[8] = x2.x; w.m[9] = x2.y; w.m[10] = x2.z; w.m[11] = x2.w;
     w.m[12] = x3.x; w.m[13] = x3.y; w.m[14] = x3.z; w.m[15] = x3.w;
-    if (b + 1 < nb) {
-      x0 = p[4 * (b + 1)];
-      x1 = p[4 * (b + 1) + 1];
-      x2 = p[4 * (b + 1) + 2];
-      x3 = p[4 * (b + 1) + 3];
-    }
     rm_md5_block(m, w);
+    stage = stage + 1 == RM_MD5_STAGES ? 0 : stage + 1;
+    ahead = ahead + 1 == RM_MD5_STAGES ? 0 : ahead + 1;
   }
-  const unsigned a = m.a;
-  return ((a & 0xffu) << 24) | ((a & 0xff00u) << 8) | ((a >> 8) & 0xff00u) | (a >> 24);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  return rm_digest_word(m);
 }
+#endif
 
 // bisect.bisect(ring, h) % len(ring) (cache_aware_router.py:106-108)
 __device__ __forceinline__ int rm_ring_owner(const unsigned* ring, const int* owner, int n, unsigned h) {
@@ -420,8 +630,44 @@ rm_route_finish_kernel(RmTree t, const int* __restrict__ qtok, const i64* __rest
                        int ring_p_n, const unsigned* ring_d, const int* ring_d_owner, int ring_d_n,
                        const unsigned char* __restrict__ msg, const int* __restrict__ nblk) {
   __shared__ unsigned wsm[16 * RM_RT_TPB];
+#ifdef RM_EMU
+  uint4* ring = nullptr;
+#else
+  __shared__ uint4 ring_sm[RM_MD5_STAGES * 4 * RM_RT_TPB];
+  uint4* ring = ring_sm + threadIdx.x;
+#endif
   const RmMd5Words words = {wsm + threadIdx.x, RM_RT_TPB};
+#ifdef RM_EMU
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
+#else
+  // The compression runs as long as the longest request of the warp, and requests that picked both ranks in the
+  // walk need none: with lengths of 1K-4K tokens and a third of the lanes idle a warp did 2.4x the work of its
+  // lanes, and at 64K requests the kernel is bound by the integer pipe.  The block's requests are dealt to its
+  // threads in order of message length (rank by counting in shared memory), so the lanes of a warp finish together
+  // and the warps left with nothing to hash leave at once: 406 -> 333 us at 64K requests.
+  __shared__ int skey[RM_RT_TPB];
+  __shared__ int sperm[RM_RT_TPB];
+  int q;
+  {
+    const int q0 = blockIdx.x * blockDim.x + threadIdx.x;
+    int k = -1;
+    if (q0 < B) {
+      const bool need = warm ? ((prefill[q0] == -1 || decode[q0] == -1) && err[q0] == 0) : true;
+      const int nb = nblk ? nblk[q0] : 0;
+      k = !need ? 0 : nb > 0 ? nb : (int)((qoff[q0 + 1] - qoff[q0]) >> 3) + 1;     // streamed form: ~8 tokens a block
+    }
+    skey[threadIdx.x] = k;
+    __syncthreads();
+    int rank = 0;
+    for (int j = 0; j < RM_RT_TPB; ++j) {
+      const int kj = skey[j];
+      rank += (kj > k) | ((kj == k) & (j < (int)threadIdx.x));
+    }
+    sperm[rank] = q0;
+    __syncthreads();
+    q = sperm[threadIdx.x];        // (giving the long quarter to a different warp in every block: 333 -> 380 us)
+  }
+#endif
   if (q >= B) return;
   int pf = -1, dc = -1;
   unsigned char e = 0;
@@ -439,7 +685,7 @@ rm_route_finish_kernel(RmTree t, const int* __restrict__ qtok, const i64* __rest
     unsigned h = 0;
     if (need_hash) {
       const int nb = nblk ? nblk[q] : 0;
-      if (nb > 0) h = rm_hash_rendered(msg + rm_msg_off(qoff[q] - qoff[0], q), nb);     // rendered by rm_route_render_kernel
+      if (nb > 0) h = rm_hash_rendered(msg + rm_msg_off(qoff[q] - qoff[0], q), nb, ring);     // rendered by rm_route_render_kernel
       else h = rm_hash_token_list(qtok + qoff[q], (int)(qoff[q + 1] - qoff[q]), words);
     }
     if (pf != -1) {
@@ -470,11 +716,11 @@ static bool rm_launch_render(rm_index* idx, const int* tokens, const i64* offset
                              const int* decode, const unsigned char* err, cudaStream_t s) {
   if (!idx->route_nblk || !idx->route_msg || B > idx->cfg.max_batch) return false;
 #ifdef RM_EMU
-  const int tpb = 1;
+  const int tpb = 1, grid = B;
 #else
-  const int tpb = RM_RENDER_TPB;
+  const int tpb = RM_RENDER_TPB, grid = (B + RM_RENDER_WPB - 1) / RM_RENDER_WPB;
 #endif
-  RM_LAUNCH(rm_route_render_kernel, B, tpb, s, tokens, offsets, B, warm, prefill, decode, err, idx->route_msg,
+  RM_LAUNCH(rm_route_render_kernel, grid, tpb, s, tokens, offsets, B, warm, prefill, decode, err, idx->route_msg,
             (u64)idx->route_msg_bytes, idx->route_nblk);
   return true;
 }

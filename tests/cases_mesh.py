@@ -150,4 +150,18 @@ def md5_awkward_keys():
     rnd = random.Random(5)
     pool = [0, 7, 10, 99, 100, 31999, 32000, 123456, 2147483647, -1, -2147483648, 999999, 1000000]
     lens = list(range(0, 40)) + [55, 56, 57, 63, 64, 65, 119, 120, 121, 127, 128, 129, 500] + [2176] * 40
-    return [[rnd.choice(pool) for _ in range(n)] for n in lens]
+    keys = [[rnd.choice(pool) for _ in range(n)] for n in lens]
+    # runs of ordinary token ids (< 100000), which the render kernel takes 128 at a time, four per lane: every digit
+    # count, the shortest and the longest text a lane can hold, lengths around the 128-token chunk, and runs broken
+    # by an id that sends one chunk through the general path
+    small = [0, 5, 9, 10, 42, 99, 100, 999, 1000, 9999, 10000, 31999, 99999]
+    for n in (128, 129, 131, 159, 160, 255, 256, 257, 300, 511, 640, 1000, 2176, 4000):
+        keys.append([rnd.choice(small) for _ in range(n)])
+    for v in (0, 7, 10, 99, 100, 1234, 99999):
+        keys.append([v] * 384)
+    keys.append([rnd.randrange(0, 100000) for _ in range(3000)])
+    broken = [rnd.randrange(0, 32000) for _ in range(700)]
+    broken[10], broken[200], broken[699] = -5, 123456, 2147483647
+    keys.append(broken)
+    keys.append([100000] + [rnd.randrange(0, 100000) for _ in range(511)])
+    return keys
