@@ -120,6 +120,7 @@ int rm_destroy(rm_index* idx) {
                   idx->ring_p, idx->ring_p_owner, idx->ring_d, idx->ring_d_owner, idx->route_msg, idx->route_nblk};
   for (void* p : ptrs)
     if (p) cudaFree(p);
+  if (idx->mail) cudaFreeHost(idx->mail);
   delete idx;
   return RM_OK;
 }
@@ -230,6 +231,7 @@ int rm_create(const rm_config* cfg, rm_index** out) {
     sc.h_tokens_cap = cfg->max_batch_tokens;
   }
 #undef A
+  if (e == cudaSuccess) e = cudaMallocHost(&idx->mail, RM_MAIL_BYTES);
   if (e != cudaSuccess) {
     rm_set_error("rm_create: device allocation failed: %s", cudaGetErrorString(e));
     rm_destroy(idx);
@@ -345,9 +347,24 @@ int rm_match_prefix_h(rm_index* idx, const int32_t* key_h, int32_t n, int32_t* o
   RmScratch& sc = idx->sc;
   int rc = rm_stage_reserve(idx, n > 0 ? n : 1, true);
   if (rc) return rc;
+  // Through the pinned mailbox when the key fits (8192 tokens): every copy is then asynchronous and the call waits
+  // once.  (Straight from / into the caller's pageable memory each of the six copies blocks the host.)
+  const bool mailed = n <= RM_EVICT_FIRST;
+  char* mail = static_cast<char*>(idx->mail);
+  i64* m_offs = reinterpret_cast<i64*>(mail);                               // [0, 16)
+  int* m_out = reinterpret_cast<int*>(mail + 16);                           // length, node
+  rm_node_info_t* m_info = reinterpret_cast<rm_node_info_t*>(mail + 64);
+  int* m_key = reinterpret_cast<int*>(mail + 4096);                         // 4 n bytes
+  i64* m_val = reinterpret_cast<i64*>(mail + 4096 + 4 * RM_EVICT_FIRST);    // 8 n bytes
+  static_assert(4096 + 12 * RM_EVICT_FIRST <= RM_MAIL_BYTES && 64 + sizeof(rm_node_info_t) <= 4096, "mailbox layout");
   const i64 offs[2] = {0, (i64)n};
-  RM_CUDA(cudaMemcpyAsync(sc.h_offsets, offs, sizeof(offs), cudaMemcpyHostToDevice, s));
-  if (n > 0) RM_CUDA(cudaMemcpyAsync(sc.h_tokens, key_h, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
+  if (mailed) {
+    m_offs[0] = 0;
+    m_offs[1] = (i64)n;
+    if (n > 0) memcpy(m_key, key_h, sizeof(int) * (size_t)n);
+  }
+  RM_CUDA(cudaMemcpyAsync(sc.h_offsets, mailed ? (const void*)m_offs : (const void*)offs, sizeof(offs), cudaMemcpyHostToDevice, s));
+  if (n > 0) RM_CUDA(cudaMemcpyAsync(sc.h_tokens, mailed ? (const void*)m_key : (const void*)key_h, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
   rc = rm_launch_match(idx, sc.h_tokens, sc.h_offsets, 1, sc.h_out_a, sc.h_out_b, s);
   if (rc) return rc;
   // values of the matched path into the staging array (written from position h_offsets[0] = 0), node record of the last node
@@ -355,11 +372,17 @@ int rm_match_prefix_h(rm_index* idx, const int32_t* key_h, int32_t n, int32_t* o
   if (rc) return rc;
   rc = rm_launch_node_info_dev(idx, sc.h_out_b, 1, s);
   if (rc) return rc;
-  RM_CUDA(cudaMemcpyAsync(out_len_h, sc.h_out_a, sizeof(int), cudaMemcpyDeviceToHost, s));
-  RM_CUDA(cudaMemcpyAsync(out_node_h, sc.h_out_b, sizeof(int), cudaMemcpyDeviceToHost, s));
-  if (n > 0) RM_CUDA(cudaMemcpyAsync(out_values_h, sc.h_values, sizeof(i64) * (size_t)n, cudaMemcpyDeviceToHost, s));
-  if (out_info_h) RM_CUDA(cudaMemcpyAsync(out_info_h, sc.info_rows, sizeof(rm_node_info_t), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaMemcpyAsync(mailed ? (void*)m_out : (void*)out_len_h, sc.h_out_a, sizeof(int), cudaMemcpyDeviceToHost, s));
+  RM_CUDA(cudaMemcpyAsync(mailed ? (void*)(m_out + 1) : (void*)out_node_h, sc.h_out_b, sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (n > 0) RM_CUDA(cudaMemcpyAsync(mailed ? (void*)m_val : (void*)out_values_h, sc.h_values, sizeof(i64) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  if (out_info_h) RM_CUDA(cudaMemcpyAsync(mailed ? m_info : out_info_h, sc.info_rows, sizeof(rm_node_info_t), cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));
+  if (mailed) {
+    *out_len_h = m_out[0];
+    *out_node_h = m_out[1];
+    if (m_out[0] > 0) memcpy(out_values_h, m_val, sizeof(i64) * (size_t)m_out[0]);
+    if (out_info_h) *out_info_h = *m_info;
+  }
   return RM_OK;
 }
 

@@ -102,6 +102,7 @@ struct RmCounters {
   int dbg_max_group;  // largest split-request group seen (diagnostics)
   int dbg_groups;     // split-request groups seen (diagnostics)
   int ev_total;       // scratch: eviction candidates (leaves up to the frontier key + the parents they expose)
+  int ev_over;        // scratch: the current rm_evict pass ran with bounds that were too small (nothing was evicted)
   u64 ev_k0;          // scratch: frontier key of the current rm_evict (rm_maint.cu)
   u64 ins_ordered;    // diagnostics: mesh insert records applied on the ordered (first-token) path
   u64 ins_resumed;    // diagnostics: mesh insert records applied on the resumed (divergence-group) path

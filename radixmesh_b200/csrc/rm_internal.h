@@ -45,12 +45,20 @@ struct RmScratch {
   rm_node_info_t* info_rows;
 };
 
+#define RM_EVICT_FIRST 8192        // evicted nodes whose (id, offset, length) travel with the count
+#define RM_MAIL_BYTES (4096 + RM_EVICT_FIRST * 16)
+
 struct rm_index {
   rm_config cfg;
   RmTree t;           // device pointers, passed by value to kernels
   RmScratch sc;
   u64 op_seq;         // logical clock: operations applied so far
   u64 ins_records;    // insert records applied since the last reset (a cold index applies its first batches in chunks)
+  int hwm_exact;      // node high-water mark the host last read from the device ...
+  u64 hwm_seq;        // ... and the logical clock at that moment: an operation creates at most three nodes, which bounds
+                      // the mark without asking the device (rm_evict sizes its grids from the bound)
+  void* mail;         // pinned host memory, RM_MAIL_BYTES: small results come back through it in one asynchronous
+                      // copy + one synchronisation (a copy into pageable memory blocks the host once per call)
   i64 hint_tokens;    // tokens of the batch being inserted when the caller knows them (the *_h entry points), else 0
   int node_bits;      // bits of a node id
   int len_bits;       // bits of an edge length / split point

@@ -89,6 +89,8 @@ int rm_launch_reset(rm_index* idx, cudaStream_t s) {
   RM_CUDA(cudaGetLastError());
   idx->op_seq = 1;   // reset itself is operation 1 of the logical clock
   idx->ins_records = 0;
+  idx->hwm_exact = 1;
+  idx->hwm_seq = idx->op_seq;
   return RM_OK;
 }
 
@@ -228,13 +230,7 @@ int rm_launch_lock(rm_index* idx, const int* nodes, int B, int dir, i64* out_del
 // A node can only be evicted after all its descendants, so a locked node pins every ancestor, whatever
 // the ancestors' own lock_ref (inc/dec pairs keep lock_ref monotone along a path, but nothing forces
 // callers to pair them: the heap loop of radix_cache.py:187-202 simply never reaches such a parent).
-__global__ void rm_evict_pin_kernel(RmTree t, int n, int* __restrict__ pinned) {
-  int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= n || x == 0) return;
-  if (t.parent[x] < 0 || t.gen[x] < 0 || t.lock_ref[x] <= 0) return;
-  int y = t.parent[x];
-  while (y > 0 && atomicExch(&pinned[y], 1) == 0) y = t.parent[y];
-}
+// (The pinning is the last step of rm_evict_count_kernel.)
 
 // Lazy stamps.  Walks and inserts stamp only the deepest node(s) they reach (one atomic per operation instead
 // of one per hop); every other node the reference would have stamped is an ancestor of such an endpoint.
@@ -252,11 +248,19 @@ __global__ void rm_evict_pin_kernel(RmTree t, int n, int* __restrict__ pinned) {
 //      (they are candidates themselves) and its own key is still <= K0, and carries on upward;
 //   4. candidates are sorted again and cut exactly.
 // The climbs are as short as the evicted region is shallow.
-__global__ void rm_evict_count_kernel(RmTree t, int n, u64* __restrict__ eff, int* __restrict__ rem) {
+__global__ void rm_evict_count_kernel(RmTree t, int n, u64* __restrict__ eff, int* __restrict__ rem, int* __restrict__ pinned) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= n) return;
+  if (x >= n || x >= t.ctr->node_hwm) return;          // n may be a host-side bound above the mark
   eff[x] = t.stamp[x];
-  if (x > 0 && t.parent[x] > 0 && t.gen[x] >= 0) atomicAdd(&rem[t.parent[x]], 1);
+  if (x == 0) return;
+  const int par = t.parent[x];
+  if (par < 0 || t.gen[x] < 0) return;
+  if (par > 0) atomicAdd(&rem[par], 1);
+  // a locked node pins every ancestor (note above; same pass over the node records)
+  if (t.lock_ref[x] > 0) {
+    int y = par;
+    while (y > 0 && atomicExch(&pinned[y], 1) == 0) y = t.parent[y];
+  }
 }
 
 __device__ __forceinline__ u64 rm_evict_key(u64 stamp, int depth_end, int depth_bits) {
@@ -270,7 +274,7 @@ __global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int*
   int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= n) return;
   u64 k = RM_NO_REQ;
-  if (x > 0 && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0 && pinned[x] == 0 && rem[x] == 0)
+  if (x > 0 && x < t.ctr->node_hwm && t.parent[x] >= 0 && t.gen[x] >= 0 && t.lock_ref[x] == 0 && pinned[x] == 0 && rem[x] == 0)
     k = rm_evict_key(t.stamp[x], t.depth_end[x], depth_bits);
   key[x] = k;
   val[x] = (unsigned)x;
@@ -293,10 +297,11 @@ struct RmEvictSel {
   u64 prefix;      // digits chosen so far (high bits of K0)
   i64 need;        // tokens still to be covered inside the prefix
   int all;         // the evictable leaves do not hold num_tokens: take every one of them
-  int pad;
+  unsigned done;   // blocks of the current level's histogram that have added their part (the last one picks the digit)
 };
 
-__global__ void rm_evict_sel_init_kernel(RmEvictSel* st, i64 num_tokens, u64* __restrict__ hw, unsigned* __restrict__ hc) {
+__global__ void rm_evict_sel_init_kernel(RmTree t, int n_bound, RmEvictSel* st, i64 num_tokens, u64* __restrict__ hw,
+                                         unsigned* __restrict__ hc) {
   for (int b = threadIdx.x; b < RM_SEL_BINS; b += blockDim.x) {
     hw[b] = 0;
     hc[b] = 0;
@@ -305,6 +310,9 @@ __global__ void rm_evict_sel_init_kernel(RmEvictSel* st, i64 num_tokens, u64* __
     st->prefix = 0;
     st->need = num_tokens;
     st->all = 0;
+    st->done = 0;
+    t.ctr->ev_total = 0;
+    t.ctr->ev_over = t.ctr->node_hwm > n_bound ? 1 : 0;      // nodes beyond the host's bound: this pass evicts nothing
   }
 }
 
@@ -406,6 +414,104 @@ __global__ void rm_evict_sel_pick_kernel(RmEvictSel* st, u64* __restrict__ hw, u
 #endif
 }
 
+#ifndef RM_EMU
+// One level of the select in ONE launch: a few blocks per SM stride over the keys (a block per 256 keys spent its
+// time clearing and flushing 4096 shared bins: 15-26 us per level at 1 M nodes), and the last block to add its part
+// picks the digit (a launch of its own: 7 us per level).
+#define RM_SEL_BPT (RM_SEL_BINS / RM_MT_TPB)     // bins per thread in the pick
+__global__ void __launch_bounds__(RM_MT_TPB)
+rm_evict_sel_level_kernel(RmTree t, const u64* __restrict__ key, int n, int shift, int up, RmEvictSel* st, u64* __restrict__ hw) {
+  // 32-bit bins (the launcher keeps a block's keys x the longest edge below 2^31; a 64-bit shared atomic is a
+  // compare-and-swap loop), and ONE atomic for a warp whose leaves all fall into the same digit: on the first level
+  // the leaves of a served tree share their top digits, and 32 lanes adding to one address serialise (26 us)
+  __shared__ unsigned sh[RM_SEL_BINS];
+  __shared__ i64 wtot[RM_MT_TPB / 32];
+  __shared__ int last_s, found_s;
+  const bool all = st->all != 0;
+  const u64 prefix = st->prefix;
+  for (int b = threadIdx.x; b < RM_SEL_BINS; b += RM_MT_TPB) sh[b] = 0;
+  __syncthreads();
+  if (!all) {
+    n = min(n, t.ctr->node_hwm);
+    for (int base = blockIdx.x * RM_MT_TPB; base < n; base += gridDim.x * RM_MT_TPB) {
+      const int x = base + (int)threadIdx.x;
+      bool in = x < n;
+      unsigned bin = 0, w = 0;
+      if (in) {
+        const u64 k = key[x];
+        const u64 kk = up ? (k << up) : (k >> shift);
+        in = k != RM_NO_REQ && (kk >> RM_SEL_BITS) == prefix;
+        bin = (unsigned)kk & (RM_SEL_BINS - 1);
+        if (in) w = (unsigned)t.edge_len[x];
+      }
+      const unsigned act = __ballot_sync(0xffffffffu, in);
+      if (act == 0) continue;
+      const int lead = __ffs(act) - 1;
+      const unsigned b0 = __shfl_sync(0xffffffffu, bin, lead);
+      if (__all_sync(0xffffffffu, !in || bin == b0)) {
+        const unsigned tot = __reduce_add_sync(0xffffffffu, w);
+        if ((int)(threadIdx.x & 31) == lead) atomicAdd(&sh[b0], tot);
+      } else if (in) {
+        atomicAdd(&sh[bin], w);
+      }
+    }
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < RM_SEL_BINS; b += RM_MT_TPB) {
+    const unsigned v = sh[b];
+    if (v) atomicAdd(&hw[b], (u64)v);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last_s = atomicAdd(&st->done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last_s) return;
+  __threadfence();
+  // the pick: exclusive scan of the 4096 weights over the block, RM_SEL_BPT consecutive bins per thread
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) found_s = 0;
+  const i64 need = st->need;
+  i64 wv[RM_SEL_BPT];
+  i64 mine = 0;
+#pragma unroll
+  for (int j = 0; j < RM_SEL_BPT; ++j) {
+    wv[j] = (i64)__ldcg(&hw[RM_SEL_BPT * threadIdx.x + j]);
+    mine += wv[j];
+  }
+  i64 inc = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const i64 o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) wtot[wid] = inc;
+  __syncthreads();
+  i64 before = inc - mine;
+  for (int w = 0; w < wid; ++w) before += wtot[w];
+  if (!all && before < need && before + mine >= need) {     // the crossing is inside my bins
+    i64 run = before;
+    int j = 0;
+#pragma unroll
+    for (int j2 = 0; j2 < RM_SEL_BPT; ++j2) {
+      if (j == j2 && run + wv[j2] < need) {
+        run += wv[j2];
+        ++j;
+      }
+    }
+    st->need = need - run;
+    st->prefix = (prefix << RM_SEL_BITS) | (u64)(RM_SEL_BPT * threadIdx.x + j);
+    found_s = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (!all && !found_s) st->all = 1;
+    st->done = 0;
+  }
+#pragma unroll
+  for (int j = 0; j < RM_SEL_BPT; ++j) hw[RM_SEL_BPT * threadIdx.x + j] = 0;
+}
+#endif
+
 // the leaves at or below K0 (K0 = the full prefix after the last level; shift_out drops padding bits of the last digit)
 __global__ void rm_evict_sel_compact_kernel(RmTree t, const u64* __restrict__ key, int n, const RmEvictSel* st, int pad_bits,
                                             u64* __restrict__ skey, unsigned* __restrict__ sval) {
@@ -454,8 +560,18 @@ __global__ void rm_evict_climb_kernel(RmTree t, int n, int depth_bits, const int
 
 // One block: walk the sorted candidates in chunks, prefix-sum their value lengths, stop at the first
 // position where the running total reaches num_tokens.  Writes the count to ctr->evict_n.
-__global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int n,
+__global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, const unsigned* __restrict__ sval, int m_bound,
                                     i64 num_tokens, int cap) {
+  // the candidate count stays on the device; more candidates than were sorted (or nodes the pass did not look at):
+  // nothing is evicted and the host repeats the call with exact sizes
+  const int n = t.ctr->ev_total;
+  if (t.ctr->ev_over != 0 || n > m_bound) {
+    if (threadIdx.x == 0) {
+      t.ctr->evict_n = 0;
+      t.ctr->ev_over = 1;
+    }
+    return;
+  }
 #ifdef RM_EMU
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   i64 run = 0;
@@ -466,6 +582,9 @@ __global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, cons
   }
   t.ctr->evict_n = k;
 #else
+  // RM_CUT_PER consecutive candidates per thread: a usual call (a few thousand candidates) is one round of the block
+  // (one candidate per thread: four block barriers per 1024 candidates, 11 us)
+#define RM_CUT_PER 8
   __shared__ i64 warp_tot[32];
   __shared__ i64 carry_s;
   __shared__ int cut_s;
@@ -476,12 +595,20 @@ __global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, cons
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int lim = min(n, cap);
-  for (int base = 0; base < lim; base += 1024) {
+  for (int base = 0; base < lim; base += 1024 * RM_CUT_PER) {
     const i64 carry = carry_s;
-    const int j = base + threadIdx.x;
-    const bool ok = j < lim && skey[j] != RM_NO_REQ;
-    const i64 v = ok ? (i64)t.edge_len[sval[j]] : 0;
-    i64 inc = v;
+    const int j0 = base + (int)threadIdx.x * RM_CUT_PER;
+    i64 v[RM_CUT_PER];
+    bool ok[RM_CUT_PER];
+    i64 sum = 0;
+#pragma unroll
+    for (int c = 0; c < RM_CUT_PER; ++c) {
+      const int j = j0 + c;
+      ok[c] = j < lim && skey[j] != RM_NO_REQ;
+      v[c] = ok[c] ? (i64)t.edge_len[sval[j]] : 0;
+      sum += v[c];
+    }
+    i64 inc = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       i64 o = __shfl_up_sync(0xffffffffu, inc, d);
@@ -499,15 +626,21 @@ __global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, cons
       warp_tot[lane] = winc - w;
     }
     __syncthreads();
-    const i64 incl = carry + warp_tot[wid] + inc;   // running total including candidate j
-    // the list ends at the first non-candidate; the cut falls after the first candidate whose
-    // running total reaches num_tokens
+    // the list ends at the first non-candidate; the cut falls after the first candidate whose running total
+    // reaches num_tokens
+    i64 run = carry + warp_tot[wid] + inc - sum;    // total before this thread's candidates
     int mycut = RM_INT_MAX;
-    if (!ok) mycut = j;
-    else if (incl >= num_tokens) mycut = j + 1;
+#pragma unroll
+    for (int c = 0; c < RM_CUT_PER; ++c) {
+      if (mycut == RM_INT_MAX) {
+        run += v[c];
+        if (!ok[c]) mycut = j0 + c;
+        else if (run >= num_tokens) mycut = j0 + c + 1;
+      }
+    }
     if (mycut != RM_INT_MAX) atomicMin(&cut_s, mycut);
     __syncthreads();
-    if (threadIdx.x == 1023) carry_s = incl;
+    if (threadIdx.x == 1023) carry_s = carry + warp_tot[wid] + inc;
     const int cut = cut_s;
     __syncthreads();
     if (cut != RM_INT_MAX) break;
@@ -519,12 +652,8 @@ __global__ void rm_evict_cut_kernel(RmTree t, const u64* __restrict__ skey, cons
 // G lanes per evicted node: lane 0 does the bookkeeping, all lanes clear the owner words of the run (a thread clearing
 // its ~230 words alone made this kernel 42 us for 4 K nodes: 41 stalls per issue on the store queue)
 template <int G>
-__global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sval, const u64* __restrict__ eff,
-                                      int* out_nodes, i64* out_offs, int* out_lens) {
-  RmGroup<G> g;
-  const int n = t.ctr->evict_n;
-  const int k = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
-  if (k >= n) return;
+__device__ __forceinline__ void rm_evict_apply_one(RmTree& t, RmGroup<G>& g, int k, const unsigned* __restrict__ sval,
+                                                   const u64* __restrict__ eff, int* out_nodes, i64* out_offs, int* out_lens) {
   const int x = (int)sval[k];
   const int par = t.parent[x];
   const i64 off = t.edge_off[x];
@@ -552,23 +681,29 @@ __global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sva
   t.free_ids[pos % (u64)t.max_nodes] = x;
 }
 
+template <int G>
+__global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sval, const u64* __restrict__ eff,
+                                      int* out_nodes, i64* out_offs, int* out_lens) {
+  RmGroup<G> g;
+  const int n = t.ctr->evict_n;
+  const int stride = (int)((gridDim.x * (unsigned)blockDim.x) / G);       // the grid is sized from a bound, not from n
+  for (int k = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G); k < n; k += stride)
+    rm_evict_apply_one<G>(t, g, k, sval, eff, out_nodes, out_offs, out_lens);
+}
+
 static int rm_bits_for(u64 v) {
   int b = 1;
   while ((v >> b) != 0 && b < 63) ++b;
   return b;
 }
 
-int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
-                    int* out_n_h, cudaStream_t s) {
+// One pass of rm_evict over the nodes [0, n) with room for m_bound candidates in the exact sort: every count the
+// kernels need stays on the device, and the host synchronises once, for the results.  Bounds that turn out too small
+// (c.ev_over) leave the tree untouched.
+static int rm_evict_pass(rm_index* idx, int n, int m_bound, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h,
+                         int* out_lens_h, RmCounters& c, cudaStream_t s) {
   RmTree& t = idx->t;
   RmScratch& sc = idx->sc;
-  idx->op_seq += 1;   // evict is one operation of the logical clock (it stamps nothing)
-  RmCounters c;
-  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
-  RM_CUDA(cudaStreamSynchronize(s));
-  const int n = c.node_hwm;
-  *out_n_h = 0;
-  if (n <= 1 || num_tokens <= 0 || cap <= 0) return RM_OK;
   const int depth_bits = idx->len_bits;
   const int bits = rm_bits_for(idx->op_seq * 2 + 1) + depth_bits + 1;
   int* pinned = sc.ev_lens;   // free until rm_evict_apply_kernel writes the evicted lengths
@@ -579,58 +714,85 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
   const int cut_tpb = 1024;
 #endif
   RM_CUDA(cudaMemsetAsync(pinned, 0, sizeof(int) * (size_t)n, s));
-  RM_LAUNCH(rm_evict_pin_kernel, grid_n, RM_MT_TPB, s, t, n, pinned);
   RM_CUDA(cudaMemsetAsync(sc.ev_rem, 0, sizeof(int) * (size_t)n, s));
-  RM_LAUNCH(rm_evict_count_kernel, grid_n, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem);
+  RM_LAUNCH(rm_evict_count_kernel, grid_n, RM_MT_TPB, s, t, n, sc.ev_eff, sc.ev_rem, pinned);
   RM_LAUNCH(rm_evict_keys_kernel, grid_n, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_rem, sc.ev_key[0], sc.ev_val[0]);
   // 1. frontier key by weighted radix select over the leaves' keys, 2. the leaves at or below it, compacted
   RmEvictSel* st = reinterpret_cast<RmEvictSel*>(sc.ev_selw + RM_SEL_BINS);
   const int levels = (bits + RM_SEL_BITS - 1) / RM_SEL_BITS;
   const int pad_bits = levels * RM_SEL_BITS - bits;                 // the key is padded at the LOW end of the last digit
-  RM_LAUNCH(rm_evict_sel_init_kernel, 1, RM_MT_TPB, s, st, num_tokens, sc.ev_selw, sc.ev_selc);
+  RM_LAUNCH(rm_evict_sel_init_kernel, 1, RM_MT_TPB, s, t, n, st, num_tokens, sc.ev_selw, sc.ev_selc);
+#ifndef RM_EMU
+  // blocks of the select: four per SM, more when a block's share of the keys times the longest edge would not fit
+  // its 32-bit shared bins
+  int sel_grid = grid_n < 148 * 4 ? grid_n : 148 * 4;
+  {
+    long long per_block = (1ll << 31) / (long long)(t.max_key_len > 0 ? t.max_key_len : 1);
+    if (per_block < RM_MT_TPB) per_block = RM_MT_TPB;
+    const long long need_blocks = ((long long)n + per_block - 1) / per_block;
+    if (need_blocks > sel_grid) sel_grid = (int)(need_blocks < grid_n ? need_blocks : grid_n);
+  }
+#endif
   for (int l = 0; l < levels; ++l) {
     const int shift = (levels - 1 - l) * RM_SEL_BITS - pad_bits;    // may be negative on the last level: keys are shifted up instead
+#ifdef RM_EMU
     RM_LAUNCH(rm_evict_sel_hist_kernel, grid_n, RM_MT_TPB, s, t, sc.ev_key[0], n, shift >= 0 ? shift : 0, shift >= 0 ? 0 : -shift, st,
               sc.ev_selw);
     RM_LAUNCH(rm_evict_sel_pick_kernel, 1, RM_SEL_PICK_TPB, s, st, sc.ev_selw, sc.ev_selc);
+#else
+    RM_LAUNCH(rm_evict_sel_level_kernel, sel_grid, RM_MT_TPB, s, t, sc.ev_key[0], n, shift >= 0 ? shift : 0,
+              shift >= 0 ? 0 : -shift, st, sc.ev_selw);
+#endif
   }
-  RM_CUDA(cudaMemsetAsync(&t.ctr->ev_total, 0, sizeof(int), s));
   int w = 1;
   RM_LAUNCH(rm_evict_sel_compact_kernel, grid_n, RM_MT_TPB, s, t, sc.ev_key[0], n, st, pad_bits, sc.ev_key[w], sc.ev_val[w]);
   RM_LAUNCH(rm_evict_sel_seal_kernel, 1, 1, s, t);
-  // 3. climb (the leaf count stays on the device), 4. exact order and cut over the candidates
+  // 3. climb, 4. exact order and cut over the candidates: ctr->ev_total of them, at most m_bound sorted
   RM_LAUNCH(rm_evict_climb_kernel, grid_n, RM_MT_TPB, s, t, n, depth_bits, pinned, sc.ev_eff, sc.ev_rem, sc.ev_key[w], sc.ev_val[w], n);
-  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
-  RM_CUDA(cudaStreamSynchronize(s));
-  const int m_all = c.ev_total < n ? c.ev_total : n;
-  if (m_all <= 0) return RM_OK;
   {
-    const int w2 = rm_sort_pairs(sc.ev_key[w], sc.ev_val[w], sc.ev_key[w ^ 1], sc.ev_val[w ^ 1], m_all, bits, sc.ev_hist, s);
+    const int w2 = rm_sort_pairs(sc.ev_key[w], sc.ev_val[w], sc.ev_key[w ^ 1], sc.ev_val[w ^ 1], m_bound, bits, sc.ev_hist, s,
+                                 &t.ctr->ev_total);
     w ^= w2;
   }
-  RM_LAUNCH(rm_evict_cut_kernel, 1, cut_tpb, s, t, sc.ev_key[w], sc.ev_val[w], m_all, num_tokens, cap);
+  RM_LAUNCH(rm_evict_cut_kernel, 1, cut_tpb, s, t, sc.ev_key[w], sc.ev_val[w], m_bound, num_tokens, cap);
   // outputs are staged in the other ping-pong buffer (large enough: n entries of 8/4 bytes)
   int* d_nodes = reinterpret_cast<int*>(sc.ev_val[w ^ 1]);
   i64* d_offs = reinterpret_cast<i64*>(sc.ev_key[w ^ 1]);
   int* d_lens = sc.ev_lens;
-  const int lim = min(m_all, cap);
+  const int lim = min(m_bound, cap);
 #ifdef RM_EMU
   RM_LAUNCH(rm_evict_apply_kernel<1>, (lim + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, t, sc.ev_val[w], sc.ev_eff, d_nodes, d_offs,
             d_lens);
 #else
-  RM_LAUNCH(rm_evict_apply_kernel<32>, (int)(((long long)lim * 32 + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, t, sc.ev_val[w],
-            sc.ev_eff, d_nodes, d_offs, d_lens);
+  {
+    // a warp per evicted node, over a grid that covers a usual call (a few thousand nodes) in one round
+    const long long want = ((long long)lim * 32 + RM_MT_TPB - 1) / RM_MT_TPB;
+    const int grid = (int)(want < 148 * 16 ? want : 148 * 16);
+    RM_LAUNCH(rm_evict_apply_kernel<32>, grid, RM_MT_TPB, s, t, sc.ev_val[w], sc.ev_eff, d_nodes, d_offs, d_lens);
+  }
 #endif
   RM_CUDA(cudaGetLastError());
-  // the count and the first results travel together: one synchronisation for the usual call (a few thousand nodes)
-  const int first = lim < 8192 ? lim : 8192;
-  RM_CUDA(cudaMemcpyAsync(&c, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
+  // the count and the first results travel together through pinned memory: one synchronisation for the usual call
+  const int first = lim < RM_EVICT_FIRST ? lim : RM_EVICT_FIRST;
+  char* mail = static_cast<char*>(idx->mail);
+  int* m_nodes = reinterpret_cast<int*>(mail + 4096);
+  int* m_lens = m_nodes + RM_EVICT_FIRST;
+  i64* m_offs = reinterpret_cast<i64*>(m_lens + RM_EVICT_FIRST);
+  RM_CUDA(cudaMemcpyAsync(mail, t.ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
   if (first > 0) {
-    RM_CUDA(cudaMemcpyAsync(out_nodes_h, d_nodes, sizeof(int) * first, cudaMemcpyDeviceToHost, s));
-    RM_CUDA(cudaMemcpyAsync(out_offs_h, d_offs, sizeof(i64) * first, cudaMemcpyDeviceToHost, s));
-    RM_CUDA(cudaMemcpyAsync(out_lens_h, d_lens, sizeof(int) * first, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(m_nodes, d_nodes, sizeof(int) * first, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(m_lens, d_lens, sizeof(int) * first, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaMemcpyAsync(m_offs, d_offs, sizeof(i64) * first, cudaMemcpyDeviceToHost, s));
   }
   RM_CUDA(cudaStreamSynchronize(s));
+  memcpy(&c, mail, sizeof(c));
+  if (!c.ev_over) {
+    const int got = c.evict_n < first ? c.evict_n : first;
+    memcpy(out_nodes_h, m_nodes, sizeof(int) * (size_t)got);
+    memcpy(out_lens_h, m_lens, sizeof(int) * (size_t)got);
+    memcpy(out_offs_h, m_offs, sizeof(i64) * (size_t)got);
+  }
+  if (c.ev_over) return RM_OK;
   const int k = c.evict_n;
   if (k > first) {
     RM_CUDA(cudaMemcpyAsync(out_nodes_h + first, d_nodes + first, sizeof(int) * (k - first), cudaMemcpyDeviceToHost, s));
@@ -638,7 +800,40 @@ int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i6
     RM_CUDA(cudaMemcpyAsync(out_lens_h + first, d_lens + first, sizeof(int) * (k - first), cudaMemcpyDeviceToHost, s));
     RM_CUDA(cudaStreamSynchronize(s));
   }
-  *out_n_h = k;
+  return RM_OK;
+}
+
+// Candidates the first pass sorts: an eviction that frees a few batches' worth of tokens takes a few thousand nodes
+#define RM_EVICT_M_OPT 65536
+
+int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
+                    int* out_n_h, cudaStream_t s) {
+  RmTree& t = idx->t;
+  idx->op_seq += 1;   // evict is one operation of the logical clock (it stamps nothing)
+  *out_n_h = 0;
+  if (num_tokens <= 0 || cap <= 0) return RM_OK;
+  // No question to the device before the work: the node high-water mark is bounded from the last exact reading (an
+  // operation of the logical clock creates at most three nodes: split, leaf, parked copy), the candidate count by
+  // RM_EVICT_M_OPT (environment override: tests force the second pass).  The pass checks both on the device and
+  // evicts nothing if either was too small; the call then runs again with exact sizes.
+  long long nb = (long long)idx->hwm_exact + 3ll * (long long)(idx->op_seq - idx->hwm_seq);
+  if (nb > t.max_nodes) nb = t.max_nodes;
+  int n = (int)nb;
+  if (n <= 1) return RM_OK;
+  RmCounters c;
+  int m_opt = RM_EVICT_M_OPT;
+  if (const char* e = getenv("RM_EVICT_M_OPT")) m_opt = atoi(e) > 1 ? atoi(e) : 2;
+  int rc = rm_evict_pass(idx, n, n < m_opt ? n : m_opt, num_tokens, cap, out_nodes_h, out_offs_h, out_lens_h, c, s);
+  if (rc != RM_OK) return rc;
+  if (c.ev_over) {
+    n = c.node_hwm;
+    rc = rm_evict_pass(idx, n, n, num_tokens, cap, out_nodes_h, out_offs_h, out_lens_h, c, s);
+    if (rc != RM_OK) return rc;
+    if (c.ev_over) return RM_E_NOSPACE;   // not reachable: the sizes were exact
+  }
+  idx->hwm_exact = c.node_hwm;
+  idx->hwm_seq = idx->op_seq;
+  *out_n_h = c.evict_n;
   if ((u64)c.n_tomb * 4 > (u64)t.table_mask + 1) return rm_table_rebuild(idx, c.node_hwm, s);
   return RM_OK;
 }

@@ -408,6 +408,14 @@ static __global__ void __launch_bounds__(RM_SORT_TPB) rm_sort_fused_kernel(u64* 
   rm_grid_dependency_wait();     // RM_LAUNCH_PDL: the producer of the items may still be running
   const int n = n_dev ? min(*n_dev, n_max) : n_max;
   if (n <= 0) return;
+  if (n_dev) {
+    // the grid was sized from the bound n_max; the tile follows the real count (rm_sort_tile), but never so small
+    // that the grid could not hold the tiles
+    int tl = ((n + 147) / 148 + RM_SORT_MIN_TILE - 1) / RM_SORT_MIN_TILE * RM_SORT_MIN_TILE;
+    const int need = ((n + (int)gridDim.x - 1) / (int)gridDim.x + RM_SORT_MIN_TILE - 1) / RM_SORT_MIN_TILE * RM_SORT_MIN_TILE;
+    tl = max(max(tl, need), RM_SORT_MIN_TILE);
+    tile = min(tl, RM_SORT_MAX_TILE);
+  }
   unsigned arrivals = 0;
   rm_sort_body(k0, v0, k1, v1, n, passes, hist, tile, (int)blockIdx.x, (int)gridDim.x, arrivals);
   if (n > RM_SORT_SOLO) rm_sort_barrier_rearm(hist, (int)gridDim.x);

@@ -30,6 +30,15 @@ def test_emu_streaming_insert_evict_compact(seed):
     cases.run_stream_evict(make_index, seed)
 
 
+@pytest.mark.parametrize("seed", range(4))
+def test_emu_evict_second_pass_with_exact_sizes(seed, monkeypatch):
+    """rm_evict sorts at most RM_EVICT_M_OPT candidates without asking the device for the count; with more it must
+    leave the tree alone and run again with exact sizes (forced here by a bound of 2 candidates)."""
+    monkeypatch.setenv("RM_EVICT_M_OPT", "2")
+    cases.run_split_evict(make_index, 40 + seed)
+    cases.run_stream_evict(make_index, 40 + seed)
+
+
 @pytest.mark.parametrize("seed", range(2))
 def test_emu_cold_batches_are_applied_in_chunks(seed):
     cases.run_cold_batch(make_index, seed)

@@ -28,6 +28,15 @@ def test_gpu_batched_match_splits_then_evict_order(seed):
     cases.run_split_evict(make_index, seed)
 
 
+@pytest.mark.parametrize("seed", range(3))
+def test_gpu_evict_second_pass_with_exact_sizes(seed, monkeypatch):
+    """rm_evict sizes its sort from a bound on the candidate count and keeps the count on the device; with more
+    candidates than the bound it must evict nothing and run again with exact sizes (forced: a bound of 2)."""
+    monkeypatch.setenv("RM_EVICT_M_OPT", "2")
+    cases.run_split_evict(make_index, 40 + seed)
+    cases.run_stream_evict(make_index, 40 + seed)
+
+
 WALKS = [("run", 4), ("run", 8), ("run", 16), ("run", 32), ("table", 2), ("table", 8), ("table", 32)]
 
 
