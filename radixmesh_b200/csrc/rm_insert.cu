@@ -390,8 +390,10 @@ __device__ __forceinline__ bool rm_ins_differs(const RmTree& t, const RmGroup<G>
 template <int G, int MESH>
 __global__ void __launch_bounds__(RM_INS_TPB)
 rm_insert_classify_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__ rval, const i64* __restrict__ roff,
-                          const int* __restrict__ rrank, int N, const int* __restrict__ xnode, int* __restrict__ c0s,
-                          int* __restrict__ mark) {
+                          const int* __restrict__ rrank, int N, const int* __restrict__ xnode, int* __restrict__ wn,
+                          int* __restrict__ low, int* __restrict__ mark) {
+  // wn[r]: the SHALLOWEST node at which record r would replace a stored value, as the tree stands before the batch
+  // (0: nowhere); low[r]: the deepest node it touches (the child it leaves the tree on, else xnode[r])
   RmGroup<G> g;
   const int r = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
   if (r >= N) return;
@@ -401,8 +403,7 @@ rm_insert_classify_kernel(RmTree t, const int* __restrict__ rtok, const i64* __r
   const i64* __restrict__ val = (MESH == 2) ? nullptr : (rval + o);
   const int owner = rrank ? rrank[r] : t.self_rank;
   const int x = xnode[r];
-  int c0 = 0;
-  bool swap = false;
+  int w = 0, lo = x;
   if (n <= t.max_key_len) {
     const int pos = x > 0 ? t.depth_end[x] : 0;
     if (pos < n) {                       // the edge the record leaves the tree on, matched in part
@@ -436,64 +437,66 @@ rm_insert_classify_kernel(RmTree t, const int* __restrict__ rtok, const i64* __r
             }
           }
         }
-        if (diff && srank > owner) swap = true;
-        if (x == 0) c0 = sl.child;
+        lo = sl.child;
+        if (diff && srank > owner) w = sl.child;
       }
     }
-    for (int v = x; v > 0;) {            // the nodes it matched in full, bottom-up
-      if (!swap && rm_ins_differs<G, MESH>(t, g, v, val, owner) && t.rank[v] > owner) swap = true;
-      const int par = t.parent[v];
-      if (par == 0) c0 = v;
-      v = par;
-    }
+    for (int v = x; v > 0; v = t.parent[v])      // the nodes it matched in full, bottom-up: the last hit is the shallowest
+      if (t.rank[v] > owner && rm_ins_differs<G, MESH>(t, g, v, val, owner)) w = v;
   }
   if (g.lane == 0) {
-    c0s[r] = c0;
-    if (swap && c0 > 0) mark[c0] = 1;
+    wn[r] = w;
+    low[r] = lo;
+    if (w > 0) mark[w] = 1;
   }
 }
 
-// group keys after the classification: bit 40 | first token for the groups that stay on the ordered path,
-// else the hash of (divergence node, next token) + 1, or 0 when the whole key is in the tree already
+// Group keys after the classification.  T = the shallowest MARKED node on the record's path (a node where some record
+// of the batch replaces the stored value): from T down, what the record finds depends on the records before it, so it
+// starts at T's parent, through T's first token - together with every other record that reaches T, whose path holds
+// the same T, and with the records that leave the tree inside T's edge, whose divergence point is that same (parent,
+// token).  A record with no marked node on its path starts at its divergence node as before.  Key: hash of (start
+// node, next token) + 1, or 0 when there is nothing to do (whole key in the tree, nothing replaced on the way).
 __global__ void rm_insert_keys3_kernel(RmTree t, const int* __restrict__ tok, const i64* __restrict__ off, int N,
-                                       const int* __restrict__ xnode, const int* __restrict__ c0s, const int* __restrict__ mark,
-                                       u64* __restrict__ key, unsigned* __restrict__ val, int* __restrict__ out_prefix,
-                                       unsigned char* __restrict__ ordered) {
+                                       int* __restrict__ xnode, const int* __restrict__ low, const int* __restrict__ mark,
+                                       u64* __restrict__ key, unsigned* __restrict__ val, int* __restrict__ out_prefix) {
   int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= N) return;
   const i64 o = off[r];
   const int n = (int)(off[r + 1] - o);
-  const int c0 = c0s[r];
   u64 k = 0;
-  const bool slow = c0 > 0 && mark[c0] != 0;
-  if (slow) {
-    k = (1ull << 40) | (u64)(unsigned)tok[o];
+  if (n > t.max_key_len) {
+    k = (1ull << 40) | (1ull << 33);              // error record: the kernel reports it
+    atomicAdd(&t.ctr->ins_resumed, 1ull);
   } else {
-    const int x = xnode[r];
+    int top = 0;
+    for (int v = low[r]; v > 0; v = t.parent[v])
+      if (mark[v]) top = v;
+    const int x = top > 0 ? t.parent[top] : xnode[r];
     const int pos = x > 0 ? t.depth_end[x] : 0;
-    if (n > t.max_key_len) k = (1ull << 40) | (1ull << 33);              // error record: the kernel reports it
-    else if (pos < n) k = 1ull + (u64)(rm_hash2((unsigned)x, (unsigned)tok[o + pos], 0) >> 12);
+    if (pos < n) k = 1ull + (u64)(rm_hash2((unsigned)x, (unsigned)tok[o + pos], 0) >> 12);
     else out_prefix[r] = n;
+    xnode[r] = x;                                 // from here on: the node the record starts at
+    atomicAdd(top > 0 ? &t.ctr->ins_ordered : &t.ctr->ins_resumed, 1ull);
   }
-  ordered[r] = slow ? 1 : 0;
-  atomicAdd(slow ? &t.ctr->ins_ordered : &t.ctr->ins_resumed, 1ull);
   key[r] = k;
   val[r] = (unsigned)r;
 }
 
-__global__ void rm_insert_unmark_kernel(int N, const int* __restrict__ c0s, int* __restrict__ mark) {
+__global__ void rm_insert_unmark_kernel(int N, const int* __restrict__ wn, int* __restrict__ mark) {
   int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r < N && c0s[r] > 0) mark[c0s[r]] = 0;
+  if (r < N && wn[r] > 0) mark[wn[r]] = 0;
 }
 
-// losses of the resumed records, booked on the tree as the apply left it (see above)
+// losses on the nodes ABOVE a record's start node (none of them is replaced by this batch), booked on the tree as the
+// apply left it (see above)
 template <int G, int MESH>
 __global__ void __launch_bounds__(RM_INS_TPB)
 rm_insert_lost_kernel(RmTree t, const i64* __restrict__ rval, const i64* __restrict__ roff, const int* __restrict__ rrank,
-                      int N, const int* __restrict__ xnode, const unsigned char* __restrict__ ordered, u64 seq_base) {
+                      int N, const int* __restrict__ xnode, u64 seq_base) {
   RmGroup<G> g;
   const int r = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
-  if (r >= N || ordered[r]) return;
+  if (r >= N) return;
   const i64 o = roff[r];
   const int n = (int)(roff[r + 1] - o);
   if (n > t.max_key_len) return;
@@ -534,14 +537,21 @@ int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const 
   // (short keys have nothing long to re-walk: a batch known to average under 64 tokens per record is applied whole)
   const bool short_keys = idx->hint_tokens > 0 && idx->hint_tokens < 64ll * N;
   idx->hint_tokens = 0;
-  const bool cold = N > RM_COLD_CHUNK && idx->ins_records < 2ull * (u64)N && !short_keys;
+  const u64 seen0 = idx->ins_records;
+  const bool cold = N > RM_COLD_CHUNK && seen0 < 2ull * (u64)N && !short_keys;
   idx->ins_records += (u64)N;
   if (!cold) return rm_launch_insert_one(idx, tokens, values, offsets, ranks, N, out_prefix_len, s);
-  for (int a = 0; a < N; a += RM_COLD_CHUNK) {
-    const int n = N - a < RM_COLD_CHUNK ? N - a : RM_COLD_CHUNK;
+  // a chunk is as large as what the tree has already seen (256, 256, 512, 1024, ...): the documents' paths are there
+  // after a few hundred records, and every chunk costs a fixed ~0.15 ms of launches
+  static const bool grow = !(getenv("RM_COLD_GROW") && atoi(getenv("RM_COLD_GROW")) == 0);
+  for (int a = 0; a < N;) {
+    u64 want = grow ? seen0 + (u64)a : (u64)RM_COLD_CHUNK;
+    if (want < RM_COLD_CHUNK) want = RM_COLD_CHUNK;
+    const int n = (u64)(N - a) < want ? N - a : (int)want;
     // offsets are absolute positions in tokens / values: a chunk is a window of the offsets, ranks and outputs
     int rc = rm_launch_insert_one(idx, tokens, values, offsets + a, ranks ? ranks + a : nullptr, n, out_prefix_len + a, s);
     if (rc) return rc;
+    a += n;
   }
   return RM_OK;
 }
@@ -573,21 +583,21 @@ static int rm_launch_insert_one(rm_index* idx, const int* tokens, const i64* val
   // mesh modes: pre-pass, conflict classification, one launch for both kinds of groups, losses of the resumed ones
   int* xnode = sc.krank;
   int* xlen = sc.uniq_pos;
-  int* c0s = reinterpret_cast<int*>(sc.uniq_min);
-  unsigned char* ordered = reinterpret_cast<unsigned char*>(sc.sufmax);
+  int* wn = reinterpret_cast<int*>(sc.uniq_min);
+  int* low = reinterpret_cast<int*>(sc.sufmax);
   int rc = rm_launch_walk_records(idx, tokens, offsets, N, seq_base, xlen, xnode, s);
   if (rc) return rc;
   const bool router = idx->cfg.mode == RM_MODE_ROUTER;
   if (router) {
     auto kc = rm_insert_classify_kernel<RM_INS_G, 2>;
-    RM_LAUNCH(kc, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, xnode, c0s, sc.ins_mark);
+    RM_LAUNCH(kc, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, xnode, wn, low, sc.ins_mark);
   } else {
     auto kc = rm_insert_classify_kernel<RM_INS_G, 1>;
-    RM_LAUNCH(kc, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, xnode, c0s, sc.ins_mark);
+    RM_LAUNCH(kc, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, xnode, wn, low, sc.ins_mark);
   }
-  RM_LAUNCH(rm_insert_keys3_kernel, (N + 255) / 256, 256, s, idx->t, tokens, offsets, N, xnode, c0s, sc.ins_mark, sc.key[0],
-            sc.val[0], out_prefix_len, ordered);
-  RM_LAUNCH(rm_insert_unmark_kernel, (N + 255) / 256, 256, s, N, c0s, sc.ins_mark);
+  RM_LAUNCH(rm_insert_keys3_kernel, (N + 255) / 256, 256, s, idx->t, tokens, offsets, N, xnode, low, sc.ins_mark, sc.key[0],
+            sc.val[0], out_prefix_len);
+  RM_LAUNCH(rm_insert_unmark_kernel, (N + 255) / 256, 256, s, N, wn, sc.ins_mark);
   RM_CUDA(cudaGetLastError());
   const int w = rm_sort_pairs(sc.key[0], sc.val[0], sc.key[1], sc.val[1], N, 41, sc.hist, s);
   RM_CUDA(cudaGetLastError());
@@ -596,13 +606,13 @@ static int rm_launch_insert_one(rm_index* idx, const int* tokens, const i64* val
     RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base,
               out_prefix_len, xnode);
     auto kl = rm_insert_lost_kernel<RM_INS_G, 2>;
-    RM_LAUNCH(kl, grid, RM_INS_TPB, s, idx->t, values, offsets, ranks, N, xnode, ordered, seq_base);
+    RM_LAUNCH(kl, grid, RM_INS_TPB, s, idx->t, values, offsets, ranks, N, xnode, seq_base);
   } else {
     auto k = rm_insert_kernel<RM_INS_G, 1>;
     RM_LAUNCH(k, grid, RM_INS_TPB, s, idx->t, tokens, values, offsets, ranks, N, sc.key[w], sc.val[w], seq_base,
               out_prefix_len, xnode);
     auto kl = rm_insert_lost_kernel<RM_INS_G, 1>;
-    RM_LAUNCH(kl, grid, RM_INS_TPB, s, idx->t, values, offsets, ranks, N, xnode, ordered, seq_base);
+    RM_LAUNCH(kl, grid, RM_INS_TPB, s, idx->t, values, offsets, ranks, N, xnode, seq_base);
   }
   RM_CUDA(cudaGetLastError());
   return RM_OK;

@@ -8,8 +8,8 @@ packed arrays in ONE exchange and every replica applies the same ordered batches
     stage()               local inserts of this rank (owner rank = this rank), packed on the host (IngestBuffer)
     exchange_and_apply()  all-gather of (records, tokens) counts, then of the padded token / value / length arrays;
                           every rank applies the records of rank 0, 1, ..., W-1 in that order, each rank's records in
-                          their local order, through rm_insert_batch (device pointers, the conflict rule of
-                          radix_mesh.py:273-323 on the device).
+                          their local order, as ONE ordered batch through rm_insert_batch (device pointers, owner rank
+                          per record, the conflict rule of radix_mesh.py:273-323 on the device).
 
 All replicas see one total order, so they end identical (the ring gives every node a different interleaving and
 relies on the lowest-rank-wins rule to converge; the same rule runs here, the order is just no longer a variable).
@@ -83,27 +83,28 @@ class NvlinkOplogExchange:
             _as_torch(g_tok).copy_(_as_torch(d_tok))
             _as_torch(g_val).copy_(_as_torch(d_val))
             _as_torch(g_len).copy_(_as_torch(d_len))
-        t_len = _as_torch(g_len)
-        for r in range(W):
-            n_r = int(cnt[r, 0])
-            if n_r == 0:
-                continue
-            # offsets of rank r's records inside its slice: exclusive prefix sum of its lengths, on the device
-            l_r = t_len[r * s_len.size:r * s_len.size + n_r].to(torch.int64)
-            o_r = torch.zeros(n_r + 1, dtype=torch.int64, device=l_r.device)
-            torch.cumsum(l_r, 0, out=o_r[1:])
-            ranks = torch.full((n_r,), r, dtype=torch.int32, device=l_r.device)
-            tok_r = _as_torch(g_tok)[r * s_tok.size:(r + 1) * s_tok.size]
-            val_r = _as_torch(g_val)[r * s_val.size:(r + 1) * s_val.size]
-            step = min(int(ix.cfg.max_batch) for ix in self.ixs)
-            for a in range(0, n_r, step):
-                b = min(a + step, n_r)
-                o_ab = (o_r[a:b + 1] - o_r[a]).contiguous()
-                lo = int(o_r[a].item()) if a else 0
-                out = torch.empty(b - a, dtype=torch.int32, device=l_r.device)
-                for ix in self.ixs:
-                    v = None if ix.mode == capi.MODE_ROUTER else self._arr(val_r[lo:])
-                    ix.insert(self._arr(tok_r[lo:]), v, self._arr(o_ab), self._arr(ranks[a:b]), b - a, self._arr(out))
+        # One ordered batch out of the W padded slices (rank 0's records, then rank 1's, ...): the true counts select
+        # the live part of every slice, the record offsets are one prefix sum, and the index takes the owner rank per
+        # record - so a round is ceil(total / max_batch) insert calls instead of one (or more) per rank.
+        dev = _as_torch(g_len).device
+        n_rec = torch.as_tensor(cnt[:, 0], device=dev)
+        n_tok = torch.as_tensor(cnt[:, 1], device=dev)
+        live_rec = torch.arange(s_len.size, device=dev)[None, :] < n_rec[:, None]
+        live_tok = torch.arange(s_tok.size, device=dev)[None, :] < n_tok[:, None]
+        lens_all = _as_torch(g_len).view(W, s_len.size)[live_rec].to(torch.int64)
+        offs_all = torch.zeros(total + 1, dtype=torch.int64, device=dev)
+        torch.cumsum(lens_all, 0, out=offs_all[1:])
+        tok_all = _as_torch(g_tok).view(W, s_tok.size)[live_tok]
+        val_all = _as_torch(g_val).view(W, s_val.size)[live_tok]
+        ranks_all = torch.repeat_interleave(torch.arange(W, dtype=torch.int32, device=dev), n_rec)
+        out = torch.empty(total, dtype=torch.int32, device=dev)
+        step = min(int(ix.cfg.max_batch) for ix in self.ixs)
+        for a in range(0, total, step):
+            b = min(a + step, total)
+            # offsets are absolute positions in tok_all / val_all (rm_insert_batch takes a window of them)
+            for ix in self.ixs:
+                v = None if ix.mode == capi.MODE_ROUTER else self._arr(val_all)
+                ix.insert(self._arr(tok_all), v, self._arr(offs_all[a:b + 1]), self._arr(ranks_all[a:b]), b - a, self._arr(out[a:b]))
         for ix in self.ixs:
             ix.check_device_error()
         self.applied += total
