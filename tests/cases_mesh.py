@@ -29,14 +29,29 @@ def rings(addrs):
     return pts, own
 
 
-def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7, max_recs=5):
+def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7, max_recs=5, max_batch=64, docs=0):
+    """docs > 0: keys are prefixes of `docs` fixed random strings of maxlen tokens (plus a short tail now and then), so
+    that large batches pile onto a few long shared paths instead of spreading over a bushy tree."""
     rnd = random.Random(seed)
     port = PortMesh(P, D, R)
     ixs = []
+    big = max_batch > 64
+    doc_keys = [[rnd.randrange(vocab) for _ in range(maxlen)] for _ in range(docs)]
+
+    def new_key():
+        if not docs:
+            return [rnd.randrange(vocab) for _ in range(rnd.randrange(1, maxlen))]
+        d = rnd.choice(doc_keys)
+        k = d[:rnd.randrange(1, maxlen + 1)]
+        if rnd.random() < 0.3:
+            k = k + [rnd.randrange(vocab, vocab + 2) for _ in range(rnd.randrange(1, 4))]
+        return k
+
     for r in range(P + D + R):
         mode = MODE_PREFILL if r < P else MODE_DECODE if r < P + D else MODE_ROUTER
-        ixs.append(make_index(mode=mode, self_rank=r, n_prefill=P, n_decode=D, max_nodes=4096, max_tokens=1 << 15,
-                              max_batch=64, max_key_len=64, max_dups=512))
+        ixs.append(make_index(mode=mode, self_rank=r, n_prefill=P, n_decode=D, max_nodes=1 << 16 if big else 4096,
+                              max_tokens=1 << 20 if big else 1 << 15, max_batch=max_batch, max_key_len=64,
+                              max_dups=1 << 15 if big else 512))
     pp, po = rings(port.p_addrs)
     dp, do = rings(port.d_addrs)
     ixs[5].set_rings(pp, po, dp, do)
@@ -47,7 +62,7 @@ def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7, max_recs=
             recs = []
             for _ in range(rnd.randrange(1, max_recs + 1)):
                 rank = rnd.randrange(P + D)
-                key = [rnd.randrange(vocab) for _ in range(rnd.randrange(1, maxlen))]
+                key = new_key()
                 variant = rnd.randrange(2)
                 val = [100 * (rank + 1) * variant + 10 * i + t for i, t in enumerate(key)]
                 recs.append((rank, key, val))

@@ -23,6 +23,13 @@ def test_emu_mesh_big_batches(seed):
     cases_mesh.run_mesh_sequence(make_index, 9000 + seed, n_steps=12, vocab=2 + seed % 2, maxlen=6 + seed % 4, max_recs=48)
 
 
+@pytest.mark.parametrize("seed", range(4))
+def test_emu_mesh_hundreds_of_records_on_shared_paths(seed):
+    """Batches of up to 300 records over four 40-token documents, five owner ranks, two value variants: replacements,
+    losses and splits of one batch land on the same long paths (grouping by the top replaced node, rm_insert.cu)."""
+    cases_mesh.run_mesh_sequence(make_index, 4000 + seed, n_steps=6, vocab=2, maxlen=40, max_recs=300, max_batch=512, docs=4)
+
+
 def test_emu_consistent_hash_vectors():
     """ConsistentHash golden vectors (recorded from the reference) through the MD5 fallback kernel."""
     import numpy as np

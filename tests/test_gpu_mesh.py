@@ -24,6 +24,14 @@ def test_gpu_mesh_binary_vocab(seed):
     cases_mesh.run_mesh_sequence(make_index, 500 + seed, n_steps=30, vocab=2, maxlen=6)
 
 
+@pytest.mark.parametrize("seed", range(6))
+def test_gpu_mesh_hundreds_of_records_on_shared_paths(seed):
+    """Batches of up to 300 records over four 40-token documents, five owner ranks, two value variants: replacements,
+    losses and splits of one batch land on the same long paths, with the groups running side by side on the GPU
+    (grouping by the top replaced node, rm_insert.cu)."""
+    cases_mesh.run_mesh_sequence(make_index, 4000 + seed, n_steps=6, vocab=2, maxlen=40, max_recs=300, max_batch=512, docs=4)
+
+
 @pytest.mark.parametrize("block", dc.golden("correctness_blocks"), ids=lambda b: b["name"])
 def test_gpu_reference_correctness_blocks(block):
     dc.replay_correctness_block(block, {})
