@@ -64,17 +64,17 @@ class NvlinkOplogExchange:
         total = int(cnt[:, 0].sum())
         if total == 0:
             return 0
-        # padded send buffers (the pad is never read: every rank's true counts are known)
-        s_tok = np.zeros(max(max_tok, 1), dtype=np.int32)
-        s_val = np.zeros(max(max_tok, 1), dtype=np.int64)
-        s_len = np.zeros(max(max_rec, 1), dtype=np.int32)
-        s_tok[:len(tok)] = tok
-        s_val[:len(val)] = val
-        s_len[:len(lens)] = lens
-        d_tok, d_val, d_len = be.to_device(s_tok), be.to_device(s_val), be.to_device(s_len)
-        g_tok = be.empty(W * s_tok.size, np.int32)
-        g_val = be.empty(W * s_val.size, np.int64)
-        g_len = be.empty(W * s_len.size, np.int32)
+        # padded send buffers on the device, filled straight from the staged arrays (the pad is never written nor read:
+        # every rank's true counts are known)
+        n_tok_pad, n_rec_pad = max(max_tok, 1), max(max_rec, 1)
+        d_tok, d_val, d_len = be.empty(n_tok_pad, np.int32), be.empty(n_tok_pad, np.int64), be.empty(n_rec_pad, np.int32)
+        if len(tok):
+            _as_torch(d_tok)[:len(tok)].copy_(torch.from_numpy(tok))
+            _as_torch(d_val)[:len(val)].copy_(torch.from_numpy(val))
+            _as_torch(d_len)[:len(lens)].copy_(torch.from_numpy(lens))
+        g_tok = be.empty(W * n_tok_pad, np.int32)
+        g_val = be.empty(W * n_tok_pad, np.int64)
+        g_len = be.empty(W * n_rec_pad, np.int32)
         if W > 1:
             dist.all_gather_into_tensor(_as_torch(g_tok), _as_torch(d_tok), group=self.group)
             dist.all_gather_into_tensor(_as_torch(g_val), _as_torch(d_val), group=self.group)
@@ -89,13 +89,13 @@ class NvlinkOplogExchange:
         dev = _as_torch(g_len).device
         n_rec = torch.as_tensor(cnt[:, 0], device=dev)
         n_tok = torch.as_tensor(cnt[:, 1], device=dev)
-        live_rec = torch.arange(s_len.size, device=dev)[None, :] < n_rec[:, None]
-        live_tok = torch.arange(s_tok.size, device=dev)[None, :] < n_tok[:, None]
-        lens_all = _as_torch(g_len).view(W, s_len.size)[live_rec].to(torch.int64)
+        live_rec = torch.arange(n_rec_pad, device=dev)[None, :] < n_rec[:, None]
+        live_tok = torch.arange(n_tok_pad, device=dev)[None, :] < n_tok[:, None]
+        lens_all = _as_torch(g_len).view(W, n_rec_pad)[live_rec].to(torch.int64)
         offs_all = torch.zeros(total + 1, dtype=torch.int64, device=dev)
         torch.cumsum(lens_all, 0, out=offs_all[1:])
-        tok_all = _as_torch(g_tok).view(W, s_tok.size)[live_tok]
-        val_all = _as_torch(g_val).view(W, s_val.size)[live_tok]
+        tok_all = _as_torch(g_tok).view(W, n_tok_pad)[live_tok]
+        val_all = _as_torch(g_val).view(W, n_tok_pad)[live_tok]
         ranks_all = torch.repeat_interleave(torch.arange(W, dtype=torch.int32, device=dev), n_rec)
         out = torch.empty(total, dtype=torch.int32, device=dev)
         step = min(int(ix.cfg.max_batch) for ix in self.ixs)

@@ -204,8 +204,13 @@ class IngestBuffer:
     def take(self):
         """(tokens, values or None, offsets, ranks) of everything staged, and an empty buffer again."""
         n, nt = self.n, self.ntok
-        out = (self._tok[:nt].copy(), self._val[:nt].copy() if self.with_values else None, self._offs[:n + 1].copy(),
-               self._rank[:n].copy())
+        # the caller keeps the filled arrays (views of them) and the buffer continues on fresh ones of the same size:
+        # no copy of the staged tokens and values (6 MB for a thousand 512-token records)
+        out = (self._tok[:nt], self._val[:nt] if self.with_values else None, self._offs[:n + 1], self._rank[:n])
+        self._tok = np.empty_like(self._tok)
+        self._val = np.empty_like(self._val)
+        self._offs = np.zeros_like(self._offs)
+        self._rank = np.empty_like(self._rank)
         self.n = 0
         self.ntok = 0
         return out
