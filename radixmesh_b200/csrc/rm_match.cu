@@ -191,6 +191,11 @@ rm_match_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ 
 // waited for its arena records only was built and measured: 52 us against 45 on C2, 72 against 62 on the target
 // shape.  With 64 warps per SM the query loads are already hidden, and the ring bookkeeping cost issue slots the
 // kernel does not have; it was removed.  profiles/README.md, round 2.)
+//
+// (So was a form in which a warp takes several queries - q, q + W, q + 2 W, ... - and asks for the first token of its
+// next query and the offsets of the one after while it walks the current one, to take the first two of a query's ~6
+// dependent round trips off its chain: 40 registers instead of 32, i.e. 48 warps per SM instead of 64, and the walk
+// went from 36.3 us to 44.6 (2 queries per warp), 48.6 (4), 54.7 (7) on C2.  Warps in flight beat a shorter chain.)
 template <int G, bool SPLIT, bool ROUTER, int DEPTH>
 __global__ void __launch_bounds__(RM_MATCH_TPB, 8)
 rm_match_rung_kernel(RmTree t, const int* __restrict__ qtok, const i64* __restrict__ qoff, int B, u64 seq_base,
