@@ -308,6 +308,11 @@ int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void
  *                      (the first out_prefix_len[r] rows of record r).
  *   rm_pages_rows_get  row ids (rm_gather_values / rm_read_arena output) -> KV indices, page_size per row.
  *   rm_pages_tokens    symbols -> page tokens (TreeNode.key).
+ *   rm_pages_retain    drop the pages that no edge of `idx` (the BASE index running on this object's symbols) holds
+ *                      any more - evicted since they were interned - so that their symbols are handed out again; the
+ *                      table is rebuilt from the live pages.  Call it between operations (every symbol interned with
+ *                      create != 0 must have reached the tree through rm_insert_batch, or it is dropped).  The
+ *                      reference's dict keys die with their nodes (radix_cache.py:347-352); no other counterpart.
  *   rm_pages_status    HOST out: symbols in use, free rows, sticky device error (RM_E_NOSPACE: table or rows exhausted;
  *                      RM_E_INVALID: two different new pages of one batch with the same 64-bit hash), page_size.
  *                      Synchronises.
@@ -323,6 +328,7 @@ int rm_pages_rows_put(rm_pages* p, const int64_t* values, int64_t n_rows, int64_
 int rm_pages_rows_free(rm_pages* p, const int64_t* rows, int64_t n, void* stream);
 int rm_pages_rows_get(rm_pages* p, const int64_t* rows, int64_t n, int64_t* out_values, void* stream);
 int rm_pages_tokens(rm_pages* p, const int32_t* syms, int64_t n, int32_t* out_tokens, void* stream);
+int rm_pages_retain(rm_pages* p, rm_index* idx, void* stream);
 int rm_pages_status(rm_pages* p, int64_t* out4_h, void* stream);
 
 /*

@@ -81,6 +81,7 @@ _PROTOS = {
     "rm_pages_rows_free": (C.c_int, [_P, _P, C.c_int64, _P]),
     "rm_pages_rows_get": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
     "rm_pages_tokens": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "rm_pages_retain": (C.c_int, [_P, _P, _P]),
     "rm_pages_status": (C.c_int, [_P, _P, _P]),
     "rm_read_arena": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
     "rm_read_segments": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P]),
@@ -479,6 +480,11 @@ class DevicePages:
     def tokens(self, syms, n, out_tokens) -> None:
         with self._mutex:
             self._check(self.lib.rm_pages_tokens(self._h, ptr(syms), int(n), ptr(out_tokens), self._s()))
+
+    def retain(self, index: "DeviceIndex") -> None:
+        """Drop the pages no edge of `index` holds any more; their symbols are reused (rm_pages_retain)."""
+        with self._mutex:
+            self._check(self.lib.rm_pages_retain(self._h, index._h, self._s()))
 
     def status(self):
         """(symbols in use, free rows, sticky device error, page_size); raises on a device error."""

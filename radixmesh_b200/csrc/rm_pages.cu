@@ -10,6 +10,9 @@
 //   rm_pages_rows_*     the value of a symbol position is the id of a ROW of P KV indices in a device row store
 //                       (put: rows for the pages of an insert; free: the rows of evicted runs and of pages an insert
 //                       found already present; get: expand row ids to the KV indices match_prefix / evict hand back).
+//   rm_pages_retain     drops the pages no edge of the tree holds any more (evicted since they were interned): their
+//                       symbols are handed out again and the table is rebuilt from the live ones.  The reference's
+//                       dict entries die with their nodes; without this the symbol space only grows.
 // Restriction (as in the host adapter this replaces): keys are taken in whole pages; the reference's callers align.
 #include "rm_internal.h"
 
@@ -26,7 +29,10 @@ struct rm_pages {
   int* store;                      // page tokens by symbol: store[sym * P + j]
   i64* vrows;                      // value rows: vrows[row * P + j]
   i64* rows_free;                  // ring of free row ids
-  u64* ctr;                        // [0] symbols handed out, [1] rows popped, [2] rows pushed, [3] sticky error
+  u64* ctr;                        // [0] symbols handed out, [1] rows popped, [2] rows pushed, [3] sticky error,
+                                   // [4] free symbols taken, [5] free symbols there are (rm_pages_retain)
+  int* sym_free;                   // symbols rm_pages_retain found unused, handed out again before fresh ones
+  unsigned char* live;             // rm_pages_retain: symbol is held by an edge of the tree
 };
 
 __device__ __forceinline__ u64 rm_page_hash(const int* __restrict__ p, int P) {
@@ -72,7 +78,12 @@ __global__ void rm_pages_claim_kernel(rm_pages pg, const int* __restrict__ token
     else cur = *reinterpret_cast<volatile u64*>(&pg.tag[i]);
     if (cur == 0ull) {
       if (create) {                                              // the slot is mine: next symbol, page stored, then published
-        const u64 s = atomicAdd(&pg.ctr[0], 1ull);
+        // a symbol rm_pages_retain freed, if one is left, else the next fresh one ([4] may run past [5]: both are
+        // set again by the next retain)
+        u64 s;
+        const u64 fr = pg.ctr[5] ? atomicAdd(&pg.ctr[4], 1ull) : ~0ull;
+        if (fr < pg.ctr[5]) s = (u64)pg.sym_free[fr];
+        else s = atomicAdd(&pg.ctr[0], 1ull);
         if ((i64)s >= pg.max_pages) {
           atomicMax(&pg.ctr[3], (u64)RM_E_NOSPACE);
           break;
@@ -143,6 +154,8 @@ __global__ void rm_pages_reset_kernel(rm_pages pg) {
     pg.ctr[1] = 0;
     pg.ctr[2] = (u64)pg.max_rows;   // ring: rows [popped, pushed) are free
     pg.ctr[3] = 0;
+    pg.ctr[4] = 0;
+    pg.ctr[5] = 0;
   }
 }
 
@@ -192,7 +205,54 @@ __global__ void rm_pages_tokens_kernel(rm_pages pg, const int* __restrict__ syms
 
 static int rm_pg_grid(i64 n) { return (int)((n + RM_PG_TPB - 1) / RM_PG_TPB); }
 
+// ---- rm_pages_retain -----------------------------------------------------------------------------------------------
+// live[s] = 1 for every symbol an owned arena position of the index holds (evicted runs have their owner words cleared)
+__global__ void rm_pages_mark_kernel(rm_pages pg, RmTree t) {
+  const u64 top = t.ctr->arena_top;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < (i64)top; i += stride) {
+    const int2 r = t.ts[i];
+    if (r.y >= 0 && r.x >= 0 && (i64)r.x < pg.max_pages) pg.live[r.x] = 1;
+  }
+}
+
+// every symbol handed out so far: a live one goes back into the (cleared) table, a dead one onto the free list
+__global__ void rm_pages_sweep_kernel(rm_pages pg) {
+  const i64 n = (i64)pg.ctr[0] < pg.max_pages ? (i64)pg.ctr[0] : pg.max_pages;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 s = (i64)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += stride) {
+    if (!pg.live[s]) {
+      const u64 at = atomicAdd(&pg.ctr[5], 1ull);
+      pg.sym_free[at] = (int)s;
+      continue;
+    }
+    const u64 tg = rm_page_hash(pg.store + s * pg.P, pg.P);
+    unsigned i = (unsigned)(tg >> 20) & pg.mask;
+    for (unsigned steps = 0; steps <= pg.mask; ++steps) {
+      if (atomicCAS(&pg.tag[i], 0ull, tg) == 0ull) {
+        pg.sym[i] = (int)s;
+        break;
+      }
+      i = (i + 1) & pg.mask;
+    }
+  }
+}
+
 extern "C" {
+
+int rm_pages_retain(rm_pages* p, rm_index* idx, void* stream) {
+  if (!p || !idx) return RM_E_INVALID;
+  RM_CUDA(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RM_CUDA(cudaMemsetAsync(p->live, 0, (size_t)p->max_pages, s));
+  RM_LAUNCH(rm_pages_mark_kernel, 148 * 8, RM_PG_TPB, s, *p, idx->t);
+  RM_CUDA(cudaMemsetAsync(p->tag, 0, sizeof(u64) * ((size_t)p->mask + 1), s));
+  RM_CUDA(cudaMemsetAsync(p->sym, 0xFF, sizeof(int) * ((size_t)p->mask + 1), s));
+  RM_CUDA(cudaMemsetAsync(p->ctr + 4, 0, 2 * sizeof(u64), s));
+  RM_LAUNCH(rm_pages_sweep_kernel, 148 * 8, RM_PG_TPB, s, *p);
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
 
 int rm_pages_create(int32_t device, int32_t page_size, int64_t max_pages, int64_t max_rows, rm_pages** out) {
   if (!out || page_size < 2 || page_size > 4096 || max_pages < 1 || max_pages > (1ll << 30) || max_rows < 1) {
@@ -218,6 +278,8 @@ int rm_pages_create(int32_t device, int32_t page_size, int64_t max_pages, int64_
   A(p->vrows, i64, (size_t)max_rows * page_size);
   A(p->rows_free, i64, max_rows);
   A(p->ctr, u64, 8);
+  A(p->sym_free, int, max_pages);
+  A(p->live, unsigned char, max_pages);
 #undef A
   if (e != cudaSuccess) {
     rm_set_error("rm_pages_create: device allocation failed: %s", cudaGetErrorString(e));
@@ -237,7 +299,7 @@ int rm_pages_create(int32_t device, int32_t page_size, int64_t max_pages, int64_
 int rm_pages_destroy(rm_pages* p) {
   if (!p) return RM_OK;
   cudaSetDevice(p->device);
-  void* ptrs[] = {p->tag, p->sym, p->store, p->vrows, p->rows_free, p->ctr};
+  void* ptrs[] = {p->tag, p->sym, p->store, p->vrows, p->rows_free, p->ctr, p->sym_free, p->live};
   for (void* q : ptrs)
     if (q) cudaFree(q);
   delete p;
@@ -319,10 +381,11 @@ int rm_pages_status(rm_pages* p, int64_t* out4_h, void* stream) {
   if (!p || !out4_h) return RM_E_INVALID;
   RM_CUDA(cudaSetDevice(p->device));
   cudaStream_t s = (cudaStream_t)stream;
-  u64 c[4];
+  u64 c[6];
   RM_CUDA(cudaMemcpyAsync(c, p->ctr, sizeof(c), cudaMemcpyDeviceToHost, s));
   RM_CUDA(cudaStreamSynchronize(s));
-  out4_h[0] = (int64_t)c[0];                 // symbols handed out
+  const u64 taken = c[4] < c[5] ? c[4] : c[5];
+  out4_h[0] = (int64_t)(c[0] - (c[5] - taken));   // symbols in use: handed out so far minus what the free list still holds
   out4_h[1] = (int64_t)(c[2] - c[1]);        // free rows
   out4_h[2] = (int64_t)c[3];                 // sticky device error
   out4_h[3] = p->P;

@@ -99,7 +99,7 @@ class RadixCache:
     def __init__(self, req_to_token_pool, token_to_kv_pool_allocator, page_size: int, disable: bool = False,
                  enable_kv_cache_events: bool = False, *, max_nodes: int = 1 << 20, max_tokens: int = 1 << 26,
                  max_batch: int = 1 << 16, max_key_len: int = 1 << 15, max_dups: int = 1 << 12, device: int = 0,
-                 _index_kwargs: Optional[dict] = None, _backend=None, _library=None):
+                 max_page_symbols: Optional[int] = None, _index_kwargs: Optional[dict] = None, _backend=None, _library=None):
         if page_size < 1 or (page_size != 1 and self.MODE != capi.MODE_BASE):
             raise ValueError("page_size > 1 is a RadixCache feature; RadixMesh hard-codes 1 (radix_mesh.py:87)")
         # Paged keys (radix_cache.py:23-32, 109-114: child key = first page, keys compared a page at a time, splits at
@@ -123,7 +123,10 @@ class RadixCache:
         self._ix = capi.DeviceIndex(**kw)
         self._be = self._ix.be
         if P > 1:
-            n_sym = max(max_tokens // P, 1) + (1 << 12)
+            # distinct pages the interning table can hold at a time (those of evicted nodes are dropped when it fills)
+            n_sym = int(max_page_symbols) if max_page_symbols else max(max_tokens // P, 1) + (1 << 12)
+            self._pg_syms_total = n_sym
+            self._pg_syms_after_retain = 0
             self._pg_rows_total = n_sym + max_batch * max(max_key_len // P, 1)
             self._pg = capi.DevicePages(P, n_sym, self._pg_rows_total, device=device, backend=self._be, library=self._ix.lib)
         self.device = getattr(self._be, "device", "cpu")
@@ -285,7 +288,13 @@ class RadixCache:
             self._pg.rows_free(dead, len(dead))
         self._invalidate()
         self._ix.check_device_error()
-        self._pg.status()
+        in_use = self._pg.status()[0]
+        # pages of evicted nodes keep their symbols until somebody asks for them back: when three quarters of the
+        # symbol space are taken - and an eighth of it has been handed out since the last time - the pages no edge holds
+        # are dropped (the reference's dict keys die with their nodes, radix_cache.py:347-352)
+        if in_use > 0.75 * self._pg_syms_total and in_use - self._pg_syms_after_retain > self._pg_syms_total // 8:
+            self._pg.retain(self._ix)
+            self._pg_syms_after_retain = self._pg.status()[0]
         return out
 
     # ------------------------------------------------------------------ public API (radix_cache.py:117-248)
@@ -294,6 +303,7 @@ class RadixCache:
         self._invalidate()
         if self._pg is not None:
             self._pg.reset()
+            self._pg_syms_after_retain = 0
 
     def match_prefix(self, key: List[int], **kwargs) -> MatchResult:
         import torch

@@ -388,3 +388,59 @@ def run_paged_batch(kw, seed):
     # every row the tree does not hold is back in the ring: rows in use = pages in the tree
     syms, free_rows, _, _ = t._pg.status()
     assert free_rows + t.total_size() // page == t._pg_rows_total
+
+
+def run_paged_symbol_reclaim(kw, seed):
+    """A stream of fresh pages through a small interning table: every round inserts keys made of pages nobody has seen,
+    then evicts most of the tree.  The pages of evicted nodes must give their symbols back (rm_pages_retain), or the
+    table (192 symbols here, ~60 new pages per round) is full after three rounds; results against the oracle's paged
+    RadixCache throughout, including keys that survive several reclaims."""
+    import random
+    from oracle.radix_port import PortRadixCache
+    rnd = random.Random(8300 + seed)
+    page = rnd.choice([2, 4])
+    alloc = FakeAllocator()
+    small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64, max_page_symbols=192)
+    small.update(kw)
+    t = RadixCache(None, alloc, page, **small)
+    be = t._be
+    orc = PortRadixCache(page)
+    vc = 0
+    fresh = 10
+    keep = [[1, 2, 3, 4, 5, 6, 7, 8][:2 * page]]      # a key re-inserted every round: it stays live
+    retains = 0
+    for rd in range(16):
+        keys = [list(keep[0])]
+        for _ in range(6):
+            n_pages = rnd.randrange(4, 12)
+            k = list(range(fresh, fresh + n_pages * page))       # tokens nobody has used: all pages new
+            fresh += n_pages * page
+            keys.append(k)
+        if rd and rnd.random() < 0.5:
+            keys.append(keys[rnd.randrange(1, len(keys))][:2 * page] + [7] * page)   # shares a prefix with a fresh key
+        vals = []
+        for k in keys:
+            vals.append(list(range(vc, vc + len(k))))
+            vc += len(k)
+        offs = np.zeros(len(keys) + 1, dtype=np.int64)
+        np.cumsum([len(k) for k in keys], out=offs[1:])
+        flat = np.asarray([x for k in keys for x in k], dtype=np.int32)
+        fv = np.asarray([x for v in vals for x in v], dtype=np.int64)
+        before = t._pg_syms_after_retain
+        got = be.to_host(t.insert_batch(be.to_device(flat), be.to_device(fv), be.to_device(offs))).tolist()
+        retains += t._pg_syms_after_retain != before
+        assert got == [orc.insert(list(k), np.asarray(v, dtype=np.int64)) for k, v in zip(keys, vals)]
+        for q in keys[:3] + [keys[-1][:page] + [5] * page]:
+            m = t.match_prefix(list(q))
+            e = orc.match_prefix(list(q))
+            assert m.device_indices.tolist() == e.indices.tolist()
+        # evict everything but what the kept key needs (it was just stamped, so it goes last)
+        n = max(orc.evictable - 2 * page, 0)
+        b0, b1 = len(alloc.freed), len(orc.freed)
+        t.evict(n)
+        orc.evict(n)
+        assert alloc.freed[b0:] == orc.freed[b1:]
+        assert (t.evictable_size(), t.total_size()) == (orc.evictable, orc.total_size())
+    assert retains >= 2, retains
+    syms, free_rows, _, _ = t._pg.status()
+    assert syms <= 192 and free_rows + t.total_size() // page == t._pg_rows_total

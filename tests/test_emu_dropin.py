@@ -110,3 +110,8 @@ def test_flatten_order_paged(seed):
 @pytest.mark.parametrize("seed", range(10))
 def test_paged_batch_entry_points(seed):
     dc.run_paged_batch(kw(), seed)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_paged_symbols_of_evicted_pages_are_reused(seed):
+    dc.run_paged_symbol_reclaim(kw(), seed)

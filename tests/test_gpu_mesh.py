@@ -224,6 +224,12 @@ def test_gpu_paged_batch_entry_points(seed):
     dc.run_paged_batch({}, seed)
 
 
+@pytest.mark.parametrize("seed", range(3))
+def test_gpu_paged_symbols_of_evicted_pages_are_reused(seed):
+    """rm_pages_retain on the GPU: a stream of fresh pages through a 192-symbol table, against the oracle."""
+    dc.run_paged_symbol_reclaim({}, seed)
+
+
 @pytest.mark.parametrize("seed", range(4))
 def test_gpu_paged_random_against_oracle(seed):
     dc.run_flatten_order({}, 50 + seed, page=2)
