@@ -295,7 +295,10 @@ int rm_read_segments(rm_index* idx, int64_t off, int64_t n, int32_t* seg_h, void
  * :148-150 page-aligned match).  A paged radix tree over tokens is a radix tree over page symbols, so an rm_index in
  * BASE mode runs unchanged on symbols; an rm_pages object beside it turns tokens into symbols on the device and keeps
  * the KV indices of a page as one row (the index's value of a symbol position is the row id).  All pointers are
- * DEVICE pointers; keys are taken in whole pages (len / page_size, the reference's callers align).
+ * DEVICE pointers; keys are taken in whole pages (len / page_size).  A key with a short last page (the reference stores
+ * it in the leaf, radix_cache.py:296-326) is passed with that page filled up by a token no key contains: it then is a
+ * page of its own, equal only to the same short page, and the caller remembers how many tokens its value row really
+ * holds (radixmesh_b200/radix_cache.py does exactly this).
  *   rm_pages_intern    key q = tokens[offsets[q] .. offsets[q+1]); its symbols go to out_syms[sym_offsets[q] ..
  *                      sym_offsets[q+1]) (sym_offsets[q+1] - sym_offsets[q] = whole pages of key q; total_pages =
  *                      sym_offsets[B]).  create != 0 (insert): unseen pages get new symbols.  create == 0 (match): the

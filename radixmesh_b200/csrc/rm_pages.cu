@@ -13,7 +13,7 @@
 //   rm_pages_retain     drops the pages no edge of the tree holds any more (evicted since they were interned): their
 //                       symbols are handed out again and the table is rebuilt from the live ones.  The reference's
 //                       dict entries die with their nodes; without this the symbol space only grows.
-// Restriction (as in the host adapter this replaces): keys are taken in whole pages; the reference's callers align.
+// Keys are taken in whole pages; a short last page arrives filled up with a reserved token (include/radixmesh_b200.h).
 #include "rm_internal.h"
 
 #define RM_PG_TPB 128

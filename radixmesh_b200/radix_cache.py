@@ -14,6 +14,8 @@ import numpy as np
 
 from . import capi
 
+PAGE_FILL = -(1 << 31)     # fills up a short last page of a paged key (RadixCache.__init__); no key may contain it
+
 
 class TreeNode:
     """Handle to a node of the device tree (reference: radix_cache.py:35-64).  Attributes are read from
@@ -129,6 +131,13 @@ class RadixCache:
             self._pg_syms_after_retain = 0
             self._pg_rows_total = n_sym + max_batch * max(max_key_len // P, 1)
             self._pg = capi.DevicePages(P, n_sym, self._pg_rows_total, device=device, backend=self._be, library=self._ix.lib)
+        # A key that is not a whole number of pages: the reference stores the short last page in the leaf, keyed by the
+        # short tuple (radix_cache.py:109-114, 296-326).  Here the short page is filled up with a token no key may
+        # contain, which makes it a page (and a symbol) of its own - equal only to the same short page, as the
+        # reference's tuple compare has it; the host remembers which value rows are short, and by how much.
+        self._ragged = {}              # value row id -> tokens the short page really holds
+        self._deficit = 0              # sum over live short rows of (page_size - tokens held)
+        self._deficit_protected = 0    # ... the part of it that sits in locked leaves
         self.device = getattr(self._be, "device", "cpu")
         self._dump_cache = None
         self._info_cache = {}
@@ -151,7 +160,7 @@ class RadixCache:
         self._flush()
         out = {}
         for cid, tok, gen in self._ix.node_children(x):
-            key = tok if self._P == 1 else tuple(self._pages_of([tok]))
+            key = tok if self._P == 1 else tuple(t for t in self._pages_of([tok]) if t != PAGE_FILL)   # a short page keys by the short tuple
             out[key] = self.root_node if cid == 0 else TreeNode(self, cid, gen)
         return out
 
@@ -204,7 +213,10 @@ class RadixCache:
         r = self._info(x)
         tok, _ = self._ix.read_arena(int(r.edge_off), int(r.edge_len), values=False)
         if self._P > 1:
-            return self._pages_of(tok)
+            toks = self._pages_of(tok)
+            while toks and toks[-1] == PAGE_FILL:       # a short last page (see __init__)
+                toks.pop()
+            return toks
         return tok.tolist()
 
     def _node_value(self, x: int):
@@ -214,7 +226,7 @@ class RadixCache:
         r = self._info(x)
         _, val = self._ix.read_arena(int(r.edge_off), int(r.edge_len))
         if self._P > 1:
-            val = self._rows_values(val)
+            val = self._run_values(val)
         return torch.from_numpy(val)
 
     def _tensor(self, a):
@@ -249,6 +261,15 @@ class RadixCache:
         self._pg.rows_get(self._be.to_device(rows), n, out)
         return self._be.to_host(out)
 
+    def _run_values(self, rows) -> np.ndarray:
+        """KV indices of one node's rows: only the last row of a run can be a short page."""
+        vals = self._rows_values(rows)
+        if len(rows) and self._ragged:
+            held = self._ragged.get(int(rows[-1]))
+            if held is not None:
+                vals = vals[:len(vals) - (self._P - held)]
+        return vals
+
     def _intern(self, tokens, offsets, B: int, create: bool):
         """Device tokens / offsets -> (symbols, symbol offsets [B+1], pages resolved per key), all on the device."""
         xp = self._xp(offsets)
@@ -279,7 +300,7 @@ class RadixCache:
         syms, soffs, _, total = self._intern(tokens, offsets, B, create=True)
         out = self._be.empty(B, np.int32)
         if total == 0:
-            return out
+            return out, None
         rows = self._be.empty(total + 1, np.int64)
         self._pg.rows_put(values, total, rows)        # values are page aligned: row i = values[i*P : (i+1)*P]
         self._ix.insert(syms, rows, soffs, None, B, out)
@@ -295,7 +316,7 @@ class RadixCache:
         if in_use > 0.75 * self._pg_syms_total and in_use - self._pg_syms_after_retain > self._pg_syms_total // 8:
             self._pg.retain(self._ix)
             self._pg_syms_after_retain = self._pg.status()[0]
-        return out
+        return out, rows
 
     # ------------------------------------------------------------------ public API (radix_cache.py:117-248)
     def reset(self) -> None:
@@ -304,6 +325,7 @@ class RadixCache:
         if self._pg is not None:
             self._pg.reset()
             self._pg_syms_after_retain = 0
+        self._ragged, self._deficit, self._deficit_protected = {}, 0, 0
 
     def match_prefix(self, key: List[int], **kwargs) -> MatchResult:
         import torch
@@ -393,17 +415,25 @@ class RadixCache:
             value = [x for x in key]
         if self._P > 1:
             P = self._P
-            if len(key) % P != 0:
-                # the reference would store a ragged last page in the leaf (radix_cache.py:296-326 never aligns);
-                # its callers insert page-aligned keys, and so must the callers of this class
-                raise ValueError(f"paged insert: key of {len(key)} tokens is not a multiple of page_size {P}")
             if len(key) == 0:
                 return 0
             be = self._be
-            v = value.cpu().numpy() if hasattr(value, "cpu") else np.asarray(value)
-            out = self._paged_insert(be.to_device(np.asarray(key, dtype=np.int32)), be.to_device(v.astype(np.int64, copy=False)),
-                                     be.to_device(np.asarray([0, len(key)], dtype=np.int64)), 1)
-            return int(be.to_host(out)[0]) * P
+            k = np.asarray(key, dtype=np.int32)
+            v = (value.cpu().numpy() if hasattr(value, "cpu") else np.asarray(value)).astype(np.int64, copy=False)
+            held = len(k) % P                     # tokens of a short last page (0: whole pages)
+            if held:
+                if (k == PAGE_FILL).any():
+                    raise ValueError(f"paged insert: token {PAGE_FILL} is reserved (it fills up a short last page)")
+                k = np.concatenate([k, np.full(P - held, PAGE_FILL, dtype=np.int32)])
+                v = np.concatenate([v, np.zeros(P - held, dtype=np.int64)])
+            out, rows = self._paged_insert(be.to_device(k), be.to_device(v), be.to_device(np.asarray([0, len(k)], dtype=np.int64)), 1)
+            matched = int(be.to_host(out)[0])
+            if held and matched < len(k) // P:    # the short page went into a new leaf: its row stays
+                row = int(be.to_host(rows[len(k) // P - 1:len(k) // P])[0])
+                self._ragged[row] = held
+                self._deficit += P - held
+            # (a matched short page counts as a whole one, exactly like _key_match_paged, radix_cache.py:23-32)
+            return matched * P
         return int(self._insert_records([(list(key), value, -1)])[0])
 
     def _insert_records(self, recs) -> np.ndarray:
@@ -428,7 +458,7 @@ class RadixCache:
         self._flush()
         N = int(offsets.shape[0]) - 1
         if self._P > 1:
-            out = self._paged_insert(tokens, values, offsets, N)
+            out, _ = self._paged_insert(tokens, values, offsets, N)
             out *= self._P
             if out_prefix_len is not None:
                 out_prefix_len[:] = out
@@ -444,20 +474,36 @@ class RadixCache:
             return
         self._flush()
         P = self._P
-        nodes, offs, lens = self._ix.evict((int(num_tokens) + P - 1) // P)   # sum(len * P) >= n  <=>  sum(len) >= ceil(n / P)
-        self._invalidate()
         if P > 1:
-            runs = [self._ix.read_arena(o, n)[1] for o, n in zip(offs.tolist(), lens.tolist())]
-            if runs:
+            # sum(len * P) >= n  <=>  sum(len) >= ceil(n / P) while every page is whole.  A short last page frees
+            # fewer tokens than its row counts for, so the call may stop early: it then goes on with what is missing
+            # (the reference's heap loop continued is the same as collecting the leaves again, radix_cache.py:183-202)
+            remaining = int(num_tokens)
+            while remaining > 0:
+                nodes, offs, lens = self._ix.evict((remaining + P - 1) // P)
+                self._invalidate()
+                runs = [self._ix.read_arena(o, n)[1] for o, n in zip(offs.tolist(), lens.tolist())]
+                if not runs:
+                    break
                 rows = np.concatenate(runs)
                 vals = self._rows_values(rows)
                 self._pg.rows_free(self._be.to_device(rows), len(rows))
-                at = 0
+                at, short = 0, False
                 for r in runs:
+                    held = self._ragged.pop(int(r[-1]), None) if self._ragged else None
+                    n_tok = len(r) * P - (P - held if held is not None else 0)
+                    if held is not None:
+                        self._deficit -= P - held
+                        short = True
                     if self.token_to_kv_pool_allocator is not None:
-                        self.token_to_kv_pool_allocator.free(self._tensor(vals[at * P:(at + len(r)) * P].copy()))
+                        self.token_to_kv_pool_allocator.free(self._tensor(vals[at * P:at * P + n_tok].copy()))
                     at += len(r)
+                    remaining -= n_tok
+                if not short:
+                    break
             return
+        nodes, offs, lens = self._ix.evict(int(num_tokens))
+        self._invalidate()
         for o, n in zip(offs.tolist(), lens.tolist()):
             _, val = self._ix.read_arena(o, n)
             if self.token_to_kv_pool_allocator is not None:
@@ -467,10 +513,23 @@ class RadixCache:
         self._flush()
         be = self._be
         d_out = be.empty(1, np.int64)
+        short = 0
+        if self._ragged and node.id != 0:
+            # the handle's own node may end in a short page: its length counts for page_size - held tokens less when
+            # its lock count crosses 0 <-> 1 (a short page is always the end of a leaf)
+            r = self._info(node._resolved())
+            crossing = (direction > 0 and int(r.lock_ref) == 0) or (direction < 0 and int(r.lock_ref) == 1)
+            if crossing and int(r.edge_len) > 0:
+                _, last = self._ix.read_arena(int(r.edge_off) + int(r.edge_len) - 1, 1)
+                held = self._ragged.get(int(last[0]))
+                if held is not None:
+                    short = self._P - held
         self._ix.lock(be.to_device(np.asarray([node.id], np.int32)), be.to_device(np.asarray([node._gen], np.int32)),
                       1, direction, d_out)
         self._invalidate()
-        return int(be.to_host(d_out)[0]) * self._P
+        self._deficit_protected += short if direction > 0 else -short
+        # inc returns minus the tokens that became protected, dec the tokens that became evictable again
+        return int(be.to_host(d_out)[0]) * self._P + short * (1 if direction > 0 else -1)
 
     def inc_lock_ref(self, node: TreeNode) -> int:
         return 0 if self.disable else self._lock(node, +1)
@@ -480,16 +539,16 @@ class RadixCache:
 
     def evictable_size(self) -> int:
         self._flush()
-        return int(self._ix.sizes().evictable) * self._P
+        return int(self._ix.sizes().evictable) * self._P - (self._deficit - self._deficit_protected)
 
     def protected_size(self) -> int:
         self._flush()
-        return int(self._ix.sizes().protected_) * self._P
+        return int(self._ix.sizes().protected_) * self._P - self._deficit_protected
 
     def total_size(self) -> int:
         """radix_cache.py:239-241, 354-364: reduced on the device (rm_total_size), eight bytes back."""
         self._flush()
-        return self._ix.total_size() * self._P
+        return self._ix.total_size() * self._P - self._deficit
 
     def all_values_flatten(self):
         """radix_cache.py:243-248: the values of the tree in the reference's order - pre-order, the children of a node
@@ -518,7 +577,7 @@ class RadixCache:
                 continue
             x = int(x)
             o, ln = int(d["edge_off"][x]), int(d["edge_len"][x])
-            out.append(self._rows_values(val[o:o + ln]) if self._P > 1 else val[o:o + ln])
+            out.append(self._run_values(val[o:o + ln]) if self._P > 1 else val[o:o + ln])
             stack.append(iter(kids.get(x, ())))
         return torch.from_numpy(np.concatenate(out))
 

@@ -444,3 +444,71 @@ def run_paged_symbol_reclaim(kw, seed):
     assert retains >= 2, retains
     syms, free_rows, _, _ = t._pg.status()
     assert syms <= 192 and free_rows + t.total_size() // page == t._pg_rows_total
+
+
+def run_paged_ragged(kw, seed):
+    """RadixCache(page_size > 1) with keys of ANY length through the reference's own call shapes: the reference stores
+    a short last page in the leaf (child key = the short tuple, a matched short page counted as a whole one by
+    _key_match_paged).  Against the oracle's paged RadixCache, which tests/test_oracle_vs_reference.py pins on ragged
+    keys: insert return values, match results and last nodes, lock deltas, freed indices of every evict, the three
+    size counters, the values in tree order, and keys / child keys of the nodes."""
+    import random
+    from oracle.radix_port import PortRadixCache
+    rnd = random.Random(8500 + seed)
+    page = rnd.choice([2, 3, 4])
+    alloc = FakeAllocator()
+    small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64)
+    small.update(kw)
+    t = RadixCache(None, alloc, page, **small)
+    orc = PortRadixCache(page)
+    vc = 0
+    held = []
+    for step in range(70):
+        op = rnd.choice(["ins", "ins", "ins", "match", "lock", "unlock", "evict"])
+        if op == "ins":
+            k = [rnd.randrange(2) for _ in range(rnd.randrange(0, 14))]
+            v = list(range(vc, vc + len(k)))
+            vc += len(k)
+            assert t.insert(list(k), np.asarray(v, dtype=np.int64)) == orc.insert(list(k), np.asarray(v, dtype=np.int64)), (step, k)
+        elif op == "match":
+            q = [rnd.randrange(2) for _ in range(rnd.randrange(0, 14))]
+            m, e = t.match_prefix(list(q)), orc.match_prefix(list(q))
+            assert m.device_indices.tolist() == e.indices.tolist()
+            assert t.full_key(m.last_device_node) == orc.full_key(e.last_node)
+            held.append((m.last_device_node, e.last_node))
+        elif op == "lock" and held:
+            a, b = held[rnd.randrange(len(held))]
+            assert t.inc_lock_ref(a) == orc.inc_lock_ref(b)
+            held.append((a, b))
+        elif op == "unlock" and held:
+            a, b = held[rnd.randrange(len(held))]
+            if b.lock_ref > 0 and b is not orc.root:
+                assert t.dec_lock_ref(a) == orc.dec_lock_ref(b)
+        elif op == "evict":
+            n = rnd.randrange(0, 12)
+            b0, b1 = len(alloc.freed), len(orc.freed)
+            t.evict(n)
+            orc.evict(n)
+            assert alloc.freed[b0:] == orc.freed[b1:], (step, n)
+            held = [(a, b) for a, b in held if b is orc.root or b.parent is not None and _alive(orc, b)]
+        assert (t.evictable_size(), t.protected_size(), t.total_size()) == (orc.evictable, orc.protected, orc.total_size()), step
+    if orc.total_size():
+        assert t.all_values_flatten().tolist() == orc.all_values_flatten().tolist()
+    # keys and child keys of the whole tree, short pages included
+    def walk(a, b):
+        assert a.key == list(b.key)
+        ka, kb = a.children, b.children
+        assert list(ka.keys()) == list(kb.keys())
+        for key in kb:
+            walk(ka[key], kb[key])
+    walk(t.root_node, orc.root)
+
+
+def _alive(orc, node):
+    """node is still reachable from the oracle's root (evicted nodes keep their parent pointer)."""
+    while node is not orc.root:
+        p = node.parent
+        if p is None or p.children.get(orc._ckey(node.key)) is not node:
+            return False
+        node = p
+    return True

@@ -53,7 +53,7 @@ def test_paged_restrictions():
     from radixmesh_b200 import RadixCache, RadixMesh, ServerArgs
     t = RadixCache(None, None, 4, max_nodes=256, max_tokens=4096, max_batch=16, max_key_len=64, **kw())
     with pytest.raises(ValueError):
-        t.insert([1, 2, 3, 4, 5], torch.arange(5))                 # not a multiple of the page
+        t.insert([1, 2, -(1 << 31)], torch.arange(3))              # the token that fills up short pages is reserved
     assert t.insert([1, 2, 3, 4, 5, 6, 7, 8], torch.arange(8)) == 0
     assert t.match_prefix([1, 2, 3, 4, 5, 6, 7]).device_indices.tolist() == [0, 1, 2, 3]   # page aligned (radix_cache.py:148-150)
     assert t.match_prefix([1, 2, 3]).device_indices.tolist() == []
@@ -110,6 +110,11 @@ def test_flatten_order_paged(seed):
 @pytest.mark.parametrize("seed", range(10))
 def test_paged_batch_entry_points(seed):
     dc.run_paged_batch(kw(), seed)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_paged_keys_with_a_short_last_page(seed):
+    dc.run_paged_ragged(kw(), seed)
 
 
 @pytest.mark.parametrize("seed", range(4))

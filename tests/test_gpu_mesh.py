@@ -224,6 +224,13 @@ def test_gpu_paged_batch_entry_points(seed):
     dc.run_paged_batch({}, seed)
 
 
+@pytest.mark.parametrize("seed", range(4))
+def test_gpu_paged_keys_with_a_short_last_page(seed):
+    """Keys that are not a whole number of pages through the single-key surface (the reference stores the short page in
+    the leaf): insert / match / lock / evict / sizes / TreeNode reads against the oracle's paged RadixCache."""
+    dc.run_paged_ragged({}, seed)
+
+
 @pytest.mark.parametrize("seed", range(3))
 def test_gpu_paged_symbols_of_evicted_pages_are_reused(seed):
     """rm_pages_retain on the GPU: a stream of fresh pages through a 192-symbol table, against the oracle."""
