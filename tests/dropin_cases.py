@@ -168,7 +168,7 @@ def replay_base_sequence(case, kw):
         assert t.evictable_size() == st["evictable"] and t.protected_size() == st["protected"]
         d = t._dump()
         from radixmesh_b200 import TreeNode
-        rows = sorted([t.full_key(TreeNode(t, x, -1)), int(d["edge_len"][x]) * t.page_size, t._node_value(x).tolist(), -1,
+        rows = sorted([t.full_key(TreeNode(t, x, -1)), len(t._node_tokens(x)), t._node_value(x).tolist(), -1,
                        int(d["lock_ref"][x])] for x in range(1, d["n"]) if d["parent"][x] >= 0)
         assert rows == [r[:5] for r in st["nodes"]]
 

@@ -41,7 +41,8 @@ def test_insert_returns_its_own_prefix_length():
     dc.run_insert_returns_own_prefix(kw())
 
 
-@pytest.mark.parametrize("case", dc.golden("paged_sequences"), ids=lambda c: f"seed{c['seed']}-page{c['page']}")
+@pytest.mark.parametrize("case", dc.golden("paged_sequences") + dc.golden("paged_ragged_sequences"),
+                         ids=lambda c: f"seed{c['seed']}-page{c['page']}")
 def test_paged_sequences(case):
     """RadixCache(page_size > 1) recorded from the reference: the drop-in runs the device index on page symbols."""
     dc.replay_base_sequence(case, kw())

@@ -156,7 +156,8 @@ def test_gpu_reset_tick_and_own_prefix():
     dc.run_insert_returns_own_prefix({})
 
 
-@pytest.mark.parametrize("case", dc.golden("paged_sequences"), ids=lambda c: f"seed{c['seed']}-page{c['page']}")
+@pytest.mark.parametrize("case", dc.golden("paged_sequences") + dc.golden("paged_ragged_sequences"),
+                         ids=lambda c: f"seed{c['seed']}-page{c['page']}")
 def test_paged_sequences(case):
     """RadixCache(page_size > 1) recorded from the reference: the drop-in runs the device index on page symbols."""
     dc.replay_base_sequence(case, {})

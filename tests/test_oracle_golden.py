@@ -7,9 +7,7 @@ from oracle.radix_port import PortConsistentHash, PortMesh, PortRadixCache, Rout
 from tests.golden_util import canon_json, load
 
 
-@pytest.mark.parametrize("case", load("base_sequences"), ids=lambda c: f"seed{c['seed']}")
-def test_base_sequences(case):
-    t = PortRadixCache(1)
+def _replay_base(case, t):
     held = []
     for op in case["ops"]:
         if op["op"] == "ins":
@@ -29,6 +27,18 @@ def test_base_sequences(case):
             t.evict(op["n"])
             assert t.freed[before:] == op["freed"]
         assert canon_json(t.canonical()) == op["state"]
+
+
+@pytest.mark.parametrize("case", load("base_sequences"), ids=lambda c: f"seed{c['seed']}")
+def test_base_sequences(case):
+    _replay_base(case, PortRadixCache(1))
+
+
+@pytest.mark.parametrize("case", load("paged_sequences") + load("paged_ragged_sequences"),
+                         ids=lambda c: f"seed{c['seed']}-page{c['page']}")
+def test_paged_sequences(case):
+    """page_size > 1, page-aligned inserts and inserts of any length (a short last page stays in the leaf)."""
+    _replay_base(case, PortRadixCache(case["page"]))
 
 
 @pytest.mark.parametrize("block", load("correctness_blocks"), ids=lambda b: b["name"])

@@ -68,13 +68,14 @@ def base_sequences():
     return out
 
 
-def paged_sequences():
+def paged_sequences(ragged=False):
     """The same kind of sequences on RadixCache(page_size 2 / 4): keys matched a page at a time, page-aligned
-    inserts (what the reference's callers do), radix_cache.py:23-32, 109-114, 148-150."""
+    inserts (what the reference's callers do), radix_cache.py:23-32, 109-114, 148-150.  ragged: inserted keys of any
+    length (page sizes 2 / 3 / 4) - the reference then keeps a short last page in the leaf."""
     out = []
     for seed in range(8):
-        rnd = random.Random(700 + seed)
-        page = rnd.choice([2, 4])
+        rnd = random.Random((900 if ragged else 700) + seed)
+        page = rnd.choice([2, 3, 4] if ragged else [2, 4])
         vocab = rnd.choice([2, 3, 5])
         maxlen = rnd.choice([9, 17, 26])
         ref = ref_harness.RefCache(page)
@@ -94,7 +95,8 @@ def paged_sequences():
             kind = rnd.choice(["ins", "ins", "match", "match", "lock", "unlock", "evict"])
             key = [rnd.randrange(vocab) for _ in range(rnd.randrange(0, maxlen))]
             if kind == "ins":
-                key = key[:len(key) // page * page]
+                if not ragged:
+                    key = key[:len(key) // page * page]
                 val = list(range(vc, vc + len(key)))
                 vc += len(key)
                 ops.append({"op": "ins", "key": key, "val": val, "ret": ref.insert(key, val)})
@@ -286,7 +288,8 @@ def main():
     only = set(sys.argv[1:])
     for name, fn in [("base_sequences", base_sequences), ("correctness_blocks", correctness_blocks),
                      ("mesh_sequences", mesh_sequences), ("consistent_hash", hash_vectors), ("oplog_wire", oplog_wire),
-                     ("paged_sequences", paged_sequences)]:
+                     ("paged_sequences", paged_sequences),
+                     ("paged_ragged_sequences", lambda: paged_sequences(ragged=True))]:
         if only and name not in only:
             continue
         data = fn()
