@@ -116,7 +116,12 @@ class RadixCache:
         self.token_to_kv_pool_allocator = token_to_kv_pool_allocator
         self.page_size = page_size
         self.disable = disable
-        self.enable_kv_cache_events = enable_kv_cache_events   # events are not produced (reference: NameError if on)
+        if enable_kv_cache_events:
+            # the reference's constructor ends in reset() -> _record_all_cleared_event() -> AllBlocksCleared(), a class
+            # it never imports (radix_cache.py:117-125, 422-424): same exception, said in full
+            raise NameError("name 'AllBlocksCleared' is not defined (the reference's KV-event classes are never imported: "
+                            "enable_kv_cache_events=True cannot construct a RadixCache there either; events are not produced)")
+        self.enable_kv_cache_events = False
         self.kv_event_queue = []
         P = self._P
         kw = dict(mode=self.MODE, max_nodes=max_nodes, max_tokens=max(max_tokens // P, 1), max_batch=max_batch,

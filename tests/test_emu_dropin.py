@@ -49,6 +49,13 @@ def test_paged_sequences(case):
 
 
 
+def test_kv_events_flag_fails_as_in_the_reference():
+    """radix_cache.py:117-125, 422-424: the constructor's reset() needs a class the module never imports."""
+    from radixmesh_b200 import RadixCache
+    with pytest.raises(NameError):
+        RadixCache(None, None, 1, enable_kv_cache_events=True, max_nodes=64, max_tokens=256, max_batch=4, max_key_len=16, **kw())
+
+
 def test_paged_restrictions():
     import torch
     from radixmesh_b200 import RadixCache, RadixMesh, ServerArgs

@@ -182,3 +182,10 @@ def test_oplog_wire_matches_reference():
         assert d.to_dict() == a.to_dict()
         e = packed.deserialize(packed.serialize(c))
         assert e.to_dict() == a.to_dict()
+
+
+def test_reference_cannot_be_built_with_kv_events():
+    """The behaviour radixmesh_b200.RadixCache(enable_kv_cache_events=True) mirrors (tests/test_emu_dropin.py)."""
+    ns = ref_harness.load()
+    with pytest.raises(NameError):
+        ns.rc.RadixCache(None, ref_harness.FakeAllocator(), 1, enable_kv_cache_events=True)
