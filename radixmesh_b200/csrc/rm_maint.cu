@@ -288,11 +288,7 @@ __global__ void rm_evict_keys_kernel(RmTree t, int n, int depth_bits, const int*
 // below K0 are then compacted, unordered, for the climb (the candidates are sorted afterwards anyway).
 #define RM_SEL_BITS 12
 #define RM_SEL_BINS (1 << RM_SEL_BITS)
-#ifdef RM_EMU
-#define RM_SEL_PICK_TPB 64
-#else
-#define RM_SEL_PICK_TPB 1024     // x 4 bins per thread = RM_SEL_BINS
-#endif
+#define RM_SEL_PICK_TPB 64        // (emulation build only: the device picks inside the level kernel)
 struct RmEvictSel {
   u64 prefix;      // digits chosen so far (high bits of K0)
   i64 need;        // tokens still to be covered inside the prefix
@@ -317,38 +313,19 @@ __global__ void rm_evict_sel_init_kernel(RmTree t, int n_bound, RmEvictSel* st, 
 }
 
 // up > 0: the last level when bits is not a multiple of 12 (the remaining low bits are shifted UP into the digit).
-// The leaves of a served tree crowd into a few digits on the first level (their stamps are recent), so the weights are
-// added up per block in shared memory first: one global atomic per block and occupied digit (global atomics per leaf:
-// 55 us at 1.2 M nodes, all on a handful of addresses).
-__global__ void __launch_bounds__(RM_MT_TPB)
-rm_evict_sel_hist_kernel(RmTree t, const u64* __restrict__ key, int n, int shift, int up, const RmEvictSel* st,
-                         u64* __restrict__ hw) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  bool in = x < n && !st->all;
-  u64 kk = 0;
-  if (in) {
-    const u64 k = key[x];
-    kk = up ? (k << up) : (k >> shift);
-    in = k != RM_NO_REQ && (kk >> RM_SEL_BITS) == st->prefix;
-  }
 #ifdef RM_EMU
-  if (in) atomicAdd(&hw[(unsigned)kk & (RM_SEL_BINS - 1)], (u64)t.edge_len[x]);
-#else
-  __shared__ u64 sh[RM_SEL_BINS];
-  for (int b = threadIdx.x; b < RM_SEL_BINS; b += RM_MT_TPB) sh[b] = 0;
-  __syncthreads();
-  if (in) atomicAdd(&sh[(unsigned)kk & (RM_SEL_BINS - 1)], (u64)t.edge_len[x]);
-  __syncthreads();
-  for (int b = threadIdx.x; b < RM_SEL_BINS; b += RM_MT_TPB) {
-    const u64 v = sh[b];
-    if (v) atomicAdd(&hw[b], v);
-  }
-#endif
+// Emulation build (threads run one after another): the level in two plain steps, histogram and pick.
+__global__ void rm_evict_sel_hist_kernel(RmTree t, const u64* __restrict__ key, int n, int shift, int up, const RmEvictSel* st,
+                                         u64* __restrict__ hw) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= n || st->all) return;
+  const u64 k = key[x];
+  const u64 kk = up ? (k << up) : (k >> shift);
+  if (k != RM_NO_REQ && (kk >> RM_SEL_BITS) == st->prefix) atomicAdd(&hw[(unsigned)kk & (RM_SEL_BINS - 1)], (u64)t.edge_len[x]);
 }
 
-// one block: the digit where the running weight reaches `need`; clears the histogram for the next level
+// the digit where the running weight reaches `need`; clears the histogram for the next level
 __global__ void rm_evict_sel_pick_kernel(RmEvictSel* st, u64* __restrict__ hw, unsigned* __restrict__ hc) {
-#ifdef RM_EMU
   if (threadIdx.x == 0 && !st->all) {
     i64 run = 0;
     int b = 0;
@@ -367,52 +344,8 @@ __global__ void rm_evict_sel_pick_kernel(RmEvictSel* st, u64* __restrict__ hw, u
     hw[b] = 0;
     hc[b] = 0;
   }
-#else
-  // 1024 threads x 4 consecutive bins: block-wide exclusive scan of the weights, then the one thread whose four bins
-  // contain the crossing names the digit (a single thread reading 4096 bins one after another took 0.1-1 ms per level)
-  __shared__ i64 wtot[32];
-  __shared__ int found_s;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (threadIdx.x == 0) found_s = 0;
-  const bool all = st->all != 0;
-  const i64 need = st->need;
-  i64 w4[4];
-  i64 mine = 0;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    w4[j] = (i64)hw[4 * threadIdx.x + j];
-    mine += w4[j];
-  }
-  i64 inc = mine;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const i64 o = __shfl_up_sync(0xffffffffu, inc, d);
-    if (lane >= d) inc += o;
-  }
-  if (lane == 31) wtot[wid] = inc;
-  __syncthreads();
-  i64 before = inc - mine;
-  for (int w = 0; w < wid; ++w) before += wtot[w];
-  if (!all && before < need && before + mine >= need) {     // the crossing is inside my four bins
-    i64 run = before;
-    int j = 0;
-    for (; j < 4; ++j) {
-      if (run + w4[j] >= need) break;
-      run += w4[j];
-    }
-    st->need = need - run;
-    st->prefix = (st->prefix << RM_SEL_BITS) | (u64)(4 * threadIdx.x + j);
-    found_s = 1;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0 && !all && !found_s) st->all = 1;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    hw[4 * threadIdx.x + j] = 0;
-    hc[4 * threadIdx.x + j] = 0;
-  }
-#endif
 }
+#endif
 
 #ifndef RM_EMU
 // One level of the select in ONE launch: a few blocks per SM stride over the keys (a block per 256 keys spent its
