@@ -4,12 +4,14 @@
 // RadixMesh._insert_helper + NodeRankConflictResolver.keep + _swap_node (radix_mesh.py:273-323,
 // 466-495; policy/conflict_resolve.py:1-6): what oplog_received does with a run of INSERT oplogs.
 //
-// Order equivalence.  Two inserts can only interact if their keys start with the same token (they
-// then share a root child); everything else about the tree they touch is disjoint.  The batch is
-// therefore stably sorted by first token, and one warp per distinct first token applies its records
-// one after another in arrival order, while different first tokens proceed in parallel.  Inside a
-// warp the lanes cooperate on the edge compares and on copying the new leaf's key/value run into
-// the arenas; node ids and arena space come from device-wide bump allocators (one atomic per record).
+// Order equivalence.  A read-only pre-pass (the walk kernel, rm_match.cu) takes every record of the batch to its
+// deepest fully matched node in the tree as it stood.  Two records can then only interact if they start changing
+// the tree at the same node through the same token, so the batch is stably sorted by a hash of (start node, next
+// token) and one warp per group applies its records one after another in arrival order, each from its own start
+// node, while different groups proceed in parallel.  The start node is the divergence node in RadixCache mode; in the
+// mesh modes it may lie higher (see "Mesh modes" below).  Inside a warp the lanes cooperate on the edge compares and
+// on copying the new leaf's key/value run into the arenas; node ids and arena space come from device-wide
+// allocators (one atomic per record).
 #include "rm_internal.h"
 #include "rm_sort.cuh"
 
@@ -20,17 +22,6 @@
 #define RM_INS_TPB 64
 #define RM_INS_G 1
 #endif
-
-// group key = first token (u32) of each record; empty records get the "none" marker
-__global__ void rm_insert_keys_kernel(const int* __restrict__ tok, const i64* __restrict__ off, int N,
-                                      u64* __restrict__ key, unsigned* __restrict__ val) {
-  int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= N) return;
-  i64 o = off[r];
-  int len = (int)(off[r + 1] - o);
-  key[r] = len > 0 ? (u64)(unsigned)tok[o] : (1ull << 32);
-  val[r] = (unsigned)r;
-}
 
 // RadixCache semantics, fast path: group key of a record after the read-only pre-pass.  Two records can only
 // interact if they leave the old tree at the same node through the same token, so the key is a hash of
@@ -103,23 +94,15 @@ __global__ void __launch_bounds__(RM_INS_TPB)
 rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__ rval, const i64* __restrict__ roff,
                  const int* __restrict__ rrank, int N, const u64* __restrict__ skey, const unsigned* __restrict__ sval,
                  u64 seq_base, int* __restrict__ out_prefix, const int* __restrict__ start) {
-  // start != NULL (RadixCache semantics): a read-only pre-pass already walked every record to its deepest
-  // fully matched node start[r] and stamped that path; groups are keyed by (that node, next token) and the
-  // walk resumes there.  start == NULL (mesh modes): groups are keyed by first token, walks start at the root.
+  // start[r]: the node record r starts at (the pre-pass already stamped the path down to its deepest fully matched
+  // node); groups are keyed by a hash of (that node, next token).
   RmGroup<G> g;
   const int i = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
   if (i >= N) return;
   const u64 gk = skey[i];
   if (i > 0 && skey[i - 1] == gk) return;  // one group per distinct key
-  if (start != nullptr && gk == 0) return;  // records the pre-pass finished
-  // mesh modes mix both kinds of groups in one launch: keys with bit 40 are first-token groups that must be
-  // applied from the root in arrival order (a record of the group replaces a stored value)
-  const bool resume = start != nullptr && (gk >> 40) == 0;
-  if (start == nullptr && gk == (1ull << 32)) {
-    // empty keys: insert returns 0 and only stamps the root (radix_cache.py:297-299)
-    for (int j = i + g.lane; j < N; j += G) out_prefix[sval[j]] = 0;
-    return;
-  }
+  if (gk == 0) return;                      // records the pre-pass finished (the whole key is in the tree, empty keys)
+  const bool resume = (gk >> 40) == 0;      // bit 40: records longer than max_key_len, reported below
   for (int j = i; j < N && skey[j] == gk; ++j) {
     const int r = (int)sval[j];
     const i64 o = roff[r];
@@ -191,12 +174,8 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
       total += m;
       // stamp: 2*op+1, or 2*op for the lower half of a node this record splits (see above).  With the
       // pre-pass other records of the batch may already have stamped c, so the stamp is a max.
-      const u64 c_before = start != nullptr ? t.stamp[c] : 0ull;
-      if (g.lane == 0) {
-        const u64 sv = (m < elen) ? seq - 1 : seq;
-        if (start != nullptr) atomicMax(&t.stamp[c], sv);
-        else t.stamp[c] = sv;
-      }
+      const u64 c_before = t.stamp[c];
+      if (g.lane == 0) atomicMax(&t.stamp[c], (m < elen) ? seq - 1 : seq);
       int target = c;
       if (m < elen) {
         // _split_node (radix_cache.py:277-294): new upper node [0, m), c keeps [m, elen)
@@ -358,21 +337,24 @@ rm_insert_kernel(RmTree t, const int* __restrict__ rtok, const i64* __restrict__
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Mesh modes, two-phase apply.  Grouping by first token alone serialises a Zipf-skewed stream on its hottest
-// prompt (one warp applies every record that starts with it: 21 K records/s measured), so the mesh modes use the
-// same scheme as RadixCache semantics - read-only pre-pass to the deepest fully matched node, groups keyed by
-// (that node, next token), walk resumed there - wherever the conflict rule allows it:
-//   * a record whose value DIFFERS from a stored node it passes either LOSES there (stored rank <= its own:
-//     nothing in the tree changes, dup_nodes gets (node, its rank), radix_mesh.py:300-310) or REPLACES the stored
-//     value (_swap_node, radix_mesh.py:466-495).  A replacement changes what every later record of the same first
-//     token compares against, so a first-token group that contains one keeps the ordered path from the root
-//     (marked through its root child; such groups and the resumed ones touch disjoint subtrees).
-//   * all other records resume at their divergence node.  Their losses are booked AFTER the apply
-//     (rm_insert_lost_kernel), walking up from the divergence node: an upper node created by a split of this same
-//     batch counts as a node of its own only if the record that made it came EARLIER (born[] holds the creating
-//     record's op seq); made later, it was still part of the node below it when this record passed, so its
-//     comparison is folded into that node's.  Values on the path cannot change meanwhile (no replacement in a
-//     resumed group reaches a node older than the batch).
+// Mesh modes.  A record whose value DIFFERS from a stored node it passes either LOSES there (stored rank <= its own:
+// nothing in the tree changes, dup_nodes gets (node, its rank), radix_mesh.py:300-310) or REPLACES the stored value
+// (_swap_node, radix_mesh.py:466-495).  A replacement changes what every later record that reaches the node compares
+// against, so where records start is decided by a classification pass between the pre-pass and the apply:
+//   * rm_insert_classify_kernel marks, per record, the SHALLOWEST node at which it would replace the stored value, as
+//     the tree stands before the batch.  Nodes above every mark of their root path are static for the batch: the first
+//     replacement at a node would have been predicted from the old tree, so no mark means no replacement.
+//   * rm_insert_keys3_kernel starts every record at the parent of the shallowest marked node T on its path, or at its
+//     divergence node when its path holds no mark.  Records that can see each other's replacements share a marked
+//     node, hence T, hence the group; a record that leaves the tree inside T's edge has (T's parent, T's first token)
+//     as its divergence point, the same key.  (History: one group per first token serialised a Zipf-skewed stream on
+//     its hottest prompt, 21 K records/s; keeping whole first-token groups on the path from the root whenever one
+//     of their records replaced something still did under alternating owner ranks, 14 ms per 1,024-record batch.)
+//   * what lies ABOVE a record's start node is static, so its losses there are booked AFTER the apply
+//     (rm_insert_lost_kernel), walking up from the start node: an upper node created by a split of this same batch
+//     counts as a node of its own only if the record that made it came EARLIER (born[] holds the creating record's op
+//     seq); made later, it was still part of the node below it when this record passed, so its comparison is folded
+//     into that node's.
 template <int G, int MESH>
 __device__ __forceinline__ bool rm_ins_differs(const RmTree& t, const RmGroup<G>& g, int v, const i64* __restrict__ val, int owner) {
   if (MESH == 2) return t.rank[v] != owner;
