@@ -142,37 +142,40 @@ struct RmMd5Words {
   __device__ __forceinline__ void set(int i, unsigned v) const { col[i * stride] = v; }
 };
 
-// The common case, 0 <= v < 100000 (every token id of a real vocabulary), without a loop: the top digit by a
-// constant division, the other four as two two-digit halves in one register (n / 10 == n * 103 >> 10 for n < 100,
-// and neither the products nor the differences carry from one half into the other), leading zeros shifted out.
-// Returns the length; text in s, first character lowest (at most 7 bytes with the separator).
+// The common case, 0 <= v < 1000000 (the token ids of every vocabulary in use: 32 K to 262 K entries), without a
+// loop: the top two digits and the lower four as two-digit numbers (n / 10 == n * 103 >> 10 for n < 100; the lower
+// two pairs share one register: neither the products nor the differences carry from one half into the other),
+// leading zeros shifted out.  Returns the length; text in s, first character lowest (at most 8 bytes with the
+// separator).
 __device__ __forceinline__ int rm_render_small(unsigned v, int lead, u64& s) {
-  const unsigned d4 = v / 10000u;
-  const unsigned r = v - d4 * 10000u;
+  const unsigned top = v / 10000u;                          // 0..99
+  const unsigned r = v - top * 10000u;
   const unsigned h = r / 100u;
   const unsigned p = h | ((r - h * 100u) << 16);
   const unsigned t = ((p * 103u) >> 10) & 0x000f000fu;      // tens of both halves
   const unsigned o = p - t * 10u;                           // ones of both halves
   const unsigned w = (t | (o << 8)) + 0x30303030u;          // d3 d2 d1 d0
-  u64 t5 = (u64)(d4 + 0x30u) | ((u64)w << 8);
-  const int nd = 1 + (v >= 10u) + (v >= 100u) + (v >= 1000u) + (v >= 10000u);
-  t5 >>= 8 * (5 - nd);
+  const unsigned tt = (top * 103u) >> 10;
+  const unsigned w2 = (tt | ((top - tt * 10u) << 8)) + 0x3030u;   // d5 d4
+  u64 t6 = (u64)w2 | ((u64)w << 16);
+  const int nd = 1 + (v >= 10u) + (v >= 100u) + (v >= 1000u) + (v >= 10000u) + (v >= 100000u);
+  t6 >>= 8 * (6 - nd);
   if (lead == 1) {
-    s = (t5 << 16) | ((u64)' ' << 8) | (u64)',';
+    s = (t6 << 16) | ((u64)' ' << 8) | (u64)',';
     return nd + 2;
   }
   if (lead == 2) {
-    s = (t5 << 8) | (u64)'[';
+    s = (t6 << 8) | (u64)'[';
     return nd + 1;
   }
-  s = t5;
+  s = t6;
   return nd;
 }
 
 // Text of one list item, first character in the lowest byte of (lo, hi): the decimal digits of v ('-' in front
 // of a negative one), preceded by ", " (lead 1) or "[" (lead 2) or nothing (lead 0).  At most 13 bytes.
 __device__ __forceinline__ int rm_render_token(int v, int lead, u64& tlo, u64& thi) {
-  if ((unsigned)v < 100000u) {
+  if ((unsigned)v < 1000000u) {
     thi = 0;
     return rm_render_small((unsigned)v, lead, tlo);
   }
@@ -289,7 +292,7 @@ __device__ unsigned rm_hash_token_list(const int* __restrict__ key, int n, const
 // scratch keeps nblk = 0 and is hashed by the streamed form above.
 #define RM_RENDER_TPB 256
 #define RM_RENDER_WPB (RM_RENDER_TPB / 32)
-#define RM_RENDER_BUF (128 * 7 + 16)
+#define RM_RENDER_BUF (128 * 8 + 16)
 
 __device__ __forceinline__ u64 rm_msg_off(i64 rel_tok, int q) { return 64ull * ((u64)((rel_tok + 3) >> 2) + 2ull * (u64)q); }
 
@@ -318,9 +321,10 @@ __device__ __forceinline__ unsigned rm_quad_rest(u64 s3, int l3, unsigned rest) 
   return (unsigned)(s3 >> (8 * ((unsigned)l3 - rest)));
 }
 
-// cin (low sh bytes) ++ s0 ++ s1 ++ s2 ++ s3 in q0..q3, first byte lowest: at most 3 + 4 * 7 = 31 bytes.  An item
-// lands in the 64-bit word its first byte falls in and spills into the next (the split shift is written so that a
-// byte offset of 0 shifts by 56 + 8, never by 64).
+// The first 32 bytes of cin (low sh bytes) ++ s0 ++ s1 ++ s2 ++ s3 in q0..q3, first byte lowest.  The text is at most
+// 3 + 4 * 8 = 35 bytes; what lies beyond the last whole 32-bit word is never stored by this lane (rm_quad_rest hands
+// it to the next), so bytes 32..34 need no home.  An item lands in the 64-bit word its first byte falls in and spills
+// into the next (the split shift is written so that a byte offset of 0 shifts by 56 + 8, never by 64).
 __device__ __forceinline__ void rm_quad_pack(unsigned cin, unsigned sh, u64 s0, int l0, u64 s1, int l1, u64 s2, int l2, u64 s3,
                                              int l3, u64& q0, u64& q1, u64& q2, u64& q3) {
   (void)l3;
@@ -381,7 +385,7 @@ rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qof
     int c0 = 0;
     while (c0 < n) {
       bool quad = c0 + 128 <= n;
-      for (int i = c0; quad && i < c0 + 128; ++i) quad = (unsigned)key[i] < 100000u;
+      for (int i = c0; quad && i < c0 + 128; ++i) quad = (unsigned)key[i] < 1000000u;
       if (quad) {
         unsigned cout = 0;
         const unsigned left = (unsigned)(total & 3ull);
@@ -428,7 +432,7 @@ rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qof
   // registers behind the 0-3 bytes that the lane before it could not fit into a whole word (those are the tail
   // of that lane's last item, at least 3 bytes long: one shuffle), stores its whole words, and hands its own
   // remainder on.  No byte stores, one prefix sum and one flush per 128 tokens: ~55 instructions per token
-  // against ~240 for the 32-token form below, which remains for the last chunk and for ids outside [0, 100000).
+  // against ~240 for the 32-token form below, which remains for the last chunk and for ids outside [0, 1000000).
   __shared__ __align__(16) unsigned char bufs[RM_RENDER_WPB][RM_RENDER_BUF];
   unsigned char* buf = bufs[wid];
   unsigned* bw = reinterpret_cast<unsigned*>(buf);
@@ -448,8 +452,8 @@ rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qof
       v1 = __ldg(kp + 1);
       v2 = __ldg(kp + 2);
       v3 = __ldg(kp + 3);
-      quad = __all_sync(0xffffffffu, ((unsigned)v0 < 100000u) & ((unsigned)v1 < 100000u) & ((unsigned)v2 < 100000u) &
-                                         ((unsigned)v3 < 100000u));
+      quad = __all_sync(0xffffffffu, ((unsigned)v0 < 1000000u) & ((unsigned)v1 < 1000000u) & ((unsigned)v2 < 1000000u) &
+                                         ((unsigned)v3 < 1000000u));
     }
     if (quad) {
       u64 s0, s1, s2, s3;
@@ -473,7 +477,7 @@ rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qof
       if (lane == 0) cin = bw[0];                            // carried over from the chunk before
       u64 q0, q1, q2, q3;
       rm_quad_pack(cin, sh, s0, l0, s1, l1, s2, l2, s3, l3, q0, q1, q2, q3);
-      const unsigned nw = (sh + tot) >> 2;                   // whole words: 2..7
+      const unsigned nw = (sh + tot) >> 2;                   // whole words: 2..8
       unsigned* o = bw + (p0 >> 2);                          // word 0 is lane 0's alone: read above, written here
       o[0] = (unsigned)q0;
       o[1] = (unsigned)(q0 >> 32);
@@ -482,6 +486,7 @@ rm_route_render_kernel(const int* __restrict__ qtok, const i64* __restrict__ qof
       if (nw > 4) o[4] = (unsigned)q2;
       if (nw > 5) o[5] = (unsigned)(q2 >> 32);
       if (nw > 6) o[6] = (unsigned)q3;
+      if (nw > 7) o[7] = (unsigned)(q3 >> 32);
       __syncwarp();
       const unsigned avail = left + chunk_total;
       const unsigned words = avail >> 2;

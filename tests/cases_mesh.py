@@ -166,7 +166,7 @@ def md5_awkward_keys():
     pool = [0, 7, 10, 99, 100, 31999, 32000, 123456, 2147483647, -1, -2147483648, 999999, 1000000]
     lens = list(range(0, 40)) + [55, 56, 57, 63, 64, 65, 119, 120, 121, 127, 128, 129, 500] + [2176] * 40
     keys = [[rnd.choice(pool) for _ in range(n)] for n in lens]
-    # runs of ordinary token ids (< 100000), which the render kernel takes 128 at a time, four per lane: every digit
+    # runs of ordinary token ids (< 1000000), which the render kernel takes 128 at a time, four per lane: every digit
     # count, the shortest and the longest text a lane can hold, lengths around the 128-token chunk, and runs broken
     # by an id that sends one chunk through the general path
     small = [0, 5, 9, 10, 42, 99, 100, 999, 1000, 9999, 10000, 31999, 99999]
@@ -178,5 +178,10 @@ def md5_awkward_keys():
     broken = [rnd.randrange(0, 32000) for _ in range(700)]
     broken[10], broken[200], broken[699] = -5, 123456, 2147483647
     keys.append(broken)
-    keys.append([100000] + [rnd.randrange(0, 100000) for _ in range(511)])
+    keys.append([1000000] + [rnd.randrange(0, 100000) for _ in range(511)])
+    # six-digit ids (vocabularies of 128 K - 262 K entries) stay on the four-per-lane path; seven digits leave it
+    keys.append([rnd.randrange(100000, 1000000) for _ in range(640)])
+    keys.append([999999] * 256)
+    keys.append([rnd.choice([0, 9, 99999, 100000, 151643, 262143, 999999]) for _ in range(1500)])
+    keys.append([rnd.randrange(0, 300000) for _ in range(255)] + [1000000] + [rnd.randrange(0, 300000) for _ in range(400)])
     return keys
