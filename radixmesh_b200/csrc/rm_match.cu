@@ -1134,6 +1134,19 @@ static int rm_launch_walk_flags(rm_index* idx, const int* tokens, const i64* off
   auto k = rm_match_rung_kernel<1, true, false, 2>;
   const long long wthreads = N;
 #else
+  // A batch that a warp per record still fits the GPU with (148 SMs x 64 warps) walks with 32 lanes and three steps
+  // in flight per record - a 512-token record is 6 rounds instead of 32, and with a few thousand records the walk is
+  // one record's latency; larger batches keep 8 lanes per record.  (RM_PREPASS_G=8 / 32 forces one form.)
+  static const int g_env = getenv("RM_PREPASS_G") ? atoi(getenv("RM_PREPASS_G")) : 0;
+  const bool wide = g_env ? g_env == 32 : N <= 148 * 64;
+  if (wide) {
+    auto kw = rm_match_rung_kernel<32, true, false, 3>;
+    const long long wt = (long long)N * 32;
+    RM_LAUNCH(kw, (int)((wt + 127) / 128), 128, s, idx->t, tokens, offsets, N, seq_base, idx->len_bits, out_len, out_node,
+              idx->sc.key[0], idx->sc.val[0], ro, walk_flags);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+  }
   const int tpb = N >= 148 * 8 * RM_MATCH_TPB ? RM_MATCH_TPB : (N >= 148 * 8 * 128 ? 128 : 64);
   auto k = rm_match_rung_kernel<8, true, false, 2>;
   const long long wthreads = (long long)N * 8;
