@@ -342,6 +342,8 @@ class RadixCache:
             n = len(key) // self._P * self._P
             if n == 0:
                 return MatchResult(torch.empty((0,), dtype=torch.int64), self.root_node, self.root_node)
+            if self._ragged and PAGE_FILL in key[:n]:
+                raise ValueError(f"paged match: token {PAGE_FILL} is reserved (it fills up a short last page)")
             lens, nodes = self.match_prefix_batch(be.to_device(np.asarray(key[:n], dtype=np.int32)),
                                                   be.to_device(np.asarray([0, n], dtype=np.int64)))
             m = int(be.to_host(lens)[0])
