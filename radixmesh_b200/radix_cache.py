@@ -143,6 +143,7 @@ class RadixCache:
         self._ragged = {}              # value row id -> tokens the short page really holds
         self._deficit = 0              # sum over live short rows of (page_size - tokens held)
         self._deficit_protected = 0    # ... the part of it that sits in locked leaves
+        self._arena_est = 0            # upper bound on the arena positions handed out (see _arena_room)
         self.device = getattr(self._be, "device", "cpu")
         self._dump_cache = None
         self._info_cache = {}
@@ -266,6 +267,26 @@ class RadixCache:
         self._pg.rows_get(self._be.to_device(rows), n, out)
         return self._be.to_host(out)
 
+    def _arena_room(self, n_tokens: int) -> None:
+        """Before an insert of up to n_tokens arena positions.  The reference's tree gives memory back when a node is
+        evicted; here an evicted run's arena positions come back only through rm_compact (arena space is handed out by
+        a bump pointer), so a cache that streams inserts and evictions compacts by itself: when three quarters of the
+        arena are handed out and at least a quarter of it belongs to evicted runs.  The device is asked only when the
+        host-side bound passes the threshold."""
+        if self.MODE != capi.MODE_BASE:
+            return
+        self._arena_est += int(n_tokens)
+        cap = int(self._ix.cfg.max_tokens)
+        if self._arena_est * 4 <= cap * 3:
+            return
+        sz = self._ix.sizes()
+        used = int(sz.arena_used) + int(n_tokens)
+        if used * 4 > cap * 3 and (used - int(sz.evictable) - int(sz.protected_)) * 4 > cap:
+            self._ix.compact()
+            self._invalidate()
+            sz = self._ix.sizes()
+        self._arena_est = int(sz.arena_used) + int(n_tokens)
+
     def _run_values(self, rows) -> np.ndarray:
         """KV indices of one node's rows: only the last row of a run can be a short page."""
         vals = self._rows_values(rows)
@@ -308,6 +329,7 @@ class RadixCache:
             return out, None
         rows = self._be.empty(total + 1, np.int64)
         self._pg.rows_put(values, total, rows)        # values are page aligned: row i = values[i*P : (i+1)*P]
+        self._arena_room(total)
         self._ix.insert(syms, rows, soffs, None, B, out)
         dead = self._rows_of_prefixes(rows, soffs, out, B, total)
         if len(dead):
@@ -331,6 +353,7 @@ class RadixCache:
             self._pg.reset()
             self._pg_syms_after_retain = 0
         self._ragged, self._deficit, self._deficit_protected = {}, 0, 0
+        self._arena_est = 0
 
     def match_prefix(self, key: List[int], **kwargs) -> MatchResult:
         import torch
@@ -454,6 +477,7 @@ class RadixCache:
                 a = v.cpu().numpy() if hasattr(v, "cpu") else np.asarray(v)
                 vals[offs[i]:offs[i + 1]] = a
         ranks = np.asarray([r for _, _, r in recs], dtype=np.int32) if self.MODE != capi.MODE_BASE else None
+        self._arena_room(int(offs[-1]))
         out = self._ix.insert_host(flat, vals, offs, ranks)
         self._invalidate()
         self._ix.check_device_error()
@@ -472,6 +496,7 @@ class RadixCache:
                 return out_prefix_len
             return out
         out = out_prefix_len if out_prefix_len is not None else self._be.empty(N, np.int32)
+        self._arena_room(int(tokens.shape[0]))
         self._ix.insert(tokens, values, offsets, ranks, N, out)
         self._invalidate()
         return out

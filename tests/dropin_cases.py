@@ -512,3 +512,46 @@ def _alive(orc, node):
             return False
         node = p
     return True
+
+
+def run_arena_recycling(kw, seed, page=1):
+    """A RadixCache that streams inserts and evictions through an arena far smaller than what it is handed in total:
+    the reference gives memory back when a node is evicted; here evicted runs come back through rm_compact, which the
+    drop-in calls by itself (RadixCache._arena_room).  40 rounds x ~600 fresh tokens through an arena of 2048
+    positions, against the oracle (matches, freed indices, sizes); handles taken before a compaction stay valid."""
+    import random
+    from oracle.radix_port import PortRadixCache
+    rnd = random.Random(8700 + seed)
+    alloc = FakeAllocator()
+    small = dict(max_nodes=1 << 12, max_tokens=2048 * page, max_batch=64, max_key_len=256)
+    small.update(kw)
+    t = RadixCache(None, alloc, page, **small)
+    orc = PortRadixCache(page)
+    vc, fresh = 0, 100
+    keep = list(range(1, 1 + 8 * page))
+    compactions = 0
+    held = None
+    for rd in range(40):
+        keys = [list(keep)]
+        for _ in range(5):
+            n = rnd.randrange(40, 200) // page * page
+            keys.append(list(range(fresh, fresh + n)))
+            fresh += n
+        before = t._arena_est
+        for k in keys:
+            v = list(range(vc, vc + len(k)))
+            vc += len(k)
+            assert t.insert(list(k), np.asarray(v, dtype=np.int64)) == orc.insert(list(k), np.asarray(v, dtype=np.int64))
+        compactions += t._arena_est < before
+        m, e = t.match_prefix(list(keep) + [7] * page), orc.match_prefix(list(keep) + [7] * page)
+        assert m.device_indices.tolist() == e.indices.tolist()
+        if held is None:
+            held = (m.last_device_node, e.last_node)
+        assert held[0].key == list(held[1].key) and held[0].value.tolist() == held[1].value.tolist()
+        n = max(orc.evictable - 8 * page, 0)
+        b0, b1 = len(alloc.freed), len(orc.freed)
+        t.evict(n)
+        orc.evict(n)
+        assert alloc.freed[b0:] == orc.freed[b1:]
+        assert (t.evictable_size(), t.total_size()) == (orc.evictable, orc.total_size())
+    assert compactions >= 3, compactions

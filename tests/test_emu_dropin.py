@@ -125,6 +125,11 @@ def test_paged_keys_with_a_short_last_page(seed):
     dc.run_paged_ragged(kw(), seed)
 
 
+@pytest.mark.parametrize("seed,page", [(0, 1), (1, 1), (2, 2), (3, 4)])
+def test_arena_of_evicted_runs_is_recycled(seed, page):
+    dc.run_arena_recycling(kw(), seed, page)
+
+
 @pytest.mark.parametrize("seed", range(4))
 def test_paged_symbols_of_evicted_pages_are_reused(seed):
     dc.run_paged_symbol_reclaim(kw(), seed)

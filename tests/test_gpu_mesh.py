@@ -232,6 +232,13 @@ def test_gpu_paged_keys_with_a_short_last_page(seed):
     dc.run_paged_ragged({}, seed)
 
 
+@pytest.mark.parametrize("seed,page", [(0, 1), (2, 2)])
+def test_gpu_arena_of_evicted_runs_is_recycled(seed, page):
+    """RadixCache compacts by itself when evicted runs hold a quarter of a nearly full arena (40 rounds of fresh keys
+    through an arena of 2048 positions), against the oracle."""
+    dc.run_arena_recycling({}, seed, page)
+
+
 @pytest.mark.parametrize("seed", range(3))
 def test_gpu_paged_symbols_of_evicted_pages_are_reused(seed):
     """rm_pages_retain on the GPU: a stream of fresh pages through a 192-symbol table, against the oracle."""
