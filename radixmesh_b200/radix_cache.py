@@ -144,6 +144,7 @@ class RadixCache:
         self._deficit = 0              # sum over live short rows of (page_size - tokens held)
         self._deficit_protected = 0    # ... the part of it that sits in locked leaves
         self._arena_est = 0            # upper bound on the arena positions handed out (see _arena_room)
+        self._arena_floor = 0          # arena positions in use right after the last compaction
         self.device = getattr(self._be, "device", "cpu")
         self._dump_cache = None
         self._info_cache = {}
@@ -273,7 +274,7 @@ class RadixCache:
         a bump pointer), so a cache that streams inserts and evictions compacts by itself: when three quarters of the
         arena are handed out and at least a quarter of it belongs to evicted runs.  The device is asked only when the
         host-side bound passes the threshold."""
-        if self.MODE != capi.MODE_BASE:
+        if self.MODE == capi.MODE_ROUTER:      # a router replica holds no values and counts nodes, not tokens
             return
         self._arena_est += int(n_tokens)
         cap = int(self._ix.cfg.max_tokens)
@@ -281,10 +282,16 @@ class RadixCache:
             return
         sz = self._ix.sizes()
         used = int(sz.arena_used) + int(n_tokens)
-        if used * 4 > cap * 3 and (used - int(sz.evictable) - int(sz.protected_)) * 4 > cap:
+        # (a mesh replica never evicts - RadixMesh.evict is a no-op like the reference's, radix_mesh.py:349-351 - so
+        # there only the runs that duplicate-node GC released come back; its parked nodes hold arena runs that neither
+        # size counter shows, hence: after a compaction the next one waits until an eighth of the arena has been handed
+        # out again)
+        if (used * 4 > cap * 3 and (used - int(sz.evictable) - int(sz.protected_)) * 4 > cap
+                and used - self._arena_floor > cap // 8):
             self._ix.compact()
             self._invalidate()
             sz = self._ix.sizes()
+            self._arena_floor = int(sz.arena_used)
         self._arena_est = int(sz.arena_used) + int(n_tokens)
 
     def _run_values(self, rows) -> np.ndarray:
@@ -353,7 +360,7 @@ class RadixCache:
             self._pg.reset()
             self._pg_syms_after_retain = 0
         self._ragged, self._deficit, self._deficit_protected = {}, 0, 0
-        self._arena_est = 0
+        self._arena_est, self._arena_floor = 0, 0
 
     def match_prefix(self, key: List[int], **kwargs) -> MatchResult:
         import torch

@@ -128,6 +128,7 @@ class RadixMesh(RadixCache):
             for i in range(0, n, step):
                 j = min(i + step, n)
                 a, b = int(offs[i]), int(offs[j])
+                self._arena_room(b - a)
                 out = self._ix.insert_host(tok[a:b], val[a:b] if val is not None else None, offs[i:j + 1] - offs[i], ranks[i:j])
             self._invalidate()
             self._ix.check_device_error()

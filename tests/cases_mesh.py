@@ -141,6 +141,11 @@ def run_mesh_sequence(make_index, seed, n_steps=25, vocab=3, maxlen=7, max_recs=
             ix.lock(ix.be.to_device(np.asarray([node], np.int32)), ix.be.to_device(np.asarray([gen], np.int32)), 1, sign, d_out)
             exp = port.nodes[rank].inc_lock_ref(onode) if sign > 0 else port.nodes[rank].dec_lock_ref(onode)
             assert int(ix.be.to_host(d_out)[0]) == exp
+        if rnd.random() < 0.15:
+            # maintenance between operations: nothing observable may change (parked nodes and the duplicate table keep
+            # pointing at the same values)
+            for ix in ixs:
+                ix.compact()
         for r, ix in enumerate(ixs):
             ix.check_device_error()
             dc_ = mesh_canonical(ix)

@@ -555,3 +555,4 @@ def run_arena_recycling(kw, seed, page=1):
         assert alloc.freed[b0:] == orc.freed[b1:]
         assert (t.evictable_size(), t.total_size()) == (orc.evictable, orc.total_size())
     assert compactions >= 3, compactions
+
