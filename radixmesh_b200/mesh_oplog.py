@@ -19,7 +19,7 @@ One process per GPU, `torch.distributed` (NCCL on the GPUs; gloo with the host-e
 """
 from __future__ import annotations
 
-from typing import List, Optional
+from typing import List
 
 import numpy as np
 

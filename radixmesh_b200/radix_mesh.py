@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import dataclasses
 import threading
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import numpy as np
 
