@@ -39,8 +39,14 @@ class NvlinkOplogExchange:
     def __init__(self, indexes: List[capi.DeviceIndex], rank: int, world: int, group=None):
         self.ixs, self.rank, self.world, self.group = list(indexes), rank, world, group
         self.be = self.ixs[0].be
-        self._stage = IngestBuffer(with_values=True)
+        self._stage = IngestBuffer(with_values=True, alloc=self._pinned if getattr(self.be, "name", "") == "cuda" else None)
         self.applied = 0
+
+    @staticmethod
+    def _pinned(n, dtype):
+        """Staging arrays in pinned host memory: their copy to the device does not block the host."""
+        import torch
+        return torch.empty(int(n), dtype={np.int32: torch.int32, np.int64: torch.int64}[dtype], pin_memory=True).numpy()
 
     def stage(self, key, value) -> None:
         """A local insert (RadixMesh.insert on this node): applied, here and everywhere, at the next exchange."""
@@ -69,8 +75,8 @@ class NvlinkOplogExchange:
         n_tok_pad, n_rec_pad = max(max_tok, 1), max(max_rec, 1)
         d_tok, d_val, d_len = be.empty(n_tok_pad, np.int32), be.empty(n_tok_pad, np.int64), be.empty(n_rec_pad, np.int32)
         if len(tok):
-            _as_torch(d_tok)[:len(tok)].copy_(torch.from_numpy(tok))
-            _as_torch(d_val)[:len(val)].copy_(torch.from_numpy(val))
+            _as_torch(d_tok)[:len(tok)].copy_(torch.from_numpy(tok), non_blocking=True)
+            _as_torch(d_val)[:len(val)].copy_(torch.from_numpy(val), non_blocking=True)
             _as_torch(d_len)[:len(lens)].copy_(torch.from_numpy(lens))
         g_tok = be.empty(W * n_tok_pad, np.int32)
         g_val = be.empty(W * n_tok_pad, np.int64)

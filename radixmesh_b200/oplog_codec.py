@@ -123,10 +123,13 @@ def with_header(buf, ttl: int, local_logic_id: Optional[int] = None) -> bytes:
 class IngestBuffer:
     """INSERT records in arrival order, as the flat arrays rm_insert_batch_h takes."""
 
-    def __init__(self, with_values: bool = True, tokens: int = 1 << 16, records: int = 1 << 10):
+    def __init__(self, with_values: bool = True, tokens: int = 1 << 16, records: int = 1 << 10, alloc=None):
+        """alloc(n, dtype) -> 1-D array for the token and value arrays (default numpy.empty); a caller that copies them
+        to a GPU passes an allocator of pinned memory (mesh_oplog.py) so that the copy is asynchronous."""
         self.with_values = with_values
-        self._tok = np.empty(tokens, dtype=np.int32)
-        self._val = np.empty(tokens if with_values else 1, dtype=np.int64)
+        self._alloc = alloc if alloc is not None else (lambda n, dt: np.empty(n, dtype=dt))
+        self._tok = self._alloc(tokens, np.int32)
+        self._val = self._alloc(tokens if with_values else 1, np.int64)
         self._offs = np.zeros(records + 1, dtype=np.int64)
         self._rank = np.empty(records, dtype=np.int32)
         self.n = 0          # records
@@ -138,9 +141,13 @@ class IngestBuffer:
     def _room(self, nk: int) -> None:
         if self.ntok + nk > self._tok.size:
             size = max(2 * self._tok.size, self.ntok + nk)
-            self._tok = np.resize(self._tok, size)
+            tok = self._alloc(size, np.int32)
+            tok[:self.ntok] = self._tok[:self.ntok]
+            self._tok = tok
             if self.with_values:
-                self._val = np.resize(self._val, size)
+                val = self._alloc(size, np.int64)
+                val[:self.ntok] = self._val[:self.ntok]
+                self._val = val
         if self.n + 1 > self._rank.size:
             cap = 2 * self._rank.size
             self._rank = np.resize(self._rank, cap)
@@ -207,8 +214,8 @@ class IngestBuffer:
         # the caller keeps the filled arrays (views of them) and the buffer continues on fresh ones of the same size:
         # no copy of the staged tokens and values (6 MB for a thousand 512-token records)
         out = (self._tok[:nt], self._val[:nt] if self.with_values else None, self._offs[:n + 1], self._rank[:n])
-        self._tok = np.empty_like(self._tok)
-        self._val = np.empty_like(self._val)
+        self._tok = self._alloc(self._tok.size, np.int32)
+        self._val = self._alloc(self._val.size, np.int64)
         self._offs = np.zeros_like(self._offs)
         self._rank = np.empty_like(self._rank)
         self.n = 0
