@@ -332,7 +332,7 @@ def _alive(orc, node):
     return True
 
 
-def run_paged_batch(kw, seed):
+def run_paged_batch(kw, seed, vocab=3, max_page_symbols=None, rounds=12, evict_max=20):
     """The *_batch additions with page_size > 1: pages interned on the device (rm_pages_intern), values as rows of a
     device row store, the index running on page symbols - against the oracle's paged RadixCache, record by record."""
     import random
@@ -340,16 +340,16 @@ def run_paged_batch(kw, seed):
     rnd = random.Random(8100 + seed)
     page = rnd.choice([2, 3, 4])
     alloc = FakeAllocator()
-    small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64)
+    small = dict(max_nodes=1 << 12, max_tokens=1 << 15, max_batch=64, max_key_len=64, max_page_symbols=max_page_symbols)
     small.update(kw)
     t = RadixCache(None, alloc, page, **small)
     be = t._be
     orc = PortRadixCache(page)
     vc = 0
-    for rd in range(12):
+    for rd in range(rounds):
         keys = []
         for _ in range(rnd.randrange(1, 12)):
-            k = [rnd.randrange(3) for _ in range(rnd.randrange(0, 24))]
+            k = [rnd.randrange(vocab) for _ in range(rnd.randrange(0, 24))]
             keys.append(k[:len(k) // page * page])
         vals = []
         for k in keys:
@@ -361,7 +361,9 @@ def run_paged_batch(kw, seed):
         fv = np.asarray([x for v in vals for x in v] or [0], dtype=np.int64)
         got = be.to_host(t.insert_batch(be.to_device(flat), be.to_device(fv), be.to_device(offs))).tolist()
         assert got == [orc.insert(list(k), np.asarray(v, dtype=np.int64)) for k, v in zip(keys, vals)]
-        qs = [[rnd.randrange(3) for _ in range(rnd.randrange(1, 26))] for _ in range(rnd.randrange(1, 16))]
+        qs = [[rnd.randrange(vocab) for _ in range(rnd.randrange(1, 26))] for _ in range(rnd.randrange(1, 16))]
+        if vocab > 3:
+            qs += [list(k) + [rnd.randrange(vocab)] * rnd.randrange(0, 5) for k in keys[:4]]   # queries that do match
         qo = np.zeros(len(qs) + 1, dtype=np.int64)
         np.cumsum([len(q) for q in qs], out=qo[1:])
         qf = np.asarray([x for q in qs for x in q], dtype=np.int32)
@@ -378,8 +380,9 @@ def run_paged_batch(kw, seed):
         for i, m in enumerate(exp):
             assert hv[vo[i]:vo[i + 1]].tolist() == m.indices.tolist()
             assert t.full_key(t._handle(int(hn[i]))) == orc.full_key(m.last_node)
-        if rd % 3 == 2:
-            n = rnd.randrange(0, 20)
+        if rd % 3 == 2 or max_page_symbols:
+            # (a small symbol table: evict down to a few dozen tokens, so that the live pages always fit it)
+            n = max(orc.evictable - rnd.randrange(0, 40), 0) if max_page_symbols else rnd.randrange(0, evict_max)
             b0, b1 = len(alloc.freed), len(orc.freed)
             t.evict(n)
             orc.evict(n)

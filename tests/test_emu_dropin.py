@@ -133,3 +133,11 @@ def test_arena_of_evicted_runs_is_recycled(seed, page):
 @pytest.mark.parametrize("seed", range(4))
 def test_paged_symbols_of_evicted_pages_are_reused(seed):
     dc.run_paged_symbol_reclaim(kw(), seed)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_paged_random_traffic_through_a_small_symbol_table(seed):
+    """Random paged inserts / matches / evictions over a vocabulary of 12 tokens with room for 256 page symbols (a batch
+    brings up to ~130 new pages, the tree is evicted down to a few dozen tokens every round): pages are dropped
+    (rm_pages_retain) and interned again all the time, under the same checks as the other paged runs."""
+    dc.run_paged_batch(kw(), 300 + seed, vocab=12, max_page_symbols=256, rounds=40)

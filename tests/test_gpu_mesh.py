@@ -240,6 +240,13 @@ def test_gpu_arena_of_evicted_runs_is_recycled(seed, page):
 
 
 @pytest.mark.parametrize("seed", range(3))
+def test_gpu_paged_random_traffic_through_a_small_symbol_table(seed):
+    """Random paged inserts / matches / evictions with room for 256 page symbols: pages are dropped (rm_pages_retain)
+    and interned again all the time (~17 reclaims per run), against the oracle."""
+    dc.run_paged_batch({}, 300 + seed, vocab=12, max_page_symbols=256, rounds=40)
+
+
+@pytest.mark.parametrize("seed", range(3))
 def test_gpu_paged_symbols_of_evicted_pages_are_reused(seed):
     """rm_pages_retain on the GPU: a stream of fresh pages through a 192-symbol table, against the oracle."""
     dc.run_paged_symbol_reclaim({}, seed)
