@@ -559,3 +559,50 @@ def run_arena_recycling(kw, seed, page=1):
         assert (t.evictable_size(), t.total_size()) == (orc.evictable, orc.total_size())
     assert compactions >= 3, compactions
 
+
+
+def run_paged_mixed_pressure(kw, seed, steps=250):
+    """Everything the paged adapter keeps books on, at once and under pressure: keys of any length (short last pages),
+    a 160-symbol interning table (pages dropped and interned again), an arena of 600 positions (the cache compacts by
+    itself), locks, and evictions of up to 120 tokens - against the oracle's paged RadixCache after every step."""
+    import random
+    from oracle.radix_port import PortRadixCache
+    rnd = random.Random(9100 + seed)
+    page = rnd.choice([2, 3, 4])
+    alloc = FakeAllocator()
+    small = dict(max_nodes=1 << 12, max_tokens=600 * page, max_batch=64, max_key_len=64, max_page_symbols=160)
+    small.update(kw)
+    t = RadixCache(None, alloc, page, **small)
+    orc = PortRadixCache(page)
+    vc, held = 0, []
+    for step in range(steps):
+        op = rnd.choice(["ins", "ins", "ins", "match", "lock", "unlock", "evict", "evict"])
+        if op == "ins":
+            k = [rnd.randrange(9) for _ in range(rnd.randrange(0, 30))]
+            v = list(range(vc, vc + len(k)))
+            vc += len(k)
+            assert t.insert(list(k), np.asarray(v, dtype=np.int64)) == orc.insert(list(k), np.asarray(v, dtype=np.int64)), (step, k)
+        elif op == "match":
+            q = [rnd.randrange(9) for _ in range(rnd.randrange(0, 30))]
+            m, e = t.match_prefix(list(q)), orc.match_prefix(list(q))
+            assert m.device_indices.tolist() == e.indices.tolist()
+            held.append((m.last_device_node, e.last_node))
+        elif op == "lock" and held:
+            a, b = held[rnd.randrange(len(held))]
+            if b is orc.root or _alive(orc, b):
+                assert t.inc_lock_ref(a) == orc.inc_lock_ref(b)
+                held.append((a, b))
+        elif op == "unlock" and held:
+            a, b = held[rnd.randrange(len(held))]
+            if b.lock_ref > 0 and b is not orc.root and _alive(orc, b):
+                assert t.dec_lock_ref(a) == orc.dec_lock_ref(b)
+        elif op == "evict":
+            n = rnd.randrange(0, 120)
+            b0, b1 = len(alloc.freed), len(orc.freed)
+            t.evict(n)
+            orc.evict(n)
+            assert alloc.freed[b0:] == orc.freed[b1:], (step, n)
+            held = [(a, b) for a, b in held if b is orc.root or _alive(orc, b)]
+        assert (t.evictable_size(), t.protected_size(), t.total_size()) == (orc.evictable, orc.protected, orc.total_size()), step
+    if orc.total_size():
+        assert t.all_values_flatten().tolist() == orc.all_values_flatten().tolist()

@@ -136,6 +136,11 @@ def test_paged_symbols_of_evicted_pages_are_reused(seed):
 
 
 @pytest.mark.parametrize("seed", range(8))
+def test_paged_short_pages_small_table_small_arena_together(seed):
+    dc.run_paged_mixed_pressure(kw(), seed)
+
+
+@pytest.mark.parametrize("seed", range(8))
 def test_paged_random_traffic_through_a_small_symbol_table(seed):
     """Random paged inserts / matches / evictions over a vocabulary of 12 tokens with room for 256 page symbols (a batch
     brings up to ~130 new pages, the tree is evicted down to a few dozen tokens every round): pages are dropped

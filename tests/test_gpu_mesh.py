@@ -239,6 +239,12 @@ def test_gpu_arena_of_evicted_runs_is_recycled(seed, page):
     dc.run_arena_recycling({}, seed, page)
 
 
+@pytest.mark.parametrize("seed", range(2))
+def test_gpu_paged_short_pages_small_table_small_arena_together(seed):
+    """Short last pages, a 160-symbol interning table, a 600-position arena, locks and evictions in one run."""
+    dc.run_paged_mixed_pressure({}, seed, steps=150)
+
+
 @pytest.mark.parametrize("seed", range(3))
 def test_gpu_paged_random_traffic_through_a_small_symbol_table(seed):
     """Random paged inserts / matches / evictions with room for 256 page symbols: pages are dropped (rm_pages_retain)
