@@ -175,7 +175,10 @@ int rm_lock_batch(rm_index* idx, const int32_t* nodes, const int32_t* gens, int3
  * _delete_leaf :347-352).  Evicted nodes are reported in the reference's eviction order:
  * out_nodes_h[k] = node id, out_offs_h[k] / out_lens_h[k] = its value run in the value arena
  * (rm_read_values reads it) so the caller can call token_to_kv_pool_allocator.free exactly as
- * radix_cache.py:195 does.  *out_n_h = number evicted (<= cap).  Synchronises.
+ * radix_cache.py:195 does.  *out_n_h = number evicted (<= cap).  Synchronises ONCE in the usual call: the host asks
+ * the device nothing before the work (the node high-water mark is bounded from its last reading, the candidate count
+ * stays on the device); when a bound turns out too small the pass evicts nothing and the call repeats it with exact
+ * sizes.  Also rebuilds the child table when a quarter of its slots are tombstones.
  */
 int rm_evict(rm_index* idx, int64_t num_tokens, int32_t cap, int32_t* out_nodes_h, int64_t* out_offs_h,
              int32_t* out_lens_h, int32_t* out_n_h, void* stream);
