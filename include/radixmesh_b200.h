@@ -288,6 +288,11 @@ int rm_dump_order(rm_index* idx, int32_t cap, uint64_t* order_h, void* stream);
 
 /* Read `n` tokens / values of the edge arenas starting at token offset `off` into HOST buffers. */
 int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream);
+/* The VALUE runs [offs_h[i], offs_h[i] + lens_h[i]) of the edge arena, i < n (n <= rm_config.max_nodes), one after
+ * another into out_values_h (sum of lens_h entries): what RadixCache.evict hands to token_to_kv_pool_allocator.free
+ * node by node (radix_cache.py:195), for all evicted nodes of an rm_evict call in one gather and one copy instead of a
+ * synchronising read per node.  Synchronises. */
+int rm_read_runs(rm_index* idx, const int64_t* offs_h, const int32_t* lens_h, int32_t n, int64_t* out_values_h, void* stream);
 
 /* Parity aid: the per-position owner map of the edge arena (node id, bit 30 = contiguous child of the node
  * owning the previous position, -1 = free) for `n` positions from `off`, to HOST.  Synchronises. */

@@ -81,6 +81,7 @@ _PROTOS = {
     "rm_pages_rows_free": (C.c_int, [_P, _P, C.c_int64, _P]),
     "rm_pages_rows_get": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
     "rm_pages_tokens": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "rm_read_runs": (C.c_int, [_P, _P, _P, C.c_int32, _P, _P]),
     "rm_pages_retain": (C.c_int, [_P, _P, _P]),
     "rm_pages_status": (C.c_int, [_P, _P, _P]),
     "rm_read_arena": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
@@ -417,6 +418,16 @@ class DeviceIndex:
         ms, n = C.c_double(0.0), C.c_int(0)
         self._check(self.lib.rm_profile_read(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def read_runs(self, offs: np.ndarray, lens: np.ndarray) -> np.ndarray:
+        """Values of the arena runs (offs[i], lens[i]), concatenated: one gather, one copy (rm_read_runs)."""
+        offs = np.ascontiguousarray(offs, dtype=np.int64)
+        lens = np.ascontiguousarray(lens, dtype=np.int32)
+        out = np.empty(int(lens.sum()), dtype=np.int64)
+        if len(lens):
+            with self._mutex:
+                self._check(self.lib.rm_read_runs(self._h, ptr(offs), ptr(lens), len(lens), ptr(out), self._s()))
+        return out
 
     def read_arena(self, off: int, n: int, values: bool = True):
         tok = np.zeros(n, np.int32)

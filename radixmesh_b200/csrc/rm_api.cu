@@ -597,6 +597,54 @@ int rm_dump_order(rm_index* idx, int32_t cap, uint64_t* order_h, void* stream) {
   return RM_OK;
 }
 
+int rm_read_runs(rm_index* idx, const int64_t* offs_h, const int32_t* lens_h, int32_t n, int64_t* out_values_h, void* stream) {
+  if (!idx || n < 0 || (n > 0 && (!offs_h || !lens_h || !out_values_h))) return RM_E_INVALID;
+  if (idx->cfg.mode == RM_MODE_ROUTER) return RM_E_MODE;
+  if (n == 0) return RM_OK;
+  if (n > idx->t.max_nodes) return RM_E_TOO_LARGE;
+  RM_CUDA(cudaSetDevice(idx->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  RmScratch& sc = idx->sc;
+  // where each run starts in the packed output: prefix sums on the host (n is a few thousand)
+  i64* at_h = (i64*)malloc(sizeof(i64) * ((size_t)n + 1));
+  if (!at_h) return RM_E_NOSPACE;
+  i64 total = 0;
+  for (int i = 0; i < n; ++i) {
+    if (offs_h[i] < 0 || lens_h[i] < 0 || offs_h[i] + lens_h[i] > idx->t.max_tokens) {
+      free(at_h);
+      return RM_E_INVALID;
+    }
+    at_h[i] = total;
+    total += lens_h[i];
+  }
+  at_h[n] = total;
+  int rc = rm_stage_reserve(idx, total > 0 ? total : 1, true);
+  if (rc) {
+    free(at_h);
+    return rc;
+  }
+  // the eviction scratch is free between calls: run starts, lengths, output positions
+  i64* d_off = reinterpret_cast<i64*>(sc.ev_key[0]);
+  i64* d_at = reinterpret_cast<i64*>(sc.ev_key[1]);
+  int* d_len = sc.ev_rem;
+  cudaError_t e = cudaMemcpyAsync(d_off, offs_h, sizeof(i64) * (size_t)n, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_len, lens_h, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_at, at_h, sizeof(i64) * (size_t)n, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);      // at_h is pageable: the copies are done before it is freed
+  free(at_h);
+  if (e != cudaSuccess) {
+    rm_set_error("rm_read_runs: %s", cudaGetErrorString(e));
+    return RM_E_CUDA;
+  }
+  if (total > 0) {
+    rc = rm_launch_copy_runs(idx, d_off, d_len, d_at, n, sc.h_values, s);
+    if (rc) return rc;
+    RM_CUDA(cudaMemcpyAsync(out_values_h, sc.h_values, sizeof(i64) * (size_t)total, cudaMemcpyDeviceToHost, s));
+    RM_CUDA(cudaStreamSynchronize(s));
+  }
+  return RM_OK;
+}
+
 int rm_read_arena(rm_index* idx, int64_t off, int64_t n, int32_t* tokens_h, int64_t* values_h, void* stream) {
   if (!idx || off < 0 || n < 0 || off + n > idx->t.max_tokens) return RM_E_INVALID;
   RM_CUDA(cudaSetDevice(idx->cfg.device));

@@ -105,6 +105,7 @@ int rm_launch_insert(rm_index* idx, const int* tokens, const i64* values, const 
 int rm_launch_reset(rm_index* idx, cudaStream_t s);
 int rm_launch_lock(rm_index* idx, const int* nodes, int B, int dir, i64* out_delta, cudaStream_t s);
 int rm_launch_lock_g(rm_index* idx, const int* nodes, const int* gens, int B, int dir, i64* out_delta, cudaStream_t s);
+int rm_launch_copy_runs(rm_index* idx, const i64* d_off, const int* d_len, const i64* d_at, int n, i64* d_out, cudaStream_t s);
 int rm_launch_evict(rm_index* idx, i64 num_tokens, int cap, int* out_nodes_h, i64* out_offs_h, int* out_lens_h,
                     int* out_n_h, cudaStream_t s);
 int rm_launch_node_info(rm_index* idx, const int* ids_h, int n, rm_node_info_t* out_h, cudaStream_t s);

@@ -624,6 +624,30 @@ __global__ void rm_evict_apply_kernel(RmTree t, const unsigned* __restrict__ sva
     rm_evict_apply_one<G>(t, g, k, sval, eff, out_nodes, out_offs, out_lens);
 }
 
+// rm_read_runs: value runs of the arena, packed one after another (a group of lanes per run)
+template <int G>
+__global__ void rm_copy_runs_kernel(RmTree t, const i64* __restrict__ off, const int* __restrict__ len, const i64* __restrict__ at,
+                                    int n, i64* __restrict__ out) {
+  RmGroup<G> g;
+  const int r = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) / G);
+  if (r >= n) return;
+  const i64 o = off[r], a = at[r];
+  const int m = len[r];
+  for (int x = g.lane; x < m; x += G) out[a + x] = t.val[o + x];
+}
+
+int rm_launch_copy_runs(rm_index* idx, const i64* d_off, const int* d_len, const i64* d_at, int n, i64* d_out, cudaStream_t s) {
+  if (n <= 0) return RM_OK;
+#ifdef RM_EMU
+  RM_LAUNCH(rm_copy_runs_kernel<1>, (n + RM_MT_TPB - 1) / RM_MT_TPB, RM_MT_TPB, s, idx->t, d_off, d_len, d_at, n, d_out);
+#else
+  RM_LAUNCH(rm_copy_runs_kernel<32>, (int)(((long long)n * 32 + RM_MT_TPB - 1) / RM_MT_TPB), RM_MT_TPB, s, idx->t, d_off, d_len, d_at,
+            n, d_out);
+#endif
+  RM_CUDA(cudaGetLastError());
+  return RM_OK;
+}
+
 static int rm_bits_for(u64 v) {
   int b = 1;
   while ((v >> b) != 0 && b < 63) ++b;
