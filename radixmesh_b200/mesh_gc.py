@@ -69,9 +69,12 @@ class GcRound:
                 continue
             off, ln = ix.gc_exec([list(k) for k, _ in l], [r for _, r in l], free_parked=(o == self.rank))
             if o == self.rank:
-                for a, n in zip(off.tolist(), ln.tolist()):
-                    if a >= 0 and n > 0:
-                        freed.append(ix.read_arena(a, n)[1].tolist())
+                keep = (off >= 0) & (ln > 0)
+                vals = ix.read_runs(off[keep], ln[keep])        # the released runs in one copy
+                at = 0
+                for n in ln[keep].tolist():
+                    freed.append(vals[at:at + n].tolist())
+                    at += n
             removed.extend(l)
         ix.check_device_error()
         return sorted(set(removed)), freed

@@ -273,9 +273,13 @@ class RadixMesh(RadixCache):
             keys = [q.key for q in oplog.gc_query if q.agree == full]
             if keys:
                 off, ln = self._ix.gc_exec([list(k.key) for k in keys], [k.node_rank for k in keys], free_parked=True)
-                for a, n in zip(off.tolist(), ln.tolist()):
-                    if a >= 0 and n > 0 and self.token_to_kv_pool_allocator is not None:
-                        self.token_to_kv_pool_allocator.free(self._tensor(self._ix.read_arena(a, n)[1]))
+                if self.token_to_kv_pool_allocator is not None:
+                    keep = (off >= 0) & (ln > 0)
+                    vals = self._ix.read_runs(off[keep], ln[keep])      # the released runs in one copy
+                    at = 0
+                    for n in ln[keep].tolist():
+                        self.token_to_kv_pool_allocator.free(self._tensor(vals[at:at + n].copy()))
+                        at += n
                 self._invalidate()
                 self._send(CacheOplog(oplog_type=CacheOplogType.GC_EXEC, node_rank=self._global_node_rank,
                                       ttl=self.sync_algo.ttl(self.args), gc_exec=keys))
