@@ -285,7 +285,7 @@ __device__ unsigned rm_hash_token_list(const int* __restrict__ key, int n, const
 // ---- two-step form of the same hash, for long requests --------------------------------------------------
 // One thread rendering AND compressing a 2K-token request is ~250 dependent instructions per token at an
 // occupancy of a few warps per SM: 1.4 ms for a batch, however small the batch.  The text of a request is
-// independent per token, so a block renders it in parallel (digit counts -> block prefix sum -> bytes) into
+// independent per token, so a warp renders it in parallel (item lengths -> warp prefix sum -> whole words) into
 // a scratch area, padded per RFC 1321; the compression, the only sequential part, then reads 64-byte blocks.
 // Place of request q's message: 64 * ((qoff[q] - qoff[0] + 3) / 4 + 2 q) bytes, which leaves room for 13 bytes
 // per token + brackets + padding without a prefix sum over the requests.  A request that does not fit the
